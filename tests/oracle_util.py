@@ -1,0 +1,104 @@
+"""ctypes access to the CPU oracle (oracle/liblsc_oracle.so) and to the real
+reference binaries in oracle/_ref/.  Test infrastructure only."""
+import ctypes
+import os
+import subprocess
+import tempfile
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+REF_DIR = os.path.join(ORACLE_DIR, "_ref")
+
+BCX = {"periodic": 0, "transmissive": 1}
+BCY = {"reflective": 0, "periodic": 1, "transmissive": 2}
+PROB = {"kh": 0, "ot": 1}
+
+
+class OracleMhdCfg(ctypes.Structure):
+    _fields_ = [("nx", ctypes.c_int), ("ny", ctypes.c_int),
+                ("x0", ctypes.c_double), ("x1", ctypes.c_double),
+                ("y0", ctypes.c_double), ("y1", ctypes.c_double),
+                ("gamma", ctypes.c_double), ("cfl", ctypes.c_double),
+                ("bcx", ctypes.c_int), ("bcy", ctypes.c_int)]
+
+
+_lib = None
+
+
+def oracle_lib():
+    global _lib
+    if _lib is None:
+        path = os.path.join(ORACLE_DIR, "liblsc_oracle.so")
+        if not os.path.exists(path):
+            subprocess.run(["make", "-C", ORACLE_DIR, "liblsc_oracle.so"], check=True)
+        _lib = ctypes.CDLL(path)
+        _lib.lsc_oracle_mhd_create.restype = ctypes.c_void_p
+        _lib.lsc_oracle_mhd_run_until.restype = ctypes.c_long
+    return _lib
+
+
+def _dp(a):
+    return a.ctypes.data_as(ctypes.POINTER(ctypes.c_double))
+
+
+def mhd_cfg(nx, ny, dom=(0.0, 1.0, 0.0, 1.0), gamma=5.0 / 3.0, cfl=0.8, bcx="periodic", bcy="periodic"):
+    return OracleMhdCfg(nx, ny, dom[0], dom[1], dom[2], dom[3], gamma, cfl, BCX[bcx], BCY[bcy])
+
+
+def mhd_ic(cfg, prob):
+    u = np.zeros((cfg.nx + 4, cfg.ny + 4, 9), dtype=np.float64)
+    oracle_lib().lsc_oracle_mhd_ic(ctypes.byref(cfg), PROB[prob], _dp(u))
+    return u
+
+
+class OracleMhd:
+    def __init__(self, cfg, u0):
+        self.cfg = cfg
+        self.lib = oracle_lib()
+        u0 = np.ascontiguousarray(u0, dtype=np.float64)
+        assert u0.shape == (cfg.nx + 4, cfg.ny + 4, 9)
+        self.h = ctypes.c_void_p(self.lib.lsc_oracle_mhd_create(ctypes.byref(cfg), _dp(u0)))
+
+    def step(self, n=1):
+        log = np.zeros((n, 3), dtype=np.float64)
+        self.lib.lsc_oracle_mhd_step(self.h, ctypes.c_long(n), _dp(log))
+        return log
+
+    def run_until(self, t_stop):
+        return self.lib.lsc_oracle_mhd_run_until(self.h, ctypes.c_double(t_stop))
+
+    def state(self):
+        u = np.zeros((self.cfg.nx + 4, self.cfg.ny + 4, 9), dtype=np.float64)
+        t = ctypes.c_double()
+        dt = ctypes.c_double()
+        ch = ctypes.c_double()
+        self.lib.lsc_oracle_mhd_get(self.h, _dp(u), ctypes.byref(t), ctypes.byref(dt), ctypes.byref(ch))
+        return u, t.value, dt.value, ch.value
+
+    def close(self):
+        if self.h:
+            self.lib.lsc_oracle_mhd_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+
+def have_ref(name="muscl_ref"):
+    return os.path.exists(os.path.join(REF_DIR, name))
+
+
+def run_muscl_ref(prob, nx, ny, dom, t_stop, cfl, bcx, bcy, nsteps, cwd=None, writedat=False):
+    """Run the real reference (patched only for configuration) and return
+    (state AoS incl. ghosts, steplog[nsteps,3] of (t,dt,ch), stderr text)."""
+    with tempfile.TemporaryDirectory() as td:
+        st = os.path.join(td, "state.bin")
+        lg = os.path.join(td, "log.bin")
+        cmd = [os.path.join(REF_DIR, "muscl_ref"), prob, str(nx), str(ny)] + [repr(float(d)) for d in dom] + \
+              [repr(float(t_stop)), repr(float(cfl)), bcx, bcy, str(nsteps), "1" if writedat else "0", st, lg]
+        r = subprocess.run(cmd, cwd=cwd or td, check=True, capture_output=True, text=True)
+        u = np.fromfile(st, dtype=np.float64).reshape(nx + 4, ny + 4, 9)
+        log = np.fromfile(lg, dtype=np.float64).reshape(-1, 3)
+    return u, log, r.stderr
