@@ -1,0 +1,147 @@
+/*
+ * lsc_b200.h -- C ABI of the B200-native 2-D finite-volume hot path
+ * (liblsc_b200.so).  Plain C, no CUDA/torch types, no exceptions cross it.
+ *
+ * The reference (JosephineMellor/LSC_internship) has NO callable interface: each
+ * solver is a single main() whose "API" is a block of constants, a commented-in
+ * initial-condition block, commented-in boundary loops, a stdout log line and
+ * .dat files.  Each entry point below therefore cites the span of the reference
+ * main() it replaces (paths relative to the reference root):
+ *
+ *   M = MHD_codes/MUSCL_NEW.cpp      S = Euler_codes/SLIC_euler_2d.cpp
+ *   G = Euler_codes/generaliseSLIC.cpp
+ *
+ * Conventions: every function returns 0 on success and a negative LSC_E* code on
+ * failure; lsc_last_error() returns a thread-local message for the last failure.
+ * Host arrays are always caller-owned and are not retained after the call
+ * returns.  One host thread drives one context; different contexts are
+ * independent.  There is no CPU fallback: without a CUDA device every create
+ * call fails with LSC_ECUDA.
+ *
+ * Host state layout (the reference's, M:673-674 / S:542-543): array of structures
+ * [i][j][k], i = x (slowest), j = y, k = component (fastest), with TWO ghost cells
+ * on every side, i.e. (nx+4)*(ny+4)*NVAR doubles.  MHD components (M:11-19):
+ * rho, rho*vx, rho*vy, rho*vz, E, Bx, By, Bz, psi.  Euler (S:10-17): rho, rho*vx,
+ * rho*vy, E.
+ */
+#ifndef LSC_B200_H
+#define LSC_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LSC_MHD_NVAR 9
+#define LSC_EULER_NVAR 4
+
+/* error codes */
+#define LSC_OK 0
+#define LSC_EINVAL (-1)  /* bad argument / configuration */
+#define LSC_ECUDA (-2)   /* CUDA runtime failure (incl. "no device") */
+#define LSC_ENOMEM (-3)  /* device or host allocation failed */
+#define LSC_ESTATE (-4)  /* call out of order (e.g. step before upload) */
+#define LSC_ENAN (-5)    /* max signal speed is not finite / not positive */
+#define LSC_ECOMM (-6)   /* NCCL failure */
+
+/* boundary types.  M:607-655 selects these by (un)commenting loops. */
+#define LSC_BC_PERIODIC 0     /* M:609-614 (x), M:641-646 (y); S:205-225 */
+#define LSC_BC_REFLECTIVE 1   /* M:625-638 (y only: mirrors cells 2,3 / ny,ny+1, negates rho*vy and By) */
+#define LSC_BC_TRANSMISSIVE 2 /* M:617-622 (x), M:649-654 (y): ghost 0,1 <- 2,3 ; n+2,n+3 <- n,n+1 */
+#define LSC_BC_TRANSMISSIVE_E 3 /* Euler only, G:199-215: ghost 0,1 <- 2 ; n+2,n+3 <- n+1 */
+
+/* initial conditions the reference ships as commented blocks */
+#define LSC_MHD_IC_KELVIN_HELMHOLTZ 0 /* M:800-808 (the committed one) */
+#define LSC_MHD_IC_ORSZAG_TANG 1      /* M:811-819 */
+
+/* Replaces the constants at the top of main(), M:659-671. */
+typedef struct lsc_mhd_config {
+    int nx, ny;            /* M:659-660  interior cells of the WHOLE grid */
+    double x0, x1, y0, y1; /* M:661-664 */
+    double gamma;          /* M:668 */
+    double cfl;            /* M:667  (C) */
+    int bc_x;              /* LSC_BC_PERIODIC | LSC_BC_TRANSMISSIVE */
+    int bc_y;              /* LSC_BC_REFLECTIVE | LSC_BC_PERIODIC | LSC_BC_TRANSMISSIVE */
+    int device;            /* CUDA device ordinal this context runs on */
+    /* slab decomposition along x (one context per GPU).  rank r of nranks owns interior
+     * columns [r*nx/nranks, (r+1)*nx/nranks) plus two halo columns per side.  nranks = 1:
+     * the whole grid.  For nranks > 1 call lsc_mhd_comm_init() before upload. */
+    int rank, nranks;
+} lsc_mhd_config;
+
+typedef struct lsc_mhd_ctx lsc_mhd_ctx;
+
+/* Called at the dump cadence of M:975 (t crossed 0.1*counter) from lsc_mhd_run_until. */
+typedef int (*lsc_mhd_dump_cb)(lsc_mhd_ctx* ctx, int counter, double t, double dt, void* user);
+/* Called once per step with the values of the log line M:836 ("t= .. dt= .. ch= .."). */
+typedef void (*lsc_mhd_log_cb)(long step, double t, double dt, double ch, void* user);
+
+const char* lsc_last_error(void);
+int lsc_device_count(void);
+
+/* pinned host memory helpers for callers that want full-rate PCIe transfers */
+int lsc_host_alloc(void** ptr, unsigned long long bytes);
+int lsc_host_free(void* ptr);
+
+/* allocate the 15 work arrays of M:673-713 -- here: 3 device-resident SoA states */
+int lsc_mhd_create(const lsc_mhd_config* cfg, lsc_mhd_ctx** out);
+int lsc_mhd_destroy(lsc_mhd_ctx* ctx);
+
+/* number of interior columns / first global interior column of this rank's slab */
+int lsc_mhd_local_nx(const lsc_mhd_ctx* ctx);
+int lsc_mhd_local_i0(const lsc_mhd_ctx* ctx);
+
+/* Fill a host AoS array [(nxl+4)][(ny+4)][9] with this rank's slab of the initial condition of
+ * M:719-825 (cell centres x0+(i-0.5)dx incl. ghosts, host libm, PrimitiveToConservative M:9-21). */
+int lsc_mhd_initial_condition(const lsc_mhd_ctx* ctx, int problem, double* aos);
+
+/* Set the state (replaces the IC loop's stores, M:822).  aos holds this rank's slab incl. its
+ * ghost/halo cells, (nxl+4)*(ny+4)*9 doubles.  Resets t = 0, step = 0. */
+int lsc_mhd_upload(lsc_mhd_ctx* ctx, const double* aos);
+
+/* Generate the initial condition slab-chunk by slab-chunk and upload it without ever holding the
+ * whole AoS array on the host (the 16384^2 case: 19 GB).  Equivalent to
+ * lsc_mhd_initial_condition + lsc_mhd_upload. */
+int lsc_mhd_init_problem(lsc_mhd_ctx* ctx, int problem);
+
+/* nsteps passes of the do{}while body M:831-971 (CFL -> x sweep -> y sweep -> copy). */
+int lsc_mhd_step(lsc_mhd_ctx* ctx, long nsteps);
+
+/* The loop M:831-1003: steps until t >= t_stop (no clamping of the last step; t overshoots),
+ * firing dump_cb when `t > 0.1*counter && t-dt <= 0.1*counter` (M:975) and log_cb every step
+ * (M:836).  Either callback may be NULL.  *steps_out (may be NULL) receives the step count. */
+int lsc_mhd_run_until(lsc_mhd_ctx* ctx, double t_stop, lsc_mhd_dump_cb dump_cb, lsc_mhd_log_cb log_cb,
+                      void* user, long* steps_out);
+
+/* t, the last dt, the last ch (= max signal speed, M:834) and the step count. Any may be NULL. */
+int lsc_mhd_get_scalars(const lsc_mhd_ctx* ctx, double* t, double* dt, double* ch, long* step);
+
+/* Copy this rank's slab back in the reference layout, ghost ring included, with exactly the ghost
+ * contents the reference's `u` holds after M:971 (boundary images; the four never-written corner
+ * cells [nx+2..nx+3][ny+2..ny+3] are zero once a step has been taken). */
+int lsc_mhd_download(lsc_mhd_ctx* ctx, double* aos);
+
+/* Byte-compatible writer of M:989-1001 / M:1022-1032 for a FULL-grid AoS array (ghost ring
+ * included, as returned by lsc_mhd_download on a single-rank context): primitive variables,
+ * default 6-digit ostream formatting, blank line after each j row. */
+int lsc_mhd_write_dat(const lsc_mhd_config* cfg, const double* aos, const char* path);
+
+/* Multi-GPU: 128-byte NCCL unique id created on rank 0 and distributed by the caller
+ * (torch.distributed broadcast, a file, MPI ...); every rank then joins the communicator.
+ * Per step the ranks exchange two halo columns of u^{n+1} with each x neighbour and all-reduce
+ * (max) the signal speed -- the only cross-rank data of the path. */
+int lsc_comm_unique_id(void* id128);
+int lsc_mhd_comm_init(lsc_mhd_ctx* ctx, const void* id128);
+
+/* Test hooks: run the device flux / reconstruction functions on n states (AoS, 9 doubles each).
+ * dir 0 = x, 1 = y.  Used by tests/ for known-answer parity against the oracle. */
+int lsc_mhd_kat_hllc(int device, int dir, long n, const double* L, const double* R, double gamma, double ch,
+                     double* F);
+int lsc_mhd_kat_fluxdef(int device, int dir, long n, const double* U, double gamma, double ch, double* F);
+
+/* number of kernels this library has launched in this process (for bench.py's gpu_launches) */
+unsigned long long lsc_kernel_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LSC_B200_H */

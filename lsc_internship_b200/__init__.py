@@ -1,0 +1,7 @@
+"""lsc_internship_b200 -- B200-native (sm_100a CUDA behind a C ABI) implementation of the
+2-D MUSCL-Hancock + HLLC + GLM ideal-MHD step of JosephineMellor/LSC_internship
+(MHD_codes/MUSCL_NEW.cpp) and of its 2-D Euler SLIC sweep (Euler_codes/SLIC_euler_2d.cpp)."""
+from ._capi import LscError, MhdConfig, lib, LIB_PATH  # noqa: F401
+from .mhd import MusclNew, kat_hllc, kat_fluxdef  # noqa: F401
+
+__all__ = ["MusclNew", "LscError", "MhdConfig", "lib", "LIB_PATH", "kat_hllc", "kat_fluxdef"]

@@ -1,0 +1,96 @@
+"""ctypes binding of liblsc_b200.so (include/lsc_b200.h).
+
+The shared library is built in-tree by `make -C lsc_internship_b200/csrc` (or
+`__graft_entry__.build()`).  There is deliberately NO fallback: if the library is
+missing, or no CUDA device is present when a solver is created, the caller gets
+an exception -- never a CPU path.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "_lib", "liblsc_b200.so")
+
+LSC_OK = 0
+BC_PERIODIC, BC_REFLECTIVE, BC_TRANSMISSIVE, BC_TRANSMISSIVE_E = 0, 1, 2, 3
+MHD_IC_KELVIN_HELMHOLTZ, MHD_IC_ORSZAG_TANG = 0, 1
+
+BC_NAMES = {"periodic": BC_PERIODIC, "reflective": BC_REFLECTIVE, "transmissive": BC_TRANSMISSIVE,
+            "transmissive_e": BC_TRANSMISSIVE_E}
+MHD_PROBLEMS = {"kh": MHD_IC_KELVIN_HELMHOLTZ, "kelvin-helmholtz": MHD_IC_KELVIN_HELMHOLTZ,
+                "ot": MHD_IC_ORSZAG_TANG, "orszag-tang": MHD_IC_ORSZAG_TANG}
+
+
+class LscError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"liblsc_b200 error {code}: {msg}")
+        self.code = code
+
+
+class MhdConfig(ctypes.Structure):
+    """struct lsc_mhd_config -- the constants of MUSCL_NEW.cpp:659-671."""
+    _fields_ = [("nx", ctypes.c_int), ("ny", ctypes.c_int),
+                ("x0", ctypes.c_double), ("x1", ctypes.c_double),
+                ("y0", ctypes.c_double), ("y1", ctypes.c_double),
+                ("gamma", ctypes.c_double), ("cfl", ctypes.c_double),
+                ("bc_x", ctypes.c_int), ("bc_y", ctypes.c_int),
+                ("device", ctypes.c_int), ("rank", ctypes.c_int), ("nranks", ctypes.c_int)]
+
+
+DUMP_CB = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_double, ctypes.c_double,
+                           ctypes.c_void_p)
+LOG_CB = ctypes.CFUNCTYPE(None, ctypes.c_long, ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_void_p)
+
+# every symbol include/lsc_b200.h declares
+EXPORTS = [
+    "lsc_last_error", "lsc_device_count", "lsc_host_alloc", "lsc_host_free",
+    "lsc_mhd_create", "lsc_mhd_destroy", "lsc_mhd_local_nx", "lsc_mhd_local_i0",
+    "lsc_mhd_initial_condition", "lsc_mhd_upload", "lsc_mhd_init_problem", "lsc_mhd_step",
+    "lsc_mhd_run_until", "lsc_mhd_get_scalars", "lsc_mhd_download", "lsc_mhd_write_dat",
+    "lsc_comm_unique_id", "lsc_mhd_comm_init", "lsc_mhd_kat_hllc", "lsc_mhd_kat_fluxdef",
+    "lsc_kernel_launch_count",
+]
+
+_lib = None
+
+
+def lib():
+    """Load liblsc_b200.so (once).  Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise LscError(-2, f"{LIB_PATH} not built: run `make -C lsc_internship_b200/csrc` "
+                           "(no CPU fallback exists)")
+    L = ctypes.CDLL(LIB_PATH, mode=ctypes.RTLD_GLOBAL)
+    dp = ctypes.POINTER(ctypes.c_double)
+    vp = ctypes.c_void_p
+    L.lsc_last_error.restype = ctypes.c_char_p
+    L.lsc_kernel_launch_count.restype = ctypes.c_ulonglong
+    L.lsc_host_alloc.argtypes = [ctypes.POINTER(vp), ctypes.c_ulonglong]
+    L.lsc_host_free.argtypes = [vp]
+    L.lsc_mhd_create.argtypes = [ctypes.POINTER(MhdConfig), ctypes.POINTER(vp)]
+    L.lsc_mhd_destroy.argtypes = [vp]
+    L.lsc_mhd_local_nx.argtypes = [vp]
+    L.lsc_mhd_local_i0.argtypes = [vp]
+    L.lsc_mhd_initial_condition.argtypes = [vp, ctypes.c_int, dp]
+    L.lsc_mhd_upload.argtypes = [vp, dp]
+    L.lsc_mhd_init_problem.argtypes = [vp, ctypes.c_int]
+    L.lsc_mhd_step.argtypes = [vp, ctypes.c_long]
+    L.lsc_mhd_run_until.argtypes = [vp, ctypes.c_double, DUMP_CB, LOG_CB, vp, ctypes.POINTER(ctypes.c_long)]
+    L.lsc_mhd_get_scalars.argtypes = [vp, dp, dp, dp, ctypes.POINTER(ctypes.c_long)]
+    L.lsc_mhd_download.argtypes = [vp, dp]
+    L.lsc_mhd_write_dat.argtypes = [ctypes.POINTER(MhdConfig), dp, ctypes.c_char_p]
+    L.lsc_comm_unique_id.argtypes = [vp]
+    L.lsc_mhd_comm_init.argtypes = [vp, vp]
+    L.lsc_mhd_kat_hllc.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_long, dp, dp, ctypes.c_double,
+                                   ctypes.c_double, dp]
+    L.lsc_mhd_kat_fluxdef.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_long, dp, ctypes.c_double,
+                                      ctypes.c_double, dp]
+    _lib = L
+    return L
+
+
+def check(rc):
+    if rc != LSC_OK:
+        raise LscError(rc, lib().lsc_last_error().decode(errors="replace"))

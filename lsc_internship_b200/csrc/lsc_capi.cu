@@ -1,0 +1,431 @@
+// lsc_capi.cu -- the C ABI of include/lsc_b200.h: contexts, transfers and the time loop
+// of MHD_codes/MUSCL_NEW.cpp main() (:658-1034) driving the sm_100a kernels.
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "../../include/lsc_b200.h"
+#include "lsc_comm.h"
+#include "mhd_host.h"
+#include "mhd_kernels.cuh"
+
+namespace {
+
+thread_local char g_err[512] = "";
+std::atomic<unsigned long long> g_launches{0};
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                        \
+    do {                                                                                      \
+        cudaError_t e_ = (expr);                                                              \
+        if (e_ != cudaSuccess)                                                                \
+            return fail(LSC_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+inline int to_kernel_bc(int bc) {
+    switch (bc) {
+        case LSC_BC_PERIODIC: return lsc::BC_PERIODIC;
+        case LSC_BC_REFLECTIVE: return lsc::BC_REFLECTIVE;
+        default: return lsc::BC_TRANSMISSIVE;
+    }
+}
+
+}  // namespace
+
+void lsc_count_launches(unsigned long long n) { g_launches += n; }
+
+struct lsc_mhd_ctx {
+    lsc_mhd_config cfg;
+    int nxl = 0, i0 = 0;  // slab: interior columns, first global interior column (0-based)
+    double dx = 0, dy = 0;
+    lsc::GridDims g{};
+    double* state[3] = {nullptr, nullptr, nullptr};
+    int cur = 0, bar = 1, prev = 2;
+    unsigned long long* d_max = nullptr;  // bit pattern of the max signal speed of state[cur]
+    unsigned long long* h_max = nullptr;  // pinned
+    double* d_stage = nullptr;            // AoS staging for transfers
+    int stage_cols = 0;
+    cudaStream_t stream = nullptr;
+    double t = 0, dt = 0, ch = 0;
+    long step = 0;
+    bool uploaded = false;
+    bool ghosts_current = false;  // x ghost/halo columns of state[cur] hold boundary images
+    lsc::Comm* comm = nullptr;
+};
+
+extern "C" {
+
+const char* lsc_last_error(void) { return g_err; }
+
+int lsc_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+unsigned long long lsc_kernel_launch_count(void) { return g_launches.load(); }
+
+int lsc_host_alloc(void** ptr, unsigned long long bytes) {
+    if (!ptr) return fail(LSC_EINVAL, "lsc_host_alloc: null out pointer");
+    CUDA_TRY(cudaHostAlloc(ptr, (size_t)bytes, cudaHostAllocDefault));
+    return LSC_OK;
+}
+
+int lsc_host_free(void* ptr) {
+    CUDA_TRY(cudaFreeHost(ptr));
+    return LSC_OK;
+}
+
+int lsc_mhd_create(const lsc_mhd_config* cfg, lsc_mhd_ctx** out) {
+    if (!cfg || !out) return fail(LSC_EINVAL, "lsc_mhd_create: null argument");
+    *out = nullptr;
+    if (cfg->nx < 4 || cfg->ny < 4) return fail(LSC_EINVAL, "nx, ny must be >= 4 (got %d x %d)", cfg->nx, cfg->ny);
+    if (!(cfg->x1 > cfg->x0) || !(cfg->y1 > cfg->y0)) return fail(LSC_EINVAL, "empty domain");
+    if (!(cfg->gamma > 1.0) || !(cfg->cfl > 0.0)) return fail(LSC_EINVAL, "gamma must be > 1 and cfl > 0");
+    if (cfg->bc_x != LSC_BC_PERIODIC && cfg->bc_x != LSC_BC_TRANSMISSIVE)
+        return fail(LSC_EINVAL, "bc_x must be periodic or transmissive (MUSCL_NEW.cpp:609-622)");
+    if (cfg->bc_y != LSC_BC_PERIODIC && cfg->bc_y != LSC_BC_TRANSMISSIVE && cfg->bc_y != LSC_BC_REFLECTIVE)
+        return fail(LSC_EINVAL, "bc_y must be reflective, periodic or transmissive (MUSCL_NEW.cpp:625-654)");
+    if (cfg->nranks < 1 || cfg->rank < 0 || cfg->rank >= cfg->nranks) return fail(LSC_EINVAL, "bad rank/nranks");
+    if (cfg->nx / cfg->nranks < 4) return fail(LSC_EINVAL, "slab narrower than 4 columns");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(LSC_ECUDA, "no CUDA device: this library has no CPU path");
+    }
+    if (cfg->device < 0 || cfg->device >= ndev) return fail(LSC_EINVAL, "device %d out of range", cfg->device);
+    CUDA_TRY(cudaSetDevice(cfg->device));
+
+    lsc_mhd_ctx* c = new (std::nothrow) lsc_mhd_ctx();
+    if (!c) return fail(LSC_ENOMEM, "host allocation failed");
+    c->cfg = *cfg;
+    const long long b0 = (long long)cfg->rank * cfg->nx / cfg->nranks;
+    const long long b1 = (long long)(cfg->rank + 1) * cfg->nx / cfg->nranks;
+    c->i0 = (int)b0;
+    c->nxl = (int)(b1 - b0);
+    c->dx = (cfg->x1 - cfg->x0) / cfg->nx;  // MUSCL_NEW.cpp:669-670
+    c->dy = (cfg->y1 - cfg->y0) / cfg->ny;
+    c->g.nxl = c->nxl;
+    c->g.ny = cfg->ny;
+    c->g.pitch = ((cfg->ny + 4 + lsc::JOFF) + 15) / 16 * 16;
+    c->g.plane = (size_t)(c->nxl + 4) * (size_t)c->g.pitch;
+    const size_t state_bytes = c->g.plane * lsc::NV * sizeof(double);
+    for (int b = 0; b < 3; ++b) {
+        if (cudaMalloc(&c->state[b], state_bytes) != cudaSuccess) {
+            cudaGetLastError();
+            lsc_mhd_destroy(c);
+            return fail(LSC_ENOMEM, "cudaMalloc of %zu bytes failed", state_bytes);
+        }
+        cudaMemset(c->state[b], 0, state_bytes);
+    }
+    // staging: at most ~256 MB of AoS columns
+    const size_t col_bytes = (size_t)(cfg->ny + 4) * lsc::NV * sizeof(double);
+    long long cols = (long long)((256ull << 20) / col_bytes);
+    if (cols < 1) cols = 1;
+    if (cols > c->nxl + 4) cols = c->nxl + 4;
+    c->stage_cols = (int)cols;
+    if (cudaMalloc(&c->d_stage, col_bytes * (size_t)cols) != cudaSuccess ||
+        cudaMalloc(&c->d_max, sizeof(unsigned long long)) != cudaSuccess ||
+        cudaHostAlloc(&c->h_max, sizeof(unsigned long long), cudaHostAllocDefault) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        cudaGetLastError();
+        lsc_mhd_destroy(c);
+        return fail(LSC_ENOMEM, "allocation of staging / scalars / stream failed");
+    }
+    *out = c;
+    return LSC_OK;
+}
+
+int lsc_mhd_destroy(lsc_mhd_ctx* c) {
+    if (!c) return LSC_OK;
+    cudaSetDevice(c->cfg.device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->comm) lsc::comm_destroy(c->comm);
+    for (int b = 0; b < 3; ++b)
+        if (c->state[b]) cudaFree(c->state[b]);
+    if (c->d_stage) cudaFree(c->d_stage);
+    if (c->d_max) cudaFree(c->d_max);
+    if (c->h_max) cudaFreeHost(c->h_max);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+    return LSC_OK;
+}
+
+int lsc_mhd_local_nx(const lsc_mhd_ctx* c) { return c ? c->nxl : LSC_EINVAL; }
+int lsc_mhd_local_i0(const lsc_mhd_ctx* c) { return c ? c->i0 : LSC_EINVAL; }
+
+int lsc_mhd_initial_condition(const lsc_mhd_ctx* c, int problem, double* aos) {
+    if (!c || !aos) return fail(LSC_EINVAL, "null argument");
+    if (problem != LSC_MHD_IC_KELVIN_HELMHOLTZ && problem != LSC_MHD_IC_ORSZAG_TANG)
+        return fail(LSC_EINVAL, "unknown problem %d", problem);
+    lsc::mhd_initial_condition(c->cfg, problem, c->i0, 0, c->nxl + 4, aos);
+    return LSC_OK;
+}
+
+}  // extern "C"
+
+namespace {
+
+// after new data has been placed in state[cur]: reset the clock and reduce the initial signal speed
+// over the reference's range (MUSCL_NEW.cpp:73-74: i,j in [1, n+1], array as uploaded, ghosts included)
+int finish_upload(lsc_mhd_ctx* c) {
+    CUDA_TRY(cudaMemsetAsync(c->d_max, 0, sizeof(unsigned long long), c->stream));
+    const int i_lo = (c->cfg.rank == 0) ? 1 : 2;
+    lsc::launch_max_speed(c->g, c->cfg.gamma, c->state[c->cur], i_lo, c->nxl + 1, 1, c->cfg.ny + 1, c->d_max,
+                          c->stream);
+    lsc_count_launches(1);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    c->t = 0;
+    c->dt = 0;
+    c->ch = 0;
+    c->step = 0;
+    c->uploaded = true;
+    c->ghosts_current = false;
+    return LSC_OK;
+}
+
+int upload_columns(lsc_mhd_ctx* c, const double* aos_chunk, int il0, int ni) {
+    const size_t col = (size_t)(c->cfg.ny + 4) * lsc::NV;
+    CUDA_TRY(cudaMemcpyAsync(c->d_stage, aos_chunk, col * ni * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    lsc::launch_aos_to_soa(c->g, c->d_stage, il0, ni, c->state[c->cur], c->stream);
+    lsc_count_launches(1);
+    CUDA_TRY(cudaGetLastError());
+    // the staging buffer is reused by the next chunk
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    return LSC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int lsc_mhd_upload(lsc_mhd_ctx* c, const double* aos) {
+    if (!c || !aos) return fail(LSC_EINVAL, "null argument");
+    CUDA_TRY(cudaSetDevice(c->cfg.device));
+    const size_t col = (size_t)(c->cfg.ny + 4) * lsc::NV;
+    for (int il = 0; il < c->nxl + 4; il += c->stage_cols) {
+        const int ni = std::min(c->stage_cols, c->nxl + 4 - il);
+        int rc = upload_columns(c, aos + col * il, il, ni);
+        if (rc) return rc;
+    }
+    return finish_upload(c);
+}
+
+int lsc_mhd_init_problem(lsc_mhd_ctx* c, int problem) {
+    if (!c) return fail(LSC_EINVAL, "null argument");
+    if (problem != LSC_MHD_IC_KELVIN_HELMHOLTZ && problem != LSC_MHD_IC_ORSZAG_TANG)
+        return fail(LSC_EINVAL, "unknown problem %d", problem);
+    CUDA_TRY(cudaSetDevice(c->cfg.device));
+    const size_t col = (size_t)(c->cfg.ny + 4) * lsc::NV;
+    const int chunk = std::min(c->stage_cols, 64);
+    double* host = nullptr;
+    CUDA_TRY(cudaHostAlloc(&host, col * chunk * sizeof(double), cudaHostAllocDefault));
+    int rc = LSC_OK;
+    for (int il = 0; il < c->nxl + 4 && rc == LSC_OK; il += chunk) {
+        const int ni = std::min(chunk, c->nxl + 4 - il);
+        lsc::mhd_initial_condition(c->cfg, problem, c->i0, il, ni, host);
+        rc = upload_columns(c, host, il, ni);
+    }
+    cudaFreeHost(host);
+    if (rc) return rc;
+    return finish_upload(c);
+}
+
+int lsc_mhd_get_scalars(const lsc_mhd_ctx* c, double* t, double* dt, double* ch, long* step) {
+    if (!c) return fail(LSC_EINVAL, "null argument");
+    if (t) *t = c->t;
+    if (dt) *dt = c->dt;
+    if (ch) *ch = c->ch;
+    if (step) *step = c->step;
+    return LSC_OK;
+}
+
+}  // extern "C"
+
+namespace {
+
+// Boundary images / neighbour data into the two ghost columns on each side of state b.
+int fill_x_ghosts(lsc_mhd_ctx* c, int b) {
+    if (c->cfg.nranks == 1) {
+        lsc::launch_x_ghosts(c->g, to_kernel_bc(c->cfg.bc_x), c->state[b], c->stream);
+        lsc_count_launches(1);
+        CUDA_TRY(cudaGetLastError());
+        return LSC_OK;
+    }
+    if (!c->comm) return fail(LSC_ESTATE, "nranks > 1 but lsc_mhd_comm_init was not called");
+    int rc = lsc::comm_exchange_halos(c->comm, c->g, to_kernel_bc(c->cfg.bc_x), c->state[b], c->stream);
+    if (rc) return fail(LSC_ECOMM, "halo exchange failed: %s", lsc::comm_error());
+    return LSC_OK;
+}
+
+// One pass of the loop body MUSCL_NEW.cpp:831-971.
+int step_once(lsc_mhd_ctx* c) {
+    // ---- ComputeTimeStep (:833-835): the reduction already ran on the device
+    if (c->cfg.nranks > 1) {
+        if (!c->comm) return fail(LSC_ESTATE, "nranks > 1 but lsc_mhd_comm_init was not called");
+        if (lsc::comm_allreduce_max_u64(c->comm, c->d_max, c->stream))
+            return fail(LSC_ECOMM, "allreduce failed: %s", lsc::comm_error());
+    }
+    CUDA_TRY(cudaMemcpyAsync(c->h_max, c->d_max, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    double max_speed;
+    std::memcpy(&max_speed, c->h_max, sizeof(double));
+    if (!(max_speed > 0.0) || !std::isfinite(max_speed))
+        return fail(LSC_ENAN, "max signal speed is %g at step %ld", max_speed, c->step);
+    const double dspace = std::min(c->dx, c->dy);      // :117
+    const double dt = c->cfg.cfl * dspace / max_speed;  // :118
+    const double ch = max_speed;                        // :834
+    c->t += dt;                                         // :835
+    c->dt = dt;
+    c->ch = ch;
+
+    // ---- applyBoundaryConditions(u) (:838) -- only the x ghost columns are ever read on the device
+    if (!c->ghosts_current) {
+        int rc = fill_x_ghosts(c, c->cur);
+        if (rc) return rc;
+        c->ghosts_current = true;
+    }
+
+    lsc::SweepParams p{};
+    p.gamma = c->cfg.gamma;
+    p.gm1 = c->cfg.gamma - 1;
+    p.ch = ch;
+    p.ch2 = ch * ch;
+    p.psi_factor = std::exp(-1.0 * (0.5 * dt) * ch / 0.18);  // psiUpdate(psi, maxSpeed, 0.5*dt), :66-69, :900
+    p.first_step = (c->step == 0) ? 1 : 0;
+
+    // ---- x sweep (:841-902)
+    p.dtdh = dt / c->dx;
+    p.hdtdh = 0.5 * (dt / c->dx);
+    p.bc_lo = (c->cfg.rank == 0) ? to_kernel_bc(c->cfg.bc_x) : -1;
+    p.bc_hi = (c->cfg.rank == c->cfg.nranks - 1) ? to_kernel_bc(c->cfg.bc_x) : -1;
+    if (c->cfg.nranks > 1 && c->cfg.bc_x == LSC_BC_PERIODIC) p.bc_lo = p.bc_hi = -1;
+    lsc::launch_x_sweep(c->g, p, c->state[c->cur], c->state[c->prev], c->state[c->bar], c->stream);
+
+    // ---- y sweep (:905-965) + copy (:969) + next step's signal speed (:71-115)
+    CUDA_TRY(cudaMemsetAsync(c->d_max, 0, sizeof(unsigned long long), c->stream));
+    p.dtdh = dt / c->dy;
+    p.hdtdh = 0.5 * (dt / c->dy);
+    p.bc_lo = p.bc_hi = to_kernel_bc(c->cfg.bc_y);
+    lsc::launch_y_sweep(c->g, p, c->state[c->bar], c->state[c->cur], c->state[c->prev], c->d_max, c->stream);
+    lsc_count_launches(2);
+    CUDA_TRY(cudaGetLastError());
+
+    // u = uPlus1 (:969): rotate; the old u^n stays as the limiter's "previous" state
+    const int next = c->prev;
+    c->prev = c->cur;
+    c->cur = next;
+    // ---- applyBoundaryConditions(u) (:971)
+    int rc = fill_x_ghosts(c, c->cur);
+    if (rc) return rc;
+    c->step += 1;
+    return LSC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int lsc_mhd_step(lsc_mhd_ctx* c, long nsteps) {
+    if (!c) return fail(LSC_EINVAL, "null argument");
+    if (!c->uploaded) return fail(LSC_ESTATE, "lsc_mhd_step before lsc_mhd_upload");
+    CUDA_TRY(cudaSetDevice(c->cfg.device));
+    for (long s = 0; s < nsteps; ++s) {
+        int rc = step_once(c);
+        if (rc) return rc;
+    }
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    return LSC_OK;
+}
+
+int lsc_mhd_run_until(lsc_mhd_ctx* c, double t_stop, lsc_mhd_dump_cb dump_cb, lsc_mhd_log_cb log_cb, void* user,
+                      long* steps_out) {
+    if (!c) return fail(LSC_EINVAL, "null argument");
+    if (!c->uploaded) return fail(LSC_ESTATE, "lsc_mhd_run_until before lsc_mhd_upload");
+    CUDA_TRY(cudaSetDevice(c->cfg.device));
+    int counter = 0;
+    long n = 0;
+    do {  // MUSCL_NEW.cpp:831
+        int rc = step_once(c);
+        if (rc) return rc;
+        ++n;
+        if (log_cb) log_cb(c->step, c->t, c->dt, c->ch, user);  // :836
+        if (c->t > 0.1 * counter && c->t - c->dt <= 0.1 * counter) {  // :975
+            if (dump_cb) {
+                rc = dump_cb(c, counter, c->t, c->dt, user);
+                if (rc) return fail(rc, "dump callback returned %d", rc);
+            }
+            counter += 1;  // :1000
+        }
+    } while (c->t < t_stop);  // :1003
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    if (steps_out) *steps_out = n;
+    return LSC_OK;
+}
+
+int lsc_mhd_download(lsc_mhd_ctx* c, double* aos) {
+    if (!c || !aos) return fail(LSC_EINVAL, "null argument");
+    if (!c->uploaded) return fail(LSC_ESTATE, "lsc_mhd_download before lsc_mhd_upload");
+    CUDA_TRY(cudaSetDevice(c->cfg.device));
+    const size_t col = (size_t)(c->cfg.ny + 4) * lsc::NV;
+    for (int il = 0; il < c->nxl + 4; il += c->stage_cols) {
+        const int ni = std::min(c->stage_cols, c->nxl + 4 - il);
+        lsc::launch_soa_to_aos(c->g, c->state[c->cur], il, ni, c->d_stage, c->stream);
+        lsc_count_launches(1);
+        CUDA_TRY(cudaGetLastError());
+        CUDA_TRY(cudaMemcpyAsync(aos + col * il, c->d_stage, col * ni * sizeof(double), cudaMemcpyDeviceToHost,
+                                 c->stream));
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
+    }
+    if (c->step > 0) {
+        // the device never stores y ghost rows (the y sweep indexes through the boundary map);
+        // rebuild the reference's ghost ring on the host from the interior
+        if (c->cfg.nranks == 1) {
+            lsc::mhd_fill_ghost_ring(c->cfg, aos);
+        } else {
+            lsc::mhd_apply_bc_y(c->cfg, c->nxl + 4, aos);
+        }
+    }
+    return LSC_OK;
+}
+
+int lsc_mhd_write_dat(const lsc_mhd_config* cfg, const double* aos, const char* path) {
+    if (!cfg || !aos || !path) return fail(LSC_EINVAL, "null argument");
+    if (lsc::mhd_write_dat(*cfg, aos, path)) return fail(LSC_EINVAL, "cannot write %s", path);
+    return LSC_OK;
+}
+
+int lsc_comm_unique_id(void* id128) {
+    if (!id128) return fail(LSC_EINVAL, "null argument");
+    if (lsc::comm_unique_id(id128)) return fail(LSC_ECOMM, "%s", lsc::comm_error());
+    return LSC_OK;
+}
+
+int lsc_mhd_comm_init(lsc_mhd_ctx* c, const void* id128) {
+    if (!c || !id128) return fail(LSC_EINVAL, "null argument");
+    if (c->cfg.nranks == 1) return LSC_OK;
+    CUDA_TRY(cudaSetDevice(c->cfg.device));
+    c->comm = lsc::comm_create(id128, c->cfg.rank, c->cfg.nranks, c->g, lsc::NV);
+    if (!c->comm) return fail(LSC_ECOMM, "%s", lsc::comm_error());
+    return LSC_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,113 @@
+// lsc_comm.cu -- NCCL halo exchange + max-allreduce for the slab decomposition along x.
+#include "lsc_comm.h"
+
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+#include <nccl.h>
+
+void lsc_count_launches(unsigned long long n);
+
+namespace lsc {
+
+static thread_local char g_comm_err[256] = "";
+const char* comm_error() { return g_comm_err; }
+
+#define NCCL_TRY(expr, ret)                                                                      \
+    do {                                                                                         \
+        ncclResult_t r_ = (expr);                                                                \
+        if (r_ != ncclSuccess) {                                                                 \
+            snprintf(g_comm_err, sizeof g_comm_err, "%s: %s", #expr, ncclGetErrorString(r_));    \
+            return ret;                                                                          \
+        }                                                                                        \
+    } while (0)
+
+struct Comm {
+    ncclComm_t nccl = nullptr;
+    int rank = 0, nranks = 1, nvar = 0;
+};
+
+static_assert(sizeof(ncclUniqueId) == 128, "lsc_comm_unique_id hands out 128 bytes");
+
+int comm_unique_id(void* id128) {
+    ncclUniqueId id;
+    NCCL_TRY(ncclGetUniqueId(&id), -1);
+    std::memcpy(id128, &id, sizeof id);
+    return 0;
+}
+
+Comm* comm_create(const void* id128, int rank, int nranks, const GridDims&, int nvar) {
+    Comm* c = new (std::nothrow) Comm();
+    if (!c) return nullptr;
+    ncclUniqueId id;
+    std::memcpy(&id, id128, sizeof id);
+    c->rank = rank;
+    c->nranks = nranks;
+    c->nvar = nvar;
+    ncclResult_t r = ncclCommInitRank(&c->nccl, nranks, id, rank);
+    if (r != ncclSuccess) {
+        snprintf(g_comm_err, sizeof g_comm_err, "ncclCommInitRank: %s", ncclGetErrorString(r));
+        delete c;
+        return nullptr;
+    }
+    return c;
+}
+
+void comm_destroy(Comm* c) {
+    if (!c) return;
+    if (c->nccl) ncclCommDestroy(c->nccl);
+    delete c;
+}
+
+// boundary image of one side only (end ranks of a non-periodic decomposition), MUSCL_NEW.cpp:617-622
+__global__ void x_ghost_side_kernel(const GridDims g, int hi_side, double* __restrict__ u) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= g.ny + 4) return;
+    double* pl = u + (size_t)blockIdx.y * g.plane;
+    const int nx = g.nxl;
+    if (hi_side) {
+        pl[cell_index(g, nx + 2, j)] = pl[cell_index(g, nx, j)];
+        pl[cell_index(g, nx + 3, j)] = pl[cell_index(g, nx + 1, j)];
+    } else {
+        pl[cell_index(g, 0, j)] = pl[cell_index(g, 2, j)];
+        pl[cell_index(g, 1, j)] = pl[cell_index(g, 3, j)];
+    }
+}
+
+int comm_exchange_halos(Comm* c, const GridDims& g, int bc_x, double* u, cudaStream_t s) {
+    const bool ring = (bc_x == BC_PERIODIC);
+    const int left = (c->rank > 0) ? c->rank - 1 : (ring ? c->nranks - 1 : -1);
+    const int right = (c->rank < c->nranks - 1) ? c->rank + 1 : (ring ? 0 : -1);
+    const size_t n = 2 * (size_t)g.pitch;  // two adjacent columns of one plane are contiguous
+    NCCL_TRY(ncclGroupStart(), -1);
+    for (int k = 0; k < c->nvar; ++k) {
+        double* pl = u + (size_t)k * g.plane;
+        if (left >= 0) {
+            NCCL_TRY(ncclSend(pl + (size_t)2 * g.pitch, n, ncclDouble, left, c->nccl, s), -1);
+            NCCL_TRY(ncclRecv(pl, n, ncclDouble, left, c->nccl, s), -1);
+        }
+        if (right >= 0) {
+            NCCL_TRY(ncclSend(pl + (size_t)g.nxl * g.pitch, n, ncclDouble, right, c->nccl, s), -1);
+            NCCL_TRY(ncclRecv(pl + (size_t)(g.nxl + 2) * g.pitch, n, ncclDouble, right, c->nccl, s), -1);
+        }
+    }
+    NCCL_TRY(ncclGroupEnd(), -1);
+    dim3 block(256), grid((g.ny + 4 + 255) / 256, c->nvar);
+    if (left < 0) {
+        x_ghost_side_kernel<<<grid, block, 0, s>>>(g, 0, u);
+        lsc_count_launches(1);
+    }
+    if (right < 0) {
+        x_ghost_side_kernel<<<grid, block, 0, s>>>(g, 1, u);
+        lsc_count_launches(1);
+    }
+    return 0;
+}
+
+int comm_allreduce_max_u64(Comm* c, unsigned long long* d_word, cudaStream_t s) {
+    NCCL_TRY(ncclAllReduce(d_word, d_word, 1, ncclUint64, ncclMax, c->nccl, s), -1);
+    return 0;
+}
+
+}  // namespace lsc

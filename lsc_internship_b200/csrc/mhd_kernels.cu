@@ -1,0 +1,407 @@
+// mhd_kernels.cu -- sm_100a kernels of the dimensionally split MHD step.
+//
+//   x_sweep_kernel : u^n (+ u^{n-1} for the limiter) -> uBar      MUSCL_NEW.cpp:838-902
+//   y_sweep_kernel : uBar (+ u^n for the limiter)    -> u^{n+1}   MUSCL_NEW.cpp:905-971, + max signal
+//                    speed of u^{n+1} for the next step           MUSCL_NEW.cpp:71-115
+//   x_ghost_kernel : ghost columns of a state                     MUSCL_NEW.cpp:609-622
+//   max_speed_kernel : stand-alone CFL reduction (initial state)  MUSCL_NEW.cpp:71-115
+//
+// Compiled with -fmad=false: FMA contraction changes the answer at the 1e-9 level
+// after one step and at the 1e-2 level after ten.
+#include "mhd_kernels.cuh"
+#include "mhd_physics.cuh"
+
+namespace lsc {
+
+__device__ __forceinline__ void load_cell(const double* __restrict__ base, size_t plane, size_t idx,
+                                          double (&u)[NV]) {
+#pragma unroll
+    for (int k = 0; k < NV; ++k) u[k] = __ldg(base + (size_t)k * plane + idx);
+}
+
+__device__ __forceinline__ void atomic_max_nonneg(unsigned long long* addr, double v) {
+    // v >= 0 and not NaN: the IEEE bit pattern is monotone in the value
+    atomicMax(addr, (unsigned long long)__double_as_longlong(v));
+}
+
+// Reduce a per-thread running maximum (started from 0.0, updated only with `>` so NaNs
+// never enter -- MUSCL_NEW.cpp:111) over the block and fold it into *out.
+__device__ __forceinline__ void block_max_to_global(double local, unsigned long long* out) {
+    __shared__ double warp_max[32];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double other = __shfl_xor_sync(0xffffffffu, local, o);
+        local = (other > local) ? other : local;
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) warp_max[warp] = local;
+    __syncthreads();
+    if (warp == 0) {
+        const int nwarps = (blockDim.x + 31) >> 5;
+        double v = (lane < nwarps) ? warp_max[lane] : 0.0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const double other = __shfl_xor_sync(0xffffffffu, v, o);
+            v = (other > v) ? other : v;
+        }
+        if (lane == 0 && v > 0.0) atomic_max_nonneg(out, v);
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// x sweep: one thread owns one row j and marches along i over a strip of columns,
+// keeping the 3-cell stencil, its primitives, the previous face state and the previous
+// interface flux in registers.  Adjacent threads are adjacent in j (the contiguous axis),
+// so every global access is a fully coalesced 8-byte-per-lane transaction, each input
+// value is loaded once per strip, and reconstruct -> predict -> HLLC -> flux difference
+// -> psi damping never leave the register file.
+// ------------------------------------------------------------------------------------
+
+// Half-step face states of cell i computed straight from global memory (strip warm-up and
+// the non-periodic boundary images, MUSCL_NEW.cpp:878-879).
+__device__ __noinline__ void x_halfstates_global(const GridDims g, const SweepParams p,
+                                                 const double* __restrict__ cur,
+                                                 const double* __restrict__ prev, int i, int j,
+                                                 double (&hL)[NV], double (&hR)[NV]) {
+    double um[NV], u0[NV], up[NV], pm[NV], p0[NV], pp[NV];
+    load_cell(cur, g.plane, cell_index(g, i - 1, j), um);
+    load_cell(cur, g.plane, cell_index(g, i, j), u0);
+    load_cell(cur, g.plane, cell_index(g, i + 1, j), up);
+    c2p_full(um, p.gm1, pm);
+    c2p_full(u0, p.gm1, p0);
+    if (p.first_step) {
+#pragma unroll
+        for (int k = 0; k < NV; ++k) pp[k] = 0.0;
+    } else {
+        double q[NV];
+        load_cell(prev, g.plane, cell_index(g, i + 1, j), q);
+        c2p_full(q, p.gm1, pp);
+    }
+#pragma unroll
+    for (int k = 0; k < NV; ++k) reconstruct1(pm[k], p0[k], pp[k], um[k], u0[k], up[k], hL[k], hR[k]);
+    predictor<0>(hL, hR, p.gm1, p.ch2, p.hdtdh);
+}
+
+template <int STRIP>
+__global__ void __launch_bounds__(128) x_sweep_kernel(const GridDims g, const SweepParams p,
+                                                      const double* __restrict__ cur,
+                                                      const double* __restrict__ prev,
+                                                      double* __restrict__ ubar) {
+    const int j = 2 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= g.ny + 2) return;
+    const int ia = 2 + blockIdx.y * STRIP;
+    const int ib = min(ia + STRIP, g.nxl + 2);  // cells [ia, ib) are updated by this thread
+    const bool lo_image = (ia == 2) && (p.bc_lo == BC_TRANSMISSIVE);
+    const bool hi_image = (ib == g.nxl + 2) && (p.bc_hi == BC_TRANSMISSIVE);
+
+    double hRprev[NV], Fprev[NV];
+    {
+        // face state R of cell ia-1; at a transmissive wall ghost cell 1 carries the half state of
+        // cell 3 (u[1] = u[3] applied to the half-step arrays, MUSCL_NEW.cpp:617-622, :878-879)
+        double hL[NV];
+        x_halfstates_global(g, p, cur, prev, lo_image ? 3 : ia - 1, j, hL, hRprev);
+    }
+    double uM[NV], u0[NV], uP[NV], PM[NV], P0[NV];
+    load_cell(cur, g.plane, cell_index(g, ia - 1, j), uM);
+    load_cell(cur, g.plane, cell_index(g, ia, j), u0);
+    load_cell(cur, g.plane, cell_index(g, ia + 1, j), uP);
+    c2p_full(uM, p.gm1, PM);
+    c2p_full(u0, p.gm1, P0);
+
+    for (int c = ia; c <= ib; ++c) {
+        double hL[NV], hR[NV];
+        if (c == ib && hi_image) {
+            x_halfstates_global(g, p, cur, prev, g.nxl, j, hL, hR);  // u[nx+2] = u[nx]
+        } else {
+            double Pp[NV];
+            if (p.first_step) {
+#pragma unroll
+                for (int k = 0; k < NV; ++k) Pp[k] = 0.0;
+            } else {
+                double q[NV];
+                load_cell(prev, g.plane, cell_index(g, c + 1, j), q);
+                c2p_full(q, p.gm1, Pp);
+            }
+#pragma unroll
+            for (int k = 0; k < NV; ++k) reconstruct1(PM[k], P0[k], Pp[k], uM[k], u0[k], uP[k], hL[k], hR[k]);
+            predictor<0>(hL, hR, p.gm1, p.ch2, p.hdtdh);
+        }
+        double F[NV];
+        hllc_flux<0>(hRprev, hL, p.gamma, p.gm1, p.ch, p.ch2, F);  // interface c-1/2 (MUSCL_NEW.cpp:884)
+        if (c > ia) {
+            // uBar[c-1] = u[c-1] - (dt/dx)(F[c-1/2] - F[c-3/2])   MUSCL_NEW.cpp:891; psi damping :900
+            const size_t o = cell_index(g, c - 1, j);
+#pragma unroll
+            for (int k = 0; k < NV; ++k) {
+                double v = uM[k] - p.dtdh * (F[k] - Fprev[k]);
+                if (k == 8) v = v * p.psi_factor;
+                ubar[(size_t)k * g.plane + o] = v;
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+            Fprev[k] = F[k];
+            hRprev[k] = hR[k];
+            uM[k] = u0[k];
+            u0[k] = uP[k];
+            PM[k] = P0[k];
+        }
+        if (c < ib) {
+            c2p_full(u0, p.gm1, P0);
+            load_cell(cur, g.plane, cell_index(g, c + 2, j), uP);
+        }
+    }
+}
+
+void launch_x_sweep(const GridDims& g, const SweepParams& p, const double* u_cur, const double* u_prev,
+                    double* u_bar, cudaStream_t s) {
+    constexpr int STRIP = 64;
+    dim3 block(128);
+    dim3 grid((g.ny + block.x - 1) / block.x, (g.nxl + STRIP - 1) / STRIP);
+    x_sweep_kernel<STRIP><<<grid, block, 0, s>>>(g, p, u_cur, u_prev, u_bar);
+}
+
+// ------------------------------------------------------------------------------------
+// y sweep: one thread per cell along the contiguous axis.  A block of BJ threads covers cells
+// jo-1 .. jo+BJ-2 of one column; face states and interface fluxes are exchanged between
+// neighbouring threads through shared memory, so a block produces BJ-2 updated cells.
+// ------------------------------------------------------------------------------------
+constexpr int BJ = 128;
+
+// Which stored cell a (possibly ghost) row index refers to, and whether the reflective sign
+// applies (MUSCL_NEW.cpp:625-654).  Interior rows map to themselves.
+__device__ __forceinline__ int map_row(int j, int ny, int bc, bool& flip) {
+    flip = false;
+    if (j >= 2 && j <= ny + 1) return j;
+    if (bc == BC_PERIODIC) return (j < 2) ? j + ny : j - ny;
+    flip = (bc == BC_REFLECTIVE);
+    return (j < 2) ? j + 2 : j - 2;
+}
+
+__device__ __forceinline__ void load_row_cell(const double* __restrict__ base, const GridDims& g, int i, int j,
+                                              int bc, double (&u)[NV]) {
+    bool flip;
+    const int js = map_row(j, g.ny, bc, flip);
+    load_cell(base, g.plane, cell_index(g, i, js), u);
+    if (flip) {
+        u[2] = -u[2];
+        u[6] = -u[6];
+    }
+}
+
+// Half-step face states (bottom, top) of cell j of column i straight from global memory.
+__device__ __noinline__ void y_halfstates_global(const GridDims g, const SweepParams p,
+                                                 const double* __restrict__ ubar,
+                                                 const double* __restrict__ cur, int i, int j,
+                                                 double (&hB)[NV], double (&hT)[NV]) {
+    double um[NV], u0[NV], up[NV], q[NV], pm[NV], p0[NV], pp[NV];
+    load_row_cell(ubar, g, i, j - 1, p.bc_lo, um);
+    load_row_cell(ubar, g, i, j, p.bc_lo, u0);
+    load_row_cell(ubar, g, i, j + 1, p.bc_lo, up);
+    load_row_cell(cur, g, i, j - 1, p.bc_lo, q);
+    c2p_full(q, p.gm1, pm);
+    load_row_cell(cur, g, i, j, p.bc_lo, q);
+    c2p_full(q, p.gm1, p0);
+    load_row_cell(cur, g, i, j + 1, p.bc_lo, q);
+    c2p_full(q, p.gm1, pp);
+#pragma unroll
+    for (int k = 0; k < NV; ++k) reconstruct1(pm[k], p0[k], pp[k], um[k], u0[k], up[k], hB[k], hT[k]);
+    predictor<1>(hB, hT, p.gm1, p.ch2, p.hdtdh);
+}
+
+__global__ void __launch_bounds__(BJ) y_sweep_kernel(const GridDims g, const SweepParams p,
+                                                     const double* __restrict__ ubar,
+                                                     const double* __restrict__ cur,
+                                                     double* __restrict__ next,
+                                                     unsigned long long* __restrict__ max_bits) {
+    __shared__ double sU[NV][BJ + 2];  // uBar of cells jo-2 .. jo+BJ-1
+    __shared__ double sP[NV][BJ + 2];  // primitives of u^n there; later the interface fluxes
+    __shared__ double sH[NV][BJ];      // bottom face state of each thread's cell
+
+    const int tid = threadIdx.x;
+    const int i = 2 + blockIdx.y;
+    const int jo = 2 + blockIdx.x * (BJ - 2);
+    const int c = jo - 1 + tid;  // this thread's cell
+    const int bc = p.bc_lo;      // the reference uses one y boundary type for both ends
+
+    for (int t = tid; t < BJ + 2; t += BJ) {
+        const int jt = jo - 2 + t;
+        if (jt <= g.ny + 3) {
+            double q[NV], v[NV];
+            load_row_cell(ubar, g, i, jt, bc, q);
+#pragma unroll
+            for (int k = 0; k < NV; ++k) sU[k][t] = q[k];
+            load_row_cell(cur, g, i, jt, bc, q);
+            c2p_full(q, p.gm1, v);
+#pragma unroll
+            for (int k = 0; k < NV; ++k) sP[k][t] = v[k];
+        }
+    }
+    __syncthreads();
+
+    const bool active = (c <= g.ny + 2);
+    double hB[NV], hT[NV], ub[NV];
+    if (active) {
+        const bool image = (bc != BC_PERIODIC) && (c == 1 || c == g.ny + 2);
+        if (image) {
+            // ghost face states are the (sign-flipped) face states of cell 3 / ny: the reference
+            // applies its boundary function to the half-step arrays (MUSCL_NEW.cpp:940-941)
+            y_halfstates_global(g, p, ubar, cur, i, (c == 1) ? 3 : g.ny, hB, hT);
+            if (bc == BC_REFLECTIVE) {
+                hB[2] = -hB[2]; hB[6] = -hB[6];
+                hT[2] = -hT[2]; hT[6] = -hT[6];
+            }
+#pragma unroll
+            for (int k = 0; k < NV; ++k) ub[k] = 0.0;
+        } else {
+            const int t = tid + 1;
+#pragma unroll
+            for (int k = 0; k < NV; ++k) {
+                ub[k] = sU[k][t];
+                reconstruct1(sP[k][t - 1], sP[k][t], sP[k][t + 1], sU[k][t - 1], ub[k], sU[k][t + 1], hB[k], hT[k]);
+            }
+            predictor<1>(hB, hT, p.gm1, p.ch2, p.hdtdh);
+        }
+#pragma unroll
+        for (int k = 0; k < NV; ++k) sH[k][tid] = hB[k];
+    }
+    __syncthreads();
+
+    // flux through the interface above cell c: FluxHLLCY(top of c, bottom of c+1)  MUSCL_NEW.cpp:945
+    double F[NV];
+    const bool has_flux = (tid < BJ - 1) && (c <= g.ny + 1);
+    if (has_flux) {
+        double nb[NV];
+#pragma unroll
+        for (int k = 0; k < NV; ++k) nb[k] = sH[k][tid + 1];
+        hllc_flux<1>(hT, nb, p.gamma, p.gm1, p.ch, p.ch2, F);
+#pragma unroll
+        for (int k = 0; k < NV; ++k) sP[k][tid] = F[k];
+    }
+    __syncthreads();
+
+    double speed = 0.0;
+    if (tid >= 1 && has_flux && c >= 2) {
+        // u^{n+1} = uBar - (dt/dy)(F[j] - F[j-1])  MUSCL_NEW.cpp:953; psi damping :963
+        double un[NV];
+        const size_t o = cell_index(g, i, c);
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+            double v = ub[k] - p.dtdh * (F[k] - sP[k][tid - 1]);
+            if (k == 8) v = v * p.psi_factor;
+            un[k] = v;
+            next[(size_t)k * g.plane + o] = v;
+        }
+        const double sp = cfl_speed(un, p.gamma);
+        if (sp > speed) speed = sp;
+    }
+    block_max_to_global(speed, max_bits);
+}
+
+void launch_y_sweep(const GridDims& g, const SweepParams& p, const double* u_bar, const double* u_cur,
+                    double* u_next, unsigned long long* max_bits, cudaStream_t s) {
+    dim3 block(BJ);
+    dim3 grid((g.ny + (BJ - 2) - 1) / (BJ - 2), g.nxl);
+    y_sweep_kernel<<<grid, block, 0, s>>>(g, p, u_bar, u_cur, u_next, max_bits);
+}
+
+// ------------------------------------------------------------------------------------
+// Ghost columns in x (single-rank case; between ranks the same columns are filled by the
+// halo exchange).  periodic: MUSCL_NEW.cpp:609-614, transmissive: :617-622.
+// ------------------------------------------------------------------------------------
+__global__ void x_ghost_kernel(const GridDims g, int bc_x, double* __restrict__ u) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= g.ny + 4) return;
+    const int k = blockIdx.y;
+    const int nx = g.nxl;
+    int dst[4] = {0, 1, nx + 2, nx + 3};
+    int src[4];
+    if (bc_x == BC_PERIODIC) {
+        src[0] = nx; src[1] = nx + 1; src[2] = 2; src[3] = 3;
+    } else {
+        src[0] = 2; src[1] = 3; src[2] = nx; src[3] = nx + 1;
+    }
+    double* pl = u + (size_t)k * g.plane;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) pl[cell_index(g, dst[q], j)] = pl[cell_index(g, src[q], j)];
+}
+
+void launch_x_ghosts(const GridDims& g, int bc_x, double* u, cudaStream_t s) {
+    dim3 block(256);
+    dim3 grid((g.ny + 4 + 255) / 256, NV);
+    x_ghost_kernel<<<grid, block, 0, s>>>(g, bc_x, u);
+}
+
+// Stand-alone CFL reduction over cells [i_lo,i_hi] x [j_lo,j_hi] (inclusive).  The reference
+// reduces over i in [1,nx+1], j in [1,ny+1] of the array as it stands BEFORE the step's boundary
+// fill (MUSCL_NEW.cpp:73-74, :833 vs :838) -- on the first step that includes analytic ghost values.
+__global__ void max_speed_kernel(const GridDims g, double gamma, const double* __restrict__ u, int i_lo,
+                                 int i_hi, int j_lo, int j_hi, unsigned long long* __restrict__ max_bits) {
+    const int j = j_lo + blockIdx.x * blockDim.x + threadIdx.x;
+    double best = 0.0;
+    if (j <= j_hi) {
+        for (int i = i_lo + blockIdx.y; i <= i_hi; i += gridDim.y) {
+            double q[NV];
+            load_cell(u, g.plane, cell_index(g, i, j), q);
+            const double sp = cfl_speed(q, gamma);
+            if (sp > best) best = sp;
+        }
+    }
+    block_max_to_global(best, max_bits);
+}
+
+void launch_max_speed(const GridDims& g, double gamma, const double* u, int i_lo, int i_hi, int j_lo, int j_hi,
+                      unsigned long long* max_bits, cudaStream_t s) {
+    dim3 block(128);
+    const int nj = j_hi - j_lo + 1, ni = i_hi - i_lo + 1;
+    dim3 grid((nj + 127) / 128, ni < 64 ? ni : 64);
+    max_speed_kernel<<<grid, block, 0, s>>>(g, gamma, u, i_lo, i_hi, j_lo, j_hi, max_bits);
+}
+
+// ------------------------------------------------------------------------------------
+// Reference array-of-structures [i][j][9] <-> device planes, for `ni` columns starting at i0.
+// The AoS chunk pointer addresses column i0 (chunk-local), rows 0..ny+3.
+// ------------------------------------------------------------------------------------
+__global__ void aos_to_soa_kernel(const GridDims g, const double* __restrict__ aos, int i0, int ni,
+                                  double* __restrict__ soa) {
+    __shared__ double tile[32 * NV];
+    const int jb = blockIdx.x * 32;
+    const int il = blockIdx.y;
+    const int nrow = g.ny + 4;
+    const int nj = min(32, nrow - jb);
+    const double* src = aos + ((size_t)il * nrow + jb) * NV;
+    for (int t = threadIdx.x; t < nj * NV; t += blockDim.x) tile[t] = src[t];
+    __syncthreads();
+    for (int t = threadIdx.x; t < nj * NV; t += blockDim.x) {
+        const int k = t / nj, jj = t - k * nj;
+        soa[(size_t)k * g.plane + cell_index(g, i0 + il, jb + jj)] = tile[jj * NV + k];
+    }
+}
+
+__global__ void soa_to_aos_kernel(const GridDims g, const double* __restrict__ soa, int i0, int ni,
+                                  double* __restrict__ aos) {
+    __shared__ double tile[32 * NV];
+    const int jb = blockIdx.x * 32;
+    const int il = blockIdx.y;
+    const int nrow = g.ny + 4;
+    const int nj = min(32, nrow - jb);
+    for (int t = threadIdx.x; t < nj * NV; t += blockDim.x) {
+        const int k = t / nj, jj = t - k * nj;
+        tile[jj * NV + k] = soa[(size_t)k * g.plane + cell_index(g, i0 + il, jb + jj)];
+    }
+    __syncthreads();
+    double* dst = aos + ((size_t)il * nrow + jb) * NV;
+    for (int t = threadIdx.x; t < nj * NV; t += blockDim.x) dst[t] = tile[t];
+}
+
+void launch_aos_to_soa(const GridDims& g, const double* aos, int i0, int ni, double* soa, cudaStream_t s) {
+    dim3 grid((g.ny + 4 + 31) / 32, ni);
+    aos_to_soa_kernel<<<grid, 96, 0, s>>>(g, aos, i0, ni, soa);
+}
+
+void launch_soa_to_aos(const GridDims& g, const double* soa, int i0, int ni, double* aos, cudaStream_t s) {
+    dim3 grid((g.ny + 4 + 31) / 32, ni);
+    soa_to_aos_kernel<<<grid, 96, 0, s>>>(g, soa, i0, ni, aos);
+}
+
+}  // namespace lsc

@@ -1,0 +1,54 @@
+// mhd_kernels.cuh -- launch-side declarations shared by the kernels and the C ABI.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace lsc {
+
+constexpr int NV = 9;  // rho, mx, my, mz, E, Bx, By, Bz, psi  (MUSCL_NEW.cpp:11-19)
+
+// Boundary-condition codes (include/lsc_b200.h mirrors these values).
+enum : int { BC_PERIODIC = 0, BC_REFLECTIVE = 1, BC_TRANSMISSIVE = 2 };
+
+// Device layout of one 9-component state: structure-of-arrays, nine fp64 planes of
+// (nxl+4) x pitch doubles.  Cell (i,j) of plane k lives at
+//     base + k*plane + i*pitch + JOFF + j
+// i = x (slow), j = y (contiguous) -- the reference's [i][j] order (MUSCL_NEW.cpp:673-674),
+// with two ghost cells per side.  JOFF = 14 and pitch % 16 == 0 put the first interior cell
+// of every column (j = 2) on a 128-byte line.
+constexpr int JOFF = 14;
+
+struct GridDims {
+    int nxl;        // interior columns held by this rank (slab along x)
+    int ny;         // interior rows
+    int pitch;      // doubles between consecutive i
+    size_t plane;   // doubles between consecutive components
+};
+
+__host__ __device__ inline size_t cell_index(const GridDims& g, int i, int j) {
+    return (size_t)i * (size_t)g.pitch + (size_t)(JOFF + j);
+}
+
+struct SweepParams {
+    double gamma, gm1;
+    double ch, ch2;      // GLM wave speed = max signal speed of this step (MUSCL_NEW.cpp:834)
+    double dtdh;         // dt/dx (x sweep) or dt/dy (y sweep)
+    double hdtdh;        // 0.5*(dt/dx)
+    double psi_factor;   // exp(-(0.5 dt) ch / 0.18), host libm (MUSCL_NEW.cpp:66-69)
+    int first_step;      // 1: limiter's "previous primitives" are all zero (MUSCL_NEW.cpp:676-677, :845)
+    int bc_lo, bc_hi;    // physical boundary type at the low/high end of the sweep axis, or -1 when the
+                         // end is an inter-rank slab edge (ghost columns then hold neighbour data)
+};
+
+void launch_x_sweep(const GridDims& g, const SweepParams& p, const double* u_cur, const double* u_prev,
+                    double* u_bar, cudaStream_t s);
+void launch_y_sweep(const GridDims& g, const SweepParams& p, const double* u_bar, const double* u_cur,
+                    double* u_next, unsigned long long* max_bits, cudaStream_t s);
+void launch_x_ghosts(const GridDims& g, int bc_x, double* u, cudaStream_t s);
+void launch_max_speed(const GridDims& g, double gamma, const double* u, int i_lo, int i_hi, int j_lo, int j_hi,
+                      unsigned long long* max_bits, cudaStream_t s);
+void launch_aos_to_soa(const GridDims& g, const double* aos, int i0, int ni, double* soa, cudaStream_t s);
+void launch_soa_to_aos(const GridDims& g, const double* soa, int i0, int ni, double* aos, cudaStream_t s);
+
+}  // namespace lsc

@@ -1,0 +1,274 @@
+// mhd_physics.cuh -- per-cell / per-interface device arithmetic of the 2-D ideal-MHD
+// MUSCL-Hancock + HLLC + mixed-GLM update.
+//
+// Bit-faithful to the reference's expressions (MHD_codes/MUSCL_NEW.cpp, cited per
+// function): same association, IEEE division and sqrt, no FMA contraction (the
+// translation unit is compiled with -fmad=false).  What differs from the reference is
+// only *how often* things are evaluated: the reference recomputes the same pure
+// sub-expressions up to 14 times per interface; here each
+// distinct value is computed once, and of the two star states only the one the
+// HLLC branch selects.  Every common sub-expression that is reused is an IDENTICAL
+// IEEE expression on identical inputs, so results are bit-identical.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "mhd_kernels.cuh"
+
+namespace lsc {
+
+// std::min / std::max as libstdc++ defines them (first argument on ties / unordered)
+__device__ __forceinline__ double std_min(double a, double b) { return (b < a) ? b : a; }
+__device__ __forceinline__ double std_max(double a, double b) { return (a < b) ? b : a; }
+
+// Non-trivial primitives of a conserved state: velocities and gas pressure.
+// MUSCL_NEW.cpp:22-34 (ConservativeToPrimitive); v0,v5..v8 are copies of u.
+struct Prim {
+    double vx, vy, vz, p;
+};
+
+__device__ __forceinline__ Prim c2p(const double (&u)[NV], double gm1) {
+    Prim q;
+    q.vx = u[1] / u[0];
+    q.vy = u[2] / u[0];
+    q.vz = u[3] / u[0];
+    q.p = (u[4] - 0.5 * u[0] * (q.vx * q.vx + q.vy * q.vy + q.vz * q.vz) -
+           0.5 * (u[5] * u[5] + u[6] * u[6] + u[7] * u[7])) * gm1;
+    return q;
+}
+
+// Full primitive vector (for the limiter ratio, which differences primitives).
+__device__ __forceinline__ void c2p_full(const double (&u)[NV], double gm1, double (&v)[NV]) {
+    Prim q = c2p(u, gm1);
+    v[0] = u[0]; v[1] = q.vx; v[2] = q.vy; v[3] = q.vz; v[4] = q.p;
+    v[5] = u[5]; v[6] = u[6]; v[7] = u[7]; v[8] = u[8];
+}
+
+// Physical flux of a conserved state.  DIR 0: FluxDefX MUSCL_NEW.cpp:36-49,
+// DIR 1: FluxDefY MUSCL_NEW.cpp:51-64.  ch2 = ch*ch.
+template <int DIR>
+__device__ __forceinline__ void flux_def(const double (&u)[NV], double gm1, double ch2, double (&f)[NV]) {
+    const Prim q = c2p(u, gm1);
+    const double B2 = u[5] * u[5] + u[6] * u[6] + u[7] * u[7];
+    const double vB = q.vx * u[5] + q.vy * u[6] + q.vz * u[7];
+    if (DIR == 0) {
+        const double rvx = u[0] * q.vx;
+        f[0] = u[1];
+        f[1] = rvx * q.vx + q.p + 0.5 * B2 - u[5] * u[5];
+        f[2] = rvx * q.vy - u[5] * u[6];
+        f[3] = rvx * q.vz - u[5] * u[7];
+        f[4] = (u[4] + q.p + 0.5 * B2) * q.vx - vB * u[5];
+        f[5] = u[8];
+        f[6] = u[6] * q.vx - u[5] * q.vy;
+        f[7] = u[7] * q.vx - u[5] * q.vz;
+        f[8] = ch2 * u[5];
+    } else {
+        const double rvx = u[0] * q.vx;
+        const double rvy = u[0] * q.vy;
+        f[0] = u[2];
+        f[1] = rvx * q.vy - u[5] * u[6];
+        f[2] = rvy * q.vy + q.p + 0.5 * B2 - u[6] * u[6];
+        f[3] = rvy * q.vz - u[6] * u[7];
+        f[4] = (u[4] + q.p + 0.5 * B2) * q.vy - vB * u[6];
+        f[5] = u[5] * q.vy - u[6] * q.vx;
+        f[6] = u[8];
+        f[7] = u[7] * q.vy - u[6] * q.vz;
+        f[8] = ch2 * u[6];
+    }
+}
+
+// Slope-limited linear reconstruction of one component.  MUSCL_NEW.cpp:845-859
+// (x) and :909-923 (y).  (pm,p0,pp) are the PRIMITIVE values the limiter ratio is
+// formed from, (um,u0,up) the CONSERVED values that are reconstructed.
+//
+// xi = fmin(2r/(1+r), 2/(1+r)) is evaluated with ONE division: both quotients share
+// the positive denominator d = fl(1+r), 2.0*r is exact, and IEEE division is
+// monotone in the numerator, so the minimum is fl(2r/d) when r <= 1 and fl(2/d)
+// otherwise (equal at r == 1; for r = +inf the reference's fmin(NaN, 0) = 0 = 2/inf;
+// NaN r gives NaN both ways).
+__device__ __forceinline__ void reconstruct1(double pm, double p0, double pp, double um, double u0,
+                                             double up, double& lo, double& hi) {
+    const double r = (p0 - pm) / ((pp - p0) + 1e-8);
+    const double dPlus = up - u0;
+    const double dMinus = u0 - um;
+    double xi;
+    if (r <= 0) {
+        xi = 0;
+    } else {
+        xi = ((r <= 1.0) ? 2.0 * r : 2.0) / (1 + r);
+    }
+    const double Delta = 0.5 * dMinus + 0.5 * dPlus;
+    lo = u0 - 0.5 * xi * Delta;
+    hi = u0 + 0.5 * xi * Delta;
+}
+
+// MUSCL-Hancock predictor: both face states advanced by half a step with the flux
+// difference across the cell.  MUSCL_NEW.cpp:865-874 (x), :929-938 (y).
+// hdtdh = 0.5*(dt/dx) (or dy).  In-place on lo/hi.
+template <int DIR>
+__device__ __forceinline__ void predictor(double (&lo)[NV], double (&hi)[NV], double gm1, double ch2,
+                                          double hdtdh) {
+    double fl[NV], fh[NV];
+    flux_def<DIR>(lo, gm1, ch2, fl);
+    flux_def<DIR>(hi, gm1, ch2, fh);
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        const double d = hdtdh * (fh[k] - fl[k]);
+        lo[k] = lo[k] - d;
+        hi[k] = hi[k] - d;
+    }
+}
+
+// fast magnetosonic speed squared along DIR.  speedsx/speedsy MUSCL_NEW.cpp:140-165,
+// :197-222 -- evaluated on the ORIGINAL state (the reference ignores its B?Tilde argument).
+__device__ __forceinline__ double fast_speed_sq(double rho, double p, double B2, double Bn, double gamma) {
+    const double cs2 = gamma * p / rho;
+    const double t = cs2 + B2 / rho;
+    return 0.5 * (t + sqrt(t * t - 4.0 * cs2 * Bn * Bn / rho));
+}
+
+// HLLC flux with mixed-GLM interface values.  FluxHLLCX MUSCL_NEW.cpp:483-515 /
+// FluxHLLCY :517-549, together with everything they call:
+//   psiAndBx/psiAndBy :121-138, wavespeedx/y :167-253, uHLLx/y :255-307,
+//   uStarX :309-395, uStarY :397-481 (incl. the :442 quirk: the RIGHT star
+//   z-momentum in y is built from the LEFT quantities).
+// L is the state left/below the interface, R the one right/above.
+template <int DIR>
+__device__ __forceinline__ void hllc_flux(const double (&L)[NV], const double (&R)[NV], double gamma,
+                                          double gm1, double ch, double ch2, double (&F)[NV]) {
+    constexpr int N = (DIR == 0) ? 5 : 6;  // normal field component
+    // ---- mixed GLM interface values (:126-127 / :135-136)
+    const double BnT = 0.5 * (L[N] + R[N]) - (1.0 / (2.0 * ch)) * (R[8] - L[8]);
+    const double psiT = 0.5 * (L[8] + R[8]) - (ch / 2.0) * (R[N] - L[N]);
+
+    // ---- primitives of the ORIGINAL states
+    const Prim qL = c2p(L, gm1), qR = c2p(R, gm1);
+    const double vnL = (DIR == 0) ? qL.vx : qL.vy;
+    const double vnR = (DIR == 0) ? qR.vx : qR.vy;
+    const double B2L = L[5] * L[5] + L[6] * L[6] + L[7] * L[7];
+    const double B2R = R[5] * R[5] + R[6] * R[6] + R[7] * R[7];
+
+    // ---- wave speeds (:178-192 / :235-250)
+    const double cfL = sqrt(fast_speed_sq(L[0], qL.p, B2L, L[N], gamma));
+    const double cfR = sqrt(fast_speed_sq(R[0], qR.p, B2R, R[N], gamma));
+    const double cmax = std_max(cfL, cfR);
+    const double sL = std_min(vnL, vnR) - cmax;
+    const double sR = std_max(vnL, vnR) + cmax;
+    const double pModL = (qL.p + 0.5 * B2L) - L[N] * L[N];
+    const double pModR = (qR.p + 0.5 * B2R) - R[N] * R[N];
+    const double qS = (R[0] * vnR * (sR - vnR) - L[0] * vnL * (sL - vnL) + pModL - pModR) /
+                      (R[0] * (sR - vnR) - L[0] * (sL - vnL));
+
+    // ---- which of the four HLLC regions (:502-512 / :536-546), evaluated in the reference's order
+    const bool regA = (sL >= 0);
+    const bool regB = !regA && (sL <= 0 && qS >= 0);
+    const bool regC = !regA && !regB && (qS <= 0 && sR >= 0);
+    const bool left = regA || regB;  // flux built from the left (modified) state
+
+    // ---- the side the branch selects; modified state S1 has S1[N]=BnT, S1[8]=psiT
+    double S[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) S[k] = left ? L[k] : R[k];
+    const Prim qs = left ? qL : qR;
+    const double ss = left ? sL : sR;
+    const double vn = left ? vnL : vnR;
+    double S1[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) S1[k] = S[k];
+    S1[N] = BnT;
+    S1[8] = psiT;
+
+    // flux of the modified state: FluxDefX/Y(x1) -- velocities unchanged, pressure re-derived
+    // with the cleaned normal field (:497-498 / :531-532)
+    double FS[NV];
+    flux_def<DIR>(S1, gm1, ch2, FS);
+
+    if (!(regB || regC)) {
+#pragma unroll
+        for (int k = 0; k < NV; ++k) F[k] = FS[k];
+        return;
+    }
+
+    // ---- HLL average of the two tangential field components (uHLLx/y; only these are consumed)
+    constexpr int T1 = (DIR == 0) ? 6 : 5;  // first tangential field component
+    double fT1L, fT1R, f7L, f7R;              // physical flux components T1 and 7 of the ORIGINAL states
+    if (DIR == 0) {
+        fT1L = L[6] * qL.vx - L[5] * qL.vy;  fT1R = R[6] * qR.vx - R[5] * qR.vy;
+        f7L = L[7] * qL.vx - L[5] * qL.vz;   f7R = R[7] * qR.vx - R[5] * qR.vz;
+    } else {
+        fT1L = L[5] * qL.vy - L[6] * qL.vx;  fT1R = R[5] * qR.vy - R[6] * qR.vx;
+        f7L = L[7] * qL.vy - L[6] * qL.vz;   f7R = R[7] * qR.vy - R[6] * qR.vz;
+    }
+    double BtH, BzH;
+    if (sL >= 0) {
+        BtH = L[T1]; BzH = L[7];
+    } else if (sL < 0 && sR > 0) {
+        BtH = (sR * R[T1] - sL * L[T1] - fT1R + fT1L) / (sR - sL);
+        BzH = (sR * R[7] - sL * L[7] - f7R + f7L) / (sR - sL);
+    } else {
+        BtH = R[T1]; BzH = R[7];
+    }
+
+    // ---- star state on the selected side (uStarX / uStarY), normal field = BnT on both sides
+    const double BnS = (sR * BnT - sL * BnT) / (sR - sL);
+    const double Bt = S[T1], Bz = S[7];
+    const double vt = (DIR == 0) ? qs.vy : qs.vx;  // tangential in-plane velocity
+    const double vz = qs.vz;
+    // B2 with the cleaned normal component, summed in x,y,z order (:335-336 / :420-421)
+    const double B2s = (DIR == 0) ? (BnT * BnT + Bt * Bt + Bz * Bz) : (Bt * Bt + BnT * BnT + Bz * Bz);
+    const double pT = qs.p + 0.5 * B2s;
+    const double pStar = S[0] * (ss - vn) * (qS - vn) + pT - BnT * BnT + BnS * BnS;
+    const double rhoS = S[0] * (ss - vn) / (ss - qS);
+    const double mnS = rhoS * qS;
+    // tangential momenta (:353-357 / :437-442)
+    const double mtS = vt * rhoS - (BnS * BtH - BnT * Bt) / (ss - qS);
+    double mzS;
+    if (DIR == 1 && !left) {
+        // MUSCL_NEW.cpp:442: momzStarR = rhoStarL*u_zL - (ByStar*BzHLL - ByL*BzL)/(sL - qStar)
+        const double rhoSL = L[0] * (sL - vnL) / (sL - qS);
+        mzS = rhoSL * qL.vz - (BnS * BzH - BnT * L[7]) / (sL - qS);
+    } else {
+        mzS = vz * rhoS - (BnS * BzH - BnT * Bz) / (ss - qS);
+    }
+    // v.B of the side state (x,y,z order) and of the star state
+    double vB, vBH;
+    if (DIR == 0) {
+        vB = BnT * vn + Bt * vt + Bz * vz;
+        vBH = (BnS * mnS + BtH * mtS + BzH * mzS) / rhoS;
+    } else {
+        vB = Bt * vt + BnT * vn + Bz * vz;
+        vBH = (BtH * mtS + BnS * mnS + BzH * mzS) / rhoS;
+    }
+    const double ES = S[4] * (rhoS / S[0]) + ((pStar * qS - pT * vn) - (BnS * vBH - BnT * vB)) / (ss - qS);
+
+    double US[NV];
+    US[0] = rhoS;
+    US[(DIR == 0) ? 1 : 2] = mnS;
+    US[(DIR == 0) ? 2 : 1] = mtS;
+    US[3] = mzS;
+    US[4] = ES;
+    US[N] = BnS;
+    US[T1] = BtH;
+    US[7] = BzH;
+    US[8] = psiT;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) F[k] = FS[k] + ss * (US[k] - S1[k]);
+}
+
+// Local signal speed for the CFL condition.  ComputeTimeStep MUSCL_NEW.cpp:75-109.
+__device__ __forceinline__ double cfl_speed(const double (&q)[NV], double gamma) {
+    const double rho = q[0], Bx = q[5], By = q[6], Bz = q[7];
+    const double ux = q[1] / rho, uy = q[2] / rho, uz = q[3] / rho;
+    const double B2 = Bx * Bx + By * By + Bz * Bz;
+    const double ke = 0.5 * rho * (ux * ux + uy * uy + uz * uz) + 0.5 * B2;
+    const double p = (gamma - 1.0) * (q[4] - ke);
+    const double a = sqrt(gamma * p / rho);
+    const double a2 = a * a;
+    const double s = a2 + B2 / rho;
+    const double s2 = s * s;  // pow(s, 2)
+    const double cfx = sqrt(0.5 * (s + sqrt(s2 - 4 * a * a * Bx * Bx / rho)));
+    const double cfy = sqrt(0.5 * (s + sqrt(s2 - 4 * a * a * By * By / rho)));
+    const double cfz = sqrt(0.5 * (s + sqrt(s2 - 4 * a * a * Bz * Bz / rho)));
+    return std_max(std_max(fabs(ux) + cfx, fabs(uy) + cfy), fabs(uz) + cfz);
+}
+
+}  // namespace lsc

@@ -1,0 +1,155 @@
+"""Host-side mirror of the reference program MHD_codes/MUSCL_NEW.cpp.
+
+The reference has no callable API: its "interface" is the block of constants at
+the top of main() (MUSCL_NEW.cpp:659-671), the initial-condition block that is
+commented in (:726-819), the boundary loops that are commented in (:607-655),
+the per-step log line (:836) and the MHD<k>.dat files (:989-1001).  `MusclNew`
+exposes exactly those knobs with the committed values as defaults and drives the
+CUDA library through its C ABI; it holds no numerical code of its own.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+from . import _capi
+from ._capi import MhdConfig, check, lib
+
+_DP = ctypes.POINTER(ctypes.c_double)
+
+
+def _dp(a):
+    return a.ctypes.data_as(_DP)
+
+
+class MusclNew:
+    """2-D ideal MHD, MUSCL-Hancock + HLLC + mixed GLM, on one B200 (or one slab of a
+    multi-GPU run).  Defaults are the committed configuration of MUSCL_NEW.cpp:
+    Kelvin-Helmholtz, 128x256 on [0,1]x[-1,1], periodic-x / reflective-y, C=0.8,
+    gamma=5/3, tStop=12."""
+
+    NVAR = 9
+
+    def __init__(self, nxCells=128, nyCells=256, x0=0.0, x1=1.0, y0=-1.0, y1=1.0, tStop=12.0, C=0.8,
+                 gamma=5.0 / 3.0, bc_x="periodic", bc_y="reflective", problem="kh", device=0, rank=0, nranks=1):
+        self.tStop = float(tStop)
+        self.problem = _capi.MHD_PROBLEMS[problem] if isinstance(problem, str) else int(problem)
+        self.cfg = MhdConfig(int(nxCells), int(nyCells), float(x0), float(x1), float(y0), float(y1),
+                             float(gamma), float(C), _capi.BC_NAMES[bc_x], _capi.BC_NAMES[bc_y],
+                             int(device), int(rank), int(nranks))
+        self._h = ctypes.c_void_p()
+        check(lib().lsc_mhd_create(ctypes.byref(self.cfg), ctypes.byref(self._h)))
+        self.nxl = lib().lsc_mhd_local_nx(self._h)
+        self.i0 = lib().lsc_mhd_local_i0(self._h)
+
+    # -- lifetime ---------------------------------------------------------
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            lib().lsc_mhd_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # -- state ------------------------------------------------------------
+    @property
+    def shape(self):
+        """Host AoS shape of this rank's slab, ghosts included (MUSCL_NEW.cpp:673-674)."""
+        return (self.nxl + 4, self.cfg.ny + 4, self.NVAR)
+
+    def initial_condition(self, problem=None):
+        """The IC loop MUSCL_NEW.cpp:719-825 for this slab, as a host array."""
+        u = np.empty(self.shape, dtype=np.float64)
+        check(lib().lsc_mhd_initial_condition(self._h, self.problem if problem is None else
+                                              (_capi.MHD_PROBLEMS[problem] if isinstance(problem, str) else problem),
+                                              _dp(u)))
+        return u
+
+    def upload(self, u):
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        if u.shape != self.shape:
+            raise ValueError(f"state must have shape {self.shape}, got {u.shape}")
+        check(lib().lsc_mhd_upload(self._h, _dp(u)))
+
+    def init_problem(self, problem=None):
+        p = self.problem if problem is None else (_capi.MHD_PROBLEMS[problem] if isinstance(problem, str) else problem)
+        check(lib().lsc_mhd_init_problem(self._h, p))
+
+    def download(self, out=None):
+        u = np.empty(self.shape, dtype=np.float64) if out is None else out
+        check(lib().lsc_mhd_download(self._h, _dp(u)))
+        return u
+
+    def comm_init(self, unique_id: bytes):
+        buf = ctypes.create_string_buffer(unique_id, 128)
+        check(lib().lsc_mhd_comm_init(self._h, ctypes.cast(buf, ctypes.c_void_p)))
+
+    # -- time loop --------------------------------------------------------
+    def step(self, nsteps=1):
+        check(lib().lsc_mhd_step(self._h, int(nsteps)))
+
+    def scalars(self):
+        t, dt, ch = ctypes.c_double(), ctypes.c_double(), ctypes.c_double()
+        n = ctypes.c_long()
+        check(lib().lsc_mhd_get_scalars(self._h, ctypes.byref(t), ctypes.byref(dt), ctypes.byref(ch),
+                                        ctypes.byref(n)))
+        return t.value, dt.value, ch.value, n.value
+
+    def run(self, tStop=None, outdir=None, log=None):
+        """The do{}while loop MUSCL_NEW.cpp:831-1003 followed by the final dump :1006-1032.
+        Writes MHD<counter>.dat into `outdir` at the reference's cadence when given; `log`
+        receives (step, t, dt, ch) per step.  Returns the number of steps taken."""
+        tStop = self.tStop if tStop is None else float(tStop)
+        state = {"counter": 0}
+        buf = np.empty(self.shape, dtype=np.float64) if outdir else None
+
+        def on_dump(_ctx, counter, t, dt, _user):
+            if outdir:
+                self.download(buf)
+                self.write_dat(buf, os.path.join(outdir, f"MHD{counter}.dat"))
+            state["counter"] = counter + 1
+            return 0
+
+        def on_log(step, t, dt, ch, _user):
+            log(step, t, dt, ch)
+
+        dump_cb = _capi.DUMP_CB(on_dump)
+        log_cb = _capi.LOG_CB(on_log) if log else ctypes.cast(None, _capi.LOG_CB)
+        n = ctypes.c_long()
+        check(lib().lsc_mhd_run_until(self._h, tStop, dump_cb, log_cb, None, ctypes.byref(n)))
+        if outdir:
+            self.download(buf)
+            self.write_dat(buf, os.path.join(outdir, f"MHD{state['counter']}.dat"))
+        return n.value
+
+    def write_dat(self, u, path):
+        """MUSCL_NEW.cpp:989-1001 -- byte-compatible .dat writer (full-grid arrays only)."""
+        if self.cfg.nranks != 1:
+            raise ValueError("write_dat needs the assembled full-grid array")
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        check(lib().lsc_mhd_write_dat(ctypes.byref(self.cfg), _dp(u), os.fsencode(path)))
+
+
+def kat_hllc(L, R, gamma, ch, direction, device=0):
+    """Device HLLC flux of n interface state pairs (test hook)."""
+    L = np.ascontiguousarray(L, dtype=np.float64)
+    R = np.ascontiguousarray(R, dtype=np.float64)
+    F = np.empty_like(L)
+    check(lib().lsc_mhd_kat_hllc(device, int(direction), L.shape[0], _dp(L), _dp(R), float(gamma), float(ch), _dp(F)))
+    return F
+
+
+def kat_fluxdef(U, gamma, ch, direction, device=0):
+    U = np.ascontiguousarray(U, dtype=np.float64)
+    F = np.empty_like(U)
+    check(lib().lsc_mhd_kat_fluxdef(device, int(direction), U.shape[0], _dp(U), float(gamma), float(ch), _dp(F)))
+    return F

@@ -1,0 +1,54 @@
+#!/usr/bin/env python3
+"""Generate the committed golden fixtures from the REAL reference.
+
+Run in the build container (needs /root/reference and oracle/_ref/muscl_ref built by
+oracle/build_ref.py).  Writes
+  tests/golden/mhd_<case>.npz      final conserved state incl. ghost ring after N steps of the
+                                   reference program + its per-step (t, dt, ch) log
+  tests/golden/dat_sha256.json     sha256 of the reference's own committed output files
+                                   MHD_plot_data/MHD{0,1,2,60,121}.dat and euler_{1,20}.dat
+The GPU box has no /root/reference; the tests there read only these fixtures.
+"""
+import hashlib
+import json
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+from oracle_util import run_muscl_ref  # noqa: E402
+
+REF = "/root/reference"
+
+MHD_CASES = {
+    # name: (prob, nx, ny, domain, bcx, bcy, nsteps)
+    "ot32_s1": ("ot", 32, 32, (0.0, 1.0, 0.0, 1.0), "periodic", "periodic", 1),
+    "ot32_s10": ("ot", 32, 32, (0.0, 1.0, 0.0, 1.0), "periodic", "periodic", 10),
+    "ot64_s40": ("ot", 64, 64, (0.0, 1.0, 0.0, 1.0), "periodic", "periodic", 40),
+    "kh32x64_s10": ("kh", 32, 64, (0.0, 1.0, -1.0, 1.0), "periodic", "reflective", 10),
+    "kh48x40_s25": ("kh", 48, 40, (0.0, 1.0, -1.0, 1.0), "periodic", "reflective", 25),
+    "ot40x24_trans_s12": ("ot", 40, 24, (0.0, 1.0, 0.0, 1.0), "transmissive", "transmissive", 12),
+    "kh36x52_trans_per_s8": ("kh", 36, 52, (0.0, 1.0, -1.0, 1.0), "transmissive", "periodic", 8),
+}
+
+
+def main():
+    for name, (prob, nx, ny, dom, bcx, bcy, n) in MHD_CASES.items():
+        u, log, _ = run_muscl_ref(prob, nx, ny, dom, 1e9, 0.8, bcx, bcy, n)
+        np.savez_compressed(os.path.join(HERE, f"mhd_{name}.npz"), u=u, log=log,
+                            meta=json.dumps(dict(prob=prob, nx=nx, ny=ny, dom=dom, bcx=bcx, bcy=bcy, nsteps=n,
+                                                 cfl=0.8, gamma="5/3")))
+        print(name, u.shape, log[-1])
+    sha = {}
+    for f in ["MHD0.dat", "MHD1.dat", "MHD2.dat", "MHD60.dat", "MHD121.dat", "euler_1.dat", "euler_20.dat"]:
+        with open(os.path.join(REF, "MHD_plot_data", f), "rb") as fh:
+            sha[f] = hashlib.sha256(fh.read()).hexdigest()
+    with open(os.path.join(HERE, "dat_sha256.json"), "w") as fh:
+        json.dump(sha, fh, indent=1, sort_keys=True)
+    print(sha)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,54 @@
+"""CPU tests of the C-ABI library: it loads, exports every symbol include/lsc_b200.h declares,
+and refuses to run without a GPU (no CPU fallback)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+import lsc_internship_b200 as lsc
+from lsc_internship_b200 import _capi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def header_symbols():
+    src = open(os.path.join(ROOT, "include", "lsc_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(lsc_[a-z0-9_]+)\s*\(", src)) - {"lsc_mhd_dump_cb", "lsc_mhd_log_cb"})
+
+
+def test_library_exports_every_declared_symbol():
+    L = lsc.lib()
+    syms = header_symbols()
+    assert len(syms) >= 20
+    for s in syms:
+        assert hasattr(L, s), f"{s} declared in include/lsc_b200.h but not exported"
+    assert set(syms) == set(_capi.EXPORTS)
+
+
+def test_config_struct_layout():
+    assert ctypes.sizeof(_capi.MhdConfig) == 4 + 4 + 6 * 8 + 5 * 4 + 4  # trailing pad to 8
+
+
+def test_no_cpu_fallback_or_bad_config():
+    L = lsc.lib()
+    if L.lsc_device_count() == 0:
+        with pytest.raises(lsc.LscError) as e:
+            lsc.MusclNew(nxCells=16, nyCells=16)
+        assert e.value.code == -2
+    else:
+        with pytest.raises(lsc.LscError) as e:
+            lsc.MusclNew(nxCells=2, nyCells=16)
+        assert e.value.code == -1
+
+
+def test_product_package_does_not_touch_oracle():
+    """The product path must not import, link or execute anything under oracle/."""
+    pkg = os.path.join(ROOT, "lsc_internship_b200")
+    for dp, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")) or f == "Makefile":
+                txt = open(os.path.join(dp, f), errors="replace").read()
+                assert not re.search(r"liblsc_oracle|oracle_util|oracle/|lsc_oracle_|import oracle", txt), \
+                    f"{f} reaches into oracle/"
