@@ -112,6 +112,16 @@ int lsc_mhd_step(lsc_mhd_ctx* ctx, long nsteps);
 int lsc_mhd_run_until(lsc_mhd_ctx* ctx, double t_stop, lsc_mhd_dump_cb dump_cb, lsc_mhd_log_cb log_cb,
                       void* user, long* steps_out);
 
+/* As lsc_mhd_step, bracketed by CUDA events on the context's own stream; *ms receives the device
+ * time of the whole call (kernels, the per-step 8-byte readback of the signal speed, ghost/halo fill). */
+int lsc_mhd_step_timed(lsc_mhd_ctx* ctx, long nsteps, float* ms);
+
+/* Per-kernel device timing for roofline reporting: when enabled, every x-sweep and y-sweep launch is
+ * bracketed by CUDA events on the launching stream.  lsc_mhd_kernel_times sums and clears them:
+ * ms[0] = x sweeps, ms[1] = y sweeps, launches[0..1] = how many of each. */
+int lsc_mhd_set_profiling(lsc_mhd_ctx* ctx, int enabled);
+int lsc_mhd_kernel_times(lsc_mhd_ctx* ctx, double ms[2], long launches[2]);
+
 /* t, the last dt, the last ch (= max signal speed, M:834) and the step count. Any may be NULL. */
 int lsc_mhd_get_scalars(const lsc_mhd_ctx* ctx, double* t, double* dt, double* ch, long* step);
 

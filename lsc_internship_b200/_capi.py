@@ -48,7 +48,7 @@ EXPORTS = [
     "lsc_mhd_initial_condition", "lsc_mhd_upload", "lsc_mhd_init_problem", "lsc_mhd_step",
     "lsc_mhd_run_until", "lsc_mhd_get_scalars", "lsc_mhd_download", "lsc_mhd_write_dat",
     "lsc_comm_unique_id", "lsc_mhd_comm_init", "lsc_mhd_kat_hllc", "lsc_mhd_kat_fluxdef",
-    "lsc_kernel_launch_count",
+    "lsc_kernel_launch_count", "lsc_mhd_step_timed", "lsc_mhd_set_profiling", "lsc_mhd_kernel_times",
 ]
 
 _lib = None
@@ -77,6 +77,9 @@ def lib():
     L.lsc_mhd_upload.argtypes = [vp, dp]
     L.lsc_mhd_init_problem.argtypes = [vp, ctypes.c_int]
     L.lsc_mhd_step.argtypes = [vp, ctypes.c_long]
+    L.lsc_mhd_step_timed.argtypes = [vp, ctypes.c_long, ctypes.POINTER(ctypes.c_float)]
+    L.lsc_mhd_set_profiling.argtypes = [vp, ctypes.c_int]
+    L.lsc_mhd_kernel_times.argtypes = [vp, dp, ctypes.POINTER(ctypes.c_long)]
     L.lsc_mhd_run_until.argtypes = [vp, ctypes.c_double, DUMP_CB, LOG_CB, vp, ctypes.POINTER(ctypes.c_long)]
     L.lsc_mhd_get_scalars.argtypes = [vp, dp, dp, dp, ctypes.POINTER(ctypes.c_long)]
     L.lsc_mhd_download.argtypes = [vp, dp]

@@ -65,6 +65,8 @@ struct lsc_mhd_ctx {
     bool uploaded = false;
     bool ghosts_current = false;  // x ghost/halo columns of state[cur] hold boundary images
     lsc::Comm* comm = nullptr;
+    bool profiling = false;
+    std::vector<cudaEvent_t> prof_events;  // quadruples: x begin, x end, y begin, y end
 };
 
 extern "C" {
@@ -318,14 +320,25 @@ int step_once(lsc_mhd_ctx* c) {
     p.bc_lo = (c->cfg.rank == 0) ? to_kernel_bc(c->cfg.bc_x) : -1;
     p.bc_hi = (c->cfg.rank == c->cfg.nranks - 1) ? to_kernel_bc(c->cfg.bc_x) : -1;
     if (c->cfg.nranks > 1 && c->cfg.bc_x == LSC_BC_PERIODIC) p.bc_lo = p.bc_hi = -1;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    if (c->profiling) {
+        for (auto& e : ev) CUDA_TRY(cudaEventCreate(&e));
+        CUDA_TRY(cudaEventRecord(ev[0], c->stream));
+    }
     lsc::launch_x_sweep(c->g, p, c->state[c->cur], c->state[c->prev], c->state[c->bar], c->stream);
+    if (c->profiling) CUDA_TRY(cudaEventRecord(ev[1], c->stream));
 
     // ---- y sweep (:905-965) + copy (:969) + next step's signal speed (:71-115)
     CUDA_TRY(cudaMemsetAsync(c->d_max, 0, sizeof(unsigned long long), c->stream));
     p.dtdh = dt / c->dy;
     p.hdtdh = 0.5 * (dt / c->dy);
     p.bc_lo = p.bc_hi = to_kernel_bc(c->cfg.bc_y);
+    if (c->profiling) CUDA_TRY(cudaEventRecord(ev[2], c->stream));
     lsc::launch_y_sweep(c->g, p, c->state[c->bar], c->state[c->cur], c->state[c->prev], c->d_max, c->stream);
+    if (c->profiling) {
+        CUDA_TRY(cudaEventRecord(ev[3], c->stream));
+        for (auto e : ev) c->prof_events.push_back(e);
+    }
     lsc_count_launches(2);
     CUDA_TRY(cudaGetLastError());
 
@@ -353,6 +366,53 @@ int lsc_mhd_step(lsc_mhd_ctx* c, long nsteps) {
         if (rc) return rc;
     }
     CUDA_TRY(cudaStreamSynchronize(c->stream));
+    return LSC_OK;
+}
+
+int lsc_mhd_step_timed(lsc_mhd_ctx* c, long nsteps, float* ms) {
+    if (!c || !ms) return fail(LSC_EINVAL, "null argument");
+    if (!c->uploaded) return fail(LSC_ESTATE, "lsc_mhd_step_timed before lsc_mhd_upload");
+    CUDA_TRY(cudaSetDevice(c->cfg.device));
+    cudaEvent_t e0, e1;
+    CUDA_TRY(cudaEventCreate(&e0));
+    CUDA_TRY(cudaEventCreate(&e1));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    CUDA_TRY(cudaEventRecord(e0, c->stream));
+    int rc = LSC_OK;
+    for (long s = 0; s < nsteps && rc == LSC_OK; ++s) rc = step_once(c);
+    if (rc == LSC_OK) {
+        CUDA_TRY(cudaEventRecord(e1, c->stream));
+        CUDA_TRY(cudaEventSynchronize(e1));
+        CUDA_TRY(cudaEventElapsedTime(ms, e0, e1));
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    return rc;
+}
+
+int lsc_mhd_set_profiling(lsc_mhd_ctx* c, int enabled) {
+    if (!c) return fail(LSC_EINVAL, "null argument");
+    c->profiling = enabled != 0;
+    return LSC_OK;
+}
+
+int lsc_mhd_kernel_times(lsc_mhd_ctx* c, double ms[2], long launches[2]) {
+    if (!c || !ms || !launches) return fail(LSC_EINVAL, "null argument");
+    CUDA_TRY(cudaSetDevice(c->cfg.device));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    ms[0] = ms[1] = 0;
+    launches[0] = launches[1] = 0;
+    for (size_t q = 0; q + 3 < c->prof_events.size(); q += 4) {
+        float a = 0, b = 0;
+        CUDA_TRY(cudaEventElapsedTime(&a, c->prof_events[q], c->prof_events[q + 1]));
+        CUDA_TRY(cudaEventElapsedTime(&b, c->prof_events[q + 2], c->prof_events[q + 3]));
+        ms[0] += a;
+        ms[1] += b;
+        launches[0] += 1;
+        launches[1] += 1;
+    }
+    for (auto e : c->prof_events) cudaEventDestroy(e);
+    c->prof_events.clear();
     return LSC_OK;
 }
 

@@ -97,6 +97,22 @@ class MusclNew:
     def step(self, nsteps=1):
         check(lib().lsc_mhd_step(self._h, int(nsteps)))
 
+    def step_timed(self, nsteps=1):
+        """step(nsteps) bracketed by CUDA events on the solver's stream; returns device milliseconds."""
+        ms = ctypes.c_float()
+        check(lib().lsc_mhd_step_timed(self._h, int(nsteps), ctypes.byref(ms)))
+        return ms.value
+
+    def set_profiling(self, enabled=True):
+        check(lib().lsc_mhd_set_profiling(self._h, 1 if enabled else 0))
+
+    def kernel_times(self):
+        """(ms_x_sweeps, ms_y_sweeps, n_x, n_y) accumulated since the last call (profiling mode)."""
+        ms = (ctypes.c_double * 2)()
+        n = (ctypes.c_long * 2)()
+        check(lib().lsc_mhd_kernel_times(self._h, ms, n))
+        return ms[0], ms[1], n[0], n[1]
+
     def scalars(self):
         t, dt, ch = ctypes.c_double(), ctypes.c_double(), ctypes.c_double()
         n = ctypes.c_long()
