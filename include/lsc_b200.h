@@ -148,6 +148,13 @@ int lsc_mhd_kat_hllc(int device, int dir, long n, const double* L, const double*
                      double* F);
 int lsc_mhd_kat_fluxdef(int device, int dir, long n, const double* U, double gamma, double ch, double* F);
 
+/* Test hook for the shared-reciprocal fp64 division used by the kernels (csrc/fp64_div.cuh): divides
+ * nblocks*256*per_thread pseudo-random operand pairs both ways on the device and counts quotients that
+ * differ bitwise from the compiler's IEEE `/` (must be 0) and pairs the guard flagged for the slow path.
+ * mode 0: solver-range operands, 1: arbitrary bit patterns, 2: half-ulp / all-ones-mantissa adversaries. */
+int lsc_kat_division(int device, unsigned long long seed, int mode, long nblocks, int per_thread,
+                     unsigned long long* mismatches, unsigned long long* flagged);
+
 /* number of kernels this library has launched in this process (for bench.py's gpu_launches) */
 unsigned long long lsc_kernel_launch_count(void);
 

@@ -9,7 +9,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "_lib", "liblsc_b200.so")
+# LSC_B200_LIB selects an alternative build of the SAME library (kernel tuning experiments)
+LIB_PATH = os.environ.get("LSC_B200_LIB") or os.path.join(_HERE, "_lib", "liblsc_b200.so")
 
 LSC_OK = 0
 BC_PERIODIC, BC_REFLECTIVE, BC_TRANSMISSIVE, BC_TRANSMISSIVE_E = 0, 1, 2, 3
@@ -48,7 +49,7 @@ EXPORTS = [
     "lsc_mhd_initial_condition", "lsc_mhd_upload", "lsc_mhd_init_problem", "lsc_mhd_step",
     "lsc_mhd_run_until", "lsc_mhd_get_scalars", "lsc_mhd_download", "lsc_mhd_write_dat",
     "lsc_comm_unique_id", "lsc_mhd_comm_init", "lsc_mhd_kat_hllc", "lsc_mhd_kat_fluxdef",
-    "lsc_kernel_launch_count", "lsc_mhd_step_timed", "lsc_mhd_set_profiling", "lsc_mhd_kernel_times",
+    "lsc_kernel_launch_count", "lsc_mhd_step_timed", "lsc_mhd_set_profiling", "lsc_mhd_kernel_times", "lsc_kat_division",
 ]
 
 _lib = None
@@ -90,6 +91,8 @@ def lib():
                                    ctypes.c_double, dp]
     L.lsc_mhd_kat_fluxdef.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_long, dp, ctypes.c_double,
                                       ctypes.c_double, dp]
+    L.lsc_kat_division.argtypes = [ctypes.c_int, ctypes.c_ulonglong, ctypes.c_int, ctypes.c_long, ctypes.c_int,
+                                   ctypes.POINTER(ctypes.c_ulonglong), ctypes.POINTER(ctypes.c_ulonglong)]
     _lib = L
     return L
 

@@ -311,6 +311,8 @@ int step_once(lsc_mhd_ctx* c) {
     p.gm1 = c->cfg.gamma - 1;
     p.ch = ch;
     p.ch2 = ch * ch;
+    p.inv2ch = 1.0 / (2.0 * ch);
+    p.halfch = ch / 2.0;
     p.psi_factor = std::exp(-1.0 * (0.5 * dt) * ch / 0.18);  // psiUpdate(psi, maxSpeed, 0.5*dt), :66-69, :900
     p.first_step = (c->step == 0) ? 1 : 0;
 

@@ -20,7 +20,12 @@ __global__ void kat_hllc_kernel(long n, const double* __restrict__ L, const doub
         l[k] = L[t * NV + k];
         r[k] = R[t * NV + k];
     }
-    hllc_flux<DIR>(l, r, gamma, gamma - 1, ch, ch * ch, f);
+    FastDiv dv;
+    hllc_flux<DIR>(dv, l, r, gamma, gamma - 1, ch, ch * ch, 1.0 / (2.0 * ch), ch / 2.0, f);
+    if (dv.bad) {
+        IeeeDiv sv;
+        hllc_flux<DIR>(sv, l, r, gamma, gamma - 1, ch, ch * ch, 1.0 / (2.0 * ch), ch / 2.0, f);
+    }
 #pragma unroll
     for (int k = 0; k < NV; ++k) F[t * NV + k] = f[k];
 }
@@ -33,9 +38,65 @@ __global__ void kat_fluxdef_kernel(long n, const double* __restrict__ U, double 
     double u[NV], f[NV];
 #pragma unroll
     for (int k = 0; k < NV; ++k) u[k] = U[t * NV + k];
-    flux_def<DIR>(u, gamma - 1, ch * ch, f);
+    FastDiv dv;
+    flux_def<DIR>(dv, u, gamma - 1, ch * ch, f);
+    if (dv.bad) {
+        IeeeDiv sv;
+        flux_def<DIR>(sv, u, gamma - 1, ch * ch, f);
+    }
 #pragma unroll
     for (int k = 0; k < NV; ++k) F[t * NV + k] = f[k];
+}
+
+// ---- the shared-reciprocal division (fp64_div.cuh) against the compiler's IEEE operator ----
+__device__ __forceinline__ unsigned long long mix64(unsigned long long z) {
+    z += 0x9e3779b97f4a7c15ull;
+    z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+    z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+    return z ^ (z >> 31);
+}
+
+// mode 0: random mantissas, exponents within +-40 of 1 (the solver's regime)
+// mode 1: fully random bit patterns (all exponents, NaN/inf/denormals): flag must catch what is unsafe
+// mode 2: divisor mantissa all ones / dividends one ulp around exact multiples (half-ulp ties)
+__global__ void kat_div_kernel(unsigned long long seed, int mode, int per_thread, unsigned long long* mismatches,
+                               unsigned long long* flagged) {
+    const unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long bad = 0, flg = 0;
+    for (int it = 0; it < per_thread; ++it) {
+        const unsigned long long ra = mix64(seed + 2 * (t * per_thread + it));
+        const unsigned long long rb = mix64(seed + 2 * (t * per_thread + it) + 1);
+        double a, b;
+        if (mode == 1) {
+            a = __longlong_as_double((long long)ra);
+            b = __longlong_as_double((long long)rb);
+        } else {
+            const unsigned long long ea = 1023 - 40 + (ra >> 52) % 81, eb = 1023 - 40 + (rb >> 52) % 81;
+            unsigned long long ma = ra & 0xfffffffffffffull, mb = rb & 0xfffffffffffffull;
+            if (mode == 2) {
+                mb |= 0xffffffffff000ull;                   // divisor just below a power of two
+                if (it & 1) ma = (ma & 0xfff) | 0xffffffffff000ull;
+            }
+            a = __longlong_as_double((long long)(((ra >> 63) << 63) | (ea << 52) | ma));
+            b = __longlong_as_double((long long)(((rb >> 63) << 63) | (eb << 52) | mb));
+            if (mode == 2 && (it & 2)) {                   // a := (small integer k) * b +- 1 ulp
+                const double k = (double)(1 + (ra & 1023));
+                a = __longlong_as_double(__double_as_longlong(k * b) + ((ra >> 20) & 1 ? 1 : -1));
+            }
+            if (mode == 0 && (it % 17) == 0) a = 0.0;      // exact zero dividends are common in the solver
+        }
+        FastDiv dv;
+        const Rcp r = dv.rcp(b);
+        const double q = dv.div(a, r);
+        const double ref = a / b;
+        if (dv.bad) {
+            ++flg;
+        } else if (__double_as_longlong(q) != __double_as_longlong(ref)) {
+            ++bad;
+        }
+    }
+    atomicAdd(mismatches, bad);
+    atomicAdd(flagged, flg);
 }
 
 static int run_kat(int device, int dir, long n, const double* a, const double* b, double gamma, double ch,
@@ -74,6 +135,27 @@ static int run_kat(int device, int dir, long n, const double* a, const double* b
 }
 
 }  // namespace lsc
+
+extern "C" int lsc_kat_division(int device, unsigned long long seed, int mode, long nblocks, int per_thread,
+                                unsigned long long* mismatches, unsigned long long* flagged) {
+    if (!mismatches || !flagged || nblocks <= 0 || per_thread <= 0) return LSC_EINVAL;
+    if (cudaSetDevice(device) != cudaSuccess) return LSC_ECUDA;
+    unsigned long long* d = nullptr;
+    if (cudaMalloc(&d, 16) != cudaSuccess) return LSC_ENOMEM;
+    cudaMemset(d, 0, 16);
+    lsc::kat_div_kernel<<<(unsigned)nblocks, 256>>>(seed, mode, per_thread, d, d + 1);
+    lsc_count_launches(1);
+    unsigned long long h[2] = {0, 0};
+    int rc = LSC_OK;
+    if (cudaDeviceSynchronize() != cudaSuccess || cudaMemcpy(h, d, 16, cudaMemcpyDeviceToHost) != cudaSuccess) {
+        cudaGetLastError();
+        rc = LSC_ECUDA;
+    }
+    cudaFree(d);
+    *mismatches = h[0];
+    *flagged = h[1];
+    return rc;
+}
 
 extern "C" int lsc_mhd_kat_hllc(int device, int dir, long n, const double* L, const double* R, double gamma,
                                 double ch, double* F) {

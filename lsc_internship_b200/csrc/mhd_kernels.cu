@@ -57,36 +57,90 @@ __device__ __forceinline__ void block_max_to_global(double local, unsigned long 
 // -> psi damping never leave the register file.
 // ------------------------------------------------------------------------------------
 
-// Half-step face states of cell i computed straight from global memory (strip warm-up and
-// the non-periodic boundary images, MUSCL_NEW.cpp:878-879).
+// Half-step face states of cell i computed straight from global memory (strip warm-up, the
+// non-periodic boundary images of MUSCL_NEW.cpp:878-879, and -- with D = IeeeDiv -- the fallback
+// when a fast division flagged an out-of-window operand).
+template <class D>
 __device__ __noinline__ void x_halfstates_global(const GridDims g, const SweepParams p,
                                                  const double* __restrict__ cur,
                                                  const double* __restrict__ prev, int i, int j,
-                                                 double (&hL)[NV], double (&hR)[NV]) {
+                                                 double (&hL)[NV], double (&hR)[NV], bool& bad) {
+    D dv;
     double um[NV], u0[NV], up[NV], pm[NV], p0[NV], pp[NV];
     load_cell(cur, g.plane, cell_index(g, i - 1, j), um);
     load_cell(cur, g.plane, cell_index(g, i, j), u0);
     load_cell(cur, g.plane, cell_index(g, i + 1, j), up);
-    c2p_full(um, p.gm1, pm);
-    c2p_full(u0, p.gm1, p0);
+    c2p_full(dv, um, p.gm1, pm);
+    c2p_full(dv, u0, p.gm1, p0);
     if (p.first_step) {
 #pragma unroll
         for (int k = 0; k < NV; ++k) pp[k] = 0.0;
     } else {
         double q[NV];
         load_cell(prev, g.plane, cell_index(g, i + 1, j), q);
-        c2p_full(q, p.gm1, pp);
+        c2p_full(dv, q, p.gm1, pp);
     }
 #pragma unroll
-    for (int k = 0; k < NV; ++k) reconstruct1(pm[k], p0[k], pp[k], um[k], u0[k], up[k], hL[k], hR[k]);
-    predictor<0>(hL, hR, p.gm1, p.ch2, p.hdtdh);
+    for (int k = 0; k < NV; ++k) reconstruct1(dv, pm[k], p0[k], pp[k], um[k], u0[k], up[k], hL[k], hR[k]);
+    predictor<0>(dv, hL, hR, p.gm1, p.ch2, p.hdtdh);
+    bad = dv.bad;
 }
 
+__device__ __forceinline__ void x_halfstates_checked(const GridDims& g, const SweepParams& p, const double* cur,
+                                                     const double* prev, int i, int j, double (&hL)[NV],
+                                                     double (&hR)[NV]) {
+    bool bad;
+    x_halfstates_global<FastDiv>(g, p, cur, prev, i, j, hL, hR, bad);
+    if (bad) x_halfstates_global<IeeeDiv>(g, p, cur, prev, i, j, hL, hR, bad);
+}
+
+template <int DIR>
+__device__ __noinline__ void hllc_flux_ieee(const double (&L)[NV], const double (&R)[NV], const SweepParams p,
+                                            double (&F)[NV]) {
+    IeeeDiv dv;
+    hllc_flux<DIR>(dv, L, R, p.gamma, p.gm1, p.ch, p.ch2, p.inv2ch, p.halfch, F);
+}
+
+template <int DIR>
+__device__ __forceinline__ void hllc_flux_checked(const double (&L)[NV], const double (&R)[NV], const SweepParams& p,
+                                                  double (&F)[NV]) {
+    FastDiv dv;
+    hllc_flux<DIR>(dv, L, R, p.gamma, p.gm1, p.ch, p.ch2, p.inv2ch, p.halfch, F);
+    if (dv.bad) hllc_flux_ieee<DIR>(L, R, p, F);
+}
+
+__device__ __noinline__ void c2p_full_ieee(const double (&u)[NV], double gm1, double (&v)[NV]) {
+    IeeeDiv dv;
+    c2p_full(dv, u, gm1, v);
+}
+
+__device__ __forceinline__ void c2p_full_checked(const double (&u)[NV], double gm1, double (&v)[NV]) {
+    FastDiv dv;
+    c2p_full(dv, u, gm1, v);
+    if (dv.bad) c2p_full_ieee(u, gm1, v);
+}
+
+#ifndef XS_BLOCK
+#define XS_BLOCK 128
+#endif
+#ifndef XS_MINB
+#define XS_MINB 1
+#endif
+#ifndef XS_STRIP
+#define XS_STRIP 64
+#endif
+#ifndef YS_MINB
+#define YS_MINB 1
+#endif
+#ifndef YS_BJ
+#define YS_BJ 128
+#endif
+
 template <int STRIP>
-__global__ void __launch_bounds__(128) x_sweep_kernel(const GridDims g, const SweepParams p,
-                                                      const double* __restrict__ cur,
-                                                      const double* __restrict__ prev,
-                                                      double* __restrict__ ubar) {
+__global__ void __launch_bounds__(XS_BLOCK, XS_MINB) x_sweep_kernel(const GridDims g, const SweepParams p,
+                                                                    const double* __restrict__ cur,
+                                                                    const double* __restrict__ prev,
+                                                                    double* __restrict__ ubar) {
     const int j = 2 + blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= g.ny + 2) return;
     const int ia = 2 + blockIdx.y * STRIP;
@@ -99,20 +153,21 @@ __global__ void __launch_bounds__(128) x_sweep_kernel(const GridDims g, const Sw
         // face state R of cell ia-1; at a transmissive wall ghost cell 1 carries the half state of
         // cell 3 (u[1] = u[3] applied to the half-step arrays, MUSCL_NEW.cpp:617-622, :878-879)
         double hL[NV];
-        x_halfstates_global(g, p, cur, prev, lo_image ? 3 : ia - 1, j, hL, hRprev);
+        x_halfstates_checked(g, p, cur, prev, lo_image ? 3 : ia - 1, j, hL, hRprev);
     }
     double uM[NV], u0[NV], uP[NV], PM[NV], P0[NV];
     load_cell(cur, g.plane, cell_index(g, ia - 1, j), uM);
     load_cell(cur, g.plane, cell_index(g, ia, j), u0);
     load_cell(cur, g.plane, cell_index(g, ia + 1, j), uP);
-    c2p_full(uM, p.gm1, PM);
-    c2p_full(u0, p.gm1, P0);
+    c2p_full_checked(uM, p.gm1, PM);
+    c2p_full_checked(u0, p.gm1, P0);
 
     for (int c = ia; c <= ib; ++c) {
         double hL[NV], hR[NV];
         if (c == ib && hi_image) {
-            x_halfstates_global(g, p, cur, prev, g.nxl, j, hL, hR);  // u[nx+2] = u[nx]
+            x_halfstates_checked(g, p, cur, prev, g.nxl, j, hL, hR);  // u[nx+2] = u[nx]
         } else {
+            FastDiv dv;
             double Pp[NV];
             if (p.first_step) {
 #pragma unroll
@@ -120,14 +175,19 @@ __global__ void __launch_bounds__(128) x_sweep_kernel(const GridDims g, const Sw
             } else {
                 double q[NV];
                 load_cell(prev, g.plane, cell_index(g, c + 1, j), q);
-                c2p_full(q, p.gm1, Pp);
+                c2p_full(dv, q, p.gm1, Pp);
             }
 #pragma unroll
-            for (int k = 0; k < NV; ++k) reconstruct1(PM[k], P0[k], Pp[k], uM[k], u0[k], uP[k], hL[k], hR[k]);
-            predictor<0>(hL, hR, p.gm1, p.ch2, p.hdtdh);
+            for (int k = 0; k < NV; ++k)
+                reconstruct1(dv, PM[k], P0[k], Pp[k], uM[k], u0[k], uP[k], hL[k], hR[k]);
+            predictor<0>(dv, hL, hR, p.gm1, p.ch2, p.hdtdh);
+            if (dv.bad) {
+                bool b2;
+                x_halfstates_global<IeeeDiv>(g, p, cur, prev, c, j, hL, hR, b2);
+            }
         }
         double F[NV];
-        hllc_flux<0>(hRprev, hL, p.gamma, p.gm1, p.ch, p.ch2, F);  // interface c-1/2 (MUSCL_NEW.cpp:884)
+        hllc_flux_checked<0>(hRprev, hL, p, F);  // interface c-1/2 (MUSCL_NEW.cpp:884)
         if (c > ia) {
             // uBar[c-1] = u[c-1] - (dt/dx)(F[c-1/2] - F[c-3/2])   MUSCL_NEW.cpp:891; psi damping :900
             const size_t o = cell_index(g, c - 1, j);
@@ -147,7 +207,7 @@ __global__ void __launch_bounds__(128) x_sweep_kernel(const GridDims g, const Sw
             PM[k] = P0[k];
         }
         if (c < ib) {
-            c2p_full(u0, p.gm1, P0);
+            c2p_full_checked(u0, p.gm1, P0);
             load_cell(cur, g.plane, cell_index(g, c + 2, j), uP);
         }
     }
@@ -155,8 +215,8 @@ __global__ void __launch_bounds__(128) x_sweep_kernel(const GridDims g, const Sw
 
 void launch_x_sweep(const GridDims& g, const SweepParams& p, const double* u_cur, const double* u_prev,
                     double* u_bar, cudaStream_t s) {
-    constexpr int STRIP = 64;
-    dim3 block(128);
+    constexpr int STRIP = XS_STRIP;
+    dim3 block(XS_BLOCK);
     dim3 grid((g.ny + block.x - 1) / block.x, (g.nxl + STRIP - 1) / STRIP);
     x_sweep_kernel<STRIP><<<grid, block, 0, s>>>(g, p, u_cur, u_prev, u_bar);
 }
@@ -166,7 +226,7 @@ void launch_x_sweep(const GridDims& g, const SweepParams& p, const double* u_cur
 // jo-1 .. jo+BJ-2 of one column; face states and interface fluxes are exchanged between
 // neighbouring threads through shared memory, so a block produces BJ-2 updated cells.
 // ------------------------------------------------------------------------------------
-constexpr int BJ = 128;
+constexpr int BJ = YS_BJ;
 
 // Which stored cell a (possibly ghost) row index refers to, and whether the reflective sign
 // applies (MUSCL_NEW.cpp:625-654).  Interior rows map to themselves.
@@ -190,26 +250,40 @@ __device__ __forceinline__ void load_row_cell(const double* __restrict__ base, c
 }
 
 // Half-step face states (bottom, top) of cell j of column i straight from global memory.
+template <class D>
 __device__ __noinline__ void y_halfstates_global(const GridDims g, const SweepParams p,
                                                  const double* __restrict__ ubar,
                                                  const double* __restrict__ cur, int i, int j,
-                                                 double (&hB)[NV], double (&hT)[NV]) {
+                                                 double (&hB)[NV], double (&hT)[NV], bool& bad) {
+    D dv;
     double um[NV], u0[NV], up[NV], q[NV], pm[NV], p0[NV], pp[NV];
     load_row_cell(ubar, g, i, j - 1, p.bc_lo, um);
     load_row_cell(ubar, g, i, j, p.bc_lo, u0);
     load_row_cell(ubar, g, i, j + 1, p.bc_lo, up);
     load_row_cell(cur, g, i, j - 1, p.bc_lo, q);
-    c2p_full(q, p.gm1, pm);
+    c2p_full(dv, q, p.gm1, pm);
     load_row_cell(cur, g, i, j, p.bc_lo, q);
-    c2p_full(q, p.gm1, p0);
+    c2p_full(dv, q, p.gm1, p0);
     load_row_cell(cur, g, i, j + 1, p.bc_lo, q);
-    c2p_full(q, p.gm1, pp);
+    c2p_full(dv, q, p.gm1, pp);
 #pragma unroll
-    for (int k = 0; k < NV; ++k) reconstruct1(pm[k], p0[k], pp[k], um[k], u0[k], up[k], hB[k], hT[k]);
-    predictor<1>(hB, hT, p.gm1, p.ch2, p.hdtdh);
+    for (int k = 0; k < NV; ++k) reconstruct1(dv, pm[k], p0[k], pp[k], um[k], u0[k], up[k], hB[k], hT[k]);
+    predictor<1>(dv, hB, hT, p.gm1, p.ch2, p.hdtdh);
+    bad = dv.bad;
 }
 
-__global__ void __launch_bounds__(BJ) y_sweep_kernel(const GridDims g, const SweepParams p,
+__device__ __noinline__ double cfl_speed_ieee(const double (&q)[NV], double gamma) {
+    IeeeDiv dv;
+    return cfl_speed(dv, q, gamma);
+}
+
+__device__ __forceinline__ double cfl_speed_checked(const double (&q)[NV], double gamma) {
+    FastDiv dv;
+    const double s = cfl_speed(dv, q, gamma);
+    return dv.bad ? cfl_speed_ieee(q, gamma) : s;
+}
+
+__global__ void __launch_bounds__(BJ, YS_MINB) y_sweep_kernel(const GridDims g, const SweepParams p,
                                                      const double* __restrict__ ubar,
                                                      const double* __restrict__ cur,
                                                      double* __restrict__ next,
@@ -232,7 +306,7 @@ __global__ void __launch_bounds__(BJ) y_sweep_kernel(const GridDims g, const Swe
 #pragma unroll
             for (int k = 0; k < NV; ++k) sU[k][t] = q[k];
             load_row_cell(cur, g, i, jt, bc, q);
-            c2p_full(q, p.gm1, v);
+            c2p_full_checked(q, p.gm1, v);
 #pragma unroll
             for (int k = 0; k < NV; ++k) sP[k][t] = v[k];
         }
@@ -246,7 +320,8 @@ __global__ void __launch_bounds__(BJ) y_sweep_kernel(const GridDims g, const Swe
         if (image) {
             // ghost face states are the (sign-flipped) face states of cell 3 / ny: the reference
             // applies its boundary function to the half-step arrays (MUSCL_NEW.cpp:940-941)
-            y_halfstates_global(g, p, ubar, cur, i, (c == 1) ? 3 : g.ny, hB, hT);
+            bool b2;
+            y_halfstates_global<IeeeDiv>(g, p, ubar, cur, i, (c == 1) ? 3 : g.ny, hB, hT, b2);
             if (bc == BC_REFLECTIVE) {
                 hB[2] = -hB[2]; hB[6] = -hB[6];
                 hT[2] = -hT[2]; hT[6] = -hT[6];
@@ -255,12 +330,18 @@ __global__ void __launch_bounds__(BJ) y_sweep_kernel(const GridDims g, const Swe
             for (int k = 0; k < NV; ++k) ub[k] = 0.0;
         } else {
             const int t = tid + 1;
+            FastDiv dv;
 #pragma unroll
             for (int k = 0; k < NV; ++k) {
                 ub[k] = sU[k][t];
-                reconstruct1(sP[k][t - 1], sP[k][t], sP[k][t + 1], sU[k][t - 1], ub[k], sU[k][t + 1], hB[k], hT[k]);
+                reconstruct1(dv, sP[k][t - 1], sP[k][t], sP[k][t + 1], sU[k][t - 1], ub[k], sU[k][t + 1], hB[k],
+                             hT[k]);
             }
-            predictor<1>(hB, hT, p.gm1, p.ch2, p.hdtdh);
+            predictor<1>(dv, hB, hT, p.gm1, p.ch2, p.hdtdh);
+            if (dv.bad) {
+                bool b2;
+                y_halfstates_global<IeeeDiv>(g, p, ubar, cur, i, c, hB, hT, b2);
+            }
         }
 #pragma unroll
         for (int k = 0; k < NV; ++k) sH[k][tid] = hB[k];
@@ -274,7 +355,7 @@ __global__ void __launch_bounds__(BJ) y_sweep_kernel(const GridDims g, const Swe
         double nb[NV];
 #pragma unroll
         for (int k = 0; k < NV; ++k) nb[k] = sH[k][tid + 1];
-        hllc_flux<1>(hT, nb, p.gamma, p.gm1, p.ch, p.ch2, F);
+        hllc_flux_checked<1>(hT, nb, p, F);
 #pragma unroll
         for (int k = 0; k < NV; ++k) sP[k][tid] = F[k];
     }
@@ -292,7 +373,7 @@ __global__ void __launch_bounds__(BJ) y_sweep_kernel(const GridDims g, const Swe
             un[k] = v;
             next[(size_t)k * g.plane + o] = v;
         }
-        const double sp = cfl_speed(un, p.gamma);
+        const double sp = cfl_speed_checked(un, p.gamma);
         if (sp > speed) speed = sp;
     }
     block_max_to_global(speed, max_bits);
@@ -343,7 +424,7 @@ __global__ void max_speed_kernel(const GridDims g, double gamma, const double* _
         for (int i = i_lo + blockIdx.y; i <= i_hi; i += gridDim.y) {
             double q[NV];
             load_cell(u, g.plane, cell_index(g, i, j), q);
-            const double sp = cfl_speed(q, gamma);
+            const double sp = cfl_speed_checked(q, gamma);
             if (sp > best) best = sp;
         }
     }

@@ -32,6 +32,7 @@ __host__ __device__ inline size_t cell_index(const GridDims& g, int i, int j) {
 
 struct SweepParams {
     double gamma, gm1;
+    double inv2ch, halfch;  // 1.0/(2.0*ch) and ch/2.0 (MUSCL_NEW.cpp:126-127), divided on the host
     double ch, ch2;      // GLM wave speed = max signal speed of this step (MUSCL_NEW.cpp:834)
     double dtdh;         // dt/dx (x sweep) or dt/dy (y sweep)
     double hdtdh;        // 0.5*(dt/dx)

@@ -12,6 +12,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include "fp64_div.cuh"
 #include "mhd_kernels.cuh"
 
 namespace lsc {
@@ -24,21 +25,26 @@ __device__ __forceinline__ double std_max(double a, double b) { return (a < b) ?
 // MUSCL_NEW.cpp:22-34 (ConservativeToPrimitive); v0,v5..v8 are copies of u.
 struct Prim {
     double vx, vy, vz, p;
+    double ke;  // 0.5*rho*(vx*vx+vy*vy+vz*vz) as it appears in the pressure expression
+    Rcp irho;  // shared refined reciprocal of the density (fp64_div.cuh)
 };
 
-__device__ __forceinline__ Prim c2p(const double (&u)[NV], double gm1) {
+template <class D>
+__device__ __forceinline__ Prim c2p(D& dv, const double (&u)[NV], double gm1) {
     Prim q;
-    q.vx = u[1] / u[0];
-    q.vy = u[2] / u[0];
-    q.vz = u[3] / u[0];
-    q.p = (u[4] - 0.5 * u[0] * (q.vx * q.vx + q.vy * q.vy + q.vz * q.vz) -
-           0.5 * (u[5] * u[5] + u[6] * u[6] + u[7] * u[7])) * gm1;
+    q.irho = dv.rcp(u[0]);
+    q.vx = dv.div(u[1], q.irho);
+    q.vy = dv.div(u[2], q.irho);
+    q.vz = dv.div(u[3], q.irho);
+    q.ke = 0.5 * u[0] * (q.vx * q.vx + q.vy * q.vy + q.vz * q.vz);
+    q.p = (u[4] - q.ke - 0.5 * (u[5] * u[5] + u[6] * u[6] + u[7] * u[7])) * gm1;
     return q;
 }
 
 // Full primitive vector (for the limiter ratio, which differences primitives).
-__device__ __forceinline__ void c2p_full(const double (&u)[NV], double gm1, double (&v)[NV]) {
-    Prim q = c2p(u, gm1);
+template <class D>
+__device__ __forceinline__ void c2p_full(D& dv, const double (&u)[NV], double gm1, double (&v)[NV]) {
+    Prim q = c2p(dv, u, gm1);
     v[0] = u[0]; v[1] = q.vx; v[2] = q.vy; v[3] = q.vz; v[4] = q.p;
     v[5] = u[5]; v[6] = u[6]; v[7] = u[7]; v[8] = u[8];
 }
@@ -46,8 +52,7 @@ __device__ __forceinline__ void c2p_full(const double (&u)[NV], double gm1, doub
 // Physical flux of a conserved state.  DIR 0: FluxDefX MUSCL_NEW.cpp:36-49,
 // DIR 1: FluxDefY MUSCL_NEW.cpp:51-64.  ch2 = ch*ch.
 template <int DIR>
-__device__ __forceinline__ void flux_def(const double (&u)[NV], double gm1, double ch2, double (&f)[NV]) {
-    const Prim q = c2p(u, gm1);
+__device__ __forceinline__ void flux_from_prim(const double (&u)[NV], const Prim& q, double ch2, double (&f)[NV]) {
     const double B2 = u[5] * u[5] + u[6] * u[6] + u[7] * u[7];
     const double vB = q.vx * u[5] + q.vy * u[6] + q.vz * u[7];
     if (DIR == 0) {
@@ -76,6 +81,12 @@ __device__ __forceinline__ void flux_def(const double (&u)[NV], double gm1, doub
     }
 }
 
+template <int DIR, class D>
+__device__ __forceinline__ void flux_def(D& dv, const double (&u)[NV], double gm1, double ch2, double (&f)[NV]) {
+    const Prim q = c2p(dv, u, gm1);
+    flux_from_prim<DIR>(u, q, ch2, f);
+}
+
 // Slope-limited linear reconstruction of one component.  MUSCL_NEW.cpp:845-859
 // (x) and :909-923 (y).  (pm,p0,pp) are the PRIMITIVE values the limiter ratio is
 // formed from, (um,u0,up) the CONSERVED values that are reconstructed.
@@ -85,16 +96,17 @@ __device__ __forceinline__ void flux_def(const double (&u)[NV], double gm1, doub
 // monotone in the numerator, so the minimum is fl(2r/d) when r <= 1 and fl(2/d)
 // otherwise (equal at r == 1; for r = +inf the reference's fmin(NaN, 0) = 0 = 2/inf;
 // NaN r gives NaN both ways).
-__device__ __forceinline__ void reconstruct1(double pm, double p0, double pp, double um, double u0,
+template <class D>
+__device__ __forceinline__ void reconstruct1(D& dv, double pm, double p0, double pp, double um, double u0,
                                              double up, double& lo, double& hi) {
-    const double r = (p0 - pm) / ((pp - p0) + 1e-8);
+    const double r = dv.div(p0 - pm, (pp - p0) + 1e-8);
     const double dPlus = up - u0;
     const double dMinus = u0 - um;
     double xi;
     if (r <= 0) {
         xi = 0;
     } else {
-        xi = ((r <= 1.0) ? 2.0 * r : 2.0) / (1 + r);
+        xi = dv.div((r <= 1.0) ? 2.0 * r : 2.0, 1 + r);
     }
     const double Delta = 0.5 * dMinus + 0.5 * dPlus;
     lo = u0 - 0.5 * xi * Delta;
@@ -104,12 +116,12 @@ __device__ __forceinline__ void reconstruct1(double pm, double p0, double pp, do
 // MUSCL-Hancock predictor: both face states advanced by half a step with the flux
 // difference across the cell.  MUSCL_NEW.cpp:865-874 (x), :929-938 (y).
 // hdtdh = 0.5*(dt/dx) (or dy).  In-place on lo/hi.
-template <int DIR>
-__device__ __forceinline__ void predictor(double (&lo)[NV], double (&hi)[NV], double gm1, double ch2,
+template <int DIR, class D>
+__device__ __forceinline__ void predictor(D& dv, double (&lo)[NV], double (&hi)[NV], double gm1, double ch2,
                                           double hdtdh) {
     double fl[NV], fh[NV];
-    flux_def<DIR>(lo, gm1, ch2, fl);
-    flux_def<DIR>(hi, gm1, ch2, fh);
+    flux_def<DIR>(dv, lo, gm1, ch2, fl);
+    flux_def<DIR>(dv, hi, gm1, ch2, fh);
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
         const double d = hdtdh * (fh[k] - fl[k]);
@@ -120,10 +132,11 @@ __device__ __forceinline__ void predictor(double (&lo)[NV], double (&hi)[NV], do
 
 // fast magnetosonic speed squared along DIR.  speedsx/speedsy MUSCL_NEW.cpp:140-165,
 // :197-222 -- evaluated on the ORIGINAL state (the reference ignores its B?Tilde argument).
-__device__ __forceinline__ double fast_speed_sq(double rho, double p, double B2, double Bn, double gamma) {
-    const double cs2 = gamma * p / rho;
-    const double t = cs2 + B2 / rho;
-    return 0.5 * (t + sqrt(t * t - 4.0 * cs2 * Bn * Bn / rho));
+template <class D>
+__device__ __forceinline__ double fast_speed_sq(D& dv, const Rcp& irho, double p, double B2, double Bn, double gamma) {
+    const double cs2 = dv.div(gamma * p, irho);
+    const double t = cs2 + dv.div(B2, irho);
+    return 0.5 * (t + sqrt(t * t - dv.div(4.0 * cs2 * Bn * Bn, irho)));
 }
 
 // HLLC flux with mixed-GLM interface values.  FluxHLLCX MUSCL_NEW.cpp:483-515 /
@@ -132,31 +145,33 @@ __device__ __forceinline__ double fast_speed_sq(double rho, double p, double B2,
 //   uStarX :309-395, uStarY :397-481 (incl. the :442 quirk: the RIGHT star
 //   z-momentum in y is built from the LEFT quantities).
 // L is the state left/below the interface, R the one right/above.
-template <int DIR>
-__device__ __forceinline__ void hllc_flux(const double (&L)[NV], const double (&R)[NV], double gamma,
-                                          double gm1, double ch, double ch2, double (&F)[NV]) {
+template <int DIR, class D>
+__device__ __forceinline__ void hllc_flux(D& dv, const double (&L)[NV], const double (&R)[NV], double gamma,
+                                          double gm1, double ch, double ch2, double inv2ch, double halfch,
+                                          double (&F)[NV]) {
     constexpr int N = (DIR == 0) ? 5 : 6;  // normal field component
     // ---- mixed GLM interface values (:126-127 / :135-136)
-    const double BnT = 0.5 * (L[N] + R[N]) - (1.0 / (2.0 * ch)) * (R[8] - L[8]);
-    const double psiT = 0.5 * (L[8] + R[8]) - (ch / 2.0) * (R[N] - L[N]);
+    // inv2ch = 1.0/(2.0*ch), halfch = ch/2.0: per-step scalars, divided once on the host
+    const double BnT = 0.5 * (L[N] + R[N]) - inv2ch * (R[8] - L[8]);
+    const double psiT = 0.5 * (L[8] + R[8]) - halfch * (R[N] - L[N]);
 
     // ---- primitives of the ORIGINAL states
-    const Prim qL = c2p(L, gm1), qR = c2p(R, gm1);
+    const Prim qL = c2p(dv, L, gm1), qR = c2p(dv, R, gm1);
     const double vnL = (DIR == 0) ? qL.vx : qL.vy;
     const double vnR = (DIR == 0) ? qR.vx : qR.vy;
     const double B2L = L[5] * L[5] + L[6] * L[6] + L[7] * L[7];
     const double B2R = R[5] * R[5] + R[6] * R[6] + R[7] * R[7];
 
     // ---- wave speeds (:178-192 / :235-250)
-    const double cfL = sqrt(fast_speed_sq(L[0], qL.p, B2L, L[N], gamma));
-    const double cfR = sqrt(fast_speed_sq(R[0], qR.p, B2R, R[N], gamma));
+    const double cfL = sqrt(fast_speed_sq(dv, qL.irho, qL.p, B2L, L[N], gamma));
+    const double cfR = sqrt(fast_speed_sq(dv, qR.irho, qR.p, B2R, R[N], gamma));
     const double cmax = std_max(cfL, cfR);
     const double sL = std_min(vnL, vnR) - cmax;
     const double sR = std_max(vnL, vnR) + cmax;
     const double pModL = (qL.p + 0.5 * B2L) - L[N] * L[N];
     const double pModR = (qR.p + 0.5 * B2R) - R[N] * R[N];
-    const double qS = (R[0] * vnR * (sR - vnR) - L[0] * vnL * (sL - vnL) + pModL - pModR) /
-                      (R[0] * (sR - vnR) - L[0] * (sL - vnL));
+    const double qS = dv.div(R[0] * vnR * (sR - vnR) - L[0] * vnL * (sL - vnL) + pModL - pModR,
+                           R[0] * (sR - vnR) - L[0] * (sL - vnL));
 
     // ---- which of the four HLLC regions (:502-512 / :536-546), evaluated in the reference's order
     const bool regA = (sL >= 0);
@@ -180,7 +195,11 @@ __device__ __forceinline__ void hllc_flux(const double (&L)[NV], const double (&
     // flux of the modified state: FluxDefX/Y(x1) -- velocities unchanged, pressure re-derived
     // with the cleaned normal field (:497-498 / :531-532)
     double FS[NV];
-    flux_def<DIR>(S1, gm1, ch2, FS);
+    {
+        Prim q1 = qs;  // S1[0..4] == S[0..4]: same velocities and kinetic term, new magnetic pressure
+        q1.p = (S1[4] - qs.ke - 0.5 * (S1[5] * S1[5] + S1[6] * S1[6] + S1[7] * S1[7])) * gm1;
+        flux_from_prim<DIR>(S1, q1, ch2, FS);
+    }
 
     if (!(regB || regC)) {
 #pragma unroll
@@ -198,18 +217,19 @@ __device__ __forceinline__ void hllc_flux(const double (&L)[NV], const double (&
         fT1L = L[5] * qL.vy - L[6] * qL.vx;  fT1R = R[5] * qR.vy - R[6] * qR.vx;
         f7L = L[7] * qL.vy - L[6] * qL.vz;   f7R = R[7] * qR.vy - R[6] * qR.vz;
     }
+    const Rcp iw = dv.rcp(sR - sL);  // shared by the three quotients over the fan width
     double BtH, BzH;
     if (sL >= 0) {
         BtH = L[T1]; BzH = L[7];
     } else if (sL < 0 && sR > 0) {
-        BtH = (sR * R[T1] - sL * L[T1] - fT1R + fT1L) / (sR - sL);
-        BzH = (sR * R[7] - sL * L[7] - f7R + f7L) / (sR - sL);
+        BtH = dv.div(sR * R[T1] - sL * L[T1] - fT1R + fT1L, iw);
+        BzH = dv.div(sR * R[7] - sL * L[7] - f7R + f7L, iw);
     } else {
         BtH = R[T1]; BzH = R[7];
     }
 
     // ---- star state on the selected side (uStarX / uStarY), normal field = BnT on both sides
-    const double BnS = (sR * BnT - sL * BnT) / (sR - sL);
+    const double BnS = dv.div(sR * BnT - sL * BnT, iw);
     const double Bt = S[T1], Bz = S[7];
     const double vt = (DIR == 0) ? qs.vy : qs.vx;  // tangential in-plane velocity
     const double vz = qs.vz;
@@ -217,28 +237,31 @@ __device__ __forceinline__ void hllc_flux(const double (&L)[NV], const double (&
     const double B2s = (DIR == 0) ? (BnT * BnT + Bt * Bt + Bz * Bz) : (Bt * Bt + BnT * BnT + Bz * Bz);
     const double pT = qs.p + 0.5 * B2s;
     const double pStar = S[0] * (ss - vn) * (qS - vn) + pT - BnT * BnT + BnS * BnS;
-    const double rhoS = S[0] * (ss - vn) / (ss - qS);
+    const Rcp is = dv.rcp(ss - qS);  // shared by the four quotients over (s - qStar)
+    const double rhoS = dv.div(S[0] * (ss - vn), is);
     const double mnS = rhoS * qS;
     // tangential momenta (:353-357 / :437-442)
-    const double mtS = vt * rhoS - (BnS * BtH - BnT * Bt) / (ss - qS);
+    const double mtS = vt * rhoS - dv.div(BnS * BtH - BnT * Bt, is);
     double mzS;
     if (DIR == 1 && !left) {
         // MUSCL_NEW.cpp:442: momzStarR = rhoStarL*u_zL - (ByStar*BzHLL - ByL*BzL)/(sL - qStar)
-        const double rhoSL = L[0] * (sL - vnL) / (sL - qS);
-        mzS = rhoSL * qL.vz - (BnS * BzH - BnT * L[7]) / (sL - qS);
+        const Rcp isl = dv.rcp(sL - qS);
+        const double rhoSL = dv.div(L[0] * (sL - vnL), isl);
+        mzS = rhoSL * qL.vz - dv.div(BnS * BzH - BnT * L[7], isl);
     } else {
-        mzS = vz * rhoS - (BnS * BzH - BnT * Bz) / (ss - qS);
+        mzS = vz * rhoS - dv.div(BnS * BzH - BnT * Bz, is);
     }
     // v.B of the side state (x,y,z order) and of the star state
     double vB, vBH;
     if (DIR == 0) {
         vB = BnT * vn + Bt * vt + Bz * vz;
-        vBH = (BnS * mnS + BtH * mtS + BzH * mzS) / rhoS;
+        vBH = dv.div(BnS * mnS + BtH * mtS + BzH * mzS, rhoS);
     } else {
         vB = Bt * vt + BnT * vn + Bz * vz;
-        vBH = (BtH * mtS + BnS * mnS + BzH * mzS) / rhoS;
+        vBH = dv.div(BtH * mtS + BnS * mnS + BzH * mzS, rhoS);
     }
-    const double ES = S[4] * (rhoS / S[0]) + ((pStar * qS - pT * vn) - (BnS * vBH - BnT * vB)) / (ss - qS);
+    const double ES = S[4] * dv.div(rhoS, qs.irho) +
+                      dv.div((pStar * qS - pT * vn) - (BnS * vBH - BnT * vB), is);
 
     double US[NV];
     US[0] = rhoS;
@@ -255,19 +278,21 @@ __device__ __forceinline__ void hllc_flux(const double (&L)[NV], const double (&
 }
 
 // Local signal speed for the CFL condition.  ComputeTimeStep MUSCL_NEW.cpp:75-109.
-__device__ __forceinline__ double cfl_speed(const double (&q)[NV], double gamma) {
+template <class D>
+__device__ __forceinline__ double cfl_speed(D& dv, const double (&q)[NV], double gamma) {
     const double rho = q[0], Bx = q[5], By = q[6], Bz = q[7];
-    const double ux = q[1] / rho, uy = q[2] / rho, uz = q[3] / rho;
+    const Rcp irho = dv.rcp(rho);
+    const double ux = dv.div(q[1], irho), uy = dv.div(q[2], irho), uz = dv.div(q[3], irho);
     const double B2 = Bx * Bx + By * By + Bz * Bz;
     const double ke = 0.5 * rho * (ux * ux + uy * uy + uz * uz) + 0.5 * B2;
     const double p = (gamma - 1.0) * (q[4] - ke);
-    const double a = sqrt(gamma * p / rho);
+    const double a = sqrt(dv.div(gamma * p, irho));
     const double a2 = a * a;
-    const double s = a2 + B2 / rho;
+    const double s = a2 + dv.div(B2, irho);
     const double s2 = s * s;  // pow(s, 2)
-    const double cfx = sqrt(0.5 * (s + sqrt(s2 - 4 * a * a * Bx * Bx / rho)));
-    const double cfy = sqrt(0.5 * (s + sqrt(s2 - 4 * a * a * By * By / rho)));
-    const double cfz = sqrt(0.5 * (s + sqrt(s2 - 4 * a * a * Bz * Bz / rho)));
+    const double cfx = sqrt(0.5 * (s + sqrt(s2 - dv.div(4 * a * a * Bx * Bx, irho))));
+    const double cfy = sqrt(0.5 * (s + sqrt(s2 - dv.div(4 * a * a * By * By, irho))));
+    const double cfz = sqrt(0.5 * (s + sqrt(s2 - dv.div(4 * a * a * Bz * Bz, irho))));
     return std_max(std_max(fabs(ux) + cfx, fabs(uy) + cfy), fabs(uz) + cfz);
 }
 

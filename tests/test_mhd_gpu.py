@@ -64,6 +64,23 @@ def oracle_hllc(Ls, Rs, gamma, ch, d):
     return F
 
 
+@pytest.mark.parametrize("mode", [0, 1, 2])
+def test_custom_division_is_ieee(mode):
+    """csrc/fp64_div.cuh vs the compiler's IEEE `/` on 2^31 operand pairs per mode: zero bitwise
+    mismatches among the pairs the guard lets through; in the solver's range nothing is flagged."""
+    import ctypes
+    bad, flagged = ctypes.c_ulonglong(), ctypes.c_ulonglong()
+    n_blocks, per_thread = 1 << 15, 256   # 2^15 * 256 * 256 = 2^31 pairs
+    rc = lsc.lib().lsc_kat_division(0, 0xC0FFEE + mode, mode, n_blocks, per_thread, ctypes.byref(bad),
+                                    ctypes.byref(flagged))
+    assert rc == 0
+    assert bad.value == 0, f"{bad.value} quotients differ from IEEE division"
+    if mode != 1:
+        assert flagged.value == 0
+    else:
+        assert flagged.value > 0
+
+
 @pytest.mark.parametrize("d", [0, 1])
 def test_kat_hllc_random_states(d):
     rng = np.random.default_rng(1234 + d)
