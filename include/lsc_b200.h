@@ -122,6 +122,10 @@ int lsc_mhd_step_timed(lsc_mhd_ctx* ctx, long nsteps, float* ms);
 int lsc_mhd_set_profiling(lsc_mhd_ctx* ctx, int enabled);
 int lsc_mhd_kernel_times(lsc_mhd_ctx* ctx, double ms[2], long launches[2]);
 
+/* How many steps had to be recomputed with the compiler's IEEE division because a fast shared-reciprocal
+ * division saw an operand outside its guarded exponent window (csrc/fp64_div.cuh).  0 in normal runs. */
+long lsc_mhd_ieee_fallback_count(const lsc_mhd_ctx* ctx);
+
 /* t, the last dt, the last ch (= max signal speed, M:834) and the step count. Any may be NULL. */
 int lsc_mhd_get_scalars(const lsc_mhd_ctx* ctx, double* t, double* dt, double* ch, long* step);
 

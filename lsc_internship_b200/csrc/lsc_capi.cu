@@ -53,10 +53,17 @@ struct lsc_mhd_ctx {
     int nxl = 0, i0 = 0;  // slab: interior columns, first global interior column (0-based)
     double dx = 0, dy = 0;
     lsc::GridDims g{};
-    double* state[3] = {nullptr, nullptr, nullptr};
-    int cur = 0, bar = 1, prev = 2;
-    unsigned long long* d_max = nullptr;  // bit pattern of the max signal speed of state[cur]
-    unsigned long long* h_max = nullptr;  // pinned
+    // four rotating states: u^n, uBar, u^{n-1}, and the buffer u^{n+1} is written to.  The fourth one
+    // keeps u^{n-1} intact until the step's status word has been read, so a step can be recomputed
+    // with IEEE division if a fast division flagged an operand (mhd_kernels.cu).
+    double* state[4] = {nullptr, nullptr, nullptr, nullptr};
+    int cur = 0, bar = 1, prev = 2, spare = 3;
+    unsigned long long* d_max = nullptr;  // [0] bit pattern of the max signal speed of state[cur], [1] flag
+    unsigned long long* h_max = nullptr;  // pinned copy of both words
+    bool pending = false;                 // status of the last launched step not read back yet
+    double max_speed = 0;                 // max signal speed of state[cur] once resolved
+    lsc::SweepParams last_px{}, last_py{};
+    long ieee_redos = 0;
     double* d_stage = nullptr;            // AoS staging for transfers
     int stage_cols = 0;
     cudaStream_t stream = nullptr;
@@ -129,7 +136,7 @@ int lsc_mhd_create(const lsc_mhd_config* cfg, lsc_mhd_ctx** out) {
     c->g.pitch = ((cfg->ny + 4 + lsc::JOFF) + 15) / 16 * 16;
     c->g.plane = (size_t)(c->nxl + 4) * (size_t)c->g.pitch;
     const size_t state_bytes = c->g.plane * lsc::NV * sizeof(double);
-    for (int b = 0; b < 3; ++b) {
+    for (int b = 0; b < 4; ++b) {
         if (cudaMalloc(&c->state[b], state_bytes) != cudaSuccess) {
             cudaGetLastError();
             lsc_mhd_destroy(c);
@@ -144,8 +151,8 @@ int lsc_mhd_create(const lsc_mhd_config* cfg, lsc_mhd_ctx** out) {
     if (cols > c->nxl + 4) cols = c->nxl + 4;
     c->stage_cols = (int)cols;
     if (cudaMalloc(&c->d_stage, col_bytes * (size_t)cols) != cudaSuccess ||
-        cudaMalloc(&c->d_max, sizeof(unsigned long long)) != cudaSuccess ||
-        cudaHostAlloc(&c->h_max, sizeof(unsigned long long), cudaHostAllocDefault) != cudaSuccess ||
+        cudaMalloc(&c->d_max, 2 * sizeof(unsigned long long)) != cudaSuccess ||
+        cudaHostAlloc(&c->h_max, 2 * sizeof(unsigned long long), cudaHostAllocDefault) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
         cudaGetLastError();
         lsc_mhd_destroy(c);
@@ -160,7 +167,7 @@ int lsc_mhd_destroy(lsc_mhd_ctx* c) {
     cudaSetDevice(c->cfg.device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->comm) lsc::comm_destroy(c->comm);
-    for (int b = 0; b < 3; ++b)
+    for (int b = 0; b < 4; ++b)
         if (c->state[b]) cudaFree(c->state[b]);
     if (c->d_stage) cudaFree(c->d_stage);
     if (c->d_max) cudaFree(c->d_max);
@@ -188,7 +195,7 @@ namespace {
 // after new data has been placed in state[cur]: reset the clock and reduce the initial signal speed
 // over the reference's range (MUSCL_NEW.cpp:73-74: i,j in [1, n+1], array as uploaded, ghosts included)
 int finish_upload(lsc_mhd_ctx* c) {
-    CUDA_TRY(cudaMemsetAsync(c->d_max, 0, sizeof(unsigned long long), c->stream));
+    CUDA_TRY(cudaMemsetAsync(c->d_max, 0, 2 * sizeof(unsigned long long), c->stream));
     const int i_lo = (c->cfg.rank == 0) ? 1 : 2;
     lsc::launch_max_speed(c->g, c->cfg.gamma, c->state[c->cur], i_lo, c->nxl + 1, 1, c->cfg.ny + 1, c->d_max,
                           c->stream);
@@ -201,6 +208,7 @@ int finish_upload(lsc_mhd_ctx* c) {
     c->step = 0;
     c->uploaded = true;
     c->ghosts_current = false;
+    c->pending = true;  // status[0] holds the initial signal speed, status[1] = 0
     return LSC_OK;
 }
 
@@ -278,18 +286,46 @@ int fill_x_ghosts(lsc_mhd_ctx* c, int b) {
     return LSC_OK;
 }
 
+// Read back {max signal speed, fast-division flag} of the step launched last.  If the flag is set the
+// step is recomputed from its inputs, which are still intact (state[prev] = u^n, state[spare] = u^{n-1}),
+// with the IeeeDiv kernels.
+int resolve_pending(lsc_mhd_ctx* c) {
+    if (!c->pending) return LSC_OK;
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        if (c->cfg.nranks > 1) {
+            if (!c->comm) return fail(LSC_ESTATE, "nranks > 1 but lsc_mhd_comm_init was not called");
+            if (lsc::comm_allreduce_max_u64(c->comm, c->d_max, 2, c->stream))
+                return fail(LSC_ECOMM, "allreduce failed: %s", lsc::comm_error());
+        }
+        CUDA_TRY(cudaMemcpyAsync(c->h_max, c->d_max, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost,
+                                 c->stream));
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
+        if (c->h_max[1] == 0 || attempt == 1) break;
+        // ---- recompute the last step with IEEE division
+        c->ieee_redos += 1;
+        CUDA_TRY(cudaMemsetAsync(c->d_max, 0, 2 * sizeof(unsigned long long), c->stream));
+        lsc::launch_x_sweep(c->g, c->last_px, true, c->state[c->prev], c->state[c->spare], c->state[c->bar],
+                            c->d_max, c->stream);
+        lsc::launch_y_sweep(c->g, c->last_py, true, c->state[c->bar], c->state[c->prev], c->state[c->cur],
+                            c->d_max, c->stream);
+        lsc_count_launches(2);
+        CUDA_TRY(cudaGetLastError());
+        int rc = fill_x_ghosts(c, c->cur);
+        if (rc) return rc;
+    }
+    std::memcpy(&c->max_speed, &c->h_max[0], sizeof(double));
+    c->pending = false;
+    return LSC_OK;
+}
+
 // One pass of the loop body MUSCL_NEW.cpp:831-971.
 int step_once(lsc_mhd_ctx* c) {
     // ---- ComputeTimeStep (:833-835): the reduction already ran on the device
-    if (c->cfg.nranks > 1) {
-        if (!c->comm) return fail(LSC_ESTATE, "nranks > 1 but lsc_mhd_comm_init was not called");
-        if (lsc::comm_allreduce_max_u64(c->comm, c->d_max, c->stream))
-            return fail(LSC_ECOMM, "allreduce failed: %s", lsc::comm_error());
+    {
+        int rc = resolve_pending(c);
+        if (rc) return rc;
     }
-    CUDA_TRY(cudaMemcpyAsync(c->h_max, c->d_max, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
-    CUDA_TRY(cudaStreamSynchronize(c->stream));
-    double max_speed;
-    std::memcpy(&max_speed, c->h_max, sizeof(double));
+    const double max_speed = c->max_speed;
     if (!(max_speed > 0.0) || !std::isfinite(max_speed))
         return fail(LSC_ENAN, "max signal speed is %g at step %ld", max_speed, c->step);
     const double dspace = std::min(c->dx, c->dy);      // :117
@@ -327,16 +363,20 @@ int step_once(lsc_mhd_ctx* c) {
         for (auto& e : ev) CUDA_TRY(cudaEventCreate(&e));
         CUDA_TRY(cudaEventRecord(ev[0], c->stream));
     }
-    lsc::launch_x_sweep(c->g, p, c->state[c->cur], c->state[c->prev], c->state[c->bar], c->stream);
+    CUDA_TRY(cudaMemsetAsync(c->d_max, 0, 2 * sizeof(unsigned long long), c->stream));
+    c->last_px = p;
+    lsc::launch_x_sweep(c->g, p, false, c->state[c->cur], c->state[c->prev], c->state[c->bar], c->d_max,
+                        c->stream);
     if (c->profiling) CUDA_TRY(cudaEventRecord(ev[1], c->stream));
 
     // ---- y sweep (:905-965) + copy (:969) + next step's signal speed (:71-115)
-    CUDA_TRY(cudaMemsetAsync(c->d_max, 0, sizeof(unsigned long long), c->stream));
     p.dtdh = dt / c->dy;
     p.hdtdh = 0.5 * (dt / c->dy);
     p.bc_lo = p.bc_hi = to_kernel_bc(c->cfg.bc_y);
     if (c->profiling) CUDA_TRY(cudaEventRecord(ev[2], c->stream));
-    lsc::launch_y_sweep(c->g, p, c->state[c->bar], c->state[c->cur], c->state[c->prev], c->d_max, c->stream);
+    c->last_py = p;
+    lsc::launch_y_sweep(c->g, p, false, c->state[c->bar], c->state[c->cur], c->state[c->spare], c->d_max,
+                        c->stream);
     if (c->profiling) {
         CUDA_TRY(cudaEventRecord(ev[3], c->stream));
         for (auto e : ev) c->prof_events.push_back(e);
@@ -345,9 +385,11 @@ int step_once(lsc_mhd_ctx* c) {
     CUDA_TRY(cudaGetLastError());
 
     // u = uPlus1 (:969): rotate; the old u^n stays as the limiter's "previous" state
-    const int next = c->prev;
+    const int next = c->spare;
+    c->spare = c->prev;
     c->prev = c->cur;
     c->cur = next;
+    c->pending = true;
     // ---- applyBoundaryConditions(u) (:971)
     int rc = fill_x_ghosts(c, c->cur);
     if (rc) return rc;
@@ -367,8 +409,7 @@ int lsc_mhd_step(lsc_mhd_ctx* c, long nsteps) {
         int rc = step_once(c);
         if (rc) return rc;
     }
-    CUDA_TRY(cudaStreamSynchronize(c->stream));
-    return LSC_OK;
+    return resolve_pending(c);  // syncs; the state is final (and IEEE-exact) when this returns
 }
 
 int lsc_mhd_step_timed(lsc_mhd_ctx* c, long nsteps, float* ms) {
@@ -382,6 +423,7 @@ int lsc_mhd_step_timed(lsc_mhd_ctx* c, long nsteps, float* ms) {
     CUDA_TRY(cudaEventRecord(e0, c->stream));
     int rc = LSC_OK;
     for (long s = 0; s < nsteps && rc == LSC_OK; ++s) rc = step_once(c);
+    if (rc == LSC_OK) rc = resolve_pending(c);
     if (rc == LSC_OK) {
         CUDA_TRY(cudaEventRecord(e1, c->stream));
         CUDA_TRY(cudaEventSynchronize(e1));
@@ -391,6 +433,8 @@ int lsc_mhd_step_timed(lsc_mhd_ctx* c, long nsteps, float* ms) {
     cudaEventDestroy(e1);
     return rc;
 }
+
+long lsc_mhd_ieee_fallback_count(const lsc_mhd_ctx* c) { return c ? c->ieee_redos : -1; }
 
 int lsc_mhd_set_profiling(lsc_mhd_ctx* c, int enabled) {
     if (!c) return fail(LSC_EINVAL, "null argument");
@@ -438,15 +482,18 @@ int lsc_mhd_run_until(lsc_mhd_ctx* c, double t_stop, lsc_mhd_dump_cb dump_cb, ls
             counter += 1;  // :1000
         }
     } while (c->t < t_stop);  // :1003
-    CUDA_TRY(cudaStreamSynchronize(c->stream));
     if (steps_out) *steps_out = n;
-    return LSC_OK;
+    return resolve_pending(c);
 }
 
 int lsc_mhd_download(lsc_mhd_ctx* c, double* aos) {
     if (!c || !aos) return fail(LSC_EINVAL, "null argument");
     if (!c->uploaded) return fail(LSC_ESTATE, "lsc_mhd_download before lsc_mhd_upload");
     CUDA_TRY(cudaSetDevice(c->cfg.device));
+    {
+        int rc = resolve_pending(c);
+        if (rc) return rc;
+    }
     const size_t col = (size_t)(c->cfg.ny + 4) * lsc::NV;
     for (int il = 0; il < c->nxl + 4; il += c->stage_cols) {
         const int ni = std::min(c->stage_cols, c->nxl + 4 - il);

@@ -105,8 +105,8 @@ int comm_exchange_halos(Comm* c, const GridDims& g, int bc_x, double* u, cudaStr
     return 0;
 }
 
-int comm_allreduce_max_u64(Comm* c, unsigned long long* d_word, cudaStream_t s) {
-    NCCL_TRY(ncclAllReduce(d_word, d_word, 1, ncclUint64, ncclMax, c->nccl, s), -1);
+int comm_allreduce_max_u64(Comm* c, unsigned long long* d_words, int count, cudaStream_t s) {
+    NCCL_TRY(ncclAllReduce(d_words, d_words, count, ncclUint64, ncclMax, c->nccl, s), -1);
     return 0;
 }
 

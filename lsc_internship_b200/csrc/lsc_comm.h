@@ -17,8 +17,8 @@ void comm_destroy(Comm* c);
 // Fill the ghost columns 0,1 and nxl+2,nxl+3 of every plane of `u`: neighbour ranks' edge columns
 // (a ring when bc_x is periodic), boundary images on the end ranks otherwise.
 int comm_exchange_halos(Comm* c, const GridDims& g, int bc_x, double* u, cudaStream_t s);
-// In-place max over ranks of one unsigned 64-bit word on the device (bit pattern of a
+// In-place max over ranks of `count` unsigned 64-bit words on the device (bit pattern of a
 // non-negative double: same ordering).
-int comm_allreduce_max_u64(Comm* c, unsigned long long* d_word, cudaStream_t s);
+int comm_allreduce_max_u64(Comm* c, unsigned long long* d_words, int count, cudaStream_t s);
 
 }  // namespace lsc

@@ -8,6 +8,14 @@
 //
 // Compiled with -fmad=false: FMA contraction changes the answer at the 1e-9 level
 // after one step and at the 1e-2 level after ten.
+//
+// Both sweeps are templated on the division policy (fp64_div.cuh).  The production
+// instantiation is FastDiv: branch-free shared-reciprocal quotients with a sticky
+// "operand outside the guarded window" flag that is OR-ed into status[1] at the end of the
+// thread.  The host reads that word together with the signal speed (status[0]); if it is
+// ever non-zero the step is recomputed from its untouched inputs with the IeeeDiv
+// instantiation (every quotient by the compiler's IEEE `/`), so the result is the
+// correctly rounded one in either case.
 #include "mhd_kernels.cuh"
 #include "mhd_physics.cuh"
 
@@ -48,6 +56,22 @@ __device__ __forceinline__ void block_max_to_global(double local, unsigned long 
     }
 }
 
+#ifndef XS_BLOCK
+#define XS_BLOCK 128
+#endif
+#ifndef XS_MINB
+#define XS_MINB 1
+#endif
+#ifndef XS_STRIP
+#define XS_STRIP 64
+#endif
+#ifndef YS_MINB
+#define YS_MINB 1
+#endif
+#ifndef YS_BJ
+#define YS_BJ 128
+#endif
+
 // ------------------------------------------------------------------------------------
 // x sweep: one thread owns one row j and marches along i over a strip of columns,
 // keeping the 3-cell stencil, its primitives, the previous face state and the previous
@@ -57,15 +81,13 @@ __device__ __forceinline__ void block_max_to_global(double local, unsigned long 
 // -> psi damping never leave the register file.
 // ------------------------------------------------------------------------------------
 
-// Half-step face states of cell i computed straight from global memory (strip warm-up, the
-// non-periodic boundary images of MUSCL_NEW.cpp:878-879, and -- with D = IeeeDiv -- the fallback
-// when a fast division flagged an out-of-window operand).
+// Half-step face states of cell i computed straight from global memory (strip warm-up and the
+// non-periodic boundary images of MUSCL_NEW.cpp:878-879).
 template <class D>
-__device__ __noinline__ void x_halfstates_global(const GridDims g, const SweepParams p,
+__device__ __noinline__ void x_halfstates_global(D& dv, const GridDims g, const SweepParams p,
                                                  const double* __restrict__ cur,
                                                  const double* __restrict__ prev, int i, int j,
-                                                 double (&hL)[NV], double (&hR)[NV], bool& bad) {
-    D dv;
+                                                 double (&hL)[NV], double (&hR)[NV]) {
     double um[NV], u0[NV], up[NV], pm[NV], p0[NV], pp[NV];
     load_cell(cur, g.plane, cell_index(g, i - 1, j), um);
     load_cell(cur, g.plane, cell_index(g, i, j), u0);
@@ -83,91 +105,49 @@ __device__ __noinline__ void x_halfstates_global(const GridDims g, const SweepPa
 #pragma unroll
     for (int k = 0; k < NV; ++k) reconstruct1(dv, pm[k], p0[k], pp[k], um[k], u0[k], up[k], hL[k], hR[k]);
     predictor<0>(dv, hL, hR, p.gm1, p.ch2, p.hdtdh);
-    bad = dv.bad;
 }
 
-__device__ __forceinline__ void x_halfstates_checked(const GridDims& g, const SweepParams& p, const double* cur,
-                                                     const double* prev, int i, int j, double (&hL)[NV],
-                                                     double (&hR)[NV]) {
-    bool bad;
-    x_halfstates_global<FastDiv>(g, p, cur, prev, i, j, hL, hR, bad);
-    if (bad) x_halfstates_global<IeeeDiv>(g, p, cur, prev, i, j, hL, hR, bad);
-}
-
-template <int DIR>
-__device__ __noinline__ void hllc_flux_ieee(const double (&L)[NV], const double (&R)[NV], const SweepParams p,
-                                            double (&F)[NV]) {
-    IeeeDiv dv;
-    hllc_flux<DIR>(dv, L, R, p.gamma, p.gm1, p.ch, p.ch2, p.inv2ch, p.halfch, F);
-}
-
-template <int DIR>
-__device__ __forceinline__ void hllc_flux_checked(const double (&L)[NV], const double (&R)[NV], const SweepParams& p,
-                                                  double (&F)[NV]) {
-    FastDiv dv;
-    hllc_flux<DIR>(dv, L, R, p.gamma, p.gm1, p.ch, p.ch2, p.inv2ch, p.halfch, F);
-    if (dv.bad) hllc_flux_ieee<DIR>(L, R, p, F);
-}
-
-__device__ __noinline__ void c2p_full_ieee(const double (&u)[NV], double gm1, double (&v)[NV]) {
-    IeeeDiv dv;
-    c2p_full(dv, u, gm1, v);
-}
-
-__device__ __forceinline__ void c2p_full_checked(const double (&u)[NV], double gm1, double (&v)[NV]) {
-    FastDiv dv;
-    c2p_full(dv, u, gm1, v);
-    if (dv.bad) c2p_full_ieee(u, gm1, v);
-}
-
-#ifndef XS_BLOCK
-#define XS_BLOCK 128
-#endif
-#ifndef XS_MINB
-#define XS_MINB 1
-#endif
-#ifndef XS_STRIP
-#define XS_STRIP 64
-#endif
-#ifndef YS_MINB
-#define YS_MINB 1
-#endif
-#ifndef YS_BJ
-#define YS_BJ 128
-#endif
-
-template <int STRIP>
+template <class D, int STRIP>
 __global__ void __launch_bounds__(XS_BLOCK, XS_MINB) x_sweep_kernel(const GridDims g, const SweepParams p,
                                                                     const double* __restrict__ cur,
                                                                     const double* __restrict__ prev,
-                                                                    double* __restrict__ ubar) {
+                                                                    double* __restrict__ ubar,
+                                                                    unsigned long long* __restrict__ status) {
     const int j = 2 + blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= g.ny + 2) return;
     const int ia = 2 + blockIdx.y * STRIP;
     const int ib = min(ia + STRIP, g.nxl + 2);  // cells [ia, ib) are updated by this thread
     const bool lo_image = (ia == 2) && (p.bc_lo == BC_TRANSMISSIVE);
     const bool hi_image = (ib == g.nxl + 2) && (p.bc_hi == BC_TRANSMISSIVE);
+    D dv;
 
     double hRprev[NV], Fprev[NV];
     {
         // face state R of cell ia-1; at a transmissive wall ghost cell 1 carries the half state of
         // cell 3 (u[1] = u[3] applied to the half-step arrays, MUSCL_NEW.cpp:617-622, :878-879)
-        double hL[NV];
-        x_halfstates_checked(g, p, cur, prev, lo_image ? 3 : ia - 1, j, hL, hRprev);
+        double tL[NV], tR[NV];
+        x_halfstates_global(dv, g, p, cur, prev, lo_image ? 3 : ia - 1, j, tL, tR);
+#pragma unroll
+        for (int k = 0; k < NV; ++k) hRprev[k] = tR[k];
     }
     double uM[NV], u0[NV], uP[NV], PM[NV], P0[NV];
     load_cell(cur, g.plane, cell_index(g, ia - 1, j), uM);
     load_cell(cur, g.plane, cell_index(g, ia, j), u0);
     load_cell(cur, g.plane, cell_index(g, ia + 1, j), uP);
-    c2p_full_checked(uM, p.gm1, PM);
-    c2p_full_checked(u0, p.gm1, P0);
+    c2p_full(dv, uM, p.gm1, PM);
+    c2p_full(dv, u0, p.gm1, P0);
 
     for (int c = ia; c <= ib; ++c) {
         double hL[NV], hR[NV];
         if (c == ib && hi_image) {
-            x_halfstates_checked(g, p, cur, prev, g.nxl, j, hL, hR);  // u[nx+2] = u[nx]
+            double tL[NV], tR[NV];
+            x_halfstates_global(dv, g, p, cur, prev, g.nxl, j, tL, tR);  // u[nx+2] = u[nx]
+#pragma unroll
+            for (int k = 0; k < NV; ++k) {
+                hL[k] = tL[k];
+                hR[k] = tR[k];
+            }
         } else {
-            FastDiv dv;
             double Pp[NV];
             if (p.first_step) {
 #pragma unroll
@@ -181,13 +161,10 @@ __global__ void __launch_bounds__(XS_BLOCK, XS_MINB) x_sweep_kernel(const GridDi
             for (int k = 0; k < NV; ++k)
                 reconstruct1(dv, PM[k], P0[k], Pp[k], uM[k], u0[k], uP[k], hL[k], hR[k]);
             predictor<0>(dv, hL, hR, p.gm1, p.ch2, p.hdtdh);
-            if (dv.bad) {
-                bool b2;
-                x_halfstates_global<IeeeDiv>(g, p, cur, prev, c, j, hL, hR, b2);
-            }
         }
         double F[NV];
-        hllc_flux_checked<0>(hRprev, hL, p, F);  // interface c-1/2 (MUSCL_NEW.cpp:884)
+        // interface c-1/2 (MUSCL_NEW.cpp:884)
+        hllc_flux<0>(dv, hRprev, hL, p.gamma, p.gm1, p.ch, p.ch2, p.inv2ch, p.halfch, F);
         if (c > ia) {
             // uBar[c-1] = u[c-1] - (dt/dx)(F[c-1/2] - F[c-3/2])   MUSCL_NEW.cpp:891; psi damping :900
             const size_t o = cell_index(g, c - 1, j);
@@ -207,18 +184,22 @@ __global__ void __launch_bounds__(XS_BLOCK, XS_MINB) x_sweep_kernel(const GridDi
             PM[k] = P0[k];
         }
         if (c < ib) {
-            c2p_full_checked(u0, p.gm1, P0);
+            c2p_full(dv, u0, p.gm1, P0);
             load_cell(cur, g.plane, cell_index(g, c + 2, j), uP);
         }
     }
+    if (dv.bad) atomicOr(status + 1, 1ull);
 }
 
-void launch_x_sweep(const GridDims& g, const SweepParams& p, const double* u_cur, const double* u_prev,
-                    double* u_bar, cudaStream_t s) {
+void launch_x_sweep(const GridDims& g, const SweepParams& p, bool ieee, const double* u_cur, const double* u_prev,
+                    double* u_bar, unsigned long long* status, cudaStream_t s) {
     constexpr int STRIP = XS_STRIP;
     dim3 block(XS_BLOCK);
     dim3 grid((g.ny + block.x - 1) / block.x, (g.nxl + STRIP - 1) / STRIP);
-    x_sweep_kernel<STRIP><<<grid, block, 0, s>>>(g, p, u_cur, u_prev, u_bar);
+    if (ieee)
+        x_sweep_kernel<IeeeDiv, STRIP><<<grid, block, 0, s>>>(g, p, u_cur, u_prev, u_bar, status);
+    else
+        x_sweep_kernel<FastDiv, STRIP><<<grid, block, 0, s>>>(g, p, u_cur, u_prev, u_bar, status);
 }
 
 // ------------------------------------------------------------------------------------
@@ -251,11 +232,10 @@ __device__ __forceinline__ void load_row_cell(const double* __restrict__ base, c
 
 // Half-step face states (bottom, top) of cell j of column i straight from global memory.
 template <class D>
-__device__ __noinline__ void y_halfstates_global(const GridDims g, const SweepParams p,
+__device__ __noinline__ void y_halfstates_global(D& dv, const GridDims g, const SweepParams p,
                                                  const double* __restrict__ ubar,
                                                  const double* __restrict__ cur, int i, int j,
-                                                 double (&hB)[NV], double (&hT)[NV], bool& bad) {
-    D dv;
+                                                 double (&hB)[NV], double (&hT)[NV]) {
     double um[NV], u0[NV], up[NV], q[NV], pm[NV], p0[NV], pp[NV];
     load_row_cell(ubar, g, i, j - 1, p.bc_lo, um);
     load_row_cell(ubar, g, i, j, p.bc_lo, u0);
@@ -269,25 +249,14 @@ __device__ __noinline__ void y_halfstates_global(const GridDims g, const SweepPa
 #pragma unroll
     for (int k = 0; k < NV; ++k) reconstruct1(dv, pm[k], p0[k], pp[k], um[k], u0[k], up[k], hB[k], hT[k]);
     predictor<1>(dv, hB, hT, p.gm1, p.ch2, p.hdtdh);
-    bad = dv.bad;
 }
 
-__device__ __noinline__ double cfl_speed_ieee(const double (&q)[NV], double gamma) {
-    IeeeDiv dv;
-    return cfl_speed(dv, q, gamma);
-}
-
-__device__ __forceinline__ double cfl_speed_checked(const double (&q)[NV], double gamma) {
-    FastDiv dv;
-    const double s = cfl_speed(dv, q, gamma);
-    return dv.bad ? cfl_speed_ieee(q, gamma) : s;
-}
-
+template <class D>
 __global__ void __launch_bounds__(BJ, YS_MINB) y_sweep_kernel(const GridDims g, const SweepParams p,
-                                                     const double* __restrict__ ubar,
-                                                     const double* __restrict__ cur,
-                                                     double* __restrict__ next,
-                                                     unsigned long long* __restrict__ max_bits) {
+                                                              const double* __restrict__ ubar,
+                                                              const double* __restrict__ cur,
+                                                              double* __restrict__ next,
+                                                              unsigned long long* __restrict__ status) {
     __shared__ double sU[NV][BJ + 2];  // uBar of cells jo-2 .. jo+BJ-1
     __shared__ double sP[NV][BJ + 2];  // primitives of u^n there; later the interface fluxes
     __shared__ double sH[NV][BJ];      // bottom face state of each thread's cell
@@ -297,6 +266,7 @@ __global__ void __launch_bounds__(BJ, YS_MINB) y_sweep_kernel(const GridDims g, 
     const int jo = 2 + blockIdx.x * (BJ - 2);
     const int c = jo - 1 + tid;  // this thread's cell
     const int bc = p.bc_lo;      // the reference uses one y boundary type for both ends
+    D dv;
 
     for (int t = tid; t < BJ + 2; t += BJ) {
         const int jt = jo - 2 + t;
@@ -306,7 +276,7 @@ __global__ void __launch_bounds__(BJ, YS_MINB) y_sweep_kernel(const GridDims g, 
 #pragma unroll
             for (int k = 0; k < NV; ++k) sU[k][t] = q[k];
             load_row_cell(cur, g, i, jt, bc, q);
-            c2p_full_checked(q, p.gm1, v);
+            c2p_full(dv, q, p.gm1, v);
 #pragma unroll
             for (int k = 0; k < NV; ++k) sP[k][t] = v[k];
         }
@@ -320,17 +290,20 @@ __global__ void __launch_bounds__(BJ, YS_MINB) y_sweep_kernel(const GridDims g, 
         if (image) {
             // ghost face states are the (sign-flipped) face states of cell 3 / ny: the reference
             // applies its boundary function to the half-step arrays (MUSCL_NEW.cpp:940-941)
-            bool b2;
-            y_halfstates_global<IeeeDiv>(g, p, ubar, cur, i, (c == 1) ? 3 : g.ny, hB, hT, b2);
+            double tB[NV], tT[NV];
+            y_halfstates_global(dv, g, p, ubar, cur, i, (c == 1) ? 3 : g.ny, tB, tT);
+#pragma unroll
+            for (int k = 0; k < NV; ++k) {
+                hB[k] = tB[k];
+                hT[k] = tT[k];
+                ub[k] = 0.0;
+            }
             if (bc == BC_REFLECTIVE) {
                 hB[2] = -hB[2]; hB[6] = -hB[6];
                 hT[2] = -hT[2]; hT[6] = -hT[6];
             }
-#pragma unroll
-            for (int k = 0; k < NV; ++k) ub[k] = 0.0;
         } else {
             const int t = tid + 1;
-            FastDiv dv;
 #pragma unroll
             for (int k = 0; k < NV; ++k) {
                 ub[k] = sU[k][t];
@@ -338,10 +311,6 @@ __global__ void __launch_bounds__(BJ, YS_MINB) y_sweep_kernel(const GridDims g, 
                              hT[k]);
             }
             predictor<1>(dv, hB, hT, p.gm1, p.ch2, p.hdtdh);
-            if (dv.bad) {
-                bool b2;
-                y_halfstates_global<IeeeDiv>(g, p, ubar, cur, i, c, hB, hT, b2);
-            }
         }
 #pragma unroll
         for (int k = 0; k < NV; ++k) sH[k][tid] = hB[k];
@@ -355,7 +324,7 @@ __global__ void __launch_bounds__(BJ, YS_MINB) y_sweep_kernel(const GridDims g, 
         double nb[NV];
 #pragma unroll
         for (int k = 0; k < NV; ++k) nb[k] = sH[k][tid + 1];
-        hllc_flux_checked<1>(hT, nb, p, F);
+        hllc_flux<1>(dv, hT, nb, p.gamma, p.gm1, p.ch, p.ch2, p.inv2ch, p.halfch, F);
 #pragma unroll
         for (int k = 0; k < NV; ++k) sP[k][tid] = F[k];
     }
@@ -373,17 +342,21 @@ __global__ void __launch_bounds__(BJ, YS_MINB) y_sweep_kernel(const GridDims g, 
             un[k] = v;
             next[(size_t)k * g.plane + o] = v;
         }
-        const double sp = cfl_speed_checked(un, p.gamma);
+        const double sp = cfl_speed(dv, un, p.gamma);
         if (sp > speed) speed = sp;
     }
-    block_max_to_global(speed, max_bits);
+    if (dv.bad) atomicOr(status + 1, 1ull);
+    block_max_to_global(speed, status);
 }
 
-void launch_y_sweep(const GridDims& g, const SweepParams& p, const double* u_bar, const double* u_cur,
-                    double* u_next, unsigned long long* max_bits, cudaStream_t s) {
+void launch_y_sweep(const GridDims& g, const SweepParams& p, bool ieee, const double* u_bar, const double* u_cur,
+                    double* u_next, unsigned long long* status, cudaStream_t s) {
     dim3 block(BJ);
     dim3 grid((g.ny + (BJ - 2) - 1) / (BJ - 2), g.nxl);
-    y_sweep_kernel<<<grid, block, 0, s>>>(g, p, u_bar, u_cur, u_next, max_bits);
+    if (ieee)
+        y_sweep_kernel<IeeeDiv><<<grid, block, 0, s>>>(g, p, u_bar, u_cur, u_next, status);
+    else
+        y_sweep_kernel<FastDiv><<<grid, block, 0, s>>>(g, p, u_bar, u_cur, u_next, status);
 }
 
 // ------------------------------------------------------------------------------------
@@ -424,7 +397,8 @@ __global__ void max_speed_kernel(const GridDims g, double gamma, const double* _
         for (int i = i_lo + blockIdx.y; i <= i_hi; i += gridDim.y) {
             double q[NV];
             load_cell(u, g.plane, cell_index(g, i, j), q);
-            const double sp = cfl_speed_checked(q, gamma);
+            IeeeDiv dv;  // cold kernel (once per upload): plain IEEE division
+            const double sp = cfl_speed(dv, q, gamma);
             if (sp > best) best = sp;
         }
     }

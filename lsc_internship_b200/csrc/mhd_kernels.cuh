@@ -42,10 +42,12 @@ struct SweepParams {
                          // end is an inter-rank slab edge (ghost columns then hold neighbour data)
 };
 
-void launch_x_sweep(const GridDims& g, const SweepParams& p, const double* u_cur, const double* u_prev,
-                    double* u_bar, cudaStream_t s);
-void launch_y_sweep(const GridDims& g, const SweepParams& p, const double* u_bar, const double* u_cur,
-                    double* u_next, unsigned long long* max_bits, cudaStream_t s);
+// status[0] = bit pattern of the max signal speed (y sweep), status[1] = sticky "a fast division saw an
+// operand outside its guarded window" flag.  ieee = true launches the IeeeDiv instantiation.
+void launch_x_sweep(const GridDims& g, const SweepParams& p, bool ieee, const double* u_cur, const double* u_prev,
+                    double* u_bar, unsigned long long* status, cudaStream_t s);
+void launch_y_sweep(const GridDims& g, const SweepParams& p, bool ieee, const double* u_bar, const double* u_cur,
+                    double* u_next, unsigned long long* status, cudaStream_t s);
 void launch_x_ghosts(const GridDims& g, int bc_x, double* u, cudaStream_t s);
 void launch_max_speed(const GridDims& g, double gamma, const double* u, int i_lo, int i_hi, int j_lo, int j_hi,
                       unsigned long long* max_bits, cudaStream_t s);

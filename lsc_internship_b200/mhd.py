@@ -113,6 +113,10 @@ class MusclNew:
         check(lib().lsc_mhd_kernel_times(self._h, ms, n))
         return ms[0], ms[1], n[0], n[1]
 
+    def ieee_fallback_count(self):
+        """Steps recomputed with IEEE division because a fast division flagged an operand."""
+        return lib().lsc_mhd_ieee_fallback_count(self._h)
+
     def scalars(self):
         t, dt, ch = ctypes.c_double(), ctypes.c_double(), ctypes.c_double()
         n = ctypes.c_long()

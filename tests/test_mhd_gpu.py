@@ -194,6 +194,30 @@ def test_random_perturbed_state_parity():
     s.close()
 
 
+def test_out_of_window_operands_take_the_ieee_path():
+    """Operands outside the fast division's guarded window (here rho*vz = 1e-200 and Bz = 1e-180 in a few
+    cells) must trigger the recompute-with-IEEE-division path and still match the oracle bit for bit."""
+    nx, ny = 48, 40
+    cfg = mhd_cfg(nx, ny)
+    u0 = mhd_ic(cfg, "ot")
+    u0[10:14, 7:30, 3] = 1e-200
+    u0[20:22, 5:9, 7] = -1e-180
+    o = OracleMhd(cfg, u0)
+    s = lsc.MusclNew(nx, ny, 0, 1, 0, 1, bc_x="periodic", bc_y="periodic", problem="ot")
+    s.upload(u0)
+    o.step(3)
+    s.step(3)
+    assert s.ieee_fallback_count() >= 1
+    assert np.array_equal(bits(s.download()), bits(o.state()[0]))
+    s.close()
+    # and a clean run never takes it
+    s = lsc.MusclNew(nx, ny, 0, 1, 0, 1, bc_x="periodic", bc_y="periodic", problem="ot")
+    s.upload(mhd_ic(cfg, "ot"))
+    s.step(5)
+    assert s.ieee_fallback_count() == 0
+    s.close()
+
+
 def test_init_problem_equals_upload():
     a = lsc.MusclNew(100, 60, 0, 1, 0, 1, bc_x="periodic", bc_y="periodic", problem="ot")
     b = lsc.MusclNew(100, 60, 0, 1, 0, 1, bc_x="periodic", bc_y="periodic", problem="ot")
