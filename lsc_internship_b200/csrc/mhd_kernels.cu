@@ -60,13 +60,13 @@ __device__ __forceinline__ void block_max_to_global(double local, unsigned long 
 #define XS_BLOCK 128
 #endif
 #ifndef XS_MINB
-#define XS_MINB 1
+#define XS_MINB 4
 #endif
 #ifndef XS_STRIP
 #define XS_STRIP 64
 #endif
 #ifndef YS_MINB
-#define YS_MINB 1
+#define YS_MINB 4
 #endif
 #ifndef YS_BJ
 #define YS_BJ 128
@@ -107,16 +107,17 @@ __device__ __noinline__ void x_halfstates_global(D& dv, const GridDims g, const 
     predictor<0>(dv, hL, hR, p.gm1, p.ch2, p.hdtdh);
 }
 
-template <class D, int STRIP>
+template <class D>
 __global__ void __launch_bounds__(XS_BLOCK, XS_MINB) x_sweep_kernel(const GridDims g, const SweepParams p,
                                                                     const double* __restrict__ cur,
                                                                     const double* __restrict__ prev,
                                                                     double* __restrict__ ubar,
-                                                                    unsigned long long* __restrict__ status) {
+                                                                    unsigned long long* __restrict__ status,
+                                                                    const int strip) {
     const int j = 2 + blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= g.ny + 2) return;
-    const int ia = 2 + blockIdx.y * STRIP;
-    const int ib = min(ia + STRIP, g.nxl + 2);  // cells [ia, ib) are updated by this thread
+    const int ia = 2 + blockIdx.y * strip;
+    const int ib = min(ia + strip, g.nxl + 2);  // cells [ia, ib) are updated by this thread
     const bool lo_image = (ia == 2) && (p.bc_lo == BC_TRANSMISSIVE);
     const bool hi_image = (ib == g.nxl + 2) && (p.bc_hi == BC_TRANSMISSIVE);
     D dv;
@@ -193,13 +194,17 @@ __global__ void __launch_bounds__(XS_BLOCK, XS_MINB) x_sweep_kernel(const GridDi
 
 void launch_x_sweep(const GridDims& g, const SweepParams& p, bool ieee, const double* u_cur, const double* u_prev,
                     double* u_bar, unsigned long long* status, cudaStream_t s) {
-    constexpr int STRIP = XS_STRIP;
+    // strip length along i: XS_STRIP columns per thread (3 warm-up cells amortised over the strip), shortened
+    // on small grids so that the launch still fills 148 SMs x 4 resident blocks a few times over
     dim3 block(XS_BLOCK);
-    dim3 grid((g.ny + block.x - 1) / block.x, (g.nxl + STRIP - 1) / STRIP);
+    const int row_blocks = (g.ny + block.x - 1) / block.x;
+    int strip = XS_STRIP;
+    while (strip > 8 && (long)row_blocks * ((g.nxl + strip - 1) / strip) < 148L * 4 * 3) strip /= 2;
+    dim3 grid(row_blocks, (g.nxl + strip - 1) / strip);
     if (ieee)
-        x_sweep_kernel<IeeeDiv, STRIP><<<grid, block, 0, s>>>(g, p, u_cur, u_prev, u_bar, status);
+        x_sweep_kernel<IeeeDiv><<<grid, block, 0, s>>>(g, p, u_cur, u_prev, u_bar, status, strip);
     else
-        x_sweep_kernel<FastDiv, STRIP><<<grid, block, 0, s>>>(g, p, u_cur, u_prev, u_bar, status);
+        x_sweep_kernel<FastDiv><<<grid, block, 0, s>>>(g, p, u_cur, u_prev, u_bar, status, strip);
 }
 
 // ------------------------------------------------------------------------------------
