@@ -45,6 +45,17 @@ def main():
     for f in ["MHD0.dat", "MHD1.dat", "MHD2.dat", "MHD60.dat", "MHD121.dat", "euler_1.dat", "euler_20.dat"]:
         with open(os.path.join(REF, "MHD_plot_data", f), "rb") as fh:
             sha[f] = hashlib.sha256(fh.read()).hexdigest()
+    # the reference program itself (committed config) run to tStop = 0.25: its stdout log and final dump
+    import subprocess
+    import tempfile
+    from oracle_util import REF_DIR
+    with tempfile.TemporaryDirectory() as td:
+        r = subprocess.run([os.path.join(REF_DIR, "muscl_ref"), "kh", "128", "256", "0", "1", "-1", "1", "0.25", "0.8",
+                            "periodic", "reflective", "-1", "1"], cwd=td, check=True, capture_output=True, text=True)
+        with open(os.path.join(HERE, "muscl_new_stdout_t025.txt"), "w") as fh:
+            fh.write(r.stdout)
+        with open(os.path.join(td, "MHD3.dat"), "rb") as fh:
+            sha["MHD3.dat@tStop=0.25"] = hashlib.sha256(fh.read()).hexdigest()
     with open(os.path.join(HERE, "dat_sha256.json"), "w") as fh:
         json.dump(sha, fh, indent=1, sort_keys=True)
     print(sha)

@@ -244,6 +244,22 @@ def test_run_until_and_dat_writer_reproduce_reference_files(tmp_path, golden_dir
         assert h == sha[f"MHD{k}.dat"], f"MHD{k}.dat differs from the reference's committed file"
 
 
+def test_cpp_driver_is_a_drop_in_for_the_reference_program(tmp_path, golden_dir):
+    """drivers/muscl_new (C++ host driver over the C ABI) with the committed defaults, tStop = 0.25: stdout must
+    equal the reference program's stdout and MHD0..3.dat must be byte-identical to the reference's files."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "drivers", "_bin", "muscl_new")
+    if not os.path.exists(exe):
+        subprocess.run(["make", "-C", os.path.join(root, "drivers")], check=True)
+    r = subprocess.run([exe, "--tstop", "0.25"], cwd=tmp_path, check=True, capture_output=True, text=True)
+    assert r.stdout == open(os.path.join(golden_dir, "muscl_new_stdout_t025.txt")).read()
+    sha = json.load(open(os.path.join(golden_dir, "dat_sha256.json")))
+    for k, key in ((0, "MHD0.dat"), (1, "MHD1.dat"), (2, "MHD2.dat"), (3, "MHD3.dat@tStop=0.25")):
+        h = hashlib.sha256(open(tmp_path / f"MHD{k}.dat", "rb").read()).hexdigest()
+        assert h == sha[key], f"MHD{k}.dat differs"
+
+
 def test_large_grid_properties():
     """At sizes the CPU oracle cannot reach quickly: conservation under periodic BCs (the flux-difference
     form telescopes; rho, momenta, E, B sums drift only by rounding) and x<->y block-periodicity."""
