@@ -112,6 +112,12 @@ int lsc_mhd_step(lsc_mhd_ctx* ctx, long nsteps);
 int lsc_mhd_run_until(lsc_mhd_ctx* ctx, double t_stop, lsc_mhd_dump_cb dump_cb, lsc_mhd_log_cb log_cb,
                       void* user, long* steps_out);
 
+/* Single-process slab group: `n` contexts created with nranks = n, rank = 0..n-1 (on one or several GPUs
+ * of this process; cfg.device per context) are advanced in lock step.  Halo columns move by peer copies
+ * between the contexts' buffers, the signal speed is reduced on the host.  Same kernels and slab-edge code
+ * as the NCCL mode; results are bit-identical to the single-context run for any n. */
+int lsc_mhd_group_step(lsc_mhd_ctx** ctxs, int n, long nsteps);
+
 /* As lsc_mhd_step, bracketed by CUDA events on the context's own stream; *ms receives the device
  * time of the whole call (kernels, the per-step 8-byte readback of the signal speed, ghost/halo fill). */
 int lsc_mhd_step_timed(lsc_mhd_ctx* ctx, long nsteps, float* ms);
@@ -133,6 +139,11 @@ int lsc_mhd_get_scalars(const lsc_mhd_ctx* ctx, double* t, double* dt, double* c
  * contents the reference's `u` holds after M:971 (boundary images; the four never-written corner
  * cells [nx+2..nx+3][ny+2..ny+3] are zero once a step has been taken). */
 int lsc_mhd_download(lsc_mhd_ctx* ctx, double* aos);
+
+/* Host helper for callers that assemble a full-grid array from slabs: rebuilds the ghost ring the
+ * reference's `u` holds after M:971 (boundary images per cfg->bc_x / bc_y with the reference's loop bounds,
+ * the four never-written corner cells zero) from the interior of `aos` [(nx+4)][(ny+4)][9]. */
+int lsc_mhd_fill_ghost_ring(const lsc_mhd_config* cfg, double* aos);
 
 /* Byte-compatible writer of M:989-1001 / M:1022-1032 for a FULL-grid AoS array (ghost ring
  * included, as returned by lsc_mhd_download on a single-rank context): primitive variables,

@@ -72,6 +72,8 @@ struct lsc_mhd_ctx {
     bool uploaded = false;
     bool ghosts_current = false;  // x ghost/halo columns of state[cur] hold boundary images
     lsc::Comm* comm = nullptr;
+    bool in_group = false;            // driven by lsc_mhd_group_step (single-process slab group)
+    cudaEvent_t halo_event = nullptr;  // "u^{n+1} complete" marker for neighbours in a group
     bool profiling = false;
     std::vector<cudaEvent_t> prof_events;  // quadruples: x begin, x end, y begin, y end
 };
@@ -153,7 +155,8 @@ int lsc_mhd_create(const lsc_mhd_config* cfg, lsc_mhd_ctx** out) {
     if (cudaMalloc(&c->d_stage, col_bytes * (size_t)cols) != cudaSuccess ||
         cudaMalloc(&c->d_max, 2 * sizeof(unsigned long long)) != cudaSuccess ||
         cudaHostAlloc(&c->h_max, 2 * sizeof(unsigned long long), cudaHostAllocDefault) != cudaSuccess ||
-        cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->halo_event, cudaEventDisableTiming) != cudaSuccess) {
         cudaGetLastError();
         lsc_mhd_destroy(c);
         return fail(LSC_ENOMEM, "allocation of staging / scalars / stream failed");
@@ -172,6 +175,7 @@ int lsc_mhd_destroy(lsc_mhd_ctx* c) {
     if (c->d_stage) cudaFree(c->d_stage);
     if (c->d_max) cudaFree(c->d_max);
     if (c->h_max) cudaFreeHost(c->h_max);
+    if (c->halo_event) cudaEventDestroy(c->halo_event);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
     return LSC_OK;
@@ -286,31 +290,45 @@ int fill_x_ghosts(lsc_mhd_ctx* c, int b) {
     return LSC_OK;
 }
 
-// Read back {max signal speed, fast-division flag} of the step launched last.  If the flag is set the
-// step is recomputed from its inputs, which are still intact (state[prev] = u^n, state[spare] = u^{n-1}),
-// with the IeeeDiv kernels.
+// 16-byte readback of {max signal speed bits, fast-division flag} of this context (no communication).
+int read_status_local(lsc_mhd_ctx* c) {
+    CUDA_TRY(cudaSetDevice(c->cfg.device));
+    CUDA_TRY(cudaMemcpyAsync(c->h_max, c->d_max, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    return LSC_OK;
+}
+
+// Recompute the step launched last with IEEE division.  Its inputs are still intact: state[prev] = u^n,
+// state[spare] = u^{n-1}; the result overwrites state[cur].
+int relaunch_last_step_ieee(lsc_mhd_ctx* c) {
+    CUDA_TRY(cudaSetDevice(c->cfg.device));
+    c->ieee_redos += 1;
+    CUDA_TRY(cudaMemsetAsync(c->d_max, 0, 2 * sizeof(unsigned long long), c->stream));
+    lsc::launch_x_sweep(c->g, c->last_px, true, c->state[c->prev], c->state[c->spare], c->state[c->bar], c->d_max,
+                        c->stream);
+    lsc::launch_y_sweep(c->g, c->last_py, true, c->state[c->bar], c->state[c->prev], c->state[c->cur], c->d_max,
+                        c->stream);
+    lsc_count_launches(2);
+    CUDA_TRY(cudaGetLastError());
+    return LSC_OK;
+}
+
+// Read back the status of the step launched last; if a fast division flagged an operand anywhere, recompute.
 int resolve_pending(lsc_mhd_ctx* c) {
     if (!c->pending) return LSC_OK;
+    if (c->in_group) return fail(LSC_ESTATE, "context belongs to a group: use the lsc_mhd_group_* calls");
     for (int attempt = 0; attempt < 2; ++attempt) {
         if (c->cfg.nranks > 1) {
             if (!c->comm) return fail(LSC_ESTATE, "nranks > 1 but lsc_mhd_comm_init was not called");
             if (lsc::comm_allreduce_max_u64(c->comm, c->d_max, 2, c->stream))
                 return fail(LSC_ECOMM, "allreduce failed: %s", lsc::comm_error());
         }
-        CUDA_TRY(cudaMemcpyAsync(c->h_max, c->d_max, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost,
-                                 c->stream));
-        CUDA_TRY(cudaStreamSynchronize(c->stream));
+        int rc = read_status_local(c);
+        if (rc) return rc;
         if (c->h_max[1] == 0 || attempt == 1) break;
-        // ---- recompute the last step with IEEE division
-        c->ieee_redos += 1;
-        CUDA_TRY(cudaMemsetAsync(c->d_max, 0, 2 * sizeof(unsigned long long), c->stream));
-        lsc::launch_x_sweep(c->g, c->last_px, true, c->state[c->prev], c->state[c->spare], c->state[c->bar],
-                            c->d_max, c->stream);
-        lsc::launch_y_sweep(c->g, c->last_py, true, c->state[c->bar], c->state[c->prev], c->state[c->cur],
-                            c->d_max, c->stream);
-        lsc_count_launches(2);
-        CUDA_TRY(cudaGetLastError());
-        int rc = fill_x_ghosts(c, c->cur);
+        rc = relaunch_last_step_ieee(c);
+        if (rc) return rc;
+        rc = fill_x_ghosts(c, c->cur);
         if (rc) return rc;
     }
     std::memcpy(&c->max_speed, &c->h_max[0], sizeof(double));
@@ -318,13 +336,10 @@ int resolve_pending(lsc_mhd_ctx* c) {
     return LSC_OK;
 }
 
-// One pass of the loop body MUSCL_NEW.cpp:831-971.
-int step_once(lsc_mhd_ctx* c) {
-    // ---- ComputeTimeStep (:833-835): the reduction already ran on the device
-    {
-        int rc = resolve_pending(c);
-        if (rc) return rc;
-    }
+// ComputeTimeStep's scalars (MUSCL_NEW.cpp:117-118, :834-835) and the two sweeps (:841-965) for one context.
+// The x ghost columns of state[cur] must be current.  Rotates the buffers (u = uPlus1, :969).
+int launch_sweeps(lsc_mhd_ctx* c) {
+    CUDA_TRY(cudaSetDevice(c->cfg.device));
     const double max_speed = c->max_speed;
     if (!(max_speed > 0.0) || !std::isfinite(max_speed))
         return fail(LSC_ENAN, "max signal speed is %g at step %ld", max_speed, c->step);
@@ -334,13 +349,6 @@ int step_once(lsc_mhd_ctx* c) {
     c->t += dt;                                         // :835
     c->dt = dt;
     c->ch = ch;
-
-    // ---- applyBoundaryConditions(u) (:838) -- only the x ghost columns are ever read on the device
-    if (!c->ghosts_current) {
-        int rc = fill_x_ghosts(c, c->cur);
-        if (rc) return rc;
-        c->ghosts_current = true;
-    }
 
     lsc::SweepParams p{};
     p.gamma = c->cfg.gamma;
@@ -390,10 +398,100 @@ int step_once(lsc_mhd_ctx* c) {
     c->prev = c->cur;
     c->cur = next;
     c->pending = true;
-    // ---- applyBoundaryConditions(u) (:971)
-    int rc = fill_x_ghosts(c, c->cur);
-    if (rc) return rc;
     c->step += 1;
+    return LSC_OK;
+}
+
+// One pass of the loop body MUSCL_NEW.cpp:831-971.
+int step_once(lsc_mhd_ctx* c) {
+    int rc = resolve_pending(c);  // ComputeTimeStep (:833): the reduction already ran on the device
+    if (rc) return rc;
+    if (!c->ghosts_current) {  // applyBoundaryConditions(u) (:838): only x ghost columns are read on the device
+        rc = fill_x_ghosts(c, c->cur);
+        if (rc) return rc;
+        c->ghosts_current = true;
+    }
+    rc = launch_sweeps(c);
+    if (rc) return rc;
+    return fill_x_ghosts(c, c->cur);  // applyBoundaryConditions(u) (:971)
+}
+
+// ---------------------------------------------------------------------------------------------
+// Single-process slab group: P contexts (on one or several GPUs of this process) advanced in lock
+// step, halos moved by cudaMemcpyPeerAsync between the contexts' buffers, max reduced on the host.
+// Same kernels and same slab-edge code path as the NCCL mode.
+// ---------------------------------------------------------------------------------------------
+int group_halo(lsc_mhd_ctx** g, int n) {
+    const bool ring = (g[0]->cfg.bc_x == LSC_BC_PERIODIC);
+    for (int r = 0; r < n; ++r) {  // mark "u^{n+1} of rank r is complete"
+        CUDA_TRY(cudaSetDevice(g[r]->cfg.device));
+        CUDA_TRY(cudaEventRecord(g[r]->halo_event, g[r]->stream));
+    }
+    for (int r = 0; r < n; ++r) {
+        lsc_mhd_ctx* c = g[r];
+        CUDA_TRY(cudaSetDevice(c->cfg.device));
+        const int left = (r > 0) ? r - 1 : (ring ? n - 1 : -1);
+        const int right = (r < n - 1) ? r + 1 : (ring ? 0 : -1);
+        const size_t bytes = 2 * (size_t)c->g.pitch * sizeof(double);
+        for (int side = 0; side < 2; ++side) {
+            const int nb = side == 0 ? left : right;
+            if (nb < 0) {
+                lsc::launch_x_ghosts_side(c->g, side, c->state[c->cur], c->stream);
+                lsc_count_launches(1);
+                continue;
+            }
+            lsc_mhd_ctx* o = g[nb];
+            CUDA_TRY(cudaStreamWaitEvent(c->stream, o->halo_event, 0));
+            for (int k = 0; k < lsc::NV; ++k) {
+                double* dst = c->state[c->cur] + (size_t)k * c->g.plane +
+                              (side == 0 ? 0 : (size_t)(c->g.nxl + 2) * c->g.pitch);
+                // left ghost <- neighbour's last two interior columns; right ghost <- its first two
+                const double* src = o->state[o->cur] + (size_t)k * o->g.plane +
+                                    (side == 0 ? (size_t)o->g.nxl * o->g.pitch : (size_t)2 * o->g.pitch);
+                CUDA_TRY(cudaMemcpyPeerAsync(dst, c->cfg.device, src, o->cfg.device, bytes, c->stream));
+            }
+        }
+    }
+    CUDA_TRY(cudaGetLastError());
+    return LSC_OK;
+}
+
+int group_resolve(lsc_mhd_ctx** g, int n) {
+    if (!g[0]->pending) return LSC_OK;
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        unsigned long long mx = 0, flag = 0;
+        for (int r = 0; r < n; ++r) {
+            int rc = read_status_local(g[r]);
+            if (rc) return rc;
+            mx = std::max(mx, g[r]->h_max[0]);
+            flag |= g[r]->h_max[1];
+        }
+        for (int r = 0; r < n; ++r) g[r]->h_max[0] = mx;
+        if (flag == 0 || attempt == 1) break;
+        for (int r = 0; r < n; ++r) {
+            int rc = relaunch_last_step_ieee(g[r]);
+            if (rc) return rc;
+        }
+        int rc = group_halo(g, n);
+        if (rc) return rc;
+    }
+    for (int r = 0; r < n; ++r) {
+        std::memcpy(&g[r]->max_speed, &g[r]->h_max[0], sizeof(double));
+        g[r]->pending = false;
+    }
+    return LSC_OK;
+}
+
+int group_check(lsc_mhd_ctx** g, int n) {
+    if (!g || n < 1) return fail(LSC_EINVAL, "empty group");
+    for (int r = 0; r < n; ++r) {
+        if (!g[r]) return fail(LSC_EINVAL, "null context in group");
+        if (g[r]->cfg.nranks != n || g[r]->cfg.rank != r)
+            return fail(LSC_EINVAL, "group member %d has rank %d of %d", r, g[r]->cfg.rank, g[r]->cfg.nranks);
+        if (!g[r]->uploaded) return fail(LSC_ESTATE, "group member %d has no state uploaded", r);
+        if (g[r]->comm) return fail(LSC_ESTATE, "group member %d is attached to NCCL", r);
+        if (g[r]->step != g[0]->step) return fail(LSC_ESTATE, "group members are at different steps");
+    }
     return LSC_OK;
 }
 
@@ -410,6 +508,30 @@ int lsc_mhd_step(lsc_mhd_ctx* c, long nsteps) {
         if (rc) return rc;
     }
     return resolve_pending(c);  // syncs; the state is final (and IEEE-exact) when this returns
+}
+
+int lsc_mhd_group_step(lsc_mhd_ctx** g, int n, long nsteps) {
+    int rc = group_check(g, n);
+    if (rc) return rc;
+    for (int r = 0; r < n; ++r) g[r]->in_group = true;
+    for (long s = 0; s < nsteps; ++s) {
+        rc = group_resolve(g, n);
+        if (rc) return rc;
+        if (!g[0]->ghosts_current) {
+            rc = group_halo(g, n);
+            if (rc) return rc;
+            for (int r = 0; r < n; ++r) g[r]->ghosts_current = true;
+        }
+        for (int r = 0; r < n; ++r) {
+            rc = launch_sweeps(g[r]);
+            if (rc) return rc;
+        }
+        rc = group_halo(g, n);
+        if (rc) return rc;
+    }
+    rc = group_resolve(g, n);
+    for (int r = 0; r < n; ++r) g[r]->in_group = false;
+    return rc;
 }
 
 int lsc_mhd_step_timed(lsc_mhd_ctx* c, long nsteps, float* ms) {
@@ -513,6 +635,12 @@ int lsc_mhd_download(lsc_mhd_ctx* c, double* aos) {
             lsc::mhd_apply_bc_y(c->cfg, c->nxl + 4, aos);
         }
     }
+    return LSC_OK;
+}
+
+int lsc_mhd_fill_ghost_ring(const lsc_mhd_config* cfg, double* aos) {
+    if (!cfg || !aos) return fail(LSC_EINVAL, "null argument");
+    lsc::mhd_fill_ghost_ring(*cfg, aos);
     return LSC_OK;
 }
 

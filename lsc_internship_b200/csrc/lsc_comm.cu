@@ -60,21 +60,6 @@ void comm_destroy(Comm* c) {
     delete c;
 }
 
-// boundary image of one side only (end ranks of a non-periodic decomposition), MUSCL_NEW.cpp:617-622
-__global__ void x_ghost_side_kernel(const GridDims g, int hi_side, double* __restrict__ u) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= g.ny + 4) return;
-    double* pl = u + (size_t)blockIdx.y * g.plane;
-    const int nx = g.nxl;
-    if (hi_side) {
-        pl[cell_index(g, nx + 2, j)] = pl[cell_index(g, nx, j)];
-        pl[cell_index(g, nx + 3, j)] = pl[cell_index(g, nx + 1, j)];
-    } else {
-        pl[cell_index(g, 0, j)] = pl[cell_index(g, 2, j)];
-        pl[cell_index(g, 1, j)] = pl[cell_index(g, 3, j)];
-    }
-}
-
 int comm_exchange_halos(Comm* c, const GridDims& g, int bc_x, double* u, cudaStream_t s) {
     const bool ring = (bc_x == BC_PERIODIC);
     const int left = (c->rank > 0) ? c->rank - 1 : (ring ? c->nranks - 1 : -1);
@@ -93,13 +78,12 @@ int comm_exchange_halos(Comm* c, const GridDims& g, int bc_x, double* u, cudaStr
         }
     }
     NCCL_TRY(ncclGroupEnd(), -1);
-    dim3 block(256), grid((g.ny + 4 + 255) / 256, c->nvar);
     if (left < 0) {
-        x_ghost_side_kernel<<<grid, block, 0, s>>>(g, 0, u);
+        launch_x_ghosts_side(g, 0, u, s);
         lsc_count_launches(1);
     }
     if (right < 0) {
-        x_ghost_side_kernel<<<grid, block, 0, s>>>(g, 1, u);
+        launch_x_ghosts_side(g, 1, u, s);
         lsc_count_launches(1);
     }
     return 0;

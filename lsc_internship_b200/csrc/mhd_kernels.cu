@@ -391,6 +391,26 @@ void launch_x_ghosts(const GridDims& g, int bc_x, double* u, cudaStream_t s) {
     x_ghost_kernel<<<grid, block, 0, s>>>(g, bc_x, u);
 }
 
+// boundary image of one side only (end ranks of a non-periodic slab decomposition), MUSCL_NEW.cpp:617-622
+__global__ void x_ghost_side_kernel(const GridDims g, int hi_side, double* __restrict__ u) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= g.ny + 4) return;
+    double* pl = u + (size_t)blockIdx.y * g.plane;
+    const int nx = g.nxl;
+    if (hi_side) {
+        pl[cell_index(g, nx + 2, j)] = pl[cell_index(g, nx, j)];
+        pl[cell_index(g, nx + 3, j)] = pl[cell_index(g, nx + 1, j)];
+    } else {
+        pl[cell_index(g, 0, j)] = pl[cell_index(g, 2, j)];
+        pl[cell_index(g, 1, j)] = pl[cell_index(g, 3, j)];
+    }
+}
+
+void launch_x_ghosts_side(const GridDims& g, int hi_side, double* u, cudaStream_t s) {
+    dim3 block(256), grid((g.ny + 4 + 255) / 256, NV);
+    x_ghost_side_kernel<<<grid, block, 0, s>>>(g, hi_side, u);
+}
+
 // Stand-alone CFL reduction over cells [i_lo,i_hi] x [j_lo,j_hi] (inclusive).  The reference
 // reduces over i in [1,nx+1], j in [1,ny+1] of the array as it stands BEFORE the step's boundary
 // fill (MUSCL_NEW.cpp:73-74, :833 vs :838) -- on the first step that includes analytic ghost values.

@@ -49,6 +49,8 @@ void launch_x_sweep(const GridDims& g, const SweepParams& p, bool ieee, const do
 void launch_y_sweep(const GridDims& g, const SweepParams& p, bool ieee, const double* u_bar, const double* u_cur,
                     double* u_next, unsigned long long* status, cudaStream_t s);
 void launch_x_ghosts(const GridDims& g, int bc_x, double* u, cudaStream_t s);
+// transmissive image of ONE side (0 = low, 1 = high): end ranks of a non-periodic slab decomposition
+void launch_x_ghosts_side(const GridDims& g, int hi_side, double* u, cudaStream_t s);
 void launch_max_speed(const GridDims& g, double gamma, const double* u, int i_lo, int i_hi, int j_lo, int j_hi,
                       unsigned long long* max_bits, cudaStream_t s);
 void launch_aos_to_soa(const GridDims& g, const double* aos, int i0, int ni, double* soa, cudaStream_t s);

@@ -159,6 +159,72 @@ class MusclNew:
         check(lib().lsc_mhd_write_dat(ctypes.byref(self.cfg), _dp(u), os.fsencode(path)))
 
 
+def slab_range(nx, rank, nranks):
+    """First global interior column and width of rank's slab (same arithmetic as lsc_mhd_create)."""
+    b0 = rank * nx // nranks
+    b1 = (rank + 1) * nx // nranks
+    return b0, b1 - b0
+
+
+def neighbours(rank, nranks, bc_x):
+    """(left, right) neighbour ranks of a slab; -1 at a non-periodic physical boundary."""
+    ring = bc_x in ("periodic", _capi.BC_PERIODIC)
+    left = rank - 1 if rank > 0 else (nranks - 1 if ring else -1)
+    right = rank + 1 if rank < nranks - 1 else (0 if ring else -1)
+    return left, right
+
+
+class MusclNewGroup:
+    """P slabs of one grid driven in lock step from this process (lsc_mhd_group_step): on one GPU for
+    decomposition-invariance tests, or one slab per GPU with peer copies over NVLink."""
+
+    def __init__(self, nslabs, devices=None, **kw):
+        ndev = lib().lsc_device_count()
+        devices = devices if devices is not None else [r % max(ndev, 1) for r in range(nslabs)]
+        self.parts = [MusclNew(device=devices[r], rank=r, nranks=nslabs, **kw) for r in range(nslabs)]
+        self.cfg = MhdConfig.from_buffer_copy(self.parts[0].cfg)
+        self.cfg.rank, self.cfg.nranks = 0, 1
+        self._arr = (ctypes.c_void_p * nslabs)(*[p._h for p in self.parts])
+
+    @property
+    def shape(self):
+        return (self.cfg.nx + 4, self.cfg.ny + 4, 9)
+
+    def upload(self, u):
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        if u.shape != self.shape:
+            raise ValueError(f"state must have shape {self.shape}")
+        for p in self.parts:
+            p.upload(u[p.i0:p.i0 + p.nxl + 4])
+
+    def init_problem(self, problem=None):
+        for p in self.parts:
+            p.init_problem(problem)
+
+    def step(self, nsteps=1):
+        check(lib().lsc_mhd_group_step(self._arr, len(self.parts), int(nsteps)))
+
+    def scalars(self):
+        return self.parts[0].scalars()
+
+    def download(self):
+        """The full-grid array in the reference layout, ghost ring rebuilt as the reference holds it."""
+        u = np.zeros(self.shape, dtype=np.float64)
+        stepped = self.parts[0].scalars()[3] > 0
+        for p in self.parts:
+            s = p.download()
+            lo = 0 if p.cfg.rank == 0 else 2
+            hi = p.nxl + 4 if p.cfg.rank == p.cfg.nranks - 1 else p.nxl + 2
+            u[p.i0 + lo:p.i0 + hi] = s[lo:hi]
+        if stepped:
+            check(lib().lsc_mhd_fill_ghost_ring(ctypes.byref(self.cfg), _dp(u)))
+        return u
+
+    def close(self):
+        for p in self.parts:
+            p.close()
+
+
 def kat_hllc(L, R, gamma, ch, direction, device=0):
     """Device HLLC flux of n interface state pairs (test hook)."""
     L = np.ascontiguousarray(L, dtype=np.float64)
