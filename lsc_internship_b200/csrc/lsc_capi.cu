@@ -61,6 +61,7 @@ struct lsc_mhd_ctx {
     unsigned long long* d_max = nullptr;  // [0] bit pattern of the max signal speed of state[cur], [1] flag
     unsigned long long* h_max = nullptr;  // pinned copy of both words
     bool pending = false;                 // status of the last launched step not read back yet
+    bool pending_step = false;            // ... and that status belongs to a step (not to an upload)
     double max_speed = 0;                 // max signal speed of state[cur] once resolved
     lsc::SweepParams last_px{}, last_py{};
     long ieee_redos = 0;
@@ -213,6 +214,7 @@ int finish_upload(lsc_mhd_ctx* c) {
     c->uploaded = true;
     c->ghosts_current = false;
     c->pending = true;  // status[0] holds the initial signal speed, status[1] = 0
+    c->pending_step = false;
     return LSC_OK;
 }
 
@@ -398,6 +400,7 @@ int launch_sweeps(lsc_mhd_ctx* c) {
     c->prev = c->cur;
     c->cur = next;
     c->pending = true;
+    c->pending_step = true;
     c->step += 1;
     return LSC_OK;
 }
@@ -612,7 +615,7 @@ int lsc_mhd_download(lsc_mhd_ctx* c, double* aos) {
     if (!c || !aos) return fail(LSC_EINVAL, "null argument");
     if (!c->uploaded) return fail(LSC_ESTATE, "lsc_mhd_download before lsc_mhd_upload");
     CUDA_TRY(cudaSetDevice(c->cfg.device));
-    {
+    if (c->pending && c->pending_step) {  // a launched step may still have to be recomputed (IEEE path)
         int rc = resolve_pending(c);
         if (rc) return rc;
     }

@@ -68,14 +68,12 @@ int comm_exchange_halos(Comm* c, const GridDims& g, int bc_x, double* u, cudaStr
     NCCL_TRY(ncclGroupStart(), -1);
     for (int k = 0; k < c->nvar; ++k) {
         double* pl = u + (size_t)k * g.plane;
-        if (left >= 0) {
-            NCCL_TRY(ncclSend(pl + (size_t)2 * g.pitch, n, ncclDouble, left, c->nccl, s), -1);
-            NCCL_TRY(ncclRecv(pl, n, ncclDouble, left, c->nccl, s), -1);
-        }
-        if (right >= 0) {
-            NCCL_TRY(ncclSend(pl + (size_t)g.nxl * g.pitch, n, ncclDouble, right, c->nccl, s), -1);
-            NCCL_TRY(ncclRecv(pl + (size_t)(g.nxl + 2) * g.pitch, n, ncclDouble, right, c->nccl, s), -1);
-        }
+        // Posting order matters when left == right (two ranks on a periodic ring): NCCL matches the sends and
+        // receives of a pair in order, so "my low columns" must meet the peer's "high ghost" receive.
+        if (left >= 0) NCCL_TRY(ncclSend(pl + (size_t)2 * g.pitch, n, ncclDouble, left, c->nccl, s), -1);
+        if (right >= 0) NCCL_TRY(ncclRecv(pl + (size_t)(g.nxl + 2) * g.pitch, n, ncclDouble, right, c->nccl, s), -1);
+        if (right >= 0) NCCL_TRY(ncclSend(pl + (size_t)g.nxl * g.pitch, n, ncclDouble, right, c->nccl, s), -1);
+        if (left >= 0) NCCL_TRY(ncclRecv(pl, n, ncclDouble, left, c->nccl, s), -1);
     }
     NCCL_TRY(ncclGroupEnd(), -1);
     if (left < 0) {

@@ -242,6 +242,22 @@ def test_slab_decomposition_is_bit_invariant(prob, nx, ny, dom, bcx, bcy, nslabs
     g.close()
 
 
+def test_nccl_slab_path_is_bit_invariant():
+    """One process per GPU over NCCL (the bench.py --gpus N path).  Needs >= 2 GPUs; skipped otherwise."""
+    import subprocess
+    import sys
+    ndev = lsc.lib().lsc_device_count()
+    if ndev < 2:
+        pytest.skip("needs >= 2 GPUs (covered on one GPU by test_slab_decomposition_is_bit_invariant)")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    n = 2 if ndev < 4 else 4
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
+                        "--master-addr", "127.0.0.1", "--master-port", "29533",
+                        os.path.join(root, "scripts", "check_nccl_invariance.py")],
+                       capture_output=True, text=True, timeout=600)
+    assert "NCCL_INVARIANCE_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
 def test_init_problem_equals_upload():
     a = lsc.MusclNew(100, 60, 0, 1, 0, 1, bc_x="periodic", bc_y="periodic", problem="ot")
     b = lsc.MusclNew(100, 60, 0, 1, 0, 1, bc_x="periodic", bc_y="periodic", problem="ot")
