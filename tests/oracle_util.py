@@ -102,3 +102,71 @@ def run_muscl_ref(prob, nx, ny, dom, t_stop, cfl, bcx, bcy, nsteps, cwd=None, wr
         u = np.fromfile(st, dtype=np.float64).reshape(nx + 4, ny + 4, 9)
         log = np.fromfile(lg, dtype=np.float64).reshape(-1, 3)
     return u, log, r.stderr
+
+
+# ----------------------------------------------------------------------------------------------
+# Euler SLIC (Euler_codes/SLIC_euler_2d.cpp, generaliseSLIC.cpp)
+# ----------------------------------------------------------------------------------------------
+EULER_BC = {"periodic": 0, "transmissive": 1}
+EULER_IC = {"ot": 0, "quadrants": 1, "cylinder": 2}
+
+
+class OracleEulerCfg(ctypes.Structure):
+    _fields_ = [("nx", ctypes.c_int), ("ny", ctypes.c_int),
+                ("x0", ctypes.c_double), ("x1", ctypes.c_double),
+                ("y0", ctypes.c_double), ("y1", ctypes.c_double),
+                ("gamma", ctypes.c_double), ("cfl", ctypes.c_double), ("omega", ctypes.c_double),
+                ("bc", ctypes.c_int)]
+
+
+def euler_cfg(nx, ny, dom=(0.0, 1.0, 0.0, 1.0), gamma=1.4, cfl=0.8, omega=0.0, bc="periodic"):
+    return OracleEulerCfg(nx, ny, dom[0], dom[1], dom[2], dom[3], gamma, cfl, omega, EULER_BC[bc])
+
+
+def euler_ic(cfg, ic):
+    u = np.zeros((cfg.nx + 4, cfg.ny + 4, 4), dtype=np.float64)
+    oracle_lib().lsc_oracle_euler_ic(ctypes.byref(cfg), EULER_IC[ic], _dp(u))
+    return u
+
+
+class OracleEuler:
+    def __init__(self, cfg, u0):
+        self.cfg = cfg
+        self.lib = oracle_lib()
+        self.lib.lsc_oracle_euler_create.restype = ctypes.c_void_p
+        u0 = np.ascontiguousarray(u0, dtype=np.float64)
+        assert u0.shape == (cfg.nx + 4, cfg.ny + 4, 4)
+        self.h = ctypes.c_void_p(self.lib.lsc_oracle_euler_create(ctypes.byref(cfg), _dp(u0)))
+
+    def step(self, n=1):
+        log = np.zeros((n, 2), dtype=np.float64)
+        self.lib.lsc_oracle_euler_step(self.h, ctypes.c_long(n), _dp(log))
+        return log
+
+    def state(self):
+        u = np.zeros((self.cfg.nx + 4, self.cfg.ny + 4, 4), dtype=np.float64)
+        t, dt = ctypes.c_double(), ctypes.c_double()
+        self.lib.lsc_oracle_euler_get(self.h, _dp(u), ctypes.byref(t), ctypes.byref(dt))
+        return u, t.value, dt.value
+
+    def close(self):
+        if self.h:
+            self.lib.lsc_oracle_euler_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+
+def run_euler_ref(which, nx, ny, dom, t_stop, cfl, gamma, nsteps, ic=0, cwd=None, writedat=False):
+    """Run oracle/_ref/slic_ref (periodic, S) or gslic_ref (transmissive, G; ic 0 = its quadrants,
+    1 = cylindrical explosion).  Returns (state incl. ghosts, log[n,2] of (t,dt), stderr)."""
+    with tempfile.TemporaryDirectory() as td:
+        st, lg = os.path.join(td, "state.bin"), os.path.join(td, "log.bin")
+        cmd = [os.path.join(REF_DIR, which), str(nx), str(ny)] + [repr(float(d)) for d in dom] + \
+              [repr(float(t_stop)), repr(float(cfl)), repr(float(gamma)), str(nsteps), "1" if writedat else "0",
+               str(ic), st, lg]
+        r = subprocess.run(cmd, cwd=cwd or td, check=True, capture_output=True, text=True)
+        u = np.fromfile(st, dtype=np.float64).reshape(nx + 4, ny + 4, 4)
+        log = np.fromfile(lg, dtype=np.float64).reshape(-1, 2)
+    return u, log, r.stderr
