@@ -170,6 +170,48 @@ int lsc_mhd_kat_fluxdef(int device, int dir, long n, const double* U, double gam
 int lsc_kat_division(int device, unsigned long long seed, int mode, long nblocks, int per_thread,
                      unsigned long long* mismatches, unsigned long long* flagged);
 
+/* ------------------------------------------------------------------------------------------------
+ * 2-D Euler SLIC (S = Euler_codes/SLIC_euler_2d.cpp, G = Euler_codes/generaliseSLIC.cpp).
+ * One step = dt (S:165-195) -> BC -> A = XthenY(u) (S:230-376) -> B = YthenX(u) (S:379-525; its second
+ * sweep is dead in the reference, S:510 vs S:519) -> u = 0.5*(A+B) (S:609-615) -> BC.
+ * ---------------------------------------------------------------------------------------------- */
+#define LSC_EULER_IC_ORSZAG_TANG 0 /* S:585-589 (committed in S) */
+#define LSC_EULER_IC_QUADRANTS 1   /* G:594-617 (committed in G) */
+#define LSC_EULER_IC_CYLINDER 2    /* cylindrical explosion of BASELINE config 3: rho,p = 1,1 inside
+                                      (x-.5)^2+(y-.5)^2 <= 0.2^2, 0.125,0.1 outside, at rest (not in the reference) */
+
+/* Replaces the constants S:529-540 / G:565-577. */
+typedef struct lsc_euler_config {
+    int nx, ny;
+    double x0, x1, y0, y1;
+    double gamma; /* S:538 */
+    double cfl;   /* S:537 */
+    double omega; /* S:539 */
+    int bc;       /* LSC_BC_PERIODIC (S:198-226) | LSC_BC_TRANSMISSIVE_E (G:199-215), both axes */
+    int device;
+} lsc_euler_config;
+
+typedef struct lsc_euler_ctx lsc_euler_ctx;
+typedef void (*lsc_euler_log_cb)(long step, double t, double dt, void* user); /* G:631 "t = .. dt = .." */
+
+int lsc_euler_create(const lsc_euler_config* cfg, lsc_euler_ctx** out);
+int lsc_euler_destroy(lsc_euler_ctx* ctx);
+/* IC loop S:552-594 / G:586-620 followed by the boundary fill S:596, into [(nx+4)][(ny+4)][4]. Host libm. */
+int lsc_euler_initial_condition(const lsc_euler_config* cfg, int problem, double* aos);
+int lsc_euler_upload(lsc_euler_ctx* ctx, const double* aos);
+int lsc_euler_init_problem(lsc_euler_ctx* ctx, int problem);
+int lsc_euler_step(lsc_euler_ctx* ctx, long nsteps);                 /* n passes of the do-body S:600-616 */
+int lsc_euler_step_timed(lsc_euler_ctx* ctx, long nsteps, float* ms);
+/* do { step } while (t < t_stop)  -- S:600-617 with t_stop = tStop/(21-counter), G:627-646 with tStop. */
+int lsc_euler_run_until(lsc_euler_ctx* ctx, double t_stop, lsc_euler_log_cb log_cb, void* user, long* steps_out);
+int lsc_euler_get_scalars(const lsc_euler_ctx* ctx, double* t, double* dt, long* step);
+int lsc_euler_download(lsc_euler_ctx* ctx, double* aos);              /* u after S:616, ghost ring included */
+/* S:621-642 (blank_line_per_row = 0, euler_<k>.dat) / G:645-667 (= 1, SLIC2d.dat) */
+int lsc_euler_write_dat(const lsc_euler_config* cfg, const double* aos, const char* path, int blank_line_per_row);
+long lsc_euler_ieee_fallback_count(const lsc_euler_ctx* ctx);
+int lsc_euler_set_profiling(lsc_euler_ctx* ctx, int enabled);
+int lsc_euler_kernel_times(lsc_euler_ctx* ctx, double ms[2], long launches[2]);
+
 /* number of kernels this library has launched in this process (for bench.py's gpu_launches) */
 unsigned long long lsc_kernel_launch_count(void);
 

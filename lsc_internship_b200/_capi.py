@@ -38,6 +38,18 @@ class MhdConfig(ctypes.Structure):
                 ("device", ctypes.c_int), ("rank", ctypes.c_int), ("nranks", ctypes.c_int)]
 
 
+class EulerConfig(ctypes.Structure):
+    """struct lsc_euler_config -- the constants of SLIC_euler_2d.cpp:529-540."""
+    _fields_ = [("nx", ctypes.c_int), ("ny", ctypes.c_int),
+                ("x0", ctypes.c_double), ("x1", ctypes.c_double),
+                ("y0", ctypes.c_double), ("y1", ctypes.c_double),
+                ("gamma", ctypes.c_double), ("cfl", ctypes.c_double), ("omega", ctypes.c_double),
+                ("bc", ctypes.c_int), ("device", ctypes.c_int)]
+
+
+EULER_PROBLEMS = {"ot": 0, "orszag-tang": 0, "quadrants": 1, "cylinder": 2}
+EULER_LOG_CB = ctypes.CFUNCTYPE(None, ctypes.c_long, ctypes.c_double, ctypes.c_double, ctypes.c_void_p)
+
 DUMP_CB = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_double, ctypes.c_double,
                            ctypes.c_void_p)
 LOG_CB = ctypes.CFUNCTYPE(None, ctypes.c_long, ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_void_p)
@@ -50,6 +62,10 @@ EXPORTS = [
     "lsc_mhd_run_until", "lsc_mhd_get_scalars", "lsc_mhd_download", "lsc_mhd_write_dat",
     "lsc_comm_unique_id", "lsc_mhd_comm_init", "lsc_mhd_kat_hllc", "lsc_mhd_kat_fluxdef",
     "lsc_kernel_launch_count", "lsc_mhd_step_timed", "lsc_mhd_set_profiling", "lsc_mhd_kernel_times", "lsc_kat_division", "lsc_mhd_ieee_fallback_count", "lsc_mhd_group_step", "lsc_mhd_fill_ghost_ring",
+    "lsc_euler_create", "lsc_euler_destroy", "lsc_euler_initial_condition", "lsc_euler_upload",
+    "lsc_euler_init_problem", "lsc_euler_step", "lsc_euler_step_timed", "lsc_euler_run_until",
+    "lsc_euler_get_scalars", "lsc_euler_download", "lsc_euler_write_dat", "lsc_euler_ieee_fallback_count",
+    "lsc_euler_set_profiling", "lsc_euler_kernel_times",
 ]
 
 _lib = None
@@ -94,6 +110,22 @@ def lib():
     L.lsc_kat_division.argtypes = [ctypes.c_int, ctypes.c_ulonglong, ctypes.c_int, ctypes.c_long, ctypes.c_int,
                                    ctypes.POINTER(ctypes.c_ulonglong), ctypes.POINTER(ctypes.c_ulonglong)]
     L.lsc_mhd_group_step.argtypes = [ctypes.POINTER(vp), ctypes.c_int, ctypes.c_long]
+    ecfg = ctypes.POINTER(EulerConfig)
+    L.lsc_euler_create.argtypes = [ecfg, ctypes.POINTER(vp)]
+    L.lsc_euler_destroy.argtypes = [vp]
+    L.lsc_euler_initial_condition.argtypes = [ecfg, ctypes.c_int, dp]
+    L.lsc_euler_upload.argtypes = [vp, dp]
+    L.lsc_euler_init_problem.argtypes = [vp, ctypes.c_int]
+    L.lsc_euler_step.argtypes = [vp, ctypes.c_long]
+    L.lsc_euler_step_timed.argtypes = [vp, ctypes.c_long, ctypes.POINTER(ctypes.c_float)]
+    L.lsc_euler_run_until.argtypes = [vp, ctypes.c_double, EULER_LOG_CB, vp, ctypes.POINTER(ctypes.c_long)]
+    L.lsc_euler_get_scalars.argtypes = [vp, dp, dp, ctypes.POINTER(ctypes.c_long)]
+    L.lsc_euler_download.argtypes = [vp, dp]
+    L.lsc_euler_write_dat.argtypes = [ecfg, dp, ctypes.c_char_p, ctypes.c_int]
+    L.lsc_euler_ieee_fallback_count.argtypes = [vp]
+    L.lsc_euler_ieee_fallback_count.restype = ctypes.c_long
+    L.lsc_euler_set_profiling.argtypes = [vp, ctypes.c_int]
+    L.lsc_euler_kernel_times.argtypes = [vp, dp, ctypes.POINTER(ctypes.c_long)]
     L.lsc_mhd_fill_ghost_ring.argtypes = [ctypes.POINTER(MhdConfig), dp]
     L.lsc_mhd_ieee_fallback_count.argtypes = [vp]
     L.lsc_mhd_ieee_fallback_count.restype = ctypes.c_long

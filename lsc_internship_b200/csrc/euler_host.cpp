@@ -1,0 +1,103 @@
+// euler_host.cpp -- host-side pieces of the Euler SLIC solver surface that must match the reference
+// bit-for-bit / byte-for-byte: initial conditions (SLIC_euler_2d.cpp:552-596, generaliseSLIC.cpp:586-622),
+// the ghost ring of a downloaded state (S:198-226, G:199-215) and the .dat writers (S:621-642, G:645-667).
+#include "euler_host.h"
+
+#include <cmath>
+#include <cstring>
+#include <fstream>
+
+namespace lsc {
+
+namespace {
+inline double* at(double* a, int ny, int i, int j) { return a + ((size_t)i * (size_t)(ny + 4) + (size_t)j) * 4; }
+inline const double* at(const double* a, int ny, int i, int j) {
+    return a + ((size_t)i * (size_t)(ny + 4) + (size_t)j) * 4;
+}
+}  // namespace
+
+// One application of the reference's boundary function (full loop ranges, x loop then y loop).
+void euler_fill_ghost_ring(const lsc_euler_config& c, double* a) {
+    const int nx = c.nx, ny = c.ny;
+    const size_t cell = 4 * sizeof(double);
+    const bool per = (c.bc == LSC_BC_PERIODIC);
+    for (int j = 0; j < ny + 4; ++j) {
+        std::memcpy(at(a, ny, 0, j), at(a, ny, per ? nx : 2, j), cell);
+        std::memcpy(at(a, ny, 1, j), at(a, ny, per ? nx + 1 : 2, j), cell);
+        std::memcpy(at(a, ny, nx + 2, j), at(a, ny, per ? 2 : nx + 1, j), cell);
+        std::memcpy(at(a, ny, nx + 3, j), at(a, ny, per ? 3 : nx + 1, j), cell);
+    }
+    for (int i = 0; i < nx + 4; ++i) {
+        std::memcpy(at(a, ny, i, 0), at(a, ny, i, per ? ny : 2), cell);
+        std::memcpy(at(a, ny, i, 1), at(a, ny, i, per ? ny + 1 : 2), cell);
+        std::memcpy(at(a, ny, i, ny + 2), at(a, ny, i, per ? 2 : ny + 1), cell);
+        std::memcpy(at(a, ny, i, ny + 3), at(a, ny, i, per ? 3 : ny + 1), cell);
+    }
+}
+
+// IC loop + the boundary fill that follows it (S:552-596).  Cell centres x0 + (i-1.5)dx (S:556-557).
+void euler_initial_condition(const lsc_euler_config& c, int problem, double* aos) {
+    const double pi = 3.14159265358979323846;  // S:540
+    const double gamma = c.gamma;
+    const double dx = (c.x1 - c.x0) / c.nx;
+    const double dy = (c.y1 - c.y0) / c.ny;
+    for (int i = 0; i < c.nx + 4; ++i)
+        for (int j = 0; j < c.ny + 4; ++j) {
+            const double x = c.x0 + (i - 1.5) * dx;
+            const double y = c.y0 + (j - 1.5) * dy;
+            double prim[4];
+            if (problem == LSC_EULER_IC_ORSZAG_TANG) {  // S:585-589
+                prim[0] = gamma * gamma;
+                prim[1] = -std::sin(2.0 * pi * y);
+                prim[2] = std::sin(2.0 * pi * x);
+                prim[3] = gamma;
+            } else if (problem == LSC_EULER_IC_QUADRANTS) {  // G:594-617
+                if (x > 0.5 && y > 0.5) {
+                    prim[0] = 1.5; prim[1] = 0; prim[2] = 0; prim[3] = 1.5;
+                } else if (x <= 0.5 && y > 0.5) {
+                    prim[0] = 0.5323; prim[1] = 1.206; prim[2] = 0; prim[3] = 0.3;
+                } else if (x <= 0.5 && y <= 0.5) {
+                    prim[0] = 0.138; prim[1] = 1.206; prim[2] = 1.206; prim[3] = 0.029;
+                } else {
+                    prim[0] = 0.5323; prim[1] = 0; prim[2] = 1.206; prim[3] = 0.3;
+                }
+            } else {  // cylindrical explosion of BASELINE config 3 (not in the reference)
+                if ((x - 0.5) * (x - 0.5) + (y - 0.5) * (y - 0.5) <= 0.2 * 0.2) {
+                    prim[0] = 1.0; prim[1] = 0; prim[2] = 0; prim[3] = 1.0;
+                } else {
+                    prim[0] = 0.125; prim[1] = 0; prim[2] = 0; prim[3] = 0.1;
+                }
+            }
+            double* u = at(aos, c.ny, i, j);  // PrimativeToConservative, S:10-17
+            u[0] = prim[0];
+            u[1] = prim[0] * prim[1];
+            u[2] = prim[0] * prim[2];
+            u[3] = prim[3] / (gamma - 1) + (0.5 * prim[0] * (prim[1] * prim[1] + prim[2] * prim[2]));
+        }
+    euler_fill_ghost_ring(c, aos);  // S:596
+}
+
+// S:621-642 (no blank lines) / G:645-667 (blank line after each j row): rows and columns 1..n+1.
+int euler_write_dat(const lsc_euler_config& c, const double* a, const char* path, int blank_line_per_row) {
+    std::ofstream output(path);
+    if (!output) return -1;
+    const double dx = (c.x1 - c.x0) / c.nx;
+    const double dy = (c.y1 - c.y0) / c.ny;
+    for (int j = 1; j < c.ny + 2; j++) {
+        for (int i = 1; i < c.nx + 2; i++) {
+            const double* u = at(a, c.ny, i, j);
+            double prim[4];  // ConservativeToPrimative, S:19-26
+            prim[0] = u[0];
+            prim[1] = u[1] / u[0];
+            prim[2] = u[2] / u[0];
+            prim[3] = (c.gamma - 1) * (u[3] - 0.5 * prim[0] * (prim[1] * prim[1] + prim[2] * prim[2]));
+            const double x = c.x0 + (i - 1) * dx;
+            const double y = c.y0 + (j - 1) * dy;
+            output << x << " " << y << " " << prim[0] << " " << prim[1] << " " << prim[2] << " " << prim[3] << "\n";
+        }
+        if (blank_line_per_row) output << "\n";
+    }
+    return output.good() ? 0 : -1;
+}
+
+}  // namespace lsc

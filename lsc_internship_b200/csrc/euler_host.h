@@ -1,0 +1,9 @@
+// euler_host.h -- host-side helpers of the Euler solver surface (see euler_host.cpp).
+#pragma once
+#include "../../include/lsc_b200.h"
+
+namespace lsc {
+void euler_initial_condition(const lsc_euler_config& c, int problem, double* aos);
+void euler_fill_ghost_ring(const lsc_euler_config& c, double* a);
+int euler_write_dat(const lsc_euler_config& c, const double* a, const char* path, int blank_line_per_row);
+}  // namespace lsc

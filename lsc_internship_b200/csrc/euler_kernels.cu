@@ -1,0 +1,317 @@
+// euler_kernels.cu -- sm_100a kernels of the 2-D Euler SLIC step (Euler_codes/SLIC_euler_2d.cpp = S).
+//
+//   euler_x_sweep_kernel : u -> ubar, the x half of XthenY (S:256-314)                  32 B read + 32 B write
+//   euler_y_sweep_kernel : A = y-sweep(ubar) (S:317-373), B = y-sweep(u) (S:405-461; the x half of YthenX is
+//                          dead in the reference: its flux goes to fluxY (S:510) while the update reads the
+//                          zero fluxX (S:519)), u' = 0.5*(A+B) (S:609-615), max signal speed of u' (S:165-195)
+//                                                                                        64 B read + 32 B write
+// Same structure as the MHD kernels (mhd_kernels.cu): x marches along i with the stencil in registers, y is one
+// thread per cell with face states and fluxes exchanged through shared memory; division policy as there.
+#include "euler_kernels.cuh"
+#include "euler_physics.cuh"
+
+namespace lsc {
+
+__device__ __forceinline__ void eload(const double* __restrict__ base, size_t plane, size_t idx, double (&u)[NE]) {
+#pragma unroll
+    for (int k = 0; k < NE; ++k) u[k] = __ldg(base + (size_t)k * plane + idx);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// x sweep.  Ghost half states are boundary images of interior half states (S:297-298): periodic ones equal a
+// reconstruction from the ghost columns; transmissive (G:199-215) ones copy the first / last interior cell.
+// ---------------------------------------------------------------------------------------------------------
+template <class D>
+__device__ __noinline__ void euler_x_halfstates_global(D& dv, const GridDims g, const EulerParams p,
+                                                       const double* __restrict__ cur, int i, int j,
+                                                       double (&hL)[NE], double (&hR)[NE]) {
+    double um[NE], u0[NE], up[NE];
+    eload(cur, g.plane, cell_index(g, i - 1, j), um);
+    eload(cur, g.plane, cell_index(g, i, j), u0);
+    eload(cur, g.plane, cell_index(g, i + 1, j), up);
+    euler_halfstates<0>(dv, um, u0, up, p.gm1, p.cm, p.cp, p.hdtdx, hL, hR);
+}
+
+template <class D>
+__global__ void __launch_bounds__(128, 4) euler_x_sweep_kernel(const GridDims g, const EulerParams p,
+                                                               const double* __restrict__ cur,
+                                                               double* __restrict__ ubar,
+                                                               unsigned long long* __restrict__ status,
+                                                               const int strip) {
+    const int j = 2 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= g.ny + 2) return;
+    const int ia = 2 + blockIdx.y * strip;
+    const int ib = min(ia + strip, g.nxl + 2);
+    const bool lo_image = (ia == 2) && (p.bcx_lo == BC_TRANSMISSIVE_E);
+    const bool hi_image = (ib == g.nxl + 2) && (p.bcx_hi == BC_TRANSMISSIVE_E);
+    D dv;
+
+    double hRprev[NE], hLprev[NE], Fprev[NE];
+    {
+        double tL[NE], tR[NE];
+        euler_x_halfstates_global(dv, g, p, cur, lo_image ? 2 : ia - 1, j, tL, tR);
+#pragma unroll
+        for (int k = 0; k < NE; ++k) {
+            hRprev[k] = tR[k];
+            hLprev[k] = tL[k];
+            Fprev[k] = 0.0;
+        }
+    }
+    double uM[NE], u0[NE], uP[NE];
+    eload(cur, g.plane, cell_index(g, ia - 1, j), uM);
+    eload(cur, g.plane, cell_index(g, ia, j), u0);
+    eload(cur, g.plane, cell_index(g, ia + 1, j), uP);
+
+    for (int c = ia; c <= ib; ++c) {
+        double hL[NE], hR[NE];
+        if (c == ib && hi_image) {
+#pragma unroll
+            for (int k = 0; k < NE; ++k) {  // u[n+2] = u[n+1] applied to the half-step arrays
+                hL[k] = hLprev[k];
+                hR[k] = hRprev[k];
+            }
+        } else {
+            euler_halfstates<0>(dv, uM, u0, uP, p.gm1, p.cm, p.cp, p.hdtdx, hL, hR);
+        }
+        double F[NE];
+        euler_force<0>(dv, hRprev, hL, p.gm1, p.hdtdx, p.hdxdt, F);  // interface c-1/2, S:302
+        if (c > ia) {
+            const size_t o = cell_index(g, c - 1, j);
+#pragma unroll
+            for (int k = 0; k < NE; ++k) ubar[(size_t)k * g.plane + o] = uM[k] - p.dtdx * (F[k] - Fprev[k]);  // S:309
+        }
+#pragma unroll
+        for (int k = 0; k < NE; ++k) {
+            Fprev[k] = F[k];
+            hRprev[k] = hR[k];
+            hLprev[k] = hL[k];
+            uM[k] = u0[k];
+            u0[k] = uP[k];
+        }
+        if (c < ib) eload(cur, g.plane, cell_index(g, c + 2, j), uP);
+    }
+    if (dv.bad) atomicOr(status + 1, 1ull);
+}
+
+void launch_euler_x_sweep(const GridDims& g, const EulerParams& p, bool ieee, const double* cur, double* ubar,
+                          unsigned long long* status, cudaStream_t s) {
+    dim3 block(128);
+    const int row_blocks = (g.ny + block.x - 1) / block.x;
+    int strip = 64;
+    while (strip > 8 && (long)row_blocks * ((g.nxl + strip - 1) / strip) < 148L * 4 * 3) strip /= 2;
+    dim3 grid(row_blocks, (g.nxl + strip - 1) / strip);
+    if (ieee)
+        euler_x_sweep_kernel<IeeeDiv><<<grid, block, 0, s>>>(g, p, cur, ubar, status, strip);
+    else
+        euler_x_sweep_kernel<FastDiv><<<grid, block, 0, s>>>(g, p, cur, ubar, status, strip);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// y sweep (both of them) + average + CFL maximum.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int EBJ = 128;
+
+// stored row that a (possibly ghost) row index refers to: periodic S:217-225, transmissive G:208-214
+__device__ __forceinline__ int emap_row(int j, int ny, int bc) {
+    if (j >= 2 && j <= ny + 1) return j;
+    if (bc == BC_PERIODIC) return (j < 2) ? j + ny : j - ny;
+    return (j < 2) ? 2 : ny + 1;
+}
+
+// One y sweep of `in` for this thread's cell: returns the updated value of cell c in `out` (valid for
+// tid in [1, EBJ-2], c in [2, ny+1]).  sH / sF: shared exchange buffers [NE][EBJ].
+template <class D>
+__device__ __forceinline__ void euler_y_pass(D& dv, const GridDims& g, const EulerParams& p,
+                                             const double* __restrict__ in, int i, int c, int tid,
+                                             double (*sH)[EBJ], double (*sF)[EBJ], double (&out)[NE]) {
+    const int ny = g.ny;
+    const bool active = (c <= ny + 2);
+    double hB[NE], hT[NE], u0[NE];
+#pragma unroll
+    for (int k = 0; k < NE; ++k) hB[k] = hT[k] = u0[k] = 0.0;
+    if (active) {
+        // ghost cells carry the half states of their boundary image: periodic -> same stencil through the wrap,
+        // transmissive -> the first / last interior cell (S:356-357 with G:208-214)
+        int s = c;
+        if (p.bcy != BC_PERIODIC) s = min(max(c, 2), ny + 1);
+        double um[NE], up[NE];
+        eload(in, g.plane, cell_index(g, i, emap_row(s - 1, ny, p.bcy)), um);
+        eload(in, g.plane, cell_index(g, i, emap_row(s, ny, p.bcy)), u0);
+        eload(in, g.plane, cell_index(g, i, emap_row(s + 1, ny, p.bcy)), up);
+        euler_halfstates<1>(dv, um, u0, up, p.gm1, p.cm, p.cp, p.hdtdy, hB, hT);
+#pragma unroll
+        for (int k = 0; k < NE; ++k) sH[k][tid] = hB[k];
+    }
+    __syncthreads();
+    const bool has_flux = (tid < EBJ - 1) && (c <= ny + 1);
+    double F[NE];
+#pragma unroll
+    for (int k = 0; k < NE; ++k) F[k] = 0.0;
+    if (has_flux) {
+        double nb[NE];
+#pragma unroll
+        for (int k = 0; k < NE; ++k) nb[k] = sH[k][tid + 1];
+        euler_force<1>(dv, hT, nb, p.gm1, p.hdtdy, p.hdydt, F);  // getFluxY(top of c, bottom of c+1), S:361
+#pragma unroll
+        for (int k = 0; k < NE; ++k) sF[k][tid] = F[k];
+    }
+    __syncthreads();
+    if (tid >= 1 && has_flux) {
+#pragma unroll
+        for (int k = 0; k < NE; ++k) out[k] = u0[k] - p.dtdy * (F[k] - sF[k][tid - 1]);  // S:370
+    }
+    __syncthreads();  // sH / sF are reused by the next pass
+}
+
+template <class D>
+__global__ void __launch_bounds__(EBJ, 4) euler_y_sweep_kernel(const GridDims g, const EulerParams p,
+                                                               const double* __restrict__ ubar,
+                                                               const double* __restrict__ cur,
+                                                               double* __restrict__ next,
+                                                               unsigned long long* __restrict__ status) {
+    __shared__ double sH[NE][EBJ];
+    __shared__ double sF[NE][EBJ];
+    __shared__ double warp_max[32];
+    const int tid = threadIdx.x;
+    const int i = 2 + blockIdx.y;
+    const int jo = 2 + blockIdx.x * (EBJ - 2);
+    const int c = jo - 1 + tid;
+    D dv;
+    double A[NE], B[NE];
+#pragma unroll
+    for (int k = 0; k < NE; ++k) A[k] = B[k] = 0.0;
+    euler_y_pass(dv, g, p, ubar, i, c, tid, sH, sF, A);  // XthenY: y sweep of ubar
+    euler_y_pass(dv, g, p, cur, i, c, tid, sH, sF, B);   // YthenX: y sweep of u (its x sweep is a no-op)
+
+    double speed = 0.0;
+    if (tid >= 1 && tid < EBJ - 1 && c <= g.ny + 1) {
+        double un[NE];
+        const size_t o = cell_index(g, i, c);
+#pragma unroll
+        for (int k = 0; k < NE; ++k) {
+            // uPlus1 = uPlus1Bar - (dt/dx)*(fluxX - fluxX) with fluxX == 0 (S:519), then the average S:612
+            const double b = B[k] - p.dtdx * (0.0 - 0.0);
+            un[k] = 0.5 * (A[k] + b);
+            next[(size_t)k * g.plane + o] = un[k];
+        }
+        const double sp = euler_cfl_speed(dv, un, p.gamma);
+        if (sp > speed) speed = sp;
+    }
+    if (dv.bad) atomicOr(status + 1, 1ull);
+    // block maximum -> status[0]
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double other = __shfl_xor_sync(0xffffffffu, speed, o);
+        speed = (other > speed) ? other : speed;
+    }
+    if ((tid & 31) == 0) warp_max[tid >> 5] = speed;
+    __syncthreads();
+    if (tid < 32) {
+        double v = (tid < EBJ / 32) ? warp_max[tid] : 0.0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const double other = __shfl_xor_sync(0xffffffffu, v, o);
+            v = (other > v) ? other : v;
+        }
+        if (tid == 0 && v > 0.0) atomicMax(status, (unsigned long long)__double_as_longlong(v));
+    }
+}
+
+void launch_euler_y_sweep(const GridDims& g, const EulerParams& p, bool ieee, const double* ubar, const double* cur,
+                          double* next, unsigned long long* status, cudaStream_t s) {
+    dim3 block(EBJ);
+    dim3 grid((g.ny + (EBJ - 2) - 1) / (EBJ - 2), g.nxl);
+    if (ieee)
+        euler_y_sweep_kernel<IeeeDiv><<<grid, block, 0, s>>>(g, p, ubar, cur, next, status);
+    else
+        euler_y_sweep_kernel<FastDiv><<<grid, block, 0, s>>>(g, p, ubar, cur, next, status);
+}
+
+// Stand-alone CFL reduction over [i_lo,i_hi] x [j_lo,j_hi]: the reference's range is [2,n+2] on the array as
+// it stands (S:173-174), ghost row/column n+2 included.
+__global__ void euler_max_speed_kernel(const GridDims g, double gamma, const double* __restrict__ u, int i_lo,
+                                       int i_hi, int j_lo, int j_hi, unsigned long long* __restrict__ status) {
+    const int j = j_lo + blockIdx.x * blockDim.x + threadIdx.x;
+    double best = 0.0;
+    if (j <= j_hi) {
+        for (int i = i_lo + blockIdx.y; i <= i_hi; i += gridDim.y) {
+            double q[NE];
+            eload(u, g.plane, cell_index(g, i, j), q);
+            IeeeDiv dv;
+            const double sp = euler_cfl_speed(dv, q, gamma);
+            if (sp > best) best = sp;
+        }
+    }
+    if (best > 0.0) atomicMax(status, (unsigned long long)__double_as_longlong(best));
+}
+
+void launch_euler_max_speed(const GridDims& g, double gamma, const double* u, int i_lo, int i_hi, int j_lo, int j_hi,
+                            unsigned long long* status, cudaStream_t s) {
+    dim3 block(128);
+    const int nj = j_hi - j_lo + 1, ni = i_hi - i_lo + 1;
+    dim3 grid((nj + 127) / 128, ni < 64 ? ni : 64);
+    euler_max_speed_kernel<<<grid, block, 0, s>>>(g, gamma, u, i_lo, i_hi, j_lo, j_hi, status);
+}
+
+// ghost columns, S:205-210 (periodic) / G:203-208 (transmissive: 0,1 <- 2 ; n+2,n+3 <- n+1)
+__global__ void euler_x_ghost_kernel(const GridDims g, int bc_x, double* __restrict__ u) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= g.ny + 4) return;
+    double* pl = u + (size_t)blockIdx.y * g.plane;
+    const int nx = g.nxl;
+    int src[4];
+    if (bc_x == BC_PERIODIC) {
+        src[0] = nx; src[1] = nx + 1; src[2] = 2; src[3] = 3;
+    } else {
+        src[0] = 2; src[1] = 2; src[2] = nx + 1; src[3] = nx + 1;
+    }
+    const int dst[4] = {0, 1, nx + 2, nx + 3};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) pl[cell_index(g, dst[q], j)] = pl[cell_index(g, src[q], j)];
+}
+
+void launch_euler_x_ghosts(const GridDims& g, int bc_x, double* u, cudaStream_t s) {
+    dim3 block(256), grid((g.ny + 4 + 255) / 256, NE);
+    euler_x_ghost_kernel<<<grid, block, 0, s>>>(g, bc_x, u);
+}
+
+// reference array-of-structures [i][j][4] <-> device planes for `ni` columns starting at i0
+__global__ void euler_aos_to_soa_kernel(const GridDims g, const double* __restrict__ aos, int i0,
+                                        double* __restrict__ soa) {
+    __shared__ double tile[32 * NE];
+    const int jb = blockIdx.x * 32, il = blockIdx.y, nrow = g.ny + 4;
+    const int nj = min(32, nrow - jb);
+    const double* src = aos + ((size_t)il * nrow + jb) * NE;
+    for (int t = threadIdx.x; t < nj * NE; t += blockDim.x) tile[t] = src[t];
+    __syncthreads();
+    for (int t = threadIdx.x; t < nj * NE; t += blockDim.x) {
+        const int k = t / nj, jj = t - k * nj;
+        soa[(size_t)k * g.plane + cell_index(g, i0 + il, jb + jj)] = tile[jj * NE + k];
+    }
+}
+
+__global__ void euler_soa_to_aos_kernel(const GridDims g, const double* __restrict__ soa, int i0,
+                                        double* __restrict__ aos) {
+    __shared__ double tile[32 * NE];
+    const int jb = blockIdx.x * 32, il = blockIdx.y, nrow = g.ny + 4;
+    const int nj = min(32, nrow - jb);
+    for (int t = threadIdx.x; t < nj * NE; t += blockDim.x) {
+        const int k = t / nj, jj = t - k * nj;
+        tile[jj * NE + k] = soa[(size_t)k * g.plane + cell_index(g, i0 + il, jb + jj)];
+    }
+    __syncthreads();
+    double* dst = aos + ((size_t)il * nrow + jb) * NE;
+    for (int t = threadIdx.x; t < nj * NE; t += blockDim.x) dst[t] = tile[t];
+}
+
+void launch_euler_aos_to_soa(const GridDims& g, const double* aos, int i0, int ni, double* soa, cudaStream_t s) {
+    dim3 grid((g.ny + 4 + 31) / 32, ni);
+    euler_aos_to_soa_kernel<<<grid, 128, 0, s>>>(g, aos, i0, soa);
+}
+
+void launch_euler_soa_to_aos(const GridDims& g, const double* soa, int i0, int ni, double* aos, cudaStream_t s) {
+    dim3 grid((g.ny + 4 + 31) / 32, ni);
+    euler_soa_to_aos_kernel<<<grid, 128, 0, s>>>(g, soa, i0, aos);
+}
+
+}  // namespace lsc

@@ -1,0 +1,29 @@
+// euler_kernels.cuh -- launch-side declarations of the Euler SLIC kernels.
+#pragma once
+#include "mhd_kernels.cuh"
+
+namespace lsc {
+
+enum : int { BC_TRANSMISSIVE_E = 3 };  // G:199-215: ghosts 0,1 <- 2 ; n+2,n+3 <- n+1
+
+struct EulerParams {
+    double gamma, gm1;
+    double cm, cp;        // 0.5*(1+omega), 0.5*(1-omega)   (S:270)
+    double dtdx, hdtdx;   // dt/dx, 0.5*(dt/dx)
+    double dtdy, hdtdy;
+    double hdxdt, hdydt;  // 0.5*dx/dt, 0.5*dy/dt            (S:129, S:156)
+    int bcx_lo, bcx_hi;   // physical x boundary type at each end of this slab, -1 at an inter-rank edge
+    int bcy;
+};
+
+void launch_euler_x_sweep(const GridDims& g, const EulerParams& p, bool ieee, const double* cur, double* ubar,
+                          unsigned long long* status, cudaStream_t s);
+void launch_euler_y_sweep(const GridDims& g, const EulerParams& p, bool ieee, const double* ubar, const double* cur,
+                          double* next, unsigned long long* status, cudaStream_t s);
+void launch_euler_max_speed(const GridDims& g, double gamma, const double* u, int i_lo, int i_hi, int j_lo, int j_hi,
+                            unsigned long long* status, cudaStream_t s);
+void launch_euler_x_ghosts(const GridDims& g, int bc_x, double* u, cudaStream_t s);
+void launch_euler_aos_to_soa(const GridDims& g, const double* aos, int i0, int ni, double* soa, cudaStream_t s);
+void launch_euler_soa_to_aos(const GridDims& g, const double* soa, int i0, int ni, double* aos, cudaStream_t s);
+
+}  // namespace lsc

@@ -48,6 +48,15 @@ inline int to_kernel_bc(int bc) {
 
 void lsc_count_launches(unsigned long long n) { g_launches += n; }
 
+// error sink shared with the other translation units of the library (lsc_common.h)
+int lsc_fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
 struct lsc_mhd_ctx {
     lsc_mhd_config cfg;
     int nxl = 0, i0 = 0;  // slab: interior columns, first global interior column (0-based)

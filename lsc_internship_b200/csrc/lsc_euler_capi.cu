@@ -1,0 +1,357 @@
+// lsc_euler_capi.cu -- C ABI of the 2-D Euler SLIC solver (include/lsc_b200.h, lsc_euler_*): the time loop of
+// Euler_codes/SLIC_euler_2d.cpp main() (S:528-643) / generaliseSLIC.cpp main() (G:564-668) driving the
+// sm_100a kernels of euler_kernels.cu.
+#include <cmath>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "euler_host.h"
+#include "euler_kernels.cuh"
+#include "lsc_common.h"
+
+struct lsc_euler_ctx {
+    lsc_euler_config cfg;
+    double dx = 0, dy = 0;
+    lsc::GridDims g{};
+    // u^n, ubar, u^{n+1}: the step never overwrites its input, so it can be recomputed with IEEE division
+    double* state[3] = {nullptr, nullptr, nullptr};
+    int cur = 0, bar = 1, next = 2;
+    unsigned long long* d_status = nullptr;  // [0] max signal speed bits of state[cur], [1] fast-division flag
+    unsigned long long* h_status = nullptr;
+    bool pending = false, pending_step = false;
+    double max_speed = 0;
+    lsc::EulerParams last_p{};
+    long ieee_redos = 0;
+    double* d_stage = nullptr;
+    int stage_cols = 0;
+    cudaStream_t stream = nullptr;
+    double t = 0, dt = 0;
+    long step = 0;
+    bool uploaded = false;
+    bool profiling = false;
+    std::vector<cudaEvent_t> prof_events;
+};
+
+namespace {
+
+int kernel_bc(int bc) { return bc == LSC_BC_PERIODIC ? lsc::BC_PERIODIC : lsc::BC_TRANSMISSIVE_E; }
+
+int e_read_status(lsc_euler_ctx* c) {
+    LSC_CUDA_TRY(cudaMemcpyAsync(c->h_status, c->d_status, 16, cudaMemcpyDeviceToHost, c->stream));
+    LSC_CUDA_TRY(cudaStreamSynchronize(c->stream));
+    return LSC_OK;
+}
+
+int e_launch(lsc_euler_ctx* c, const lsc::EulerParams& p, bool ieee, int in, int out) {
+    LSC_CUDA_TRY(cudaMemsetAsync(c->d_status, 0, 16, c->stream));
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    const bool prof = c->profiling && !ieee;
+    if (prof) {
+        for (auto& e : ev) LSC_CUDA_TRY(cudaEventCreate(&e));
+        LSC_CUDA_TRY(cudaEventRecord(ev[0], c->stream));
+    }
+    lsc::launch_euler_x_sweep(c->g, p, ieee, c->state[in], c->state[c->bar], c->d_status, c->stream);
+    if (prof) {
+        LSC_CUDA_TRY(cudaEventRecord(ev[1], c->stream));
+        LSC_CUDA_TRY(cudaEventRecord(ev[2], c->stream));
+    }
+    lsc::launch_euler_y_sweep(c->g, p, ieee, c->state[c->bar], c->state[in], c->state[out], c->d_status, c->stream);
+    if (prof) {
+        LSC_CUDA_TRY(cudaEventRecord(ev[3], c->stream));
+        for (auto e : ev) c->prof_events.push_back(e);
+    }
+    // applyBoundaryConditions(u) after the average (S:616): only x ghost columns are read on the device
+    lsc::launch_euler_x_ghosts(c->g, kernel_bc(c->cfg.bc), c->state[out], c->stream);
+    lsc_count_launches(3);
+    LSC_CUDA_TRY(cudaGetLastError());
+    return LSC_OK;
+}
+
+// status of the step launched last; recompute it with IEEE division if a fast division flagged an operand
+int e_resolve(lsc_euler_ctx* c) {
+    if (!c->pending) return LSC_OK;
+    int rc = e_read_status(c);
+    if (rc) return rc;
+    if (c->pending_step && c->h_status[1] != 0) {
+        c->ieee_redos += 1;
+        // the step's input is the state that was `cur` before the rotation, i.e. the one now in `next`
+        rc = e_launch(c, c->last_p, true, c->next, c->cur);
+        if (rc) return rc;
+        rc = e_read_status(c);
+        if (rc) return rc;
+    }
+    std::memcpy(&c->max_speed, &c->h_status[0], sizeof(double));
+    c->pending = false;
+    return LSC_OK;
+}
+
+// body of the do-loop S:600-616
+int e_step_once(lsc_euler_ctx* c) {
+    int rc = e_resolve(c);
+    if (rc) return rc;
+    if (!(c->max_speed > 0.0) || !std::isfinite(c->max_speed))
+        return lsc_fail(LSC_ENAN, "max signal speed is %g at step %ld", c->max_speed, c->step);
+    double dspace = c->dx;  // S:166-169
+    if (c->dy < c->dx) dspace = c->dy;
+    const double dt = c->cfg.cfl * dspace / c->max_speed;  // S:192
+    c->dt = dt;
+    c->t += dt;  // S:602
+    lsc::EulerParams p{};
+    p.gamma = c->cfg.gamma;
+    p.gm1 = c->cfg.gamma - 1;
+    p.cm = 0.5 * (1 + c->cfg.omega);
+    p.cp = 0.5 * (1 - c->cfg.omega);
+    p.dtdx = dt / c->dx;
+    p.hdtdx = 0.5 * (dt / c->dx);
+    p.dtdy = dt / c->dy;
+    p.hdtdy = 0.5 * (dt / c->dy);
+    p.hdxdt = 0.5 * c->dx / dt;
+    p.hdydt = 0.5 * c->dy / dt;
+    p.bcx_lo = p.bcx_hi = p.bcy = kernel_bc(c->cfg.bc);
+    c->last_p = p;
+    rc = e_launch(c, p, false, c->cur, c->next);
+    if (rc) return rc;
+    const int old = c->cur;
+    c->cur = c->next;
+    c->next = old;
+    c->pending = true;
+    c->pending_step = true;
+    c->step += 1;
+    return LSC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int lsc_euler_create(const lsc_euler_config* cfg, lsc_euler_ctx** out) {
+    if (!cfg || !out) return lsc_fail(LSC_EINVAL, "lsc_euler_create: null argument");
+    *out = nullptr;
+    if (cfg->nx < 4 || cfg->ny < 4) return lsc_fail(LSC_EINVAL, "nx, ny must be >= 4 (got %d x %d)", cfg->nx, cfg->ny);
+    if (!(cfg->x1 > cfg->x0) || !(cfg->y1 > cfg->y0)) return lsc_fail(LSC_EINVAL, "empty domain");
+    if (!(cfg->gamma > 1.0) || !(cfg->cfl > 0.0)) return lsc_fail(LSC_EINVAL, "gamma must be > 1 and cfl > 0");
+    if (cfg->bc != LSC_BC_PERIODIC && cfg->bc != LSC_BC_TRANSMISSIVE_E)
+        return lsc_fail(LSC_EINVAL, "bc must be LSC_BC_PERIODIC (S:198-226) or LSC_BC_TRANSMISSIVE_E (G:199-215)");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return lsc_fail(LSC_ECUDA, "no CUDA device: this library has no CPU path");
+    }
+    if (cfg->device < 0 || cfg->device >= ndev) return lsc_fail(LSC_EINVAL, "device %d out of range", cfg->device);
+    LSC_CUDA_TRY(cudaSetDevice(cfg->device));
+    lsc_euler_ctx* c = new (std::nothrow) lsc_euler_ctx();
+    if (!c) return lsc_fail(LSC_ENOMEM, "host allocation failed");
+    c->cfg = *cfg;
+    c->dx = (cfg->x1 - cfg->x0) / cfg->nx;  // S:546-547
+    c->dy = (cfg->y1 - cfg->y0) / cfg->ny;
+    c->g.nxl = cfg->nx;
+    c->g.ny = cfg->ny;
+    c->g.pitch = ((cfg->ny + 4 + lsc::JOFF) + 15) / 16 * 16;
+    c->g.plane = (size_t)(cfg->nx + 4) * (size_t)c->g.pitch;
+    const size_t state_bytes = c->g.plane * 4 * sizeof(double);
+    const size_t col_bytes = (size_t)(cfg->ny + 4) * 4 * sizeof(double);
+    long long cols = (long long)((256ull << 20) / col_bytes);
+    if (cols < 1) cols = 1;
+    if (cols > cfg->nx + 4) cols = cfg->nx + 4;
+    c->stage_cols = (int)cols;
+    bool ok = true;
+    for (int b = 0; b < 3 && ok; ++b) {
+        ok = cudaMalloc(&c->state[b], state_bytes) == cudaSuccess;
+        if (ok) cudaMemset(c->state[b], 0, state_bytes);
+    }
+    ok = ok && cudaMalloc(&c->d_stage, col_bytes * (size_t)cols) == cudaSuccess &&
+         cudaMalloc(&c->d_status, 16) == cudaSuccess &&
+         cudaHostAlloc(&c->h_status, 16, cudaHostAllocDefault) == cudaSuccess &&
+         cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess;
+    if (!ok) {
+        cudaGetLastError();
+        lsc_euler_destroy(c);
+        return lsc_fail(LSC_ENOMEM, "device allocation failed (%zu bytes per state)", state_bytes);
+    }
+    *out = c;
+    return LSC_OK;
+}
+
+int lsc_euler_destroy(lsc_euler_ctx* c) {
+    if (!c) return LSC_OK;
+    cudaSetDevice(c->cfg.device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    for (int b = 0; b < 3; ++b)
+        if (c->state[b]) cudaFree(c->state[b]);
+    if (c->d_stage) cudaFree(c->d_stage);
+    if (c->d_status) cudaFree(c->d_status);
+    if (c->h_status) cudaFreeHost(c->h_status);
+    for (auto e : c->prof_events) cudaEventDestroy(e);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+    return LSC_OK;
+}
+
+int lsc_euler_initial_condition(const lsc_euler_config* cfg, int problem, double* aos) {
+    if (!cfg || !aos) return lsc_fail(LSC_EINVAL, "null argument");
+    if (problem < LSC_EULER_IC_ORSZAG_TANG || problem > LSC_EULER_IC_CYLINDER)
+        return lsc_fail(LSC_EINVAL, "unknown problem %d", problem);
+    lsc::euler_initial_condition(*cfg, problem, aos);
+    return LSC_OK;
+}
+
+int lsc_euler_upload(lsc_euler_ctx* c, const double* aos) {
+    if (!c || !aos) return lsc_fail(LSC_EINVAL, "null argument");
+    LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
+    const size_t col = (size_t)(c->cfg.ny + 4) * 4;
+    const int ncol = c->cfg.nx + 4;
+    for (int il = 0; il < ncol; il += c->stage_cols) {
+        const int ni = std::min(c->stage_cols, ncol - il);
+        LSC_CUDA_TRY(cudaMemcpyAsync(c->d_stage, aos + col * il, col * ni * sizeof(double), cudaMemcpyHostToDevice,
+                                     c->stream));
+        lsc::launch_euler_aos_to_soa(c->g, c->d_stage, il, ni, c->state[c->cur], c->stream);
+        lsc_count_launches(1);
+        LSC_CUDA_TRY(cudaGetLastError());
+        LSC_CUDA_TRY(cudaStreamSynchronize(c->stream));
+    }
+    // ComputeTimeStep of the first step sees the array as given, over i,j in [2, n+2] (S:173-174); then the
+    // loop's own boundary fill (S:604) -- on the device only the x ghost columns are ever read
+    LSC_CUDA_TRY(cudaMemsetAsync(c->d_status, 0, 16, c->stream));
+    lsc::launch_euler_max_speed(c->g, c->cfg.gamma, c->state[c->cur], 2, c->cfg.nx + 2, 2, c->cfg.ny + 2, c->d_status,
+                                c->stream);
+    lsc::launch_euler_x_ghosts(c->g, kernel_bc(c->cfg.bc), c->state[c->cur], c->stream);
+    lsc_count_launches(2);
+    LSC_CUDA_TRY(cudaGetLastError());
+    LSC_CUDA_TRY(cudaStreamSynchronize(c->stream));
+    c->t = c->dt = 0;
+    c->step = 0;
+    c->uploaded = true;
+    c->pending = true;
+    c->pending_step = false;
+    return LSC_OK;
+}
+
+int lsc_euler_init_problem(lsc_euler_ctx* c, int problem) {
+    if (!c) return lsc_fail(LSC_EINVAL, "null argument");
+    std::vector<double> host;
+    try {
+        host.resize((size_t)(c->cfg.nx + 4) * (c->cfg.ny + 4) * 4);
+    } catch (...) {
+        return lsc_fail(LSC_ENOMEM, "host allocation failed");
+    }
+    int rc = lsc_euler_initial_condition(&c->cfg, problem, host.data());
+    if (rc) return rc;
+    return lsc_euler_upload(c, host.data());
+}
+
+int lsc_euler_step(lsc_euler_ctx* c, long nsteps) {
+    if (!c) return lsc_fail(LSC_EINVAL, "null argument");
+    if (!c->uploaded) return lsc_fail(LSC_ESTATE, "lsc_euler_step before lsc_euler_upload");
+    LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
+    for (long s = 0; s < nsteps; ++s) {
+        int rc = e_step_once(c);
+        if (rc) return rc;
+    }
+    return e_resolve(c);
+}
+
+int lsc_euler_step_timed(lsc_euler_ctx* c, long nsteps, float* ms) {
+    if (!c || !ms) return lsc_fail(LSC_EINVAL, "null argument");
+    if (!c->uploaded) return lsc_fail(LSC_ESTATE, "lsc_euler_step_timed before lsc_euler_upload");
+    LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
+    cudaEvent_t e0, e1;
+    LSC_CUDA_TRY(cudaEventCreate(&e0));
+    LSC_CUDA_TRY(cudaEventCreate(&e1));
+    LSC_CUDA_TRY(cudaStreamSynchronize(c->stream));
+    LSC_CUDA_TRY(cudaEventRecord(e0, c->stream));
+    int rc = LSC_OK;
+    for (long s = 0; s < nsteps && rc == LSC_OK; ++s) rc = e_step_once(c);
+    if (rc == LSC_OK) rc = e_resolve(c);
+    if (rc == LSC_OK) {
+        LSC_CUDA_TRY(cudaEventRecord(e1, c->stream));
+        LSC_CUDA_TRY(cudaEventSynchronize(e1));
+        LSC_CUDA_TRY(cudaEventElapsedTime(ms, e0, e1));
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    return rc;
+}
+
+int lsc_euler_run_until(lsc_euler_ctx* c, double t_stop, lsc_euler_log_cb log_cb, void* user, long* steps_out) {
+    if (!c) return lsc_fail(LSC_EINVAL, "null argument");
+    if (!c->uploaded) return lsc_fail(LSC_ESTATE, "lsc_euler_run_until before lsc_euler_upload");
+    LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
+    long n = 0;
+    do {  // S:600 / G:627
+        int rc = e_step_once(c);
+        if (rc) return rc;
+        ++n;
+        if (log_cb) log_cb(c->step, c->t, c->dt, user);  // G:631
+    } while (c->t < t_stop);  // S:617 / G:646
+    if (steps_out) *steps_out = n;
+    return e_resolve(c);
+}
+
+int lsc_euler_get_scalars(const lsc_euler_ctx* c, double* t, double* dt, long* step) {
+    if (!c) return lsc_fail(LSC_EINVAL, "null argument");
+    if (t) *t = c->t;
+    if (dt) *dt = c->dt;
+    if (step) *step = c->step;
+    return LSC_OK;
+}
+
+int lsc_euler_download(lsc_euler_ctx* c, double* aos) {
+    if (!c || !aos) return lsc_fail(LSC_EINVAL, "null argument");
+    if (!c->uploaded) return lsc_fail(LSC_ESTATE, "lsc_euler_download before lsc_euler_upload");
+    LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
+    if (c->pending && c->pending_step) {
+        int rc = e_resolve(c);
+        if (rc) return rc;
+    }
+    const size_t col = (size_t)(c->cfg.ny + 4) * 4;
+    const int ncol = c->cfg.nx + 4;
+    for (int il = 0; il < ncol; il += c->stage_cols) {
+        const int ni = std::min(c->stage_cols, ncol - il);
+        lsc::launch_euler_soa_to_aos(c->g, c->state[c->cur], il, ni, c->d_stage, c->stream);
+        lsc_count_launches(1);
+        LSC_CUDA_TRY(cudaGetLastError());
+        LSC_CUDA_TRY(cudaMemcpyAsync(aos + col * il, c->d_stage, col * ni * sizeof(double), cudaMemcpyDeviceToHost,
+                                     c->stream));
+        LSC_CUDA_TRY(cudaStreamSynchronize(c->stream));
+    }
+    // y ghost rows are never stored on the device: rebuild the reference's ghost ring (S:616) on the host
+    if (c->step > 0) lsc::euler_fill_ghost_ring(c->cfg, aos);
+    return LSC_OK;
+}
+
+int lsc_euler_write_dat(const lsc_euler_config* cfg, const double* aos, const char* path, int blank_line_per_row) {
+    if (!cfg || !aos || !path) return lsc_fail(LSC_EINVAL, "null argument");
+    if (lsc::euler_write_dat(*cfg, aos, path, blank_line_per_row)) return lsc_fail(LSC_EINVAL, "cannot write %s", path);
+    return LSC_OK;
+}
+
+long lsc_euler_ieee_fallback_count(const lsc_euler_ctx* c) { return c ? c->ieee_redos : -1; }
+
+int lsc_euler_set_profiling(lsc_euler_ctx* c, int enabled) {
+    if (!c) return lsc_fail(LSC_EINVAL, "null argument");
+    c->profiling = enabled != 0;
+    return LSC_OK;
+}
+
+int lsc_euler_kernel_times(lsc_euler_ctx* c, double ms[2], long launches[2]) {
+    if (!c || !ms || !launches) return lsc_fail(LSC_EINVAL, "null argument");
+    LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
+    LSC_CUDA_TRY(cudaStreamSynchronize(c->stream));
+    ms[0] = ms[1] = 0;
+    launches[0] = launches[1] = 0;
+    for (size_t q = 0; q + 3 < c->prof_events.size(); q += 4) {
+        float a = 0, b = 0;
+        LSC_CUDA_TRY(cudaEventElapsedTime(&a, c->prof_events[q], c->prof_events[q + 1]));
+        LSC_CUDA_TRY(cudaEventElapsedTime(&b, c->prof_events[q + 2], c->prof_events[q + 3]));
+        ms[0] += a;
+        ms[1] += b;
+        launches[0] += 1;
+        launches[1] += 1;
+    }
+    for (auto e : c->prof_events) cudaEventDestroy(e);
+    c->prof_events.clear();
+    return LSC_OK;
+}
+
+}  // extern "C"

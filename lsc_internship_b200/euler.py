@@ -1,0 +1,136 @@
+"""Host-side mirror of the reference programs Euler_codes/SLIC_euler_2d.cpp (S) and
+Euler_codes/generaliseSLIC.cpp (G): 2-D Euler, SLIC (limited MUSCL-Hancock + FORCE flux), averaged
+XthenY / YthenX.  As for MHD, the reference has no callable API; `SlicEuler2d` exposes the constants of
+main() (S:529-540), the initial-condition block, the boundary loops, the stdout line and the .dat files,
+and drives the CUDA library through its C ABI.  No numerical code lives here."""
+import ctypes
+import os
+
+import numpy as np
+
+from . import _capi
+from ._capi import EulerConfig, check, lib
+
+_DP = ctypes.POINTER(ctypes.c_double)
+
+
+def _dp(a):
+    return a.ctypes.data_as(_DP)
+
+
+class SlicEuler2d:
+    """Defaults = the committed configuration of SLIC_euler_2d.cpp: 100x100 on [0,1]^2, periodic, Euler
+    "Orszag-Tang" initial data, C = 0.8, gamma = 1.4, omega = 0, tStop = 0.5.
+    bc="transmissive" + problem="quadrants" gives generaliseSLIC.cpp's committed configuration."""
+
+    NVAR = 4
+
+    def __init__(self, nxCells=100, nyCells=100, x0=0.0, x1=1.0, y0=0.0, y1=1.0, tStop=0.5, C=0.8, gamma=1.4,
+                 omega=0.0, bc="periodic", problem="ot", device=0):
+        self.tStop = float(tStop)
+        self.problem = _capi.EULER_PROBLEMS[problem] if isinstance(problem, str) else int(problem)
+        bcv = {"periodic": _capi.BC_PERIODIC, "transmissive": _capi.BC_TRANSMISSIVE_E}[bc]
+        self.cfg = EulerConfig(int(nxCells), int(nyCells), float(x0), float(x1), float(y0), float(y1), float(gamma),
+                               float(C), float(omega), bcv, int(device))
+        self._h = ctypes.c_void_p()
+        check(lib().lsc_euler_create(ctypes.byref(self.cfg), ctypes.byref(self._h)))
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            lib().lsc_euler_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def shape(self):
+        return (self.cfg.nx + 4, self.cfg.ny + 4, self.NVAR)
+
+    def _prob(self, problem):
+        if problem is None:
+            return self.problem
+        return _capi.EULER_PROBLEMS[problem] if isinstance(problem, str) else int(problem)
+
+    def initial_condition(self, problem=None):
+        """IC loop + the boundary fill after it (S:552-596), as a host array."""
+        u = np.empty(self.shape, dtype=np.float64)
+        check(lib().lsc_euler_initial_condition(ctypes.byref(self.cfg), self._prob(problem), _dp(u)))
+        return u
+
+    def upload(self, u):
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        if u.shape != self.shape:
+            raise ValueError(f"state must have shape {self.shape}, got {u.shape}")
+        check(lib().lsc_euler_upload(self._h, _dp(u)))
+
+    def init_problem(self, problem=None):
+        check(lib().lsc_euler_init_problem(self._h, self._prob(problem)))
+
+    def download(self, out=None):
+        u = np.empty(self.shape, dtype=np.float64) if out is None else out
+        check(lib().lsc_euler_download(self._h, _dp(u)))
+        return u
+
+    def step(self, nsteps=1):
+        check(lib().lsc_euler_step(self._h, int(nsteps)))
+
+    def step_timed(self, nsteps=1):
+        ms = ctypes.c_float()
+        check(lib().lsc_euler_step_timed(self._h, int(nsteps), ctypes.byref(ms)))
+        return ms.value
+
+    def set_profiling(self, enabled=True):
+        check(lib().lsc_euler_set_profiling(self._h, 1 if enabled else 0))
+
+    def kernel_times(self):
+        ms = (ctypes.c_double * 2)()
+        n = (ctypes.c_long * 2)()
+        check(lib().lsc_euler_kernel_times(self._h, ms, n))
+        return ms[0], ms[1], n[0], n[1]
+
+    def scalars(self):
+        t, dt = ctypes.c_double(), ctypes.c_double()
+        n = ctypes.c_long()
+        check(lib().lsc_euler_get_scalars(self._h, ctypes.byref(t), ctypes.byref(dt), ctypes.byref(n)))
+        return t.value, dt.value, n.value
+
+    def ieee_fallback_count(self):
+        return lib().lsc_euler_ieee_fallback_count(self._h)
+
+    def run_until(self, t_stop, log=None):
+        """do { step } while (t < t_stop) -- S:600-617 / G:627-646.  Returns the number of steps."""
+        cb = _capi.EULER_LOG_CB((lambda n, t, dt, _u: log(n, t, dt))) if log else ctypes.cast(None, _capi.EULER_LOG_CB)
+        n = ctypes.c_long()
+        check(lib().lsc_euler_run_until(self._h, float(t_stop), cb, None, ctypes.byref(n)))
+        return n.value
+
+    def write_dat(self, u, path, blank_line_per_row=False):
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        check(lib().lsc_euler_write_dat(ctypes.byref(self.cfg), _dp(u), os.fsencode(path), int(blank_line_per_row)))
+
+    def run(self, outdir=None, stdout=None):
+        """main() of SLIC_euler_2d.cpp from S:598: twenty segments, segment k runs do{}while(t < tStop/(21-k)) and
+        then writes euler_<k>.dat and prints the segment time (S:618-642).  Returns total steps."""
+        total = 0
+        buf = np.empty(self.shape, dtype=np.float64) if outdir else None
+        for counter in range(1, 21):
+            seg = self.tStop / (21 - counter)
+            total += self.run_until(seg)
+            if stdout is not None:
+                stdout.append(seg)
+            if outdir:
+                self.download(buf)
+                self.write_dat(buf, os.path.join(outdir, f"euler_{counter}.dat"))
+        return total
+
+    def run_generalise(self, outdir=None, log=None):
+        """main() of generaliseSLIC.cpp from G:625: one do{}while(t < tStop), then SLIC2d.dat (G:645-667)."""
+        n = self.run_until(self.tStop, log)
+        if outdir:
+            u = self.download()
+            self.write_dat(u, os.path.join(outdir, "SLIC2d.dat"), blank_line_per_row=True)
+        return n

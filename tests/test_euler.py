@@ -1,0 +1,195 @@
+"""Euler SLIC (Euler_codes/SLIC_euler_2d.cpp, generaliseSLIC.cpp): CPU tests of the oracle against the fixtures
+made by the real reference, and GPU parity tests (bitwise) of the CUDA path through the C ABI."""
+import glob
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle_util import OracleEuler, euler_cfg, euler_ic, have_ref, run_euler_ref
+
+GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "euler_*.npz")))
+IDS = [os.path.basename(p)[6:-4] for p in GOLDEN]
+DOM = (0.0, 1.0, 0.0, 1.0)
+
+
+def bits(a):
+    return np.ascontiguousarray(a).view(np.uint64)
+
+
+# ------------------------------------------------------------------ CPU: oracle vs the real reference
+@pytest.mark.parametrize("path", GOLDEN, ids=IDS)
+def test_oracle_matches_golden(path):
+    z = np.load(path)
+    m = json.loads(str(z["meta"]))
+    cfg = euler_cfg(m["nx"], m["ny"], DOM, bc=m["bc"])
+    o = OracleEuler(cfg, euler_ic(cfg, m["ic"]))
+    log = o.step(m["nsteps"])
+    assert np.array_equal(bits(log), bits(z["log"]))
+    assert np.array_equal(bits(o.state()[0]), bits(z["u"]))
+
+
+def test_golden_present():
+    assert len(GOLDEN) >= 4
+
+
+@pytest.mark.skipif(not have_ref("slic_ref"), reason="oracle/_ref/slic_ref not built")
+@pytest.mark.parametrize("exe,bc,ic,code,nx,ny,n", [
+    ("slic_ref", "periodic", "ot", 0, 24, 28, 9),
+    ("gslic_ref", "transmissive", "quadrants", 0, 30, 22, 11),
+    ("gslic_ref", "transmissive", "cylinder", 1, 32, 32, 14),
+])
+def test_oracle_matches_live_reference(exe, bc, ic, code, nx, ny, n):
+    cfg = euler_cfg(nx, ny, DOM, bc=bc)
+    o = OracleEuler(cfg, euler_ic(cfg, ic))
+    log = o.step(n)
+    ur, logr, _ = run_euler_ref(exe, nx, ny, DOM, 1e9, 0.8, 1.4, n, ic=code)
+    assert np.array_equal(bits(log), bits(logr))
+    assert np.array_equal(bits(o.state()[0]), bits(ur))
+
+
+# ------------------------------------------------------------------ GPU parity
+gpu = pytest.mark.gpu
+
+
+@gpu
+@pytest.mark.parametrize("path", GOLDEN, ids=IDS)
+def test_cuda_matches_reference_golden(path):
+    import lsc_internship_b200 as lsc
+    z = np.load(path)
+    m = json.loads(str(z["meta"]))
+    s = lsc.SlicEuler2d(m["nx"], m["ny"], bc=m["bc"], problem=m["ic"])
+    u0 = s.initial_condition()
+    s.upload(u0)
+    log = []
+    for _ in range(m["nsteps"]):
+        s.step(1)
+        t, dt, _n = s.scalars()
+        log.append((t, dt))
+    u = s.download()
+    assert s.ieee_fallback_count() == 0
+    s.close()
+    assert np.array_equal(bits(np.array(log)), bits(z["log"])), "(t, dt) log differs from the reference"
+    assert np.array_equal(bits(u), bits(z["u"])), "state differs from the reference"
+
+
+@gpu
+@pytest.mark.parametrize("bc,ic,nx,ny,n", [
+    ("periodic", "ot", 256, 256, 10),
+    ("transmissive", "cylinder", 200, 136, 10),       # BASELINE config 3 at a size the oracle finishes quickly
+    ("transmissive", "quadrants", 131, 67, 8),        # ragged
+    ("periodic", "ot", 126, 126, 5),                  # exactly one y block
+    ("periodic", "ot", 4, 4, 3),                      # minimum
+    ("transmissive", "quadrants", 5, 9, 4),
+])
+def test_cuda_matches_oracle(bc, ic, nx, ny, n):
+    import lsc_internship_b200 as lsc
+    cfg = euler_cfg(nx, ny, DOM, bc=bc)
+    u0 = euler_ic(cfg, ic)
+    s = lsc.SlicEuler2d(nx, ny, bc=bc, problem=ic)
+    assert np.array_equal(bits(s.initial_condition()), bits(u0)), "library IC differs from the reference formulas"
+    s.upload(u0)
+    assert np.array_equal(bits(s.download()), bits(u0))
+    o = OracleEuler(cfg, u0)
+    for k in range(n):
+        lo = o.step(1)[0]
+        s.step(1)
+        t, dt, _ = s.scalars()
+        assert (t, dt) == tuple(lo), f"step {k}"
+    u, ur = s.download(), o.state()[0]
+    s.close()
+    # BASELINE tolerance: max relative L-inf <= 1e-12 per conserved variable; enforced gate: every bit
+    for k in range(4):
+        den = np.max(np.abs(ur[2:-2, 2:-2, k]))
+        assert np.max(np.abs(u[2:-2, 2:-2, k] - ur[2:-2, 2:-2, k])) <= 1e-12 * max(den, 1e-300)
+    assert np.array_equal(bits(u), bits(ur))
+
+
+@gpu
+def test_random_state_parity():
+    import lsc_internship_b200 as lsc
+    nx, ny = 90, 70
+    cfg = euler_cfg(nx, ny, DOM, bc="periodic")
+    rng = np.random.default_rng(77)
+    rho = rng.uniform(0.5, 2.0, (nx + 4, ny + 4))
+    vx, vy = rng.uniform(-1, 1, (2, nx + 4, ny + 4))
+    p = rng.uniform(0.5, 2.0, (nx + 4, ny + 4))
+    u0 = np.stack([rho, rho * vx, rho * vy, p / 0.4 + 0.5 * rho * (vx * vx + vy * vy)], axis=-1)
+    o = OracleEuler(cfg, u0)
+    s = lsc.SlicEuler2d(nx, ny, bc="periodic")
+    s.upload(u0)          # ghosts as given: the first dt sees row/column n+2 of the uploaded array (S:173-174)
+    o.step(4)
+    s.step(4)
+    assert np.array_equal(bits(s.download()), bits(o.state()[0]))
+    s.close()
+
+
+@gpu
+def test_out_of_window_operands_take_the_ieee_path():
+    import lsc_internship_b200 as lsc
+    nx, ny = 40, 36
+    cfg = euler_cfg(nx, ny, DOM, bc="periodic")
+    u0 = euler_ic(cfg, "ot")
+    u0[5:9, 6:20, 1] = 1e-210
+    o = OracleEuler(cfg, u0)
+    s = lsc.SlicEuler2d(nx, ny)
+    s.upload(u0)
+    o.step(3)
+    s.step(3)
+    assert s.ieee_fallback_count() >= 1
+    assert np.array_equal(bits(s.download()), bits(o.state()[0]))
+    s.close()
+
+
+@gpu
+def test_committed_program_reproduces_reference_dat_files(tmp_path, golden_dir):
+    """SlicEuler2d().run() = main() of SLIC_euler_2d.cpp as committed: all twenty euler_<k>.dat must be
+    byte-identical to the files committed in the reference repo (MHD_plot_data/euler_*.dat)."""
+    import lsc_internship_b200 as lsc
+    sha = json.load(open(os.path.join(golden_dir, "dat_sha256.json")))
+    s = lsc.SlicEuler2d()
+    s.init_problem()
+    times = []
+    steps = s.run(outdir=str(tmp_path), stdout=times)
+    s.close()
+    assert steps == 152       # the reference takes 152 steps (oracle/_ref/slic_ref)
+    for k in range(1, 21):
+        h = hashlib.sha256(open(tmp_path / f"euler_{k}.dat", "rb").read()).hexdigest()
+        assert h == sha[f"euler_{k}.dat"], f"euler_{k}.dat differs from the reference's committed file"
+
+
+@gpu
+def test_generalise_slic_program(tmp_path, golden_dir):
+    """generaliseSLIC.cpp as committed (transmissive, four quadrants): SLIC2d.dat byte-identical to what the real
+    program writes, and the 't = .. dt = ..' log identical."""
+    import lsc_internship_b200 as lsc
+    sha = json.load(open(os.path.join(golden_dir, "dat_sha256.json")))
+    s = lsc.SlicEuler2d(bc="transmissive", problem="quadrants")
+    s.init_problem()
+    lines = []
+    n = s.run_generalise(outdir=str(tmp_path), log=lambda k, t, dt: lines.append(f"t = {t:.6g} dt = {dt:.6g}"))
+    s.close()
+    ref = open(os.path.join(golden_dir, "generalise_slic_stdout.txt")).read().splitlines()
+    assert n == len(ref) == 141
+    assert lines == ref
+    h = hashlib.sha256(open(tmp_path / "SLIC2d.dat", "rb").read()).hexdigest()
+    assert h == sha["SLIC2d.dat@generaliseSLIC"]
+
+
+@gpu
+def test_large_grid_conservation():
+    """4096^2 (BASELINE config 3 size) with periodic BCs: mass, momenta and energy are conserved to rounding."""
+    import lsc_internship_b200 as lsc
+    n = 4096
+    s = lsc.SlicEuler2d(n, n, bc="periodic", problem="ot")
+    s.init_problem()
+    u0 = s.download()[2:-2, 2:-2]
+    s.step(5)
+    u1 = s.download()[2:-2, 2:-2]
+    s.close()
+    assert np.isfinite(u1).all()
+    for k in (0, 3):
+        a, b = u0[..., k].sum(dtype=np.longdouble), u1[..., k].sum(dtype=np.longdouble)
+        assert abs(a - b) / abs(a) < 1e-12
