@@ -70,6 +70,11 @@ def main():
             fh.write(r.stdout)
         with open(os.path.join(td, "MHD3.dat"), "rb") as fh:
             sha["MHD3.dat@tStop=0.25"] = hashlib.sha256(fh.read()).hexdigest()
+    with tempfile.TemporaryDirectory() as td:
+        r = subprocess.run([os.path.join(REF_DIR, "slic_ref"), "100", "100", "0", "1", "0", "1", "0.5", "0.8", "1.4", "-1",
+                            "1"], cwd=td, check=True, capture_output=True, text=True)
+        with open(os.path.join(HERE, "slic_euler_2d_stdout.txt"), "w") as fh:
+            fh.write(r.stdout)
     # generaliseSLIC.cpp as committed (no golden output exists in the reference repo for it: Euler_codes/SLIC2d.dat
     # was written by TabEoS.cpp) -- record what the real program writes here
     with tempfile.TemporaryDirectory() as td:

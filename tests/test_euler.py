@@ -179,6 +179,29 @@ def test_generalise_slic_program(tmp_path, golden_dir):
 
 
 @gpu
+def test_cpp_drivers_are_drop_ins(tmp_path, golden_dir):
+    """drivers/slic_euler_2d with no arguments = SLIC_euler_2d.cpp; with --generalise = generaliseSLIC.cpp: stdout and
+    output files identical to the real programs'."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "drivers", "_bin", "slic_euler_2d")
+    if not os.path.exists(exe):
+        subprocess.run(["make", "-C", os.path.join(root, "drivers")], check=True)
+    sha = json.load(open(os.path.join(golden_dir, "dat_sha256.json")))
+    a = tmp_path / "s"
+    a.mkdir()
+    r = subprocess.run([exe], cwd=a, check=True, capture_output=True, text=True)
+    assert r.stdout == open(os.path.join(golden_dir, "slic_euler_2d_stdout.txt")).read()
+    for k in (1, 7, 20):
+        assert hashlib.sha256(open(a / f"euler_{k}.dat", "rb").read()).hexdigest() == sha[f"euler_{k}.dat"]
+    b = tmp_path / "g"
+    b.mkdir()
+    r = subprocess.run([exe, "--generalise"], cwd=b, check=True, capture_output=True, text=True)
+    assert r.stdout == open(os.path.join(golden_dir, "generalise_slic_stdout.txt")).read()
+    assert hashlib.sha256(open(b / "SLIC2d.dat", "rb").read()).hexdigest() == sha["SLIC2d.dat@generaliseSLIC"]
+
+
+@gpu
 def test_large_grid_conservation():
     """4096^2 (BASELINE config 3 size) with periodic BCs: mass, momenta and energy are conserved to rounding."""
     import lsc_internship_b200 as lsc
