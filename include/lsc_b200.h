@@ -128,8 +128,9 @@ int lsc_mhd_step_timed(lsc_mhd_ctx* ctx, long nsteps, float* ms);
 int lsc_mhd_set_profiling(lsc_mhd_ctx* ctx, int enabled);
 int lsc_mhd_kernel_times(lsc_mhd_ctx* ctx, double ms[2], long launches[2]);
 
-/* How many steps had to be recomputed with the compiler's IEEE division because a fast shared-reciprocal
- * division saw an operand outside its guarded exponent window (csrc/fp64_div.cuh).  0 in normal runs. */
+/* How many thread blocks the device-side IEEE fix kernels had to recompute so far because a fast
+ * shared-reciprocal division saw an operand outside its guarded exponent window (csrc/fp64_div.cuh; e.g. the
+ * denormal momenta at a numerical front).  0 for smooth problems such as Orszag-Tang / Kelvin-Helmholtz. */
 long lsc_mhd_ieee_fallback_count(const lsc_mhd_ctx* ctx);
 
 /* t, the last dt, the last ch (= max signal speed, M:834) and the step count. Any may be NULL. */
@@ -166,7 +167,9 @@ int lsc_mhd_kat_fluxdef(int device, int dir, long n, const double* U, double gam
 /* Test hook for the shared-reciprocal fp64 division used by the kernels (csrc/fp64_div.cuh): divides
  * nblocks*256*per_thread pseudo-random operand pairs both ways on the device and counts quotients that
  * differ bitwise from the compiler's IEEE `/` (must be 0) and pairs the guard flagged for the slow path.
- * mode 0: solver-range operands, 1: arbitrary bit patterns, 2: half-ulp / all-ones-mantissa adversaries. */
+ * mode 0: solver-range operands, 1: arbitrary bit patterns, 2: half-ulp / all-ones-mantissa adversaries,
+ * 3: tiny / denormal / zero dividends.  mode + 10: the same for the branching policy (BranchDiv), which never
+ * flags -- all of its quotients must equal IEEE. */
 int lsc_kat_division(int device, unsigned long long seed, int mode, long nblocks, int per_thread,
                      unsigned long long* mismatches, unsigned long long* flagged);
 

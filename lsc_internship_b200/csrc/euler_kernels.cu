@@ -7,8 +7,15 @@
 //                                                                                        64 B read + 32 B write
 // Same structure as the MHD kernels (mhd_kernels.cu): x marches along i with the stencil in registers, y is one
 // thread per cell with face states and fluxes exchanged through shared memory; division policy as there.
+#include <algorithm>
+
 #include "euler_kernels.cuh"
 #include "euler_physics.cuh"
+
+// production division policy of these kernels (fp64_div.cuh); overridable for experiments
+#ifndef EULER_FAST_POLICY
+#define EULER_FAST_POLICY FastDiv
+#endif
 
 namespace lsc {
 
@@ -32,15 +39,15 @@ __device__ __noinline__ void euler_x_halfstates_global(D& dv, const GridDims g, 
     euler_halfstates<0>(dv, um, u0, up, p.gm1, p.cm, p.cp, p.hdtdx, hL, hR);
 }
 
+constexpr long EFIX_GRID = 148 * 4;  // persistent grid of the fix kernels (see mhd_kernels.cu)
+
 template <class D>
-__global__ void __launch_bounds__(128, 4) euler_x_sweep_kernel(const GridDims g, const EulerParams p,
-                                                               const double* __restrict__ cur,
-                                                               double* __restrict__ ubar,
-                                                               unsigned long long* __restrict__ status,
-                                                               const int strip) {
-    const int j = 2 + blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= g.ny + 2) return;
-    const int ia = 2 + blockIdx.y * strip;
+__device__ __forceinline__ bool euler_x_sweep_block(const GridDims& g, const EulerParams& p,
+                                                    const double* __restrict__ cur, double* __restrict__ ubar,
+                                                    const int bx, const int by, const int strip) {
+    const int j = 2 + bx * blockDim.x + threadIdx.x;
+    if (j >= g.ny + 2) return false;
+    const int ia = 2 + by * strip;
     const int ib = min(ia + strip, g.nxl + 2);
     const bool lo_image = (ia == 2) && (p.bcx_lo == BC_TRANSMISSIVE_E);
     const bool hi_image = (ib == g.nxl + 2) && (p.bcx_hi == BC_TRANSMISSIVE_E);
@@ -90,20 +97,49 @@ __global__ void __launch_bounds__(128, 4) euler_x_sweep_kernel(const GridDims g,
         }
         if (c < ib) eload(cur, g.plane, cell_index(g, c + 2, j), uP);
     }
-    if (dv.bad) atomicOr(status + 1, 1ull);
+    return dv.bad;
 }
 
-void launch_euler_x_sweep(const GridDims& g, const EulerParams& p, bool ieee, const double* cur, double* ubar,
-                          unsigned long long* status, cudaStream_t s) {
+template <class D>
+__global__ void __launch_bounds__(128, 4) euler_x_sweep_kernel(const GridDims g, const EulerParams p,
+                                                               const double* __restrict__ cur,
+                                                               double* __restrict__ ubar,
+                                                               unsigned long long* __restrict__ status,
+                                                               unsigned* __restrict__ fix_list, const int strip) {
+    const bool bad = euler_x_sweep_block<D>(g, p, cur, ubar, blockIdx.x, blockIdx.y, strip);
+    if (__syncthreads_or(bad) && threadIdx.x == 0)
+        fix_list[atomicAdd(status + 1, 1ull)] = blockIdx.y * gridDim.x + blockIdx.x;
+}
+
+__global__ void __launch_bounds__(128) euler_x_sweep_fix_kernel(const GridDims g, const EulerParams p,
+                                                                const double* __restrict__ cur,
+                                                                double* __restrict__ ubar,
+                                                                const unsigned long long* __restrict__ status,
+                                                                const unsigned* __restrict__ fix_list,
+                                                                const int strip, const unsigned nbx) {
+    const unsigned long long count = status[1];
+    for (unsigned long long q = blockIdx.x; q < count; q += gridDim.x) {
+        const unsigned bid = fix_list[q];
+        euler_x_sweep_block<IeeeDiv>(g, p, cur, ubar, (int)(bid % nbx), (int)(bid / nbx), strip);
+    }
+}
+
+void launch_euler_x_sweep(const GridDims& g, const EulerParams& p, const double* cur, double* ubar,
+                          unsigned long long* status, unsigned* fix_list, cudaStream_t s) {
     dim3 block(128);
     const int row_blocks = (g.ny + block.x - 1) / block.x;
     int strip = 64;
     while (strip > 8 && (long)row_blocks * ((g.nxl + strip - 1) / strip) < 148L * 4 * 3) strip /= 2;
     dim3 grid(row_blocks, (g.nxl + strip - 1) / strip);
-    if (ieee)
-        euler_x_sweep_kernel<IeeeDiv><<<grid, block, 0, s>>>(g, p, cur, ubar, status, strip);
-    else
-        euler_x_sweep_kernel<FastDiv><<<grid, block, 0, s>>>(g, p, cur, ubar, status, strip);
+    euler_x_sweep_kernel<EULER_FAST_POLICY><<<grid, block, 0, s>>>(g, p, cur, ubar, status, fix_list, strip);
+    const unsigned nfix = (unsigned)std::min<long>(EFIX_GRID, (long)grid.x * grid.y);
+    euler_x_sweep_fix_kernel<<<nfix, block, 0, s>>>(g, p, cur, ubar, status, fix_list, strip, grid.x);
+}
+
+long euler_fix_list_entries(const GridDims& g) {
+    const long xb = (long)((g.ny + 127) / 128) * ((g.nxl + 7) / 8);
+    const long yb = (long)((g.ny + 125) / 126) * g.nxl;
+    return std::max(xb, yb);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -164,17 +200,15 @@ __device__ __forceinline__ void euler_y_pass(D& dv, const GridDims& g, const Eul
 }
 
 template <class D>
-__global__ void __launch_bounds__(EBJ, 4) euler_y_sweep_kernel(const GridDims g, const EulerParams p,
-                                                               const double* __restrict__ ubar,
-                                                               const double* __restrict__ cur,
-                                                               double* __restrict__ next,
-                                                               unsigned long long* __restrict__ status) {
+__device__ __forceinline__ bool euler_y_sweep_block(const GridDims& g, const EulerParams& p,
+                                                    const double* __restrict__ ubar, const double* __restrict__ cur,
+                                                    double* __restrict__ next, const int bx, const int by,
+                                                    double& speed) {
     __shared__ double sH[NE][EBJ];
     __shared__ double sF[NE][EBJ];
-    __shared__ double warp_max[32];
     const int tid = threadIdx.x;
-    const int i = 2 + blockIdx.y;
-    const int jo = 2 + blockIdx.x * (EBJ - 2);
+    const int i = 2 + by;
+    const int jo = 2 + bx * (EBJ - 2);
     const int c = jo - 1 + tid;
     D dv;
     double A[NE], B[NE];
@@ -183,7 +217,7 @@ __global__ void __launch_bounds__(EBJ, 4) euler_y_sweep_kernel(const GridDims g,
     euler_y_pass(dv, g, p, ubar, i, c, tid, sH, sF, A);  // XthenY: y sweep of ubar
     euler_y_pass(dv, g, p, cur, i, c, tid, sH, sF, B);   // YthenX: y sweep of u (its x sweep is a no-op)
 
-    double speed = 0.0;
+    speed = 0.0;
     if (tid >= 1 && tid < EBJ - 1 && c <= g.ny + 1) {
         double un[NE];
         const size_t o = cell_index(g, i, c);
@@ -197,8 +231,13 @@ __global__ void __launch_bounds__(EBJ, 4) euler_y_sweep_kernel(const GridDims g,
         const double sp = euler_cfl_speed(dv, un, p.gamma);
         if (sp > speed) speed = sp;
     }
-    if (dv.bad) atomicOr(status + 1, 1ull);
-    // block maximum -> status[0]
+    return dv.bad;
+}
+
+// block maximum of `speed` -> status[0]
+__device__ __forceinline__ void euler_block_max(double speed, unsigned long long* status) {
+    __shared__ double warp_max[32];
+    const int tid = threadIdx.x;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         const double other = __shfl_xor_sync(0xffffffffu, speed, o);
@@ -217,14 +256,46 @@ __global__ void __launch_bounds__(EBJ, 4) euler_y_sweep_kernel(const GridDims g,
     }
 }
 
-void launch_euler_y_sweep(const GridDims& g, const EulerParams& p, bool ieee, const double* ubar, const double* cur,
-                          double* next, unsigned long long* status, cudaStream_t s) {
+template <class D>
+__global__ void __launch_bounds__(EBJ, 4) euler_y_sweep_kernel(const GridDims g, const EulerParams p,
+                                                               const double* __restrict__ ubar,
+                                                               const double* __restrict__ cur,
+                                                               double* __restrict__ next,
+                                                               unsigned long long* __restrict__ status,
+                                                               unsigned* __restrict__ fix_list) {
+    double speed;
+    const bool bad = euler_y_sweep_block<D>(g, p, ubar, cur, next, blockIdx.x, blockIdx.y, speed);
+    if (__syncthreads_or(bad)) {
+        if (threadIdx.x == 0) fix_list[atomicAdd(status + 2, 1ull)] = blockIdx.y * gridDim.x + blockIdx.x;
+    } else {
+        euler_block_max(speed, status);
+    }
+}
+
+__global__ void __launch_bounds__(EBJ) euler_y_sweep_fix_kernel(const GridDims g, const EulerParams p,
+                                                                const double* __restrict__ ubar,
+                                                                const double* __restrict__ cur,
+                                                                double* __restrict__ next,
+                                                                unsigned long long* __restrict__ status,
+                                                                const unsigned* __restrict__ fix_list,
+                                                                const unsigned nbx) {
+    const unsigned long long count = status[2];
+    for (unsigned long long q = blockIdx.x; q < count; q += gridDim.x) {
+        const unsigned bid = fix_list[q];
+        double speed;
+        euler_y_sweep_block<IeeeDiv>(g, p, ubar, cur, next, (int)(bid % nbx), (int)(bid / nbx), speed);
+        euler_block_max(speed, status);
+        __syncthreads();
+    }
+}
+
+void launch_euler_y_sweep(const GridDims& g, const EulerParams& p, const double* ubar, const double* cur, double* next,
+                          unsigned long long* status, unsigned* fix_list, cudaStream_t s) {
     dim3 block(EBJ);
     dim3 grid((g.ny + (EBJ - 2) - 1) / (EBJ - 2), g.nxl);
-    if (ieee)
-        euler_y_sweep_kernel<IeeeDiv><<<grid, block, 0, s>>>(g, p, ubar, cur, next, status);
-    else
-        euler_y_sweep_kernel<FastDiv><<<grid, block, 0, s>>>(g, p, ubar, cur, next, status);
+    euler_y_sweep_kernel<EULER_FAST_POLICY><<<grid, block, 0, s>>>(g, p, ubar, cur, next, status, fix_list);
+    const unsigned nfix = (unsigned)std::min<long>(EFIX_GRID, (long)grid.x * grid.y);
+    euler_y_sweep_fix_kernel<<<nfix, block, 0, s>>>(g, p, ubar, cur, next, status, fix_list, grid.x);
 }
 
 // Stand-alone CFL reduction over [i_lo,i_hi] x [j_lo,j_hi]: the reference's range is [2,n+2] on the array as

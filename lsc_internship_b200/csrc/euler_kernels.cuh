@@ -16,10 +16,12 @@ struct EulerParams {
     int bcy;
 };
 
-void launch_euler_x_sweep(const GridDims& g, const EulerParams& p, bool ieee, const double* cur, double* ubar,
-                          unsigned long long* status, cudaStream_t s);
-void launch_euler_y_sweep(const GridDims& g, const EulerParams& p, bool ieee, const double* ubar, const double* cur,
-                          double* next, unsigned long long* status, cudaStream_t s);
+// status / fix_list as in mhd_kernels.cuh: [0] max speed bits, [1]/[2] x/y blocks recomputed with IEEE division
+void launch_euler_x_sweep(const GridDims& g, const EulerParams& p, const double* cur, double* ubar,
+                          unsigned long long* status, unsigned* fix_list, cudaStream_t s);
+void launch_euler_y_sweep(const GridDims& g, const EulerParams& p, const double* ubar, const double* cur, double* next,
+                          unsigned long long* status, unsigned* fix_list, cudaStream_t s);
+long euler_fix_list_entries(const GridDims& g);
 void launch_euler_max_speed(const GridDims& g, double gamma, const double* u, int i_lo, int i_hi, int j_lo, int j_hi,
                             unsigned long long* status, cudaStream_t s);
 void launch_euler_x_ghosts(const GridDims& g, int bc_x, double* u, cudaStream_t s);

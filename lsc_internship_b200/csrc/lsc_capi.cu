@@ -36,6 +36,8 @@ int fail(int code, const char* fmt, ...) {
             return fail(LSC_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); \
     } while (0)
 
+constexpr size_t STATUS_BYTES = 4 * sizeof(unsigned long long);
+
 inline int to_kernel_bc(int bc) {
     switch (bc) {
         case LSC_BC_PERIODIC: return lsc::BC_PERIODIC;
@@ -62,17 +64,18 @@ struct lsc_mhd_ctx {
     int nxl = 0, i0 = 0;  // slab: interior columns, first global interior column (0-based)
     double dx = 0, dy = 0;
     lsc::GridDims g{};
-    // four rotating states: u^n, uBar, u^{n-1}, and the buffer u^{n+1} is written to.  The fourth one
-    // keeps u^{n-1} intact until the step's status word has been read, so a step can be recomputed
-    // with IEEE division if a fast division flagged an operand (mhd_kernels.cu).
-    double* state[4] = {nullptr, nullptr, nullptr, nullptr};
-    int cur = 0, bar = 1, prev = 2, spare = 3;
-    unsigned long long* d_max = nullptr;  // [0] bit pattern of the max signal speed of state[cur], [1] flag
-    unsigned long long* h_max = nullptr;  // pinned copy of both words
+    // three rotating states: u^n, uBar, and u^{n-1} whose buffer receives u^{n+1}
+    double* state[3] = {nullptr, nullptr, nullptr};
+    int cur = 0, bar = 1, prev = 2;
+    // status words: [0] bit pattern of the max signal speed of state[cur], [1]/[2] number of x/y sweep blocks
+    // recomputed with IEEE division in the last step (mhd_kernels.cu), [3] unused
+    unsigned long long* d_max = nullptr;
+    unsigned long long* h_max = nullptr;  // pinned copy
+    unsigned* d_fix = nullptr;            // y-sweep block indices flagged by the fast sweep
+    unsigned* d_xflags = nullptr;         // per-block flags of the x sweep (all zero between steps)
     bool pending = false;                 // status of the last launched step not read back yet
     bool pending_step = false;            // ... and that status belongs to a step (not to an upload)
     double max_speed = 0;                 // max signal speed of state[cur] once resolved
-    lsc::SweepParams last_px{}, last_py{};
     long ieee_redos = 0;
     double* d_stage = nullptr;            // AoS staging for transfers
     int stage_cols = 0;
@@ -148,7 +151,7 @@ int lsc_mhd_create(const lsc_mhd_config* cfg, lsc_mhd_ctx** out) {
     c->g.pitch = ((cfg->ny + 4 + lsc::JOFF) + 15) / 16 * 16;
     c->g.plane = (size_t)(c->nxl + 4) * (size_t)c->g.pitch;
     const size_t state_bytes = c->g.plane * lsc::NV * sizeof(double);
-    for (int b = 0; b < 4; ++b) {
+    for (int b = 0; b < 3; ++b) {
         if (cudaMalloc(&c->state[b], state_bytes) != cudaSuccess) {
             cudaGetLastError();
             lsc_mhd_destroy(c);
@@ -163,8 +166,11 @@ int lsc_mhd_create(const lsc_mhd_config* cfg, lsc_mhd_ctx** out) {
     if (cols > c->nxl + 4) cols = c->nxl + 4;
     c->stage_cols = (int)cols;
     if (cudaMalloc(&c->d_stage, col_bytes * (size_t)cols) != cudaSuccess ||
-        cudaMalloc(&c->d_max, 2 * sizeof(unsigned long long)) != cudaSuccess ||
-        cudaHostAlloc(&c->h_max, 2 * sizeof(unsigned long long), cudaHostAllocDefault) != cudaSuccess ||
+        cudaMalloc(&c->d_max, STATUS_BYTES) != cudaSuccess ||
+        cudaMalloc(&c->d_fix, sizeof(unsigned) * (size_t)lsc::y_sweep_block_count(c->g)) != cudaSuccess ||
+        cudaMalloc(&c->d_xflags, sizeof(unsigned) * (size_t)lsc::x_sweep_block_count(c->g)) != cudaSuccess ||
+        cudaMemset(c->d_xflags, 0, sizeof(unsigned) * (size_t)lsc::x_sweep_block_count(c->g)) != cudaSuccess ||
+        cudaHostAlloc(&c->h_max, STATUS_BYTES, cudaHostAllocDefault) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->halo_event, cudaEventDisableTiming) != cudaSuccess) {
         cudaGetLastError();
@@ -180,8 +186,10 @@ int lsc_mhd_destroy(lsc_mhd_ctx* c) {
     cudaSetDevice(c->cfg.device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->comm) lsc::comm_destroy(c->comm);
-    for (int b = 0; b < 4; ++b)
+    for (int b = 0; b < 3; ++b)
         if (c->state[b]) cudaFree(c->state[b]);
+    if (c->d_fix) cudaFree(c->d_fix);
+    if (c->d_xflags) cudaFree(c->d_xflags);
     if (c->d_stage) cudaFree(c->d_stage);
     if (c->d_max) cudaFree(c->d_max);
     if (c->h_max) cudaFreeHost(c->h_max);
@@ -209,7 +217,7 @@ namespace {
 // after new data has been placed in state[cur]: reset the clock and reduce the initial signal speed
 // over the reference's range (MUSCL_NEW.cpp:73-74: i,j in [1, n+1], array as uploaded, ghosts included)
 int finish_upload(lsc_mhd_ctx* c) {
-    CUDA_TRY(cudaMemsetAsync(c->d_max, 0, 2 * sizeof(unsigned long long), c->stream));
+    CUDA_TRY(cudaMemsetAsync(c->d_max, 0, STATUS_BYTES, c->stream));
     const int i_lo = (c->cfg.rank == 0) ? 1 : 2;
     lsc::launch_max_speed(c->g, c->cfg.gamma, c->state[c->cur], i_lo, c->nxl + 1, 1, c->cfg.ny + 1, c->d_max,
                           c->stream);
@@ -304,44 +312,24 @@ int fill_x_ghosts(lsc_mhd_ctx* c, int b) {
 // 16-byte readback of {max signal speed bits, fast-division flag} of this context (no communication).
 int read_status_local(lsc_mhd_ctx* c) {
     CUDA_TRY(cudaSetDevice(c->cfg.device));
-    CUDA_TRY(cudaMemcpyAsync(c->h_max, c->d_max, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaMemcpyAsync(c->h_max, c->d_max, STATUS_BYTES, cudaMemcpyDeviceToHost, c->stream));
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     return LSC_OK;
 }
 
-// Recompute the step launched last with IEEE division.  Its inputs are still intact: state[prev] = u^n,
-// state[spare] = u^{n-1}; the result overwrites state[cur].
-int relaunch_last_step_ieee(lsc_mhd_ctx* c) {
-    CUDA_TRY(cudaSetDevice(c->cfg.device));
-    c->ieee_redos += 1;
-    CUDA_TRY(cudaMemsetAsync(c->d_max, 0, 2 * sizeof(unsigned long long), c->stream));
-    lsc::launch_x_sweep(c->g, c->last_px, true, c->state[c->prev], c->state[c->spare], c->state[c->bar], c->d_max,
-                        c->stream);
-    lsc::launch_y_sweep(c->g, c->last_py, true, c->state[c->bar], c->state[c->prev], c->state[c->cur], c->d_max,
-                        c->stream);
-    lsc_count_launches(2);
-    CUDA_TRY(cudaGetLastError());
-    return LSC_OK;
-}
-
-// Read back the status of the step launched last; if a fast division flagged an operand anywhere, recompute.
+// Read back the status of the step launched last (max signal speed of the new state; how many blocks the
+// device-side IEEE fix kernels had to recompute).
 int resolve_pending(lsc_mhd_ctx* c) {
     if (!c->pending) return LSC_OK;
     if (c->in_group) return fail(LSC_ESTATE, "context belongs to a group: use the lsc_mhd_group_* calls");
-    for (int attempt = 0; attempt < 2; ++attempt) {
-        if (c->cfg.nranks > 1) {
-            if (!c->comm) return fail(LSC_ESTATE, "nranks > 1 but lsc_mhd_comm_init was not called");
-            if (lsc::comm_allreduce_max_u64(c->comm, c->d_max, 2, c->stream))
-                return fail(LSC_ECOMM, "allreduce failed: %s", lsc::comm_error());
-        }
-        int rc = read_status_local(c);
-        if (rc) return rc;
-        if (c->h_max[1] == 0 || attempt == 1) break;
-        rc = relaunch_last_step_ieee(c);
-        if (rc) return rc;
-        rc = fill_x_ghosts(c, c->cur);
-        if (rc) return rc;
+    if (c->cfg.nranks > 1) {
+        if (!c->comm) return fail(LSC_ESTATE, "nranks > 1 but lsc_mhd_comm_init was not called");
+        if (lsc::comm_allreduce_max_u64(c->comm, c->d_max, 1, c->stream))
+            return fail(LSC_ECOMM, "allreduce failed: %s", lsc::comm_error());
     }
+    int rc = read_status_local(c);
+    if (rc) return rc;
+    if (c->pending_step) c->ieee_redos += (long)(c->h_max[1] + c->h_max[2]);
     std::memcpy(&c->max_speed, &c->h_max[0], sizeof(double));
     c->pending = false;
     return LSC_OK;
@@ -382,9 +370,8 @@ int launch_sweeps(lsc_mhd_ctx* c) {
         for (auto& e : ev) CUDA_TRY(cudaEventCreate(&e));
         CUDA_TRY(cudaEventRecord(ev[0], c->stream));
     }
-    CUDA_TRY(cudaMemsetAsync(c->d_max, 0, 2 * sizeof(unsigned long long), c->stream));
-    c->last_px = p;
-    lsc::launch_x_sweep(c->g, p, false, c->state[c->cur], c->state[c->prev], c->state[c->bar], c->d_max,
+    CUDA_TRY(cudaMemsetAsync(c->d_max, 0, STATUS_BYTES, c->stream));
+    lsc::launch_x_sweep(c->g, p, c->state[c->cur], c->state[c->prev], c->state[c->bar], c->d_max, c->d_xflags,
                         c->stream);
     if (c->profiling) CUDA_TRY(cudaEventRecord(ev[1], c->stream));
 
@@ -393,19 +380,17 @@ int launch_sweeps(lsc_mhd_ctx* c) {
     p.hdtdh = 0.5 * (dt / c->dy);
     p.bc_lo = p.bc_hi = to_kernel_bc(c->cfg.bc_y);
     if (c->profiling) CUDA_TRY(cudaEventRecord(ev[2], c->stream));
-    c->last_py = p;
-    lsc::launch_y_sweep(c->g, p, false, c->state[c->bar], c->state[c->cur], c->state[c->spare], c->d_max,
+    lsc::launch_y_sweep(c->g, p, c->state[c->bar], c->state[c->cur], c->state[c->prev], c->d_max, c->d_fix,
                         c->stream);
     if (c->profiling) {
         CUDA_TRY(cudaEventRecord(ev[3], c->stream));
         for (auto e : ev) c->prof_events.push_back(e);
     }
-    lsc_count_launches(2);
+    lsc_count_launches(4);
     CUDA_TRY(cudaGetLastError());
 
     // u = uPlus1 (:969): rotate; the old u^n stays as the limiter's "previous" state
-    const int next = c->spare;
-    c->spare = c->prev;
+    const int next = c->prev;
     c->prev = c->cur;
     c->cur = next;
     c->pending = true;
@@ -470,25 +455,15 @@ int group_halo(lsc_mhd_ctx** g, int n) {
 
 int group_resolve(lsc_mhd_ctx** g, int n) {
     if (!g[0]->pending) return LSC_OK;
-    for (int attempt = 0; attempt < 2; ++attempt) {
-        unsigned long long mx = 0, flag = 0;
-        for (int r = 0; r < n; ++r) {
-            int rc = read_status_local(g[r]);
-            if (rc) return rc;
-            mx = std::max(mx, g[r]->h_max[0]);
-            flag |= g[r]->h_max[1];
-        }
-        for (int r = 0; r < n; ++r) g[r]->h_max[0] = mx;
-        if (flag == 0 || attempt == 1) break;
-        for (int r = 0; r < n; ++r) {
-            int rc = relaunch_last_step_ieee(g[r]);
-            if (rc) return rc;
-        }
-        int rc = group_halo(g, n);
+    unsigned long long mx = 0;
+    for (int r = 0; r < n; ++r) {
+        int rc = read_status_local(g[r]);
         if (rc) return rc;
+        mx = std::max(mx, g[r]->h_max[0]);
     }
     for (int r = 0; r < n; ++r) {
-        std::memcpy(&g[r]->max_speed, &g[r]->h_max[0], sizeof(double));
+        if (g[r]->pending_step) g[r]->ieee_redos += (long)(g[r]->h_max[1] + g[r]->h_max[2]);
+        std::memcpy(&g[r]->max_speed, &mx, sizeof(double));
         g[r]->pending = false;
     }
     return LSC_OK;

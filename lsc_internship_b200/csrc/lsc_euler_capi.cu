@@ -14,14 +14,15 @@ struct lsc_euler_ctx {
     lsc_euler_config cfg;
     double dx = 0, dy = 0;
     lsc::GridDims g{};
-    // u^n, ubar, u^{n+1}: the step never overwrites its input, so it can be recomputed with IEEE division
+    // u^n, ubar, u^{n+1}
     double* state[3] = {nullptr, nullptr, nullptr};
     int cur = 0, bar = 1, next = 2;
-    unsigned long long* d_status = nullptr;  // [0] max signal speed bits of state[cur], [1] fast-division flag
+    // [0] max signal speed bits of state[cur], [1]/[2] x/y blocks recomputed with IEEE division, [3] unused
+    unsigned long long* d_status = nullptr;
+    unsigned* d_fix = nullptr;
     unsigned long long* h_status = nullptr;
     bool pending = false, pending_step = false;
     double max_speed = 0;
-    lsc::EulerParams last_p{};
     long ieee_redos = 0;
     double* d_stage = nullptr;
     int stage_cols = 0;
@@ -38,49 +39,43 @@ namespace {
 int kernel_bc(int bc) { return bc == LSC_BC_PERIODIC ? lsc::BC_PERIODIC : lsc::BC_TRANSMISSIVE_E; }
 
 int e_read_status(lsc_euler_ctx* c) {
-    LSC_CUDA_TRY(cudaMemcpyAsync(c->h_status, c->d_status, 16, cudaMemcpyDeviceToHost, c->stream));
+    LSC_CUDA_TRY(cudaMemcpyAsync(c->h_status, c->d_status, 32, cudaMemcpyDeviceToHost, c->stream));
     LSC_CUDA_TRY(cudaStreamSynchronize(c->stream));
     return LSC_OK;
 }
 
-int e_launch(lsc_euler_ctx* c, const lsc::EulerParams& p, bool ieee, int in, int out) {
-    LSC_CUDA_TRY(cudaMemsetAsync(c->d_status, 0, 16, c->stream));
+int e_launch(lsc_euler_ctx* c, const lsc::EulerParams& p, int in, int out) {
+    LSC_CUDA_TRY(cudaMemsetAsync(c->d_status, 0, 32, c->stream));
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
-    const bool prof = c->profiling && !ieee;
+    const bool prof = c->profiling;
     if (prof) {
         for (auto& e : ev) LSC_CUDA_TRY(cudaEventCreate(&e));
         LSC_CUDA_TRY(cudaEventRecord(ev[0], c->stream));
     }
-    lsc::launch_euler_x_sweep(c->g, p, ieee, c->state[in], c->state[c->bar], c->d_status, c->stream);
+    lsc::launch_euler_x_sweep(c->g, p, c->state[in], c->state[c->bar], c->d_status, c->d_fix, c->stream);
     if (prof) {
         LSC_CUDA_TRY(cudaEventRecord(ev[1], c->stream));
         LSC_CUDA_TRY(cudaEventRecord(ev[2], c->stream));
     }
-    lsc::launch_euler_y_sweep(c->g, p, ieee, c->state[c->bar], c->state[in], c->state[out], c->d_status, c->stream);
+    lsc::launch_euler_y_sweep(c->g, p, c->state[c->bar], c->state[in], c->state[out], c->d_status, c->d_fix,
+                              c->stream);
     if (prof) {
         LSC_CUDA_TRY(cudaEventRecord(ev[3], c->stream));
         for (auto e : ev) c->prof_events.push_back(e);
     }
     // applyBoundaryConditions(u) after the average (S:616): only x ghost columns are read on the device
     lsc::launch_euler_x_ghosts(c->g, kernel_bc(c->cfg.bc), c->state[out], c->stream);
-    lsc_count_launches(3);
+    lsc_count_launches(5);
     LSC_CUDA_TRY(cudaGetLastError());
     return LSC_OK;
 }
 
-// status of the step launched last; recompute it with IEEE division if a fast division flagged an operand
+// status of the step launched last: max signal speed of the new state, blocks the IEEE fix kernels recomputed
 int e_resolve(lsc_euler_ctx* c) {
     if (!c->pending) return LSC_OK;
     int rc = e_read_status(c);
     if (rc) return rc;
-    if (c->pending_step && c->h_status[1] != 0) {
-        c->ieee_redos += 1;
-        // the step's input is the state that was `cur` before the rotation, i.e. the one now in `next`
-        rc = e_launch(c, c->last_p, true, c->next, c->cur);
-        if (rc) return rc;
-        rc = e_read_status(c);
-        if (rc) return rc;
-    }
+    if (c->pending_step) c->ieee_redos += (long)(c->h_status[1] + c->h_status[2]);
     std::memcpy(&c->max_speed, &c->h_status[0], sizeof(double));
     c->pending = false;
     return LSC_OK;
@@ -109,8 +104,7 @@ int e_step_once(lsc_euler_ctx* c) {
     p.hdxdt = 0.5 * c->dx / dt;
     p.hdydt = 0.5 * c->dy / dt;
     p.bcx_lo = p.bcx_hi = p.bcy = kernel_bc(c->cfg.bc);
-    c->last_p = p;
-    rc = e_launch(c, p, false, c->cur, c->next);
+    rc = e_launch(c, p, c->cur, c->next);
     if (rc) return rc;
     const int old = c->cur;
     c->cur = c->next;
@@ -161,8 +155,9 @@ int lsc_euler_create(const lsc_euler_config* cfg, lsc_euler_ctx** out) {
         if (ok) cudaMemset(c->state[b], 0, state_bytes);
     }
     ok = ok && cudaMalloc(&c->d_stage, col_bytes * (size_t)cols) == cudaSuccess &&
-         cudaMalloc(&c->d_status, 16) == cudaSuccess &&
-         cudaHostAlloc(&c->h_status, 16, cudaHostAllocDefault) == cudaSuccess &&
+         cudaMalloc(&c->d_status, 32) == cudaSuccess &&
+         cudaMalloc(&c->d_fix, sizeof(unsigned) * (size_t)lsc::euler_fix_list_entries(c->g)) == cudaSuccess &&
+         cudaHostAlloc(&c->h_status, 32, cudaHostAllocDefault) == cudaSuccess &&
          cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess;
     if (!ok) {
         cudaGetLastError();
@@ -181,6 +176,7 @@ int lsc_euler_destroy(lsc_euler_ctx* c) {
         if (c->state[b]) cudaFree(c->state[b]);
     if (c->d_stage) cudaFree(c->d_stage);
     if (c->d_status) cudaFree(c->d_status);
+    if (c->d_fix) cudaFree(c->d_fix);
     if (c->h_status) cudaFreeHost(c->h_status);
     for (auto e : c->prof_events) cudaEventDestroy(e);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -212,7 +208,7 @@ int lsc_euler_upload(lsc_euler_ctx* c, const double* aos) {
     }
     // ComputeTimeStep of the first step sees the array as given, over i,j in [2, n+2] (S:173-174); then the
     // loop's own boundary fill (S:604) -- on the device only the x ghost columns are ever read
-    LSC_CUDA_TRY(cudaMemsetAsync(c->d_status, 0, 16, c->stream));
+    LSC_CUDA_TRY(cudaMemsetAsync(c->d_status, 0, 32, c->stream));
     lsc::launch_euler_max_speed(c->g, c->cfg.gamma, c->state[c->cur], 2, c->cfg.nx + 2, 2, c->cfg.ny + 2, c->d_status,
                                 c->stream);
     lsc::launch_euler_x_ghosts(c->g, kernel_bc(c->cfg.bc), c->state[c->cur], c->stream);

@@ -59,6 +59,9 @@ __device__ __forceinline__ unsigned long long mix64(unsigned long long z) {
 // mode 0: random mantissas, exponents within +-40 of 1 (the solver's regime)
 // mode 1: fully random bit patterns (all exponents, NaN/inf/denormals): flag must catch what is unsafe
 // mode 2: divisor mantissa all ones / dividends one ulp around exact multiples (half-ulp ties)
+// mode 3: tiny, denormal and zero dividends over solver-range divisors (numerical fronts into gas at rest)
+// POLICY: FastDiv (sticky flag) or BranchDiv (never flags: every quotient must equal IEEE)
+template <class POLICY>
 __global__ void kat_div_kernel(unsigned long long seed, int mode, int per_thread, unsigned long long* mismatches,
                                unsigned long long* flagged) {
     const unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -70,6 +73,12 @@ __global__ void kat_div_kernel(unsigned long long seed, int mode, int per_thread
         if (mode == 1) {
             a = __longlong_as_double((long long)ra);
             b = __longlong_as_double((long long)rb);
+        } else if (mode == 3) {
+            const unsigned long long eb = 1023 - 40 + (rb >> 52) % 81;
+            b = __longlong_as_double((long long)(((rb >> 63) << 63) | (eb << 52) | (rb & 0xfffffffffffffull)));
+            const unsigned long long ea = (ra >> 52) % 300;  // exponent field 0..299: denormal .. 2^-724
+            a = __longlong_as_double((long long)(((ra >> 63) << 63) | (ea << 52) | (ra & 0xfffffffffffffull)));
+            if ((it % 5) == 0) a = __longlong_as_double((long long)((ra >> 63) << 63));  // +-0
         } else {
             const unsigned long long ea = 1023 - 40 + (ra >> 52) % 81, eb = 1023 - 40 + (rb >> 52) % 81;
             unsigned long long ma = ra & 0xfffffffffffffull, mb = rb & 0xfffffffffffffull;
@@ -85,14 +94,14 @@ __global__ void kat_div_kernel(unsigned long long seed, int mode, int per_thread
             }
             if (mode == 0 && (it % 17) == 0) a = 0.0;      // exact zero dividends are common in the solver
         }
-        FastDiv dv;
+        POLICY dv;
         const Rcp r = dv.rcp(b);
         const double q = dv.div(a, r);
         const double ref = a / b;
         if (dv.bad) {
             ++flg;
-        } else if (__double_as_longlong(q) != __double_as_longlong(ref)) {
-            ++bad;
+        } else if (__double_as_longlong(q) != __double_as_longlong(ref) && !(q != q && ref != ref)) {
+            ++bad;  // (two NaNs count as equal)
         }
     }
     atomicAdd(mismatches, bad);
@@ -143,7 +152,10 @@ extern "C" int lsc_kat_division(int device, unsigned long long seed, int mode, l
     unsigned long long* d = nullptr;
     if (cudaMalloc(&d, 16) != cudaSuccess) return LSC_ENOMEM;
     cudaMemset(d, 0, 16);
-    lsc::kat_div_kernel<<<(unsigned)nblocks, 256>>>(seed, mode, per_thread, d, d + 1);
+    if (mode >= 10)
+        lsc::kat_div_kernel<lsc::BranchDiv><<<(unsigned)nblocks, 256>>>(seed, mode - 10, per_thread, d, d + 1);
+    else
+        lsc::kat_div_kernel<lsc::FastDiv><<<(unsigned)nblocks, 256>>>(seed, mode, per_thread, d, d + 1);
     lsc_count_launches(1);
     unsigned long long h[2] = {0, 0};
     int rc = LSC_OK;

@@ -9,15 +9,22 @@
 // Compiled with -fmad=false: FMA contraction changes the answer at the 1e-9 level
 // after one step and at the 1e-2 level after ten.
 //
-// Both sweeps are templated on the division policy (fp64_div.cuh).  The production
-// instantiation is FastDiv: branch-free shared-reciprocal quotients with a sticky
-// "operand outside the guarded window" flag that is OR-ed into status[1] at the end of the
-// thread.  The host reads that word together with the signal speed (status[0]); if it is
-// ever non-zero the step is recomputed from its untouched inputs with the IeeeDiv
-// instantiation (every quotient by the compiler's IEEE `/`), so the result is the
-// correctly rounded one in either case.
+// Both sweeps are templated on the division policy (fp64_div.cuh).  The production instantiation is
+// FastDiv: branch-free shared-reciprocal quotients with a sticky "operand outside the guarded window"
+// flag.  A thread block in which any thread raised the flag appends its index to a device-side list
+// (status[1] / status[2] count the entries); right after each sweep a small persistent "fix" kernel --
+// the IeeeDiv instantiation of the same block function, every quotient by the compiler's IEEE `/` --
+// recomputes exactly those blocks.  No host round trip, no branch per quotient, and the result is the
+// correctly rounded one for any input (e.g. the denormal momenta at a numerical front).
+#include <algorithm>
+
 #include "mhd_kernels.cuh"
 #include "mhd_physics.cuh"
+
+// production division policy of these kernels (fp64_div.cuh); overridable for experiments
+#ifndef MHD_FAST_POLICY
+#define MHD_FAST_POLICY FastDiv
+#endif
 
 namespace lsc {
 
@@ -72,6 +79,8 @@ __device__ __forceinline__ void block_max_to_global(double local, unsigned long 
 #define YS_BJ 128
 #endif
 
+constexpr long FIX_GRID = 148 * 4;  // persistent grid of the fix kernels
+
 // ------------------------------------------------------------------------------------
 // x sweep: one thread owns one row j and marches along i over a strip of columns,
 // keeping the 3-cell stencil, its primitives, the previous face state and the previous
@@ -108,15 +117,13 @@ __device__ __noinline__ void x_halfstates_global(D& dv, const GridDims g, const 
 }
 
 template <class D>
-__global__ void __launch_bounds__(XS_BLOCK, XS_MINB) x_sweep_kernel(const GridDims g, const SweepParams p,
-                                                                    const double* __restrict__ cur,
-                                                                    const double* __restrict__ prev,
-                                                                    double* __restrict__ ubar,
-                                                                    unsigned long long* __restrict__ status,
-                                                                    const int strip) {
-    const int j = 2 + blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= g.ny + 2) return;
-    const int ia = 2 + blockIdx.y * strip;
+__device__ __forceinline__ bool x_sweep_block(const GridDims& g, const SweepParams& p,
+                                              const double* __restrict__ cur, const double* __restrict__ prev,
+                                              double* __restrict__ ubar, const int bx, const int by,
+                                              const int strip) {
+    const int j = 2 + bx * blockDim.x + threadIdx.x;
+    if (j >= g.ny + 2) return false;
+    const int ia = 2 + by * strip;
     const int ib = min(ia + strip, g.nxl + 2);  // cells [ia, ib) are updated by this thread
     const bool lo_image = (ia == 2) && (p.bc_lo == BC_TRANSMISSIVE);
     const bool hi_image = (ib == g.nxl + 2) && (p.bc_hi == BC_TRANSMISSIVE);
@@ -189,11 +196,43 @@ __global__ void __launch_bounds__(XS_BLOCK, XS_MINB) x_sweep_kernel(const GridDi
             load_cell(cur, g.plane, cell_index(g, c + 2, j), uP);
         }
     }
-    if (dv.bad) atomicOr(status + 1, 1ull);
+    return dv.bad;
 }
 
-void launch_x_sweep(const GridDims& g, const SweepParams& p, bool ieee, const double* u_cur, const double* u_prev,
-                    double* u_bar, unsigned long long* status, cudaStream_t s) {
+template <class D>
+__global__ void __launch_bounds__(XS_BLOCK, XS_MINB) x_sweep_kernel(const GridDims g, const SweepParams p,
+                                                                    const double* __restrict__ cur,
+                                                                    const double* __restrict__ prev,
+                                                                    double* __restrict__ ubar,
+                                                                    unsigned* __restrict__ block_flags,
+                                                                    const int strip) {
+    // threads of the x sweep are independent: no barrier, a flagged thread just marks its block
+    if (x_sweep_block<D>(g, p, cur, prev, ubar, blockIdx.x, blockIdx.y, strip))
+        block_flags[blockIdx.y * gridDim.x + blockIdx.x] = 1u;
+}
+
+// Recompute the blocks a fast sweep flagged, with IEEE division (persistent grid over the device-side list).
+__global__ void __launch_bounds__(XS_BLOCK) x_sweep_fix_kernel(const GridDims g, const SweepParams p,
+                                                               const double* __restrict__ cur,
+                                                               const double* __restrict__ prev,
+                                                               double* __restrict__ ubar,
+                                                               unsigned long long* __restrict__ status,
+                                                               unsigned* __restrict__ block_flags,
+                                                               const int strip, const unsigned nbx,
+                                                               const unsigned nblocks) {
+    for (unsigned bid = blockIdx.x; bid < nblocks; bid += gridDim.x) {
+        if (block_flags[bid] == 0u) continue;  // uniform across the block
+        x_sweep_block<IeeeDiv>(g, p, cur, prev, ubar, (int)(bid % nbx), (int)(bid / nbx), strip);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            block_flags[bid] = 0u;  // all-zero again for the next step
+            atomicAdd(status + 1, 1ull);
+        }
+    }
+}
+
+void launch_x_sweep(const GridDims& g, const SweepParams& p, const double* u_cur, const double* u_prev,
+                    double* u_bar, unsigned long long* status, unsigned* x_flags, cudaStream_t s) {
     // strip length along i: XS_STRIP columns per thread (3 warm-up cells amortised over the strip), shortened
     // on small grids so that the launch still fills 148 SMs x 4 resident blocks a few times over
     dim3 block(XS_BLOCK);
@@ -201,10 +240,15 @@ void launch_x_sweep(const GridDims& g, const SweepParams& p, bool ieee, const do
     int strip = XS_STRIP;
     while (strip > 8 && (long)row_blocks * ((g.nxl + strip - 1) / strip) < 148L * 4 * 3) strip /= 2;
     dim3 grid(row_blocks, (g.nxl + strip - 1) / strip);
-    if (ieee)
-        x_sweep_kernel<IeeeDiv><<<grid, block, 0, s>>>(g, p, u_cur, u_prev, u_bar, status, strip);
-    else
-        x_sweep_kernel<FastDiv><<<grid, block, 0, s>>>(g, p, u_cur, u_prev, u_bar, status, strip);
+    x_sweep_kernel<MHD_FAST_POLICY><<<grid, block, 0, s>>>(g, p, u_cur, u_prev, u_bar, x_flags, strip);
+    const unsigned nblocks = grid.x * grid.y;
+    const unsigned nfix = (unsigned)std::min<long>(FIX_GRID, (long)nblocks);
+    x_sweep_fix_kernel<<<nfix, block, 0, s>>>(g, p, u_cur, u_prev, u_bar, status, x_flags, strip, grid.x, nblocks);
+}
+
+long x_sweep_block_count(const GridDims& g) {
+    const int row_blocks = (g.ny + XS_BLOCK - 1) / XS_BLOCK;
+    return (long)row_blocks * ((g.nxl + 7) / 8);  // strip is never shorter than 8
 }
 
 // ------------------------------------------------------------------------------------
@@ -256,19 +300,20 @@ __device__ __noinline__ void y_halfstates_global(D& dv, const GridDims g, const 
     predictor<1>(dv, hB, hT, p.gm1, p.ch2, p.hdtdh);
 }
 
+// One block of the y sweep at block coordinates (bx, by).  Returns this thread's sticky division flag and its
+// contribution to the CFL maximum in `speed`.  All threads of the block must call it (it synchronises).
 template <class D>
-__global__ void __launch_bounds__(BJ, YS_MINB) y_sweep_kernel(const GridDims g, const SweepParams p,
-                                                              const double* __restrict__ ubar,
-                                                              const double* __restrict__ cur,
-                                                              double* __restrict__ next,
-                                                              unsigned long long* __restrict__ status) {
+__device__ __forceinline__ bool y_sweep_block(const GridDims& g, const SweepParams& p,
+                                              const double* __restrict__ ubar, const double* __restrict__ cur,
+                                              double* __restrict__ next, const int bx, const int by,
+                                              double& speed) {
     __shared__ double sU[NV][BJ + 2];  // uBar of cells jo-2 .. jo+BJ-1
     __shared__ double sP[NV][BJ + 2];  // primitives of u^n there; later the interface fluxes
     __shared__ double sH[NV][BJ];      // bottom face state of each thread's cell
 
     const int tid = threadIdx.x;
-    const int i = 2 + blockIdx.y;
-    const int jo = 2 + blockIdx.x * (BJ - 2);
+    const int i = 2 + by;
+    const int jo = 2 + bx * (BJ - 2);
     const int c = jo - 1 + tid;  // this thread's cell
     const int bc = p.bc_lo;      // the reference uses one y boundary type for both ends
     D dv;
@@ -335,7 +380,7 @@ __global__ void __launch_bounds__(BJ, YS_MINB) y_sweep_kernel(const GridDims g, 
     }
     __syncthreads();
 
-    double speed = 0.0;
+    speed = 0.0;
     if (tid >= 1 && has_flux && c >= 2) {
         // u^{n+1} = uBar - (dt/dy)(F[j] - F[j-1])  MUSCL_NEW.cpp:953; psi damping :963
         double un[NV];
@@ -350,19 +395,50 @@ __global__ void __launch_bounds__(BJ, YS_MINB) y_sweep_kernel(const GridDims g, 
         const double sp = cfl_speed(dv, un, p.gamma);
         if (sp > speed) speed = sp;
     }
-    if (dv.bad) atomicOr(status + 1, 1ull);
-    block_max_to_global(speed, status);
+    return dv.bad;
 }
 
-void launch_y_sweep(const GridDims& g, const SweepParams& p, bool ieee, const double* u_bar, const double* u_cur,
-                    double* u_next, unsigned long long* status, cudaStream_t s) {
+template <class D>
+__global__ void __launch_bounds__(BJ, YS_MINB) y_sweep_kernel(const GridDims g, const SweepParams p,
+                                                              const double* __restrict__ ubar,
+                                                              const double* __restrict__ cur,
+                                                              double* __restrict__ next,
+                                                              unsigned long long* __restrict__ status,
+                                                              unsigned* __restrict__ fix_list) {
+    double speed;
+    const bool bad = y_sweep_block<D>(g, p, ubar, cur, next, blockIdx.x, blockIdx.y, speed);
+    if (__syncthreads_or(bad)) {  // whole block is recomputed by the fix kernel; its maximum must not count
+        if (threadIdx.x == 0) fix_list[atomicAdd(status + 2, 1ull)] = blockIdx.y * gridDim.x + blockIdx.x;
+    } else {
+        block_max_to_global(speed, status);
+    }
+}
+
+__global__ void __launch_bounds__(BJ) y_sweep_fix_kernel(const GridDims g, const SweepParams p,
+                                                         const double* __restrict__ ubar,
+                                                         const double* __restrict__ cur, double* __restrict__ next,
+                                                         unsigned long long* __restrict__ status,
+                                                         const unsigned* __restrict__ fix_list, const unsigned nbx) {
+    const unsigned long long count = status[2];
+    for (unsigned long long q = blockIdx.x; q < count; q += gridDim.x) {
+        const unsigned bid = fix_list[q];
+        double speed;
+        y_sweep_block<IeeeDiv>(g, p, ubar, cur, next, (int)(bid % nbx), (int)(bid / nbx), speed);
+        block_max_to_global(speed, status);
+        __syncthreads();  // shared tiles are reused by the next list entry
+    }
+}
+
+void launch_y_sweep(const GridDims& g, const SweepParams& p, const double* u_bar, const double* u_cur,
+                    double* u_next, unsigned long long* status, unsigned* fix_list, cudaStream_t s) {
     dim3 block(BJ);
     dim3 grid((g.ny + (BJ - 2) - 1) / (BJ - 2), g.nxl);
-    if (ieee)
-        y_sweep_kernel<IeeeDiv><<<grid, block, 0, s>>>(g, p, u_bar, u_cur, u_next, status);
-    else
-        y_sweep_kernel<FastDiv><<<grid, block, 0, s>>>(g, p, u_bar, u_cur, u_next, status);
+    y_sweep_kernel<MHD_FAST_POLICY><<<grid, block, 0, s>>>(g, p, u_bar, u_cur, u_next, status, fix_list);
+    const unsigned nfix = (unsigned)std::min<long>(FIX_GRID, (long)grid.x * grid.y);
+    y_sweep_fix_kernel<<<nfix, block, 0, s>>>(g, p, u_bar, u_cur, u_next, status, fix_list, grid.x);
 }
+
+long y_sweep_block_count(const GridDims& g) { return (long)((g.ny + (BJ - 2) - 1) / (BJ - 2)) * g.nxl; }
 
 // ------------------------------------------------------------------------------------
 // Ghost columns in x (single-rank case; between ranks the same columns are filled by the

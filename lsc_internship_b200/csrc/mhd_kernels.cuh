@@ -42,12 +42,17 @@ struct SweepParams {
                          // end is an inter-rank slab edge (ghost columns then hold neighbour data)
 };
 
-// status[0] = bit pattern of the max signal speed (y sweep), status[1] = sticky "a fast division saw an
-// operand outside its guarded window" flag.  ieee = true launches the IeeeDiv instantiation.
-void launch_x_sweep(const GridDims& g, const SweepParams& p, bool ieee, const double* u_cur, const double* u_prev,
-                    double* u_bar, unsigned long long* status, cudaStream_t s);
-void launch_y_sweep(const GridDims& g, const SweepParams& p, bool ieee, const double* u_bar, const double* u_cur,
-                    double* u_next, unsigned long long* status, cudaStream_t s);
+// status[0] = bit pattern of the max signal speed (y sweep), status[1] / status[2] = number of x / y sweep
+// blocks in which a fast division saw an operand outside its guarded window; those block indices are in
+// recomputed with IEEE division by the fix kernel launched right behind each sweep.  The x sweep marks them in
+// x_flags (x_sweep_block_count entries, all zero on entry and again on exit), the y sweep lists them in fix_list
+// (y_sweep_block_count entries).
+void launch_x_sweep(const GridDims& g, const SweepParams& p, const double* u_cur, const double* u_prev,
+                    double* u_bar, unsigned long long* status, unsigned* x_flags, cudaStream_t s);
+void launch_y_sweep(const GridDims& g, const SweepParams& p, const double* u_bar, const double* u_cur,
+                    double* u_next, unsigned long long* status, unsigned* fix_list, cudaStream_t s);
+long x_sweep_block_count(const GridDims& g);
+long y_sweep_block_count(const GridDims& g);
 void launch_x_ghosts(const GridDims& g, int bc_x, double* u, cudaStream_t s);
 // transmissive image of ONE side (0 = low, 1 = high): end ranks of a non-periodic slab decomposition
 void launch_x_ghosts_side(const GridDims& g, int hi_side, double* u, cudaStream_t s);

@@ -64,6 +64,16 @@ def oracle_hllc(Ls, Rs, gamma, ch, d):
     return F
 
 
+@pytest.mark.parametrize("mode", [10, 11, 12, 13])
+def test_branching_division_is_ieee_everywhere(mode):
+    """BranchDiv (used where numerical fronts carry denormal momenta): every quotient equals IEEE `/`, for solver-range,
+    arbitrary, adversarial and tiny/denormal/zero operands alike; it never defers to a recompute."""
+    import ctypes
+    bad, flagged = ctypes.c_ulonglong(), ctypes.c_ulonglong()
+    rc = lsc.lib().lsc_kat_division(0, 0xBEEF + mode, mode, 1 << 14, 256, ctypes.byref(bad), ctypes.byref(flagged))
+    assert rc == 0 and bad.value == 0 and flagged.value == 0
+
+
 @pytest.mark.parametrize("mode", [0, 1, 2])
 def test_custom_division_is_ieee(mode):
     """csrc/fp64_div.cuh vs the compiler's IEEE `/` on 2^31 operand pairs per mode: zero bitwise
