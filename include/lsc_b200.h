@@ -164,6 +164,13 @@ int lsc_mhd_kat_hllc(int device, int dir, long n, const double* L, const double*
                      double* F);
 int lsc_mhd_kat_fluxdef(int device, int dir, long n, const double* U, double gamma, double ch, double* F);
 
+/* Test hook for the CFL reduction's warp filter (csrc/mhd_physics.cuh: cfl_speed_upper_f32): for n states
+ * returns exact_and_bound[2t] = the exact fp64 signal speed (ComputeTimeStep, MUSCL_NEW.cpp:75-109) and
+ * [2t+1] = the single-precision upper bound of (signal speed / run_max) the y sweep uses to skip warps that
+ * cannot raise the running maximum run_max (NaN = "not trusted, evaluate exactly"). */
+int lsc_mhd_kat_cfl_bound(int device, long n, const double* U, double gamma, double run_max,
+                          double* exact_and_bound);
+
 /* Test hook for the shared-reciprocal fp64 division used by the kernels (csrc/fp64_div.cuh): divides
  * nblocks*256*per_thread pseudo-random operand pairs both ways on the device and counts quotients that
  * differ bitwise from the compiler's IEEE `/` (must be 0) and pairs the guard flagged for the slow path.

@@ -97,7 +97,7 @@ __device__ __forceinline__ bool euler_x_sweep_block(const GridDims& g, const Eul
         }
         if (c < ib) eload(cur, g.plane, cell_index(g, c + 2, j), uP);
     }
-    return dv.bad;
+    return dv.bad();
 }
 
 template <class D>
@@ -231,7 +231,7 @@ __device__ __forceinline__ bool euler_y_sweep_block(const GridDims& g, const Eul
         const double sp = euler_cfl_speed(dv, un, p.gamma);
         if (sp > speed) speed = sp;
     }
-    return dv.bad;
+    return dv.bad();
 }
 
 // block maximum of `speed` -> status[0]

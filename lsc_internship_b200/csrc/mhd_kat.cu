@@ -22,7 +22,7 @@ __global__ void kat_hllc_kernel(long n, const double* __restrict__ L, const doub
     }
     FastDiv dv;
     hllc_flux<DIR>(dv, l, r, gamma, gamma - 1, ch, ch * ch, 1.0 / (2.0 * ch), ch / 2.0, f);
-    if (dv.bad) {
+    if (dv.bad()) {
         IeeeDiv sv;
         hllc_flux<DIR>(sv, l, r, gamma, gamma - 1, ch, ch * ch, 1.0 / (2.0 * ch), ch / 2.0, f);
     }
@@ -40,7 +40,7 @@ __global__ void kat_fluxdef_kernel(long n, const double* __restrict__ U, double 
     for (int k = 0; k < NV; ++k) u[k] = U[t * NV + k];
     FastDiv dv;
     flux_def<DIR>(dv, u, gamma - 1, ch * ch, f);
-    if (dv.bad) {
+    if (dv.bad()) {
         IeeeDiv sv;
         flux_def<DIR>(sv, u, gamma - 1, ch * ch, f);
     }
@@ -95,10 +95,15 @@ __global__ void kat_div_kernel(unsigned long long seed, int mode, int per_thread
             if (mode == 0 && (it % 17) == 0) a = 0.0;      // exact zero dividends are common in the solver
         }
         POLICY dv;
-        const Rcp r = dv.rcp(b);
-        const double q = dv.div(a, r);
+        double q;
+        if (it & 4) {
+            q = dv.div(a, b);  // the single-quotient form (its own window bookkeeping)
+        } else {
+            const Rcp r = dv.rcp(b);
+            q = dv.div(a, r);
+        }
         const double ref = a / b;
-        if (dv.bad) {
+        if (dv.bad()) {
             ++flg;
         } else if (__double_as_longlong(q) != __double_as_longlong(ref) && !(q != q && ref != ref)) {
             ++bad;  // (two NaNs count as equal)
@@ -106,6 +111,20 @@ __global__ void kat_div_kernel(unsigned long long seed, int mode, int per_thread
     }
     atomicAdd(mismatches, bad);
     atomicAdd(flagged, flg);
+}
+
+// exact signal speed (IEEE division) and the fp32 upper bound of speed/run_max; out[2t] = exact, out[2t+1] = bound
+__global__ void kat_cfl_bound_kernel(long n, const double* __restrict__ U, double gamma, double run_max,
+                                     double* __restrict__ out) {
+    const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    double u[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) u[k] = U[t * NV + k];
+    IeeeDiv dv;
+    out[2 * t] = cfl_speed(dv, u, gamma);
+    out[2 * t + 1] = (double)cfl_speed_over_max_f32(u, __double2float_ru(gamma), __double2float_ru(gamma - 1),
+                                                    __frcp_ru(__double2float_rd(run_max)));
 }
 
 static int run_kat(int device, int dir, long n, const double* a, const double* b, double gamma, double ch,
@@ -166,6 +185,29 @@ extern "C" int lsc_kat_division(int device, unsigned long long seed, int mode, l
     cudaFree(d);
     *mismatches = h[0];
     *flagged = h[1];
+    return rc;
+}
+
+extern "C" int lsc_mhd_kat_cfl_bound(int device, long n, const double* U, double gamma, double run_max,
+                                     double* exact_and_bound) {
+    if (n <= 0 || !U || !exact_and_bound) return LSC_EINVAL;
+    if (cudaSetDevice(device) != cudaSuccess) return LSC_ECUDA;
+    double *du = nullptr, *dout = nullptr;
+    int rc = LSC_OK;
+    if (cudaMalloc(&du, (size_t)n * lsc::NV * 8) != cudaSuccess || cudaMalloc(&dout, (size_t)n * 16) != cudaSuccess) {
+        rc = LSC_ENOMEM;
+    } else {
+        cudaMemcpy(du, U, (size_t)n * lsc::NV * 8, cudaMemcpyHostToDevice);
+        lsc::kat_cfl_bound_kernel<<<(unsigned)((n + 127) / 128), 128>>>(n, du, gamma, run_max, dout);
+        lsc_count_launches(1);
+        if (cudaDeviceSynchronize() != cudaSuccess ||
+            cudaMemcpy(exact_and_bound, dout, (size_t)n * 16, cudaMemcpyDeviceToHost) != cudaSuccess) {
+            cudaGetLastError();
+            rc = LSC_ECUDA;
+        }
+    }
+    cudaFree(du);
+    cudaFree(dout);
     return rc;
 }
 

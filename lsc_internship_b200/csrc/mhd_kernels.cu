@@ -17,6 +17,7 @@
 // recomputes exactly those blocks.  No host round trip, no branch per quotient, and the result is the
 // correctly rounded one for any input (e.g. the denormal momenta at a numerical front).
 #include <algorithm>
+#include <type_traits>
 
 #include "mhd_kernels.cuh"
 #include "mhd_physics.cuh"
@@ -196,7 +197,7 @@ __device__ __forceinline__ bool x_sweep_block(const GridDims& g, const SweepPara
             load_cell(cur, g.plane, cell_index(g, c + 2, j), uP);
         }
     }
-    return dv.bad;
+    return dv.bad();
 }
 
 template <class D>
@@ -306,7 +307,15 @@ template <class D>
 __device__ __forceinline__ bool y_sweep_block(const GridDims& g, const SweepParams& p,
                                               const double* __restrict__ ubar, const double* __restrict__ cur,
                                               double* __restrict__ next, const int bx, const int by,
-                                              double& speed) {
+                                              double& speed, const unsigned long long* status) {
+    // Fast instantiation only: the running exact maximum of the blocks that already finished (stale is fine,
+    // it only grows), rounded down to fp32.  Read first so that its latency hides behind the tile load.
+    constexpr bool FILTER = !std::is_same<D, IeeeDiv>::value;
+    float inv_run_max = 0.0f;  // 1/R rounded up (R = 0 -> +inf -> every warp evaluates)
+    if (FILTER) {
+        const float r = __double2float_rd(__longlong_as_double((long long)*(const volatile unsigned long long*)status));
+        inv_run_max = __frcp_ru(r);
+    }
     __shared__ double sU[NV][BJ + 2];  // uBar of cells jo-2 .. jo+BJ-1
     __shared__ double sP[NV][BJ + 2];  // primitives of u^n there; later the interface fluxes
     __shared__ double sH[NV][BJ];      // bottom face state of each thread's cell
@@ -381,9 +390,10 @@ __device__ __forceinline__ bool y_sweep_block(const GridDims& g, const SweepPara
     __syncthreads();
 
     speed = 0.0;
-    if (tid >= 1 && has_flux && c >= 2) {
+    const bool updates = (tid >= 1 && has_flux && c >= 2);
+    double un[NV];
+    if (updates) {
         // u^{n+1} = uBar - (dt/dy)(F[j] - F[j-1])  MUSCL_NEW.cpp:953; psi damping :963
-        double un[NV];
         const size_t o = cell_index(g, i, c);
 #pragma unroll
         for (int k = 0; k < NV; ++k) {
@@ -392,10 +402,24 @@ __device__ __forceinline__ bool y_sweep_block(const GridDims& g, const SweepPara
             un[k] = v;
             next[(size_t)k * g.plane + o] = v;
         }
+    }
+    // Signal speed of the new state for the next step's CFL condition (MUSCL_NEW.cpp:75-111).  Only the global
+    // maximum is consumed, so a warp evaluates the exact fp64 expression only if one of its cells could hold
+    // it: its fp32 upper bound is not provably below the running exact maximum.  Skipped cells are < that
+    // running maximum <= the final maximum, so the result is the same bit pattern whatever the block order.
+    bool evaluate = updates;
+    if (FILTER) {
+        bool candidate = false;
+        if (updates)
+            candidate = !(cfl_speed_over_max_f32(un, __double2float_ru(p.gamma), __double2float_ru(p.gm1), inv_run_max) < 1.0f);
+        const bool warp_has_candidate = __any_sync(0xffffffffu, candidate);  // every lane votes (no short circuit)
+        evaluate = updates && warp_has_candidate;
+    }
+    if (evaluate) {
         const double sp = cfl_speed(dv, un, p.gamma);
         if (sp > speed) speed = sp;
     }
-    return dv.bad;
+    return dv.bad();
 }
 
 template <class D>
@@ -406,7 +430,7 @@ __global__ void __launch_bounds__(BJ, YS_MINB) y_sweep_kernel(const GridDims g, 
                                                               unsigned long long* __restrict__ status,
                                                               unsigned* __restrict__ fix_list) {
     double speed;
-    const bool bad = y_sweep_block<D>(g, p, ubar, cur, next, blockIdx.x, blockIdx.y, speed);
+    const bool bad = y_sweep_block<D>(g, p, ubar, cur, next, blockIdx.x, blockIdx.y, speed, status);
     if (__syncthreads_or(bad)) {  // whole block is recomputed by the fix kernel; its maximum must not count
         if (threadIdx.x == 0) fix_list[atomicAdd(status + 2, 1ull)] = blockIdx.y * gridDim.x + blockIdx.x;
     } else {
@@ -423,7 +447,7 @@ __global__ void __launch_bounds__(BJ) y_sweep_fix_kernel(const GridDims g, const
     for (unsigned long long q = blockIdx.x; q < count; q += gridDim.x) {
         const unsigned bid = fix_list[q];
         double speed;
-        y_sweep_block<IeeeDiv>(g, p, ubar, cur, next, (int)(bid % nbx), (int)(bid / nbx), speed);
+        y_sweep_block<IeeeDiv>(g, p, ubar, cur, next, (int)(bid % nbx), (int)(bid / nbx), speed, status);
         block_max_to_global(speed, status);
         __syncthreads();  // shared tiles are reused by the next list entry
     }

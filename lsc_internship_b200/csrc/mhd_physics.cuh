@@ -296,4 +296,49 @@ __device__ __forceinline__ double cfl_speed(D& dv, const double (&q)[NV], double
     return std_max(std_max(fabs(ux) + cfx, fabs(uy) + cfy), fabs(uz) + cfz);
 }
 
+// Single-precision UPPER BOUND of cfl_speed(q) / R for the y sweep's warp filter: a cell with bound < 1 has an
+// exact signal speed below the running exact maximum R and cannot raise it, so its warp may skip the fp64
+// evaluation.  Everything is formed in units of R (inv_r = 1/R rounded up), which makes the estimate invariant
+// under the scalings of the state (rho, m, E -> c*rho, c*m, c*E; B -> sqrt(c)*B; any velocity unit): fp32
+// underflow can then only lose contributions that are < 1e-13 of R.  Conservative by construction:
+//   * the pressure, the one cancellation-prone term, gets +1e-6*(|E| + kinetic + magnetic) before use;
+//   * the inner radicand s^2 - 4 a^2 b_d^2 (cancels when a ~ b with B along d) gets +2e-6*s^2;
+//   * the total is inflated by 2^-10, three orders above the accumulated fp32 rounding (~20 ops * 6e-8) and
+//     the error of the approximate rcp/sqrt (2^-22);
+//   * the scale factors 1/(rho R), 1/(rho R^2) must lie in [1e-25, 1e25], otherwise the result is NaN.
+// NaN/inf anywhere (negative pressure, fp32 overflow, R = 0) propagates to the result; the caller evaluates
+// exactly unless `bound < 1` holds.  tests/test_mhd_gpu.py::test_cfl_upper_bound checks bound*R >= exact.
+__device__ __forceinline__ float cfl_speed_over_max_f32(const double (&q)[NV], float gamma_up, float gm1_up,
+                                                        float inv_r) {
+    const float rho = (float)q[0];
+    float ir;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ir) : "f"(rho));
+    const float kv = ir * inv_r;  // momentum -> velocity / R
+    const float k = kv * inv_r;   // energy density -> speed^2 / R^2
+    const float vx = fabsf((float)q[1]) * kv, vy = fabsf((float)q[2]) * kv, vz = fabsf((float)q[3]) * kv;
+    const float e = (float)q[4] * k;
+    const float b1 = (float)q[5], b2 = (float)q[6], b3 = (float)q[7];
+    const float bx2 = (b1 * k) * b1, by2 = (b2 * k) * b2, bz2 = (b3 * k) * b3;
+    const float B2 = bx2 + by2 + bz2;
+    const float ke = 0.5f * ((vx * vx + vy * vy) + vz * vz);
+    const float mag = 0.5f * B2;
+    const float pk = gm1_up * ((e - ke - mag) + 1e-6f * (fabsf(e) + ke + mag));  // p / (rho R^2), upper bound
+    const float a2 = gamma_up * pk;
+    const float s = a2 + B2;
+    const float s2 = s * s;
+    const float pad = 2e-6f * s2;
+    const float fa = 4.0f * a2;
+    float rx, ry, rz, cx, cy, cz;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(rx) : "f"(fmaxf(s2 - fa * bx2, 0.0f) + pad));
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(ry) : "f"(fmaxf(s2 - fa * by2, 0.0f) + pad));
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(rz) : "f"(fmaxf(s2 - fa * bz2, 0.0f) + pad));
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(cx) : "f"(0.5f * (s + rx)));
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(cy) : "f"(0.5f * (s + ry)));
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(cz) : "f"(0.5f * (s + rz)));
+    const float sx = vx + cx, sy = vy + cy, sz = vz + cz;
+    float best = fmax3_nan(sx, sy, sz) * 1.0009765625f;  // NaN-propagating maximum
+    const bool scales_ok = fminf(k, kv) > 1e-25f && fmaxf(k, kv) < 1e25f;
+    return scales_ok ? best : __int_as_float(0x7fc00000);
+}
+
 }  // namespace lsc

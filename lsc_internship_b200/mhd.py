@@ -234,6 +234,14 @@ def kat_hllc(L, R, gamma, ch, direction, device=0):
     return F
 
 
+def kat_cfl_bound(U, gamma, run_max, device=0):
+    """(exact fp64 signal speed, fp32 upper bound of speed/run_max used by the y sweep's warp filter) per state."""
+    U = np.ascontiguousarray(U, dtype=np.float64)
+    out = np.empty((U.shape[0], 2), dtype=np.float64)
+    check(lib().lsc_mhd_kat_cfl_bound(device, U.shape[0], _dp(U), float(gamma), float(run_max), _dp(out)))
+    return out[:, 0], out[:, 1]
+
+
 def kat_fluxdef(U, gamma, ch, direction, device=0):
     U = np.ascontiguousarray(U, dtype=np.float64)
     F = np.empty_like(U)

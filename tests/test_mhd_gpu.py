@@ -121,6 +121,59 @@ def test_kat_hllc_all_four_regions(d):
     assert np.array_equal(bits(F), bits(Fo))
 
 
+def test_cfl_upper_bound():
+    """The y sweep skips the exact signal speed for warps whose fp32 upper bound of speed/run_max is < 1
+    (mhd_physics.cuh: cfl_speed_over_max_f32).  The bound times run_max must be >= the exact speed (up to 1e-12
+    of run_max, the fp32 underflow floor) wherever it is finite; everything else is evaluated exactly anyway.  Regimes: solver range, low beta
+    (pressure = tiny remainder of E), field aligned with one axis (inner radicand cancels), a == b, states at
+    rest, huge/tiny scales around the fp32 range."""
+    rng = np.random.default_rng(2024)
+    n = 400000
+    g = 5.0 / 3.0
+    rho = 10.0 ** rng.uniform(-3, 3, n)
+    v = rng.uniform(-3, 3, (n, 3)) * 10.0 ** rng.uniform(-6, 1, (n, 1))
+    B = rng.uniform(-3, 3, (n, 3)) * 10.0 ** rng.uniform(-6, 1, (n, 1))
+    p = 10.0 ** rng.uniform(-9, 3, n)
+    q = n // 8
+    B[:q, 1:] = 0.0                                   # field along x
+    B[q:2 * q, 0] = 0.0; B[q:2 * q, 2] = 0.0          # field along y
+    B[2 * q:3 * q] = 0.0                              # hydro
+    v[3 * q:4 * q] = 0.0                              # at rest
+    # a^2 == b^2 with the field along one axis: s^2 - 4 a^2 b_d^2 cancels completely
+    B[4 * q:5 * q, 1:] = 0.0
+    B[4 * q:5 * q, 0] = np.sqrt(g * p[4 * q:5 * q])
+    scale = np.ones(n)
+    scale[5 * q:6 * q] = 10.0 ** rng.uniform(-30, 30, q)   # whole state scaled: exercises fp32 under/overflow
+    U = np.empty((n, 9))
+    U[:, 0] = rho * scale
+    U[:, 1:4] = rho[:, None] * v * scale[:, None]
+    U[:, 5:8] = B * np.sqrt(scale)[:, None]
+    U[:, 4] = (p / (g - 1) + 0.5 * rho * (v * v).sum(1)) * scale + 0.5 * (U[:, 5:8] ** 2).sum(1)
+    U[:, 8] = rng.uniform(-1, 1, n)
+    med = float(np.median(np.sqrt(g * p / rho)))
+    for run_max in (med, 1e-3 * med, 1e3 * med, 1e-20, 1e20, 0.0):
+        exact, bound = lsc.kat_cfl_bound(U, g, run_max)
+        trusted = np.isfinite(bound)
+        # fp32 underflow may lose contributions below 1e-13 of run_max (irrelevant next to the threshold 1)
+        ok = ~np.isfinite(exact) | ~trusted | (bound * run_max >= exact - 1e-12 * run_max)
+        assert ok.all(), (f"run_max={run_max}: {(~ok).sum()} states with bound < exact, worst ratio "
+                          f"{np.min(bound[~ok] * run_max / exact[~ok])}")
+        # the decision the kernel takes: never skip a state that could raise the maximum
+        assert not np.any((bound < 1.0) & (exact >= run_max))
+        if run_max == 0.0:
+            assert not trusted.any()
+    # and it is a useful bound where it matters: within 1% of the exact speed for ordinary states
+    exact, bound = lsc.kat_cfl_bound(U, g, med)
+    ordinary = np.isfinite(bound) & np.isfinite(exact) & (scale == 1.0) & (p > 1e-3 * U[:, 4])
+    assert ordinary.sum() > n // 4
+    assert np.median(bound[ordinary] * med / exact[ordinary]) < 1.01
+    # a NaN exact speed (negative pressure) never matters: it is ignored by the reduction either way
+    U2 = U[:1000].copy()
+    U2[:, 4] = 0.0
+    e2, b2 = lsc.kat_cfl_bound(U2, g, med)
+    assert np.all(np.isnan(e2) | (b2 * med >= e2) | ~np.isfinite(b2))
+
+
 @pytest.mark.parametrize("d", [0, 1])
 def test_kat_fluxdef(d):
     import ctypes
