@@ -117,6 +117,23 @@ __device__ __noinline__ void x_halfstates_global(D& dv, const GridDims g, const 
     predictor<0>(dv, hL, hR, p.gm1, p.ch2, p.hdtdh);
 }
 
+__device__ __forceinline__ void prefetch_cell_l1(const double* __restrict__ base, size_t plane, size_t idx) {
+#pragma unroll
+    for (int k = 0; k < NV; ++k) asm volatile("prefetch.global.L1 [%0];" ::"l"(base + (size_t)k * plane + idx));
+}
+
+// The non-trivial primitives (vx, vy, vz, p) of a cell are carried from one column to the next; the five that
+// are copies of conserved components (rho, B, psi) are taken from the reloaded conserved state.
+__device__ __forceinline__ void prim_vector(const double (&u)[NV], const double (&nt)[4], double (&v)[NV]) {
+    v[0] = u[0]; v[1] = nt[0]; v[2] = nt[1]; v[3] = nt[2]; v[4] = nt[3];
+    v[5] = u[5]; v[6] = u[6]; v[7] = u[7]; v[8] = u[8];
+}
+
+// One strip of one row.  Carried in registers from column to column: the right face state of the previous
+// cell, the previous interface flux and the 4 non-trivial primitives of the previous cell (22 doubles).  The
+// conserved 3-cell stencil is NOT carried: a column loaded for cell c is needed again for cells c+1, c+2 and for
+// the update of cell c -- it is re-read through L1 (lines were prefetched one column ahead and are private to
+// this warp's rows), which costs one issue slot per value where a register spill would cost two.
 template <class D>
 __device__ __forceinline__ bool x_sweep_block(const GridDims& g, const SweepParams& p,
                                               const double* __restrict__ cur, const double* __restrict__ prev,
@@ -130,7 +147,9 @@ __device__ __forceinline__ bool x_sweep_block(const GridDims& g, const SweepPara
     const bool hi_image = (ib == g.nxl + 2) && (p.bc_hi == BC_TRANSMISSIVE);
     D dv;
 
-    double hRprev[NV], Fprev[NV];
+    prefetch_cell_l1(cur, g.plane, cell_index(g, ia + 1, j));
+    if (!p.first_step) prefetch_cell_l1(prev, g.plane, cell_index(g, ia + 1, j));
+    double hRprev[NV], Fprev[NV], PMnt[4];
     {
         // face state R of cell ia-1; at a transmissive wall ghost cell 1 carries the half state of
         // cell 3 (u[1] = u[3] applied to the half-step arrays, MUSCL_NEW.cpp:617-622, :878-879)
@@ -138,16 +157,18 @@ __device__ __forceinline__ bool x_sweep_block(const GridDims& g, const SweepPara
         x_halfstates_global(dv, g, p, cur, prev, lo_image ? 3 : ia - 1, j, tL, tR);
 #pragma unroll
         for (int k = 0; k < NV; ++k) hRprev[k] = tR[k];
+        double uM[NV];
+        load_cell(cur, g.plane, cell_index(g, ia - 1, j), uM);
+        const Prim q = c2p(dv, uM, p.gm1);
+        PMnt[0] = q.vx; PMnt[1] = q.vy; PMnt[2] = q.vz; PMnt[3] = q.p;
     }
-    double uM[NV], u0[NV], uP[NV], PM[NV], P0[NV];
-    load_cell(cur, g.plane, cell_index(g, ia - 1, j), uM);
-    load_cell(cur, g.plane, cell_index(g, ia, j), u0);
-    load_cell(cur, g.plane, cell_index(g, ia + 1, j), uP);
-    c2p_full(dv, uM, p.gm1, PM);
-    c2p_full(dv, u0, p.gm1, P0);
 
     for (int c = ia; c <= ib; ++c) {
-        double hL[NV], hR[NV];
+        if (c + 2 <= g.nxl + 3) {
+            prefetch_cell_l1(cur, g.plane, cell_index(g, c + 2, j));
+            if (!p.first_step) prefetch_cell_l1(prev, g.plane, cell_index(g, c + 2, j));
+        }
+        double hL[NV], hR[NV], P0nt[4];
         if (c == ib && hi_image) {
             double tL[NV], tR[NV];
             x_halfstates_global(dv, g, p, cur, prev, g.nxl, j, tL, tR);  // u[nx+2] = u[nx]
@@ -156,8 +177,13 @@ __device__ __forceinline__ bool x_sweep_block(const GridDims& g, const SweepPara
                 hL[k] = tL[k];
                 hR[k] = tR[k];
             }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) P0nt[k] = 0.0;  // last column of the strip: not carried further
         } else {
-            double Pp[NV];
+            double uM[NV], u0[NV], uP[NV], PM[NV], P0[NV], Pp[NV];
+            load_cell(cur, g.plane, cell_index(g, c - 1, j), uM);
+            load_cell(cur, g.plane, cell_index(g, c, j), u0);
+            load_cell(cur, g.plane, cell_index(g, c + 1, j), uP);
             if (p.first_step) {
 #pragma unroll
                 for (int k = 0; k < NV; ++k) Pp[k] = 0.0;
@@ -166,6 +192,12 @@ __device__ __forceinline__ bool x_sweep_block(const GridDims& g, const SweepPara
                 load_cell(prev, g.plane, cell_index(g, c + 1, j), q);
                 c2p_full(dv, q, p.gm1, Pp);
             }
+            {
+                const Prim q0 = c2p(dv, u0, p.gm1);
+                P0nt[0] = q0.vx; P0nt[1] = q0.vy; P0nt[2] = q0.vz; P0nt[3] = q0.p;
+            }
+            prim_vector(uM, PMnt, PM);
+            prim_vector(u0, P0nt, P0);
 #pragma unroll
             for (int k = 0; k < NV; ++k)
                 reconstruct1(dv, PM[k], P0[k], Pp[k], uM[k], u0[k], uP[k], hL[k], hR[k]);
@@ -179,7 +211,7 @@ __device__ __forceinline__ bool x_sweep_block(const GridDims& g, const SweepPara
             const size_t o = cell_index(g, c - 1, j);
 #pragma unroll
             for (int k = 0; k < NV; ++k) {
-                double v = uM[k] - p.dtdh * (F[k] - Fprev[k]);
+                double v = __ldg(cur + (size_t)k * g.plane + o) - p.dtdh * (F[k] - Fprev[k]);
                 if (k == 8) v = v * p.psi_factor;
                 ubar[(size_t)k * g.plane + o] = v;
             }
@@ -188,14 +220,9 @@ __device__ __forceinline__ bool x_sweep_block(const GridDims& g, const SweepPara
         for (int k = 0; k < NV; ++k) {
             Fprev[k] = F[k];
             hRprev[k] = hR[k];
-            uM[k] = u0[k];
-            u0[k] = uP[k];
-            PM[k] = P0[k];
         }
-        if (c < ib) {
-            c2p_full(dv, u0, p.gm1, P0);
-            load_cell(cur, g.plane, cell_index(g, c + 2, j), uP);
-        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) PMnt[k] = P0nt[k];
     }
     return dv.bad();
 }
