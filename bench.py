@@ -302,6 +302,14 @@ def main_gpu(args):
     per_x, per_y = ms_x / max(nxk, 1), ms_y / max(nyk, 1)
     dom_name, dom_ms = ("x_sweep_kernel", per_x) if per_x >= per_y else ("y_sweep_kernel", per_y)
     achieved = cells_local * B_ALG_X / (dom_ms * 1e-3) / 1e9
+    traffic, traffic_src = None, None
+    try:  # dram bytes per cell of that kernel from the committed ncu --set full capture, scaled to this launch
+        with open(os.path.join(ROOT, "profiles", "r1_v2_traffic.json")) as f:
+            tj = json.load(f)
+        traffic = tj[dom_name]["bytes_per_cell"] * cells_local
+        traffic_src = tj["source"]
+    except Exception:
+        pass
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -321,12 +329,13 @@ def main_gpu(args):
                 "seconds": e2e_s, "result_finite": finite},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": dom_name, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                      "algorithmic_bytes_per_cell": B_ALG_X, "cells_per_launch": cells_local,
                      "launch_ms": dom_ms, "x_sweep_ms": per_x, "y_sweep_ms": per_y,
                      "whole_step_frac_of_measured": value * B_ALG / world / (peak * 1e9),
                      "whole_step_frac_of_nominal_8TBs": value * B_ALG / world / (NOMINAL_HBM_GBS * 1e9),
-                     "note": "fp64-pipe bound (no FMA, IEEE div/sqrt), see DESIGN.md and profiles/"},
+                     "note": "bound by the fp64 pipe / issue port, not HBM (no FMA contraction, IEEE div/sqrt): ncu "
+                             "sm__inst_executed_pipe_fp64 61 % (x) / 52 % (y) of peak, profiles/r1_v2_summary.md"},
         "sim": {"t": t_sim, "dt": dt_sim, "ch": ch_sim, "steps_taken": nstep},
     }
     if world == 1 and not args.no_cpu_baseline:

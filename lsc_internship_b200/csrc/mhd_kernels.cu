@@ -71,7 +71,7 @@ __device__ __forceinline__ void block_max_to_global(double local, unsigned long 
 #define XS_MINB 4
 #endif
 #ifndef XS_STRIP
-#define XS_STRIP 64
+#define XS_STRIP 128
 #endif
 #ifndef YS_MINB
 #define YS_MINB 4
