@@ -60,7 +60,7 @@ EXPORTS = [
     "lsc_mhd_create", "lsc_mhd_destroy", "lsc_mhd_local_nx", "lsc_mhd_local_i0",
     "lsc_mhd_initial_condition", "lsc_mhd_upload", "lsc_mhd_init_problem", "lsc_mhd_step",
     "lsc_mhd_run_until", "lsc_mhd_get_scalars", "lsc_mhd_download", "lsc_mhd_write_dat",
-    "lsc_comm_unique_id", "lsc_mhd_comm_init", "lsc_mhd_kat_hllc", "lsc_mhd_kat_fluxdef", "lsc_mhd_kat_cfl_bound",
+    "lsc_comm_unique_id", "lsc_mhd_comm_init", "lsc_mhd_kat_hllc", "lsc_mhd_kat_fluxdef", "lsc_mhd_kat_cfl_bound", "lsc_mhd_set_arithmetic",
     "lsc_kernel_launch_count", "lsc_mhd_step_timed", "lsc_mhd_set_profiling", "lsc_mhd_kernel_times", "lsc_kat_division", "lsc_mhd_ieee_fallback_count", "lsc_mhd_group_step", "lsc_mhd_fill_ghost_ring",
     "lsc_euler_create", "lsc_euler_destroy", "lsc_euler_initial_condition", "lsc_euler_upload",
     "lsc_euler_init_problem", "lsc_euler_step", "lsc_euler_step_timed", "lsc_euler_run_until",
@@ -107,6 +107,7 @@ def lib():
                                    ctypes.c_double, dp]
     L.lsc_mhd_kat_fluxdef.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_long, dp, ctypes.c_double,
                                       ctypes.c_double, dp]
+    L.lsc_mhd_set_arithmetic.argtypes = [vp, ctypes.c_int]
     L.lsc_mhd_kat_cfl_bound.argtypes = [ctypes.c_int, ctypes.c_long, dp, ctypes.c_double, ctypes.c_double, dp]
     L.lsc_kat_division.argtypes = [ctypes.c_int, ctypes.c_ulonglong, ctypes.c_int, ctypes.c_long, ctypes.c_int,
                                    ctypes.POINTER(ctypes.c_ulonglong), ctypes.POINTER(ctypes.c_ulonglong)]

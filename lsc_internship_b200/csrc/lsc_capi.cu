@@ -88,6 +88,7 @@ struct lsc_mhd_ctx {
     bool in_group = false;            // driven by lsc_mhd_group_step (single-process slab group)
     cudaEvent_t halo_event = nullptr;  // "u^{n+1} complete" marker for neighbours in a group
     bool profiling = false;
+    bool relaxed = false;  // LSC_ARITH_RELAXED: FMA-contracted sweeps with 1-multiply quotients (not the parity path)
     std::vector<cudaEvent_t> prof_events;  // quadruples: x begin, x end, y begin, y end
 };
 
@@ -282,6 +283,13 @@ int lsc_mhd_init_problem(lsc_mhd_ctx* c, int problem) {
     return finish_upload(c);
 }
 
+int lsc_mhd_set_arithmetic(lsc_mhd_ctx* c, int mode) {
+    if (!c) return fail(LSC_EINVAL, "null argument");
+    if (mode != LSC_ARITH_REFERENCE && mode != LSC_ARITH_RELAXED) return fail(LSC_EINVAL, "unknown arithmetic mode %d", mode);
+    c->relaxed = (mode == LSC_ARITH_RELAXED);
+    return LSC_OK;
+}
+
 int lsc_mhd_get_scalars(const lsc_mhd_ctx* c, double* t, double* dt, double* ch, long* step) {
     if (!c) return fail(LSC_EINVAL, "null argument");
     if (t) *t = c->t;
@@ -371,8 +379,12 @@ int launch_sweeps(lsc_mhd_ctx* c) {
         CUDA_TRY(cudaEventRecord(ev[0], c->stream));
     }
     CUDA_TRY(cudaMemsetAsync(c->d_max, 0, STATUS_BYTES, c->stream));
-    lsc::launch_x_sweep(c->g, p, c->state[c->cur], c->state[c->prev], c->state[c->bar], c->d_max, c->d_xflags,
-                        c->stream);
+    if (c->relaxed)
+        lsc::launch_x_sweep_relaxed(c->g, p, c->state[c->cur], c->state[c->prev], c->state[c->bar], c->d_xflags,
+                                    c->stream);
+    else
+        lsc::launch_x_sweep(c->g, p, c->state[c->cur], c->state[c->prev], c->state[c->bar], c->d_max, c->d_xflags,
+                            c->stream);
     if (c->profiling) CUDA_TRY(cudaEventRecord(ev[1], c->stream));
 
     // ---- y sweep (:905-965) + copy (:969) + next step's signal speed (:71-115)
@@ -380,8 +392,12 @@ int launch_sweeps(lsc_mhd_ctx* c) {
     p.hdtdh = 0.5 * (dt / c->dy);
     p.bc_lo = p.bc_hi = to_kernel_bc(c->cfg.bc_y);
     if (c->profiling) CUDA_TRY(cudaEventRecord(ev[2], c->stream));
-    lsc::launch_y_sweep(c->g, p, c->state[c->bar], c->state[c->cur], c->state[c->prev], c->d_max, c->d_fix,
-                        c->stream);
+    if (c->relaxed)
+        lsc::launch_y_sweep_relaxed(c->g, p, c->state[c->bar], c->state[c->cur], c->state[c->prev], c->d_max,
+                                    c->d_fix, c->stream);
+    else
+        lsc::launch_y_sweep(c->g, p, c->state[c->bar], c->state[c->cur], c->state[c->prev], c->d_max, c->d_fix,
+                            c->stream);
     if (c->profiling) {
         CUDA_TRY(cudaEventRecord(ev[3], c->stream));
         for (auto e : ev) c->prof_events.push_back(e);

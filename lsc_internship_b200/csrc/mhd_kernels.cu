@@ -239,6 +239,7 @@ __global__ void __launch_bounds__(XS_BLOCK, XS_MINB) x_sweep_kernel(const GridDi
         block_flags[blockIdx.y * gridDim.x + blockIdx.x] = 1u;
 }
 
+#ifndef LSC_RELAXED_TU
 // Recompute the blocks a fast sweep flagged, with IEEE division (persistent grid over the device-side list).
 __global__ void __launch_bounds__(XS_BLOCK) x_sweep_fix_kernel(const GridDims g, const SweepParams p,
                                                                const double* __restrict__ cur,
@@ -278,6 +279,17 @@ long x_sweep_block_count(const GridDims& g) {
     const int row_blocks = (g.ny + XS_BLOCK - 1) / XS_BLOCK;
     return (long)row_blocks * ((g.nxl + 7) / 8);  // strip is never shorter than 8
 }
+#else  // LSC_RELAXED_TU
+void launch_x_sweep_relaxed(const GridDims& g, const SweepParams& p, const double* u_cur, const double* u_prev,
+                            double* u_bar, unsigned* x_flags, cudaStream_t s) {
+    dim3 block(XS_BLOCK);
+    const int row_blocks = (g.ny + block.x - 1) / block.x;
+    int strip = XS_STRIP;
+    while (strip > 8 && (long)row_blocks * ((g.nxl + strip - 1) / strip) < 148L * 4 * 3) strip /= 2;
+    dim3 grid(row_blocks, (g.nxl + strip - 1) / strip);
+    x_sweep_kernel<RelaxedDiv><<<grid, block, 0, s>>>(g, p, u_cur, u_prev, u_bar, x_flags, strip);
+}
+#endif
 
 // ------------------------------------------------------------------------------------
 // y sweep: one thread per cell along the contiguous axis.  A block of BJ threads covers cells
@@ -465,6 +477,7 @@ __global__ void __launch_bounds__(BJ, YS_MINB) y_sweep_kernel(const GridDims g, 
     }
 }
 
+#ifndef LSC_RELAXED_TU
 __global__ void __launch_bounds__(BJ) y_sweep_fix_kernel(const GridDims g, const SweepParams p,
                                                          const double* __restrict__ ubar,
                                                          const double* __restrict__ cur, double* __restrict__ next,
@@ -490,6 +503,15 @@ void launch_y_sweep(const GridDims& g, const SweepParams& p, const double* u_bar
 }
 
 long y_sweep_block_count(const GridDims& g) { return (long)((g.ny + (BJ - 2) - 1) / (BJ - 2)) * g.nxl; }
+#else  // LSC_RELAXED_TU
+void launch_y_sweep_relaxed(const GridDims& g, const SweepParams& p, const double* u_bar, const double* u_cur,
+                            double* u_next, unsigned long long* status, unsigned* fix_list, cudaStream_t s) {
+    dim3 block(BJ);
+    dim3 grid((g.ny + (BJ - 2) - 1) / (BJ - 2), g.nxl);
+    y_sweep_kernel<RelaxedDiv><<<grid, block, 0, s>>>(g, p, u_bar, u_cur, u_next, status, fix_list);
+}
+#endif
+#ifndef LSC_RELAXED_TU
 
 // ------------------------------------------------------------------------------------
 // Ghost columns in x (single-rank case; between ranks the same columns are filled by the
@@ -611,4 +633,5 @@ void launch_soa_to_aos(const GridDims& g, const double* soa, int i0, int ni, dou
     soa_to_aos_kernel<<<grid, 96, 0, s>>>(g, soa, i0, ni, aos);
 }
 
+#endif  // !LSC_RELAXED_TU
 }  // namespace lsc

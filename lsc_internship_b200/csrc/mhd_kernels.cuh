@@ -51,6 +51,11 @@ void launch_x_sweep(const GridDims& g, const SweepParams& p, const double* u_cur
                     double* u_bar, unsigned long long* status, unsigned* x_flags, cudaStream_t s);
 void launch_y_sweep(const GridDims& g, const SweepParams& p, const double* u_bar, const double* u_cur,
                     double* u_next, unsigned long long* status, unsigned* fix_list, cudaStream_t s);
+// relaxed-arithmetic instantiations (mhd_kernels_relaxed.cu: FMA contraction, 1-multiply quotients; no fix pass)
+void launch_x_sweep_relaxed(const GridDims& g, const SweepParams& p, const double* u_cur, const double* u_prev,
+                            double* u_bar, unsigned* x_flags, cudaStream_t s);
+void launch_y_sweep_relaxed(const GridDims& g, const SweepParams& p, const double* u_bar, const double* u_cur,
+                            double* u_next, unsigned long long* status, unsigned* fix_list, cudaStream_t s);
 long x_sweep_block_count(const GridDims& g);
 long y_sweep_block_count(const GridDims& g);
 void launch_x_ghosts(const GridDims& g, int bc_x, double* u, cudaStream_t s);

@@ -31,7 +31,8 @@ class MusclNew:
     NVAR = 9
 
     def __init__(self, nxCells=128, nyCells=256, x0=0.0, x1=1.0, y0=-1.0, y1=1.0, tStop=12.0, C=0.8,
-                 gamma=5.0 / 3.0, bc_x="periodic", bc_y="reflective", problem="kh", device=0, rank=0, nranks=1):
+                 gamma=5.0 / 3.0, bc_x="periodic", bc_y="reflective", problem="kh", device=0, rank=0, nranks=1,
+                 arithmetic="reference"):
         self.tStop = float(tStop)
         self.problem = _capi.MHD_PROBLEMS[problem] if isinstance(problem, str) else int(problem)
         self.cfg = MhdConfig(int(nxCells), int(nyCells), float(x0), float(x1), float(y0), float(y1),
@@ -41,6 +42,10 @@ class MusclNew:
         check(lib().lsc_mhd_create(ctypes.byref(self.cfg), ctypes.byref(self._h)))
         self.nxl = lib().lsc_mhd_local_nx(self._h)
         self.i0 = lib().lsc_mhd_local_i0(self._h)
+        # "reference": bit-for-bit the reference's IEEE arithmetic (default, the parity path);
+        # "relaxed": FMA-contracted sweeps with 1-multiply quotients (include/lsc_b200.h: LSC_ARITH_RELAXED)
+        self.arithmetic = arithmetic
+        check(lib().lsc_mhd_set_arithmetic(self._h, {"reference": 0, "relaxed": 1}[arithmetic]))
 
     # -- lifetime ---------------------------------------------------------
     def close(self):

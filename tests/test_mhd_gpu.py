@@ -386,3 +386,43 @@ def test_step_before_upload_fails():
         s.step(1)
     assert e.value.code == -4
     s.close()
+
+
+def test_relaxed_arithmetic_deviation():
+    """the FMA-contracted / 1-multiply-quotient instantiation is NOT a parity path.  This test
+    only pins how far it drifts from the reference on config 1 (OT 256^2, 10 steps) so the number quoted in
+    DESIGN.md stays honest: relative L-inf per conserved variable (max|a-b| / max|b|), and that the
+    default arithmetic is untouched by the mode switch."""
+    nx = ny = 256
+    cfg = mhd_cfg(nx, ny)
+    u0 = mhd_ic(cfg, "ot")
+    o = OracleMhd(cfg, u0)
+    o.step(10)
+    ur = o.state()[0]
+    out = {}
+    for mode in ("relaxed", "reference"):
+        s = lsc.MusclNew(nx, ny, 0.0, 1.0, 0.0, 1.0, bc_x="periodic", bc_y="periodic", problem="ot", arithmetic=mode)
+        s.upload(u0)
+        s.step(10)
+        out[mode] = s.download()
+        s.close()
+    assert np.array_equal(bits(out["reference"][2:-2, 2:-2]), bits(ur[2:-2, 2:-2]))
+    a, b = out["relaxed"][2:-2, 2:-2], ur[2:-2, 2:-2]
+    rel, l1 = [], []
+    for k in range(9):
+        scale = np.max(np.abs(b[..., k]))
+        rel.append(float(np.max(np.abs(a[..., k] - b[..., k])) / scale) if scale > 0 else 0.0)
+        m = np.mean(np.abs(b[..., k]))
+        l1.append(float(np.mean(np.abs(a[..., k] - b[..., k])) / m) if m > 0 else 0.0)
+    print("relaxed arithmetic, OT 256^2, 10 steps, rel L-inf per variable:", " ".join(f"{r:.2e}" for r in rel))
+    print("relaxed arithmetic, OT 256^2, 10 steps, rel L1    per variable:", " ".join(f"{r:.2e}" for r in l1))
+    assert np.isfinite(a).all()
+    assert not np.array_equal(bits(a), bits(b))          # it really is a different arithmetic
+    # The reference scheme amplifies rounding differences by ~1e4 per step until they saturate at the amplitude
+    # of its grid-scale limiter chatter (SURVEY section 0 fact 4).  The reference ITSELF shows the same drift when
+    # only its compiler flags change: oracle/mhd_oracle.c built with -mfma -ffp-contract=fast vs the default
+    # build gives, for this very case, rel L-inf 3.3e-3 / L1 3.1e-4 in density after 10 steps (1 step: 3e-10,
+    # 2 steps: 2e-6, 5 steps: 2e-3; DESIGN.md section 10).  The relaxed kernels must stay inside that envelope.
+    for k in (0, 1, 2, 4, 5, 6):                          # the variables that are not identically ~0 in OT
+        assert rel[k] < 2e-2, (k, rel[k])
+        assert l1[k] < 2e-3, (k, l1[k])
