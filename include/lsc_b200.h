@@ -208,6 +208,10 @@ typedef struct lsc_euler_config {
     double omega; /* S:539 */
     int bc;       /* LSC_BC_PERIODIC (S:198-226) | LSC_BC_TRANSMISSIVE_E (G:199-215), both axes */
     int device;
+    /* slab decomposition along x, as for MHD: rank r of nranks owns interior columns
+     * [r*nx/nranks, (r+1)*nx/nranks) plus two halo columns per side; every host array of a context with
+     * nranks > 1 is that slab, [(nxl+4)][(ny+4)][4].  nranks <= 1: the whole grid. */
+    int rank, nranks;
 } lsc_euler_config;
 
 typedef struct lsc_euler_ctx lsc_euler_ctx;
@@ -215,7 +219,16 @@ typedef void (*lsc_euler_log_cb)(long step, double t, double dt, void* user); /*
 
 int lsc_euler_create(const lsc_euler_config* cfg, lsc_euler_ctx** out);
 int lsc_euler_destroy(lsc_euler_ctx* ctx);
-/* IC loop S:552-594 / G:586-620 followed by the boundary fill S:596, into [(nx+4)][(ny+4)][4]. Host libm. */
+int lsc_euler_local_nx(const lsc_euler_ctx* ctx);
+int lsc_euler_local_i0(const lsc_euler_ctx* ctx);
+/* one process per GPU: join the NCCL communicator (id from lsc_comm_unique_id on rank 0).  Per step the ranks
+ * exchange two halo columns of the new u with each x neighbour and all-reduce (max) the signal speed. */
+int lsc_euler_comm_init(lsc_euler_ctx* ctx, const void* id128);
+/* single process: advance the n slabs of one grid (contexts with rank 0..n-1 of n, on any devices of this
+ * process) in lock step, halos by peer copies, max on the host -- same kernels and slab-edge path as NCCL. */
+int lsc_euler_group_step(lsc_euler_ctx** slabs, int n, long nsteps);
+/* IC loop S:552-594 / G:586-620 followed by the boundary fill S:596, into [(nx+4)][(ny+4)][4] (the slab
+ * [(nxl+4)][(ny+4)][4] of cfg->rank when cfg->nranks > 1). Host libm. */
 int lsc_euler_initial_condition(const lsc_euler_config* cfg, int problem, double* aos);
 int lsc_euler_upload(lsc_euler_ctx* ctx, const double* aos);
 int lsc_euler_init_problem(lsc_euler_ctx* ctx, int problem);

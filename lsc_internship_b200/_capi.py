@@ -44,7 +44,8 @@ class EulerConfig(ctypes.Structure):
                 ("x0", ctypes.c_double), ("x1", ctypes.c_double),
                 ("y0", ctypes.c_double), ("y1", ctypes.c_double),
                 ("gamma", ctypes.c_double), ("cfl", ctypes.c_double), ("omega", ctypes.c_double),
-                ("bc", ctypes.c_int), ("device", ctypes.c_int)]
+                ("bc", ctypes.c_int), ("device", ctypes.c_int),
+                ("rank", ctypes.c_int), ("nranks", ctypes.c_int)]
 
 
 EULER_PROBLEMS = {"ot": 0, "orszag-tang": 0, "quadrants": 1, "cylinder": 2}
@@ -65,7 +66,8 @@ EXPORTS = [
     "lsc_euler_create", "lsc_euler_destroy", "lsc_euler_initial_condition", "lsc_euler_upload",
     "lsc_euler_init_problem", "lsc_euler_step", "lsc_euler_step_timed", "lsc_euler_run_until",
     "lsc_euler_get_scalars", "lsc_euler_download", "lsc_euler_write_dat", "lsc_euler_ieee_fallback_count",
-    "lsc_euler_set_profiling", "lsc_euler_kernel_times",
+    "lsc_euler_set_profiling", "lsc_euler_kernel_times", "lsc_euler_local_nx", "lsc_euler_local_i0",
+    "lsc_euler_comm_init", "lsc_euler_group_step",
 ]
 
 _lib = None
@@ -115,6 +117,10 @@ def lib():
     ecfg = ctypes.POINTER(EulerConfig)
     L.lsc_euler_create.argtypes = [ecfg, ctypes.POINTER(vp)]
     L.lsc_euler_destroy.argtypes = [vp]
+    L.lsc_euler_local_nx.argtypes = [vp]
+    L.lsc_euler_local_i0.argtypes = [vp]
+    L.lsc_euler_comm_init.argtypes = [vp, vp]
+    L.lsc_euler_group_step.argtypes = [ctypes.POINTER(vp), ctypes.c_int, ctypes.c_long]
     L.lsc_euler_initial_condition.argtypes = [ecfg, ctypes.c_int, dp]
     L.lsc_euler_upload.argtypes = [vp, dp]
     L.lsc_euler_init_problem.argtypes = [vp, ctypes.c_int]

@@ -16,16 +16,32 @@ inline const double* at(const double* a, int ny, int i, int j) {
 }
 }  // namespace
 
-// One application of the reference's boundary function (full loop ranges, x loop then y loop).
+// Slab of rank r of P along x: interior columns [b0, b1) of the global grid.
+void euler_slab_range(const lsc_euler_config& c, int& b0, int& b1) {
+    const int P = c.nranks > 1 ? c.nranks : 1, r = c.nranks > 1 ? c.rank : 0;
+    b0 = (int)((long long)c.nx * r / P);
+    b1 = (int)((long long)c.nx * (r + 1) / P);
+}
+
+// One application of the reference's boundary function (full loop ranges, x loop then y loop) to a slab of
+// nxl interior columns: the x images only where the slab ends at the physical boundary -- elsewhere the two
+// columns on that side are a neighbour's interior cells and stay as they are.
 void euler_fill_ghost_ring(const lsc_euler_config& c, double* a) {
-    const int nx = c.nx, ny = c.ny;
+    int b0, b1;
+    euler_slab_range(c, b0, b1);
+    const int nx = b1 - b0, ny = c.ny;
+    const bool whole = (nx == c.nx);
     const size_t cell = 4 * sizeof(double);
     const bool per = (c.bc == LSC_BC_PERIODIC);
     for (int j = 0; j < ny + 4; ++j) {
-        std::memcpy(at(a, ny, 0, j), at(a, ny, per ? nx : 2, j), cell);
-        std::memcpy(at(a, ny, 1, j), at(a, ny, per ? nx + 1 : 2, j), cell);
-        std::memcpy(at(a, ny, nx + 2, j), at(a, ny, per ? 2 : nx + 1, j), cell);
-        std::memcpy(at(a, ny, nx + 3, j), at(a, ny, per ? 3 : nx + 1, j), cell);
+        if (whole || (!per && b0 == 0)) {
+            std::memcpy(at(a, ny, 0, j), at(a, ny, per ? nx : 2, j), cell);
+            std::memcpy(at(a, ny, 1, j), at(a, ny, per ? nx + 1 : 2, j), cell);
+        }
+        if (whole || (!per && b1 == c.nx)) {
+            std::memcpy(at(a, ny, nx + 2, j), at(a, ny, per ? 2 : nx + 1, j), cell);
+            std::memcpy(at(a, ny, nx + 3, j), at(a, ny, per ? 3 : nx + 1, j), cell);
+        }
     }
     for (int i = 0; i < nx + 4; ++i) {
         std::memcpy(at(a, ny, i, 0), at(a, ny, i, per ? ny : 2), cell);
@@ -35,13 +51,26 @@ void euler_fill_ghost_ring(const lsc_euler_config& c, double* a) {
     }
 }
 
-// IC loop + the boundary fill that follows it (S:552-596).  Cell centres x0 + (i-1.5)dx (S:556-557).
+// IC loop + the boundary fill that follows it (S:552-596).  Cell centres x0 + (i-1.5)dx (S:556-557), i the
+// GLOBAL column index.  For a slab the array holds columns b0 .. b1+3 of the global padded grid; its halo
+// columns are the neighbour's interior cells, i.e. the same formula at their own coordinates, except at a
+// periodic wrap where they are what the reference's boundary fill would have copied there (the formula at the
+// coordinates of the source column).
 void euler_initial_condition(const lsc_euler_config& c, int problem, double* aos) {
     const double pi = 3.14159265358979323846;  // S:540
     const double gamma = c.gamma;
     const double dx = (c.x1 - c.x0) / c.nx;
     const double dy = (c.y1 - c.y0) / c.ny;
-    for (int i = 0; i < c.nx + 4; ++i)
+    int b0, b1;
+    euler_slab_range(c, b0, b1);
+    const int nxl = b1 - b0;
+    const bool slab = (nxl != c.nx);
+    for (int il = 0; il < nxl + 4; ++il) {
+        int i = b0 + il;  // global padded column
+        if (slab && c.bc == LSC_BC_PERIODIC) {
+            if (i < 2) i += c.nx;
+            else if (i > c.nx + 1) i -= c.nx;
+        }
         for (int j = 0; j < c.ny + 4; ++j) {
             const double x = c.x0 + (i - 1.5) * dx;
             const double y = c.y0 + (j - 1.5) * dy;
@@ -68,12 +97,13 @@ void euler_initial_condition(const lsc_euler_config& c, int problem, double* aos
                     prim[0] = 0.125; prim[1] = 0; prim[2] = 0; prim[3] = 0.1;
                 }
             }
-            double* u = at(aos, c.ny, i, j);  // PrimativeToConservative, S:10-17
+            double* u = at(aos, c.ny, il, j);  // PrimativeToConservative, S:10-17
             u[0] = prim[0];
             u[1] = prim[0] * prim[1];
             u[2] = prim[0] * prim[2];
             u[3] = prim[3] / (gamma - 1) + (0.5 * prim[0] * (prim[1] * prim[1] + prim[2] * prim[2]));
         }
+    }
     euler_fill_ghost_ring(c, aos);  // S:596
 }
 

@@ -3,6 +3,7 @@
 #include "../../include/lsc_b200.h"
 
 namespace lsc {
+void euler_slab_range(const lsc_euler_config& c, int& b0, int& b1);
 void euler_initial_condition(const lsc_euler_config& c, int problem, double* aos);
 void euler_fill_ghost_ring(const lsc_euler_config& c, double* a);
 int euler_write_dat(const lsc_euler_config& c, const double* a, const char* path, int blank_line_per_row);

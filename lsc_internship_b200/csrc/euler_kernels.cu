@@ -346,6 +346,28 @@ void launch_euler_x_ghosts(const GridDims& g, int bc_x, double* u, cudaStream_t 
     euler_x_ghost_kernel<<<grid, block, 0, s>>>(g, bc_x, u);
 }
 
+// transmissive image of ONE side (0 = low, 1 = high), G:203-208: end ranks of a slab decomposition
+__global__ void euler_x_ghost_side_kernel(const GridDims g, int hi_side, double* __restrict__ u) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= g.ny + 4) return;
+    double* pl = u + (size_t)blockIdx.y * g.plane;
+    const int nx = g.nxl;
+    if (hi_side) {
+        const double v = pl[cell_index(g, nx + 1, j)];
+        pl[cell_index(g, nx + 2, j)] = v;
+        pl[cell_index(g, nx + 3, j)] = v;
+    } else {
+        const double v = pl[cell_index(g, 2, j)];
+        pl[cell_index(g, 0, j)] = v;
+        pl[cell_index(g, 1, j)] = v;
+    }
+}
+
+void launch_euler_x_ghosts_side(const GridDims& g, int hi_side, double* u, cudaStream_t s) {
+    dim3 block(256), grid((g.ny + 4 + 255) / 256, NE);
+    euler_x_ghost_side_kernel<<<grid, block, 0, s>>>(g, hi_side, u);
+}
+
 // reference array-of-structures [i][j][4] <-> device planes for `ni` columns starting at i0
 __global__ void euler_aos_to_soa_kernel(const GridDims g, const double* __restrict__ aos, int i0,
                                         double* __restrict__ soa) {

@@ -25,6 +25,7 @@ long euler_fix_list_entries(const GridDims& g);
 void launch_euler_max_speed(const GridDims& g, double gamma, const double* u, int i_lo, int i_hi, int j_lo, int j_hi,
                             unsigned long long* status, cudaStream_t s);
 void launch_euler_x_ghosts(const GridDims& g, int bc_x, double* u, cudaStream_t s);
+void launch_euler_x_ghosts_side(const GridDims& g, int hi_side, double* u, cudaStream_t s);
 void launch_euler_aos_to_soa(const GridDims& g, const double* aos, int i0, int ni, double* soa, cudaStream_t s);
 void launch_euler_soa_to_aos(const GridDims& g, const double* soa, int i0, int ni, double* aos, cudaStream_t s);
 

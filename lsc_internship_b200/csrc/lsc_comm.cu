@@ -7,6 +7,8 @@
 
 #include <nccl.h>
 
+#include "euler_kernels.cuh"
+
 void lsc_count_launches(unsigned long long n);
 
 namespace lsc {
@@ -76,12 +78,12 @@ int comm_exchange_halos(Comm* c, const GridDims& g, int bc_x, double* u, cudaStr
         if (left >= 0) NCCL_TRY(ncclRecv(pl, n, ncclDouble, left, c->nccl, s), -1);
     }
     NCCL_TRY(ncclGroupEnd(), -1);
-    if (left < 0) {
-        launch_x_ghosts_side(g, 0, u, s);
-        lsc_count_launches(1);
-    }
-    if (right < 0) {
-        launch_x_ghosts_side(g, 1, u, s);
+    // end ranks of a non-periodic decomposition: the boundary image of that side (MHD: M:617-622, 4 variables:
+    // the Euler map G:203-208)
+    for (int side = 0; side < 2; ++side) {
+        if ((side == 0 ? left : right) >= 0) continue;
+        if (c->nvar == NV) launch_x_ghosts_side(g, side, u, s);
+        else launch_euler_x_ghosts_side(g, side, u, s);
         lsc_count_launches(1);
     }
     return 0;

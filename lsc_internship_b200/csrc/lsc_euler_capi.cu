@@ -8,10 +8,12 @@
 
 #include "euler_host.h"
 #include "euler_kernels.cuh"
+#include "lsc_comm.h"
 #include "lsc_common.h"
 
 struct lsc_euler_ctx {
     lsc_euler_config cfg;
+    int nxl = 0, i0 = 0;  // slab: interior columns, first global interior column (0-based)
     double dx = 0, dy = 0;
     lsc::GridDims g{};
     // u^n, ubar, u^{n+1}
@@ -32,6 +34,9 @@ struct lsc_euler_ctx {
     bool uploaded = false;
     bool profiling = false;
     std::vector<cudaEvent_t> prof_events;
+    lsc::Comm* comm = nullptr;         // NCCL mode (one process per GPU)
+    bool in_group = false;             // driven by lsc_euler_group_step
+    cudaEvent_t halo_event = nullptr;  // "new u complete" marker for neighbours in a group
 };
 
 namespace {
@@ -41,6 +46,21 @@ int kernel_bc(int bc) { return bc == LSC_BC_PERIODIC ? lsc::BC_PERIODIC : lsc::B
 int e_read_status(lsc_euler_ctx* c) {
     LSC_CUDA_TRY(cudaMemcpyAsync(c->h_status, c->d_status, 32, cudaMemcpyDeviceToHost, c->stream));
     LSC_CUDA_TRY(cudaStreamSynchronize(c->stream));
+    return LSC_OK;
+}
+
+// boundary images / neighbour data into the two ghost columns on each side of state b
+int e_fill_x_ghosts(lsc_euler_ctx* c, int b) {
+    if (c->cfg.nranks <= 1) {
+        lsc::launch_euler_x_ghosts(c->g, kernel_bc(c->cfg.bc), c->state[b], c->stream);
+        lsc_count_launches(1);
+        LSC_CUDA_TRY(cudaGetLastError());
+        return LSC_OK;
+    }
+    if (!c->comm) return lsc_fail(LSC_ESTATE, "nranks > 1 but lsc_euler_comm_init was not called");
+    const int bc = c->cfg.bc == LSC_BC_PERIODIC ? lsc::BC_PERIODIC : lsc::BC_TRANSMISSIVE;
+    if (lsc::comm_exchange_halos(c->comm, c->g, bc, c->state[b], c->stream))
+        return lsc_fail(LSC_ECOMM, "halo exchange failed: %s", lsc::comm_error());
     return LSC_OK;
 }
 
@@ -63,16 +83,21 @@ int e_launch(lsc_euler_ctx* c, const lsc::EulerParams& p, int in, int out) {
         LSC_CUDA_TRY(cudaEventRecord(ev[3], c->stream));
         for (auto e : ev) c->prof_events.push_back(e);
     }
-    // applyBoundaryConditions(u) after the average (S:616): only x ghost columns are read on the device
-    lsc::launch_euler_x_ghosts(c->g, kernel_bc(c->cfg.bc), c->state[out], c->stream);
-    lsc_count_launches(5);
+    lsc_count_launches(4);
     LSC_CUDA_TRY(cudaGetLastError());
-    return LSC_OK;
+    // applyBoundaryConditions(u) after the average (S:616): only x ghost columns are read on the device
+    return c->in_group ? LSC_OK : e_fill_x_ghosts(c, out);
 }
 
 // status of the step launched last: max signal speed of the new state, blocks the IEEE fix kernels recomputed
 int e_resolve(lsc_euler_ctx* c) {
     if (!c->pending) return LSC_OK;
+    if (c->in_group) return lsc_fail(LSC_ESTATE, "context belongs to a group: use lsc_euler_group_step");
+    if (c->cfg.nranks > 1) {
+        if (!c->comm) return lsc_fail(LSC_ESTATE, "nranks > 1 but lsc_euler_comm_init was not called");
+        if (lsc::comm_allreduce_max_u64(c->comm, c->d_status, 1, c->stream))
+            return lsc_fail(LSC_ECOMM, "allreduce failed: %s", lsc::comm_error());
+    }
     int rc = e_read_status(c);
     if (rc) return rc;
     if (c->pending_step) c->ieee_redos += (long)(c->h_status[1] + c->h_status[2]);
@@ -82,9 +107,16 @@ int e_resolve(lsc_euler_ctx* c) {
 }
 
 // body of the do-loop S:600-616
+int e_step_launch(lsc_euler_ctx* c);
 int e_step_once(lsc_euler_ctx* c) {
     int rc = e_resolve(c);
     if (rc) return rc;
+    return e_step_launch(c);
+}
+
+// everything of the loop body after ComputeTimeStep's reduction is known (c->max_speed)
+int e_step_launch(lsc_euler_ctx* c) {
+    int rc = LSC_OK;
     if (!(c->max_speed > 0.0) || !std::isfinite(c->max_speed))
         return lsc_fail(LSC_ENAN, "max signal speed is %g at step %ld", c->max_speed, c->step);
     double dspace = c->dx;  // S:166-169
@@ -103,7 +135,12 @@ int e_step_once(lsc_euler_ctx* c) {
     p.hdtdy = 0.5 * (dt / c->dy);
     p.hdxdt = 0.5 * c->dx / dt;
     p.hdydt = 0.5 * c->dy / dt;
-    p.bcx_lo = p.bcx_hi = p.bcy = kernel_bc(c->cfg.bc);
+    p.bcy = kernel_bc(c->cfg.bc);
+    // physical boundary type at each end of this slab; -1 at an inter-rank edge (ghost columns = neighbour data)
+    const bool split = c->cfg.nranks > 1;
+    const bool ring = split && c->cfg.bc == LSC_BC_PERIODIC;
+    p.bcx_lo = (ring || (split && c->cfg.rank > 0)) ? -1 : kernel_bc(c->cfg.bc);
+    p.bcx_hi = (ring || (split && c->cfg.rank < c->cfg.nranks - 1)) ? -1 : kernel_bc(c->cfg.bc);
     rc = e_launch(c, p, c->cur, c->next);
     if (rc) return rc;
     const int old = c->cur;
@@ -115,9 +152,99 @@ int e_step_once(lsc_euler_ctx* c) {
     return LSC_OK;
 }
 
+// ---- single-process slab group (same slab-edge code path as NCCL; see lsc_capi.cu) ----------------------
+int eg_halo(lsc_euler_ctx** g, int n) {
+    const bool ring = (g[0]->cfg.bc == LSC_BC_PERIODIC);
+    for (int r = 0; r < n; ++r) {
+        LSC_CUDA_TRY(cudaSetDevice(g[r]->cfg.device));
+        LSC_CUDA_TRY(cudaEventRecord(g[r]->halo_event, g[r]->stream));
+    }
+    for (int r = 0; r < n; ++r) {
+        lsc_euler_ctx* c = g[r];
+        LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
+        const int left = (r > 0) ? r - 1 : (ring ? n - 1 : -1);
+        const int right = (r < n - 1) ? r + 1 : (ring ? 0 : -1);
+        const size_t bytes = 2 * (size_t)c->g.pitch * sizeof(double);
+        for (int side = 0; side < 2; ++side) {
+            const int nb = side == 0 ? left : right;
+            if (nb < 0) {
+                lsc::launch_euler_x_ghosts_side(c->g, side, c->state[c->cur], c->stream);
+                lsc_count_launches(1);
+                continue;
+            }
+            lsc_euler_ctx* o = g[nb];
+            LSC_CUDA_TRY(cudaStreamWaitEvent(c->stream, o->halo_event, 0));
+            for (int k = 0; k < 4; ++k) {
+                double* dst = c->state[c->cur] + (size_t)k * c->g.plane +
+                              (side == 0 ? 0 : (size_t)(c->g.nxl + 2) * c->g.pitch);
+                const double* src = o->state[o->cur] + (size_t)k * o->g.plane +
+                                    (side == 0 ? (size_t)o->g.nxl * o->g.pitch : (size_t)2 * o->g.pitch);
+                LSC_CUDA_TRY(cudaMemcpyPeerAsync(dst, c->cfg.device, src, o->cfg.device, bytes, c->stream));
+            }
+        }
+    }
+    LSC_CUDA_TRY(cudaGetLastError());
+    return LSC_OK;
+}
+
+int eg_resolve(lsc_euler_ctx** g, int n) {
+    if (!g[0]->pending) return LSC_OK;
+    unsigned long long mx = 0;
+    for (int r = 0; r < n; ++r) {
+        LSC_CUDA_TRY(cudaSetDevice(g[r]->cfg.device));
+        int rc = e_read_status(g[r]);
+        if (rc) return rc;
+        if (g[r]->h_status[0] > mx) mx = g[r]->h_status[0];
+    }
+    for (int r = 0; r < n; ++r) {
+        if (g[r]->pending_step) g[r]->ieee_redos += (long)(g[r]->h_status[1] + g[r]->h_status[2]);
+        std::memcpy(&g[r]->max_speed, &mx, sizeof(double));
+        g[r]->pending = false;
+    }
+    return LSC_OK;
+}
+
 }  // namespace
 
 extern "C" {
+
+int lsc_euler_local_nx(const lsc_euler_ctx* c) { return c ? c->nxl : -1; }
+int lsc_euler_local_i0(const lsc_euler_ctx* c) { return c ? c->i0 : -1; }
+
+int lsc_euler_comm_init(lsc_euler_ctx* c, const void* id128) {
+    if (!c || !id128) return lsc_fail(LSC_EINVAL, "null argument");
+    if (c->cfg.nranks <= 1) return LSC_OK;
+    if (c->comm) return lsc_fail(LSC_ESTATE, "communicator already initialised");
+    LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
+    c->comm = lsc::comm_create(id128, c->cfg.rank, c->cfg.nranks, c->g, 4);
+    if (!c->comm) return lsc_fail(LSC_ECOMM, "%s", lsc::comm_error());
+    return LSC_OK;
+}
+
+int lsc_euler_group_step(lsc_euler_ctx** g, int n, long nsteps) {
+    if (!g || n < 1) return lsc_fail(LSC_EINVAL, "empty group");
+    for (int r = 0; r < n; ++r) {
+        if (!g[r]) return lsc_fail(LSC_EINVAL, "null context in group");
+        if (g[r]->cfg.nranks != n || g[r]->cfg.rank != r)
+            return lsc_fail(LSC_EINVAL, "group member %d has rank %d of %d", r, g[r]->cfg.rank, g[r]->cfg.nranks);
+        if (!g[r]->uploaded) return lsc_fail(LSC_ESTATE, "group member %d has no state uploaded", r);
+        if (g[r]->comm) return lsc_fail(LSC_ESTATE, "group member %d is attached to NCCL", r);
+        if (g[r]->step != g[0]->step) return lsc_fail(LSC_ESTATE, "group members are at different steps");
+    }
+    for (int r = 0; r < n; ++r) g[r]->in_group = true;
+    int rc = LSC_OK;
+    for (long s = 0; s < nsteps && rc == LSC_OK; ++s) {
+        rc = eg_resolve(g, n);
+        for (int r = 0; r < n && rc == LSC_OK; ++r) {
+            LSC_CUDA_TRY(cudaSetDevice(g[r]->cfg.device));
+            rc = e_step_launch(g[r]);
+        }
+        if (rc == LSC_OK) rc = eg_halo(g, n);
+    }
+    if (rc == LSC_OK) rc = eg_resolve(g, n);
+    for (int r = 0; r < n; ++r) g[r]->in_group = false;
+    return rc;
+}
 
 int lsc_euler_create(const lsc_euler_config* cfg, lsc_euler_ctx** out) {
     if (!cfg || !out) return lsc_fail(LSC_EINVAL, "lsc_euler_create: null argument");
@@ -134,20 +261,33 @@ int lsc_euler_create(const lsc_euler_config* cfg, lsc_euler_ctx** out) {
     }
     if (cfg->device < 0 || cfg->device >= ndev) return lsc_fail(LSC_EINVAL, "device %d out of range", cfg->device);
     LSC_CUDA_TRY(cudaSetDevice(cfg->device));
+    if (cfg->nranks > 1 && (cfg->rank < 0 || cfg->rank >= cfg->nranks)) return lsc_fail(LSC_EINVAL, "bad rank/nranks");
     lsc_euler_ctx* c = new (std::nothrow) lsc_euler_ctx();
     if (!c) return lsc_fail(LSC_ENOMEM, "host allocation failed");
     c->cfg = *cfg;
+    if (c->cfg.nranks < 1) {
+        c->cfg.nranks = 1;
+        c->cfg.rank = 0;
+    }
+    int b0, b1;
+    lsc::euler_slab_range(c->cfg, b0, b1);
+    c->i0 = b0;
+    c->nxl = b1 - b0;
+    if (c->nxl < 4) {
+        delete c;
+        return lsc_fail(LSC_EINVAL, "slab of rank %d has %d columns (need >= 4)", cfg->rank, b1 - b0);
+    }
     c->dx = (cfg->x1 - cfg->x0) / cfg->nx;  // S:546-547
     c->dy = (cfg->y1 - cfg->y0) / cfg->ny;
-    c->g.nxl = cfg->nx;
+    c->g.nxl = c->nxl;
     c->g.ny = cfg->ny;
     c->g.pitch = ((cfg->ny + 4 + lsc::JOFF) + 15) / 16 * 16;
-    c->g.plane = (size_t)(cfg->nx + 4) * (size_t)c->g.pitch;
+    c->g.plane = (size_t)(c->nxl + 4) * (size_t)c->g.pitch;
     const size_t state_bytes = c->g.plane * 4 * sizeof(double);
     const size_t col_bytes = (size_t)(cfg->ny + 4) * 4 * sizeof(double);
     long long cols = (long long)((256ull << 20) / col_bytes);
     if (cols < 1) cols = 1;
-    if (cols > cfg->nx + 4) cols = cfg->nx + 4;
+    if (cols > c->nxl + 4) cols = c->nxl + 4;
     c->stage_cols = (int)cols;
     bool ok = true;
     for (int b = 0; b < 3 && ok; ++b) {
@@ -158,7 +298,8 @@ int lsc_euler_create(const lsc_euler_config* cfg, lsc_euler_ctx** out) {
          cudaMalloc(&c->d_status, 32) == cudaSuccess &&
          cudaMalloc(&c->d_fix, sizeof(unsigned) * (size_t)lsc::euler_fix_list_entries(c->g)) == cudaSuccess &&
          cudaHostAlloc(&c->h_status, 32, cudaHostAllocDefault) == cudaSuccess &&
-         cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess;
+         cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess &&
+         cudaEventCreateWithFlags(&c->halo_event, cudaEventDisableTiming) == cudaSuccess;
     if (!ok) {
         cudaGetLastError();
         lsc_euler_destroy(c);
@@ -178,6 +319,8 @@ int lsc_euler_destroy(lsc_euler_ctx* c) {
     if (c->d_status) cudaFree(c->d_status);
     if (c->d_fix) cudaFree(c->d_fix);
     if (c->h_status) cudaFreeHost(c->h_status);
+    if (c->comm) lsc::comm_destroy(c->comm);
+    if (c->halo_event) cudaEventDestroy(c->halo_event);
     for (auto e : c->prof_events) cudaEventDestroy(e);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -196,7 +339,7 @@ int lsc_euler_upload(lsc_euler_ctx* c, const double* aos) {
     if (!c || !aos) return lsc_fail(LSC_EINVAL, "null argument");
     LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
     const size_t col = (size_t)(c->cfg.ny + 4) * 4;
-    const int ncol = c->cfg.nx + 4;
+    const int ncol = c->nxl + 4;
     for (int il = 0; il < ncol; il += c->stage_cols) {
         const int ni = std::min(c->stage_cols, ncol - il);
         LSC_CUDA_TRY(cudaMemcpyAsync(c->d_stage, aos + col * il, col * ni * sizeof(double), cudaMemcpyHostToDevice,
@@ -209,11 +352,16 @@ int lsc_euler_upload(lsc_euler_ctx* c, const double* aos) {
     // ComputeTimeStep of the first step sees the array as given, over i,j in [2, n+2] (S:173-174); then the
     // loop's own boundary fill (S:604) -- on the device only the x ghost columns are ever read
     LSC_CUDA_TRY(cudaMemsetAsync(c->d_status, 0, 32, c->stream));
-    lsc::launch_euler_max_speed(c->g, c->cfg.gamma, c->state[c->cur], 2, c->cfg.nx + 2, 2, c->cfg.ny + 2, c->d_status,
+    // (a slab's share of that range: its own interior columns, plus global column nx+2 on the last rank)
+    const int i_hi = c->nxl + ((c->cfg.rank == c->cfg.nranks - 1) ? 2 : 1);
+    lsc::launch_euler_max_speed(c->g, c->cfg.gamma, c->state[c->cur], 2, i_hi, 2, c->cfg.ny + 2, c->d_status,
                                 c->stream);
-    lsc::launch_euler_x_ghosts(c->g, kernel_bc(c->cfg.bc), c->state[c->cur], c->stream);
-    lsc_count_launches(2);
+    lsc_count_launches(1);
     LSC_CUDA_TRY(cudaGetLastError());
+    if (c->cfg.nranks <= 1) {
+        int rc = e_fill_x_ghosts(c, c->cur);
+        if (rc) return rc;
+    }  // slabs: the uploaded halo columns already hold the neighbours' cells / the caller's boundary images
     LSC_CUDA_TRY(cudaStreamSynchronize(c->stream));
     c->t = c->dt = 0;
     c->step = 0;
@@ -227,7 +375,7 @@ int lsc_euler_init_problem(lsc_euler_ctx* c, int problem) {
     if (!c) return lsc_fail(LSC_EINVAL, "null argument");
     std::vector<double> host;
     try {
-        host.resize((size_t)(c->cfg.nx + 4) * (c->cfg.ny + 4) * 4);
+        host.resize((size_t)(c->nxl + 4) * (c->cfg.ny + 4) * 4);
     } catch (...) {
         return lsc_fail(LSC_ENOMEM, "host allocation failed");
     }
@@ -296,12 +444,12 @@ int lsc_euler_download(lsc_euler_ctx* c, double* aos) {
     if (!c || !aos) return lsc_fail(LSC_EINVAL, "null argument");
     if (!c->uploaded) return lsc_fail(LSC_ESTATE, "lsc_euler_download before lsc_euler_upload");
     LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
-    if (c->pending && c->pending_step) {
+    if (c->pending && c->pending_step && !c->in_group) {
         int rc = e_resolve(c);
         if (rc) return rc;
     }
     const size_t col = (size_t)(c->cfg.ny + 4) * 4;
-    const int ncol = c->cfg.nx + 4;
+    const int ncol = c->nxl + 4;
     for (int il = 0; il < ncol; il += c->stage_cols) {
         const int ni = std::min(c->stage_cols, ncol - il);
         lsc::launch_euler_soa_to_aos(c->g, c->state[c->cur], il, ni, c->d_stage, c->stream);

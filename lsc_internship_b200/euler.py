@@ -26,14 +26,22 @@ class SlicEuler2d:
     NVAR = 4
 
     def __init__(self, nxCells=100, nyCells=100, x0=0.0, x1=1.0, y0=0.0, y1=1.0, tStop=0.5, C=0.8, gamma=1.4,
-                 omega=0.0, bc="periodic", problem="ot", device=0):
+                 omega=0.0, bc="periodic", problem="ot", device=0, rank=0, nranks=1):
         self.tStop = float(tStop)
         self.problem = _capi.EULER_PROBLEMS[problem] if isinstance(problem, str) else int(problem)
         bcv = {"periodic": _capi.BC_PERIODIC, "transmissive": _capi.BC_TRANSMISSIVE_E}[bc]
         self.cfg = EulerConfig(int(nxCells), int(nyCells), float(x0), float(x1), float(y0), float(y1), float(gamma),
-                               float(C), float(omega), bcv, int(device))
+                               float(C), float(omega), bcv, int(device), int(rank), int(nranks))
         self._h = ctypes.c_void_p()
         check(lib().lsc_euler_create(ctypes.byref(self.cfg), ctypes.byref(self._h)))
+        # slab of this rank: nxl interior columns starting at global interior column i0
+        self.nxl = lib().lsc_euler_local_nx(self._h)
+        self.i0 = lib().lsc_euler_local_i0(self._h)
+
+    def comm_init(self, unique_id):
+        """Join the NCCL communicator of the slab decomposition (id from lsc_comm_unique_id on rank 0)."""
+        buf = ctypes.create_string_buffer(bytes(unique_id), 128)
+        check(lib().lsc_euler_comm_init(self._h, ctypes.cast(buf, ctypes.c_void_p)))
 
     def close(self):
         if getattr(self, "_h", None) and self._h.value:
@@ -48,7 +56,8 @@ class SlicEuler2d:
 
     @property
     def shape(self):
-        return (self.cfg.nx + 4, self.cfg.ny + 4, self.NVAR)
+        """host array of this context: the whole padded grid, or this rank's padded slab"""
+        return (self.nxl + 4, self.cfg.ny + 4, self.NVAR)
 
     def _prob(self, problem):
         if problem is None:
@@ -134,3 +143,44 @@ class SlicEuler2d:
             u = self.download()
             self.write_dat(u, os.path.join(outdir, "SLIC2d.dat"), blank_line_per_row=True)
         return n
+
+
+class SlicEuler2dGroup:
+    """The n slabs of one grid advanced in lock step inside ONE process (lsc_euler_group_step): halos by peer
+    copies, the CFL maximum on the host.  Same kernels and slab-edge code path as the NCCL mode; used to check
+    that the decomposition does not change a single bit."""
+
+    def __init__(self, nslabs, devices=None, **kw):
+        ndev = lib().lsc_device_count()
+        devices = devices if devices is not None else [r % max(ndev, 1) for r in range(nslabs)]
+        self.parts = [SlicEuler2d(device=devices[r], rank=r, nranks=nslabs, **kw) for r in range(nslabs)]
+        self._arr = (ctypes.c_void_p * nslabs)(*[p._h for p in self.parts])
+        self.nx, self.ny = self.parts[0].cfg.nx, self.parts[0].cfg.ny
+
+    def init_problem(self, problem=None):
+        for p in self.parts:
+            p.init_problem(problem)
+
+    def upload(self, u):
+        """u: the whole padded grid [(nx+4)][(ny+4)][4]; every slab takes its columns incl. halos"""
+        for p in self.parts:
+            p.upload(u[p.i0:p.i0 + p.nxl + 4])
+
+    def step(self, nsteps=1):
+        check(lib().lsc_euler_group_step(self._arr, len(self.parts), int(nsteps)))
+
+    def download(self):
+        u = np.empty((self.nx + 4, self.ny + 4, 4), dtype=np.float64)
+        for r, p in enumerate(self.parts):
+            a = p.download()
+            lo = 0 if r == 0 else 2
+            hi = p.nxl + 4 if r == len(self.parts) - 1 else p.nxl + 2
+            u[p.i0 + lo:p.i0 + hi] = a[lo:hi]
+        return u
+
+    def scalars(self):
+        return self.parts[0].scalars()
+
+    def close(self):
+        for p in self.parts:
+            p.close()

@@ -31,6 +31,31 @@ def test_config_struct_layout():
     assert ctypes.sizeof(_capi.MhdConfig) == 4 + 4 + 6 * 8 + 5 * 4 + 4  # trailing pad to 8
 
 
+@pytest.mark.parametrize("bc", ["periodic", "transmissive"])
+@pytest.mark.parametrize("problem", [0, 1, 2])
+def test_euler_slab_initial_condition_is_the_global_one(bc, problem):
+    """lsc_euler_initial_condition for rank r of P (host code, no GPU): every slab equals the corresponding
+    columns of the whole-grid array -- interior columns and the halo columns that are a neighbour's interior --
+    and at a periodic wrap / physical edge holds what the reference's boundary fill (S:596) puts there."""
+    import numpy as np
+    L = lsc.lib()
+    nx, ny, P = 37, 21, 3
+    bcv = {"periodic": _capi.BC_PERIODIC, "transmissive": _capi.BC_TRANSMISSIVE_E}[bc]
+    dp = ctypes.POINTER(ctypes.c_double)
+    whole_cfg = _capi.EulerConfig(nx, ny, 0.0, 1.0, 0.0, 1.0, 1.4, 0.8, 0.0, bcv, 0, 0, 1)
+    whole = np.empty((nx + 4, ny + 4, 4))
+    assert L.lsc_euler_initial_condition(ctypes.byref(whole_cfg), problem, whole.ctypes.data_as(dp)) == 0
+    covered = 0
+    for r in range(P):
+        b0, b1 = nx * r // P, nx * (r + 1) // P
+        cfg = _capi.EulerConfig(nx, ny, 0.0, 1.0, 0.0, 1.0, 1.4, 0.8, 0.0, bcv, 0, r, P)
+        slab = np.empty((b1 - b0 + 4, ny + 4, 4))
+        assert L.lsc_euler_initial_condition(ctypes.byref(cfg), problem, slab.ctypes.data_as(dp)) == 0
+        assert np.array_equal(slab.view(np.uint64), whole[b0:b1 + 4].view(np.uint64)), f"rank {r}"
+        covered += b1 - b0
+    assert covered == nx
+
+
 def test_no_cpu_fallback_or_bad_config():
     L = lsc.lib()
     if L.lsc_device_count() == 0:

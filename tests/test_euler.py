@@ -108,6 +108,41 @@ def test_cuda_matches_oracle(bc, ic, nx, ny, n):
 
 
 @gpu
+@pytest.mark.parametrize("bc,ic,nx,ny,P,n", [
+    ("periodic", "ot", 96, 64, 2, 6),                 # two slabs on a periodic ring: each is both neighbours
+    ("periodic", "ot", 101, 40, 3, 5),                # ragged slabs
+    ("transmissive", "cylinder", 120, 72, 4, 6),      # end slabs carry the G:203-208 images
+    ("transmissive", "quadrants", 33, 20, 2, 5),
+])
+def test_slab_decomposition_does_not_change_a_bit(bc, ic, nx, ny, P, n):
+    """SURVEY 8e (S/G row): P slabs along x, two halo columns per neighbour and one max per step.  The slab
+    group (peer-copy halos, the same kernels and slab-edge path the NCCL ranks run) must reproduce the
+    single-context state and (t, dt) exactly, and both must equal the oracle."""
+    import lsc_internship_b200 as lsc
+    cfg = euler_cfg(nx, ny, DOM, bc=bc)
+    u0 = euler_ic(cfg, ic)
+    one = lsc.SlicEuler2d(nx, ny, bc=bc, problem=ic)
+    one.upload(u0)
+    one.step(n)
+    grp = lsc.SlicEuler2dGroup(P, nxCells=nx, nyCells=ny, bc=bc, problem=ic)
+    grp.upload(u0)
+    grp.step(n)
+    o = OracleEuler(cfg, u0)
+    o.step(n)
+    assert grp.scalars() == one.scalars()
+    a, b = grp.download(), one.download()
+    assert np.array_equal(bits(a), bits(b))
+    assert np.array_equal(bits(a), bits(o.state()[0]))
+    # library-generated slabs (no whole-grid array on the host) give the same run
+    grp2 = lsc.SlicEuler2dGroup(P, nxCells=nx, nyCells=ny, bc=bc, problem=ic)
+    grp2.init_problem()
+    grp2.step(n)
+    assert np.array_equal(bits(grp2.download()), bits(a))
+    for x in (one, grp, grp2):
+        x.close()
+
+
+@gpu
 def test_random_state_parity():
     import lsc_internship_b200 as lsc
     nx, ny = 90, 70
