@@ -2,9 +2,13 @@
  * oracle/euler_oracle.c -- CPU restatement of the reference's 2-D Euler SLIC step
  * (Euler_codes/SLIC_euler_2d.cpp = S, transmissive variant Euler_codes/generaliseSLIC.cpp = G).
  *
+ * and of the tabulated-EoS variant MHD_codes/TabEoS.cpp = T (same sweeps, EoS by table lookup, T:147-438).
+ *
  * TEST INFRASTRUCTURE ONLY (see mhd_oracle.c).  Parity pin: bit-identical to the real reference programs
  * compiled by oracle/build_ref_euler.py (oracle/_ref/slic_ref, gslic_ref); slic_ref reproduces the
- * reference's committed MHD_plot_data/euler_{1..20}.dat byte-for-byte.
+ * reference's committed MHD_plot_data/euler_{1..20}.dat byte-for-byte.  Table path: bit-identical to
+ * oracle/_ref/tabeos_ref (the real TabEoS.cpp) run on the synthetic table of tests/oracle_util.py; the real
+ * Plasma19_EoS.txt is not in the reference tree, so that path is NOT pinned against the committed SLIC2d.dat.
  *
  * Layout: AoS u[(i*(ny+4)+j)*4 + k], k = rho, rho*vx, rho*vy, E (S:10-17), two ghosts per side.
  */
@@ -21,12 +25,21 @@ typedef struct {
     int bc; /* 0 periodic (S:198-226), 1 transmissive (G:199-215) */
 } lsc_oracle_euler_cfg;
 
+/* Tabulated EoS of MHD_codes/TabEoS.cpp (= T): 500 densities, 500 pressures, sound speed and specific
+ * internal energy as [pressure index][density index] (T:18-133).  NULL = ideal gas (S / G). */
+#define NT 500
+typedef struct {
+    const double *dens, *pres, *sound, *en;
+} eos_table_t;
+
 typedef struct {
     lsc_oracle_euler_cfg c;
     size_t ncell;
     double dx, dy, t, dt;
     long step;
     double *u, *A, *B, *flux, *ubar, *rL, *rR, *hL, *hR;
+    eos_table_t tab;  /* tab.dens == NULL: ideal gas */
+    double *tab_store;
 } euler_t;
 
 #define EAT(a, i, j) ((a) + ((size_t)(i) * (size_t)(ny + 4) + (size_t)(j)) * NE)
@@ -59,17 +72,136 @@ void lsc_oracle_euler_fluxdef(const double *x, double g, int dir, double *f) {
     }
 }
 
-/* FORCE flux, S:111-136 (x) / S:139-163 (y); h = dx or dy */
-void lsc_oracle_euler_force(const double *x, const double *y, double h, double dt, double g, int dir, double *F) {
+/* ---- tabulated EoS, T:147-404 ------------------------------------------------------------------------ */
+/* T:147-153 */
+static double tab_bilinear(double f_NE, double f_SE, double f_SW, double f_NW, double x, double y) {
+    double f_x_y1 = (1 - x) * f_SW + x * f_SE;
+    double f_x_y2 = (1 - x) * f_NW + x * f_NE;
+    return (1 - y) * f_x_y1 + y * f_x_y2;
+}
+
+/* T:156-163 */
+static double tab_reverse_bilinear(double f_NE, double f_SE, double f_SW, double f_NW, double x, double f_x_y) {
+    double f_x_y1 = (1 - x) * f_SW + x * f_SE;
+    double f_x_y2 = (1 - x) * f_NW + x * f_NE;
+    double y = (f_x_y - f_x_y1) / (f_x_y2 - f_x_y1);
+    if (f_x_y2 == f_x_y1) y = 1;
+    return y;
+}
+
+/* the bisection every lookup starts with (T:174-191, :211-228, :257-275, :339-356, :364-384): brackets `v` in
+ * the ascending axis `a`; point2 starts at 499, or at 500 in SoundSpeed's pressure search (T:366) */
+static void tab_bracket(const double *a, double v, int point2, int *lo, int *hi) {
+    int point1 = 0, half;
+    while (abs(point1 - point2) > 1) {
+        half = (point1 + point2) / 2;
+        if (v > a[half]) point1 = half;
+        else point2 = half;
+    }
+    if (point1 >= 499) point1 = 499;
+    if (point2 >= 499) point2 = 499;
+    if (point1 <= 0) point1 = 0;
+    if (point2 <= 0) point2 = 0;
+    *lo = point1;
+    *hi = point2;
+}
+
+/* PrimativeToConservative, T:166-246 */
+void lsc_oracle_tabeos_p2c(const eos_table_t *tb, const double *prim, double *consv) {
+    consv[0] = prim[0];
+    consv[1] = prim[0] * prim[1];
+    consv[2] = prim[0] * prim[2];
+    double rho = prim[0], p = prim[3];
+    int db, dt_, pb, pt;
+    tab_bracket(tb->dens, rho, 499, &db, &dt_);
+    double density_ratio = (rho - tb->dens[db]) / (tb->dens[dt_] - tb->dens[db]);
+    if (tb->dens[db] == tb->dens[dt_]) density_ratio = 1;
+    tab_bracket(tb->pres, p, 499, &pb, &pt);
+    double pressure_ratio = (p - tb->pres[pb]) / (tb->pres[pt] - tb->pres[pb]);
+    if (tb->pres[pb] == tb->pres[pt]) pressure_ratio = 1;
+    double energy = tab_bilinear(tb->en[pt * NT + dt_], tb->en[pb * NT + dt_], tb->en[pb * NT + db], tb->en[pt * NT + db],
+                                 density_ratio, pressure_ratio);
+    consv[3] = energy * rho + 0.5 * rho * (prim[1] * prim[1] + prim[2] * prim[2]);
+}
+
+/* ConservativeToPrimative, T:248-327.  The pressure bracket is captured BEFORE the clamps (T:303-310). */
+void lsc_oracle_tabeos_c2p(const eos_table_t *tb, const double *consv, double *prim) {
+    prim[0] = consv[0];
+    prim[1] = consv[1] / consv[0];
+    prim[2] = consv[2] / consv[0];
+    double rho = prim[0];
+    int db, dt_;
+    tab_bracket(tb->dens, rho, 499, &db, &dt_);
+    double density_ratio = (rho - tb->dens[db]) / (tb->dens[dt_] - tb->dens[db]);
+    if (tb->dens[db] == tb->dens[dt_]) density_ratio = 1;
+    double e = (consv[3] - 0.5 * rho * (prim[1] * prim[1] + prim[2] * prim[2])) / rho;
+    int point1 = 0, point2 = 499, half;
+    while (abs(point1 - point2) > 1) {
+        half = (point1 + point2) / 2;
+        if (e > (tb->en[half * NT + db] + density_ratio * (tb->en[half * NT + dt_] - tb->en[half * NT + db]))) point1 = half;
+        else point2 = half;
+    }
+    int pt = point2, pb = point1;
+    double pressure_ratio = tab_reverse_bilinear(tb->en[pt * NT + dt_], tb->en[pb * NT + dt_], tb->en[pb * NT + db],
+                                                 tb->en[pt * NT + db], density_ratio, e);
+    prim[3] = pressure_ratio * (tb->pres[pt] - tb->pres[pb]) + tb->pres[pb];
+}
+
+/* SoundSpeed, T:330-404 */
+double lsc_oracle_tabeos_sound(const eos_table_t *tb, const double *u) {
+    double prim[NE];
+    lsc_oracle_tabeos_c2p(tb, u, prim);
+    double rho = u[0], p = prim[3];
+    int db, dt_, pb, pt;
+    tab_bracket(tb->dens, rho, 499, &db, &dt_);
+    double density_ratio = (rho - tb->dens[db]) / (tb->dens[dt_] - tb->dens[db]);
+    if (tb->dens[db] == tb->dens[dt_]) density_ratio = 1;
+    tab_bracket(tb->pres, p, 500, &pb, &pt); /* T:366: starts at 500; index 500 is never read */
+    double pressure_ratio = (p - tb->pres[pb]) / (tb->pres[pt] - tb->pres[pb]);
+    if (tb->pres[pb] == tb->pres[pt]) pressure_ratio = 1;
+    return tab_bilinear(tb->sound[pt * NT + dt_], tb->sound[pb * NT + dt_], tb->sound[pb * NT + db],
+                        tb->sound[pt * NT + db], density_ratio, pressure_ratio);
+}
+
+/* fluxX_def / fluxY_def with the table, T:408-438 */
+void lsc_oracle_tabeos_fluxdef(const eos_table_t *tb, const double *x, int dir, double *f) {
+    double prim[NE];
+    lsc_oracle_tabeos_c2p(tb, x, prim);
+    double rho = prim[0], v_x = prim[1], v_y = prim[2], p = prim[3];
+    if (dir == 0) {
+        f[0] = x[1];
+        f[1] = rho * v_x * v_x + p;
+        f[2] = rho * v_x * v_y;
+        f[3] = (x[3] + p) * v_x;
+    } else {
+        f[0] = x[2];
+        f[1] = rho * v_x * v_y;
+        f[2] = rho * v_y * v_y + p;
+        f[3] = (x[3] + p) * v_y;
+    }
+}
+
+static void fluxdef_eos(const eos_table_t *tb, const double *x, double g, int dir, double *f) {
+    if (tb && tb->dens) lsc_oracle_tabeos_fluxdef(tb, x, dir, f);
+    else lsc_oracle_euler_fluxdef(x, g, dir, f);
+}
+
+/* FORCE flux, S:111-136 (x) / S:139-163 (y), T:440-492; h = dx or dy */
+static void force_eos(const eos_table_t *tb, const double *x, const double *y, double h, double dt, double g, int dir,
+                      double *F) {
     double f1[NE], f2[NE], uh[NE], ri[NE];
-    lsc_oracle_euler_fluxdef(x, g, dir, f1);
-    lsc_oracle_euler_fluxdef(y, g, dir, f2);
+    fluxdef_eos(tb, x, g, dir, f1);
+    fluxdef_eos(tb, y, g, dir, f2);
     for (int k = 0; k < NE; ++k) uh[k] = 0.5 * (x[k] + y[k]) - 0.5 * (dt / h) * (f2[k] - f1[k]);
-    lsc_oracle_euler_fluxdef(uh, g, dir, ri);
+    fluxdef_eos(tb, uh, g, dir, ri);
     for (int k = 0; k < NE; ++k) {
         double lf = (0.5 * h / dt) * (x[k] - y[k]) + 0.5 * (f1[k] + f2[k]);
         F[k] = 0.5 * (lf + ri[k]);
     }
+}
+
+void lsc_oracle_euler_force(const double *x, const double *y, double h, double dt, double g, int dir, double *F) {
+    force_eos(NULL, x, y, h, dt, g, dir, F);
 }
 
 /* S:198-226 (periodic, full loop ranges) / G:199-215 (transmissive) */
@@ -114,6 +246,15 @@ static double euler_dt(const euler_t *m) {
     for (int i = 2; i <= nx + 2; ++i)
         for (int j = 2; j <= ny + 2; ++j) {
             const double *q = EAT(m->u, i, j);
+            if (m->tab.dens) { /* T:505-521 */
+                double prim[NE];
+                lsc_oracle_tabeos_c2p(&m->tab, q, prim);
+                double speed = sqrt(prim[1] * prim[1] + prim[2] * prim[2]);
+                double sound_speed = lsc_oracle_tabeos_sound(&m->tab, q);
+                double new_speed = speed + sound_speed;
+                if (new_speed > best) best = new_speed;
+                continue;
+            }
             double rho = q[0], vx = q[1] / rho, vy = q[2] / rho;
             double speed = sqrt(vx * vx + vy * vy);
             double KE = 0.5 * rho * speed * speed;
@@ -161,8 +302,8 @@ static void sweep(euler_t *m, const double *in, double *out, int dir) {
     for (int j = 2; j < ny + 2; ++j)
         for (int i = 2; i < nx + 2; ++i) {
             double fl[NE], fr[NE];
-            lsc_oracle_euler_fluxdef(EAT(m->rL, i, j), g, dir, fl);
-            lsc_oracle_euler_fluxdef(EAT(m->rR, i, j), g, dir, fr);
+            fluxdef_eos(&m->tab, EAT(m->rL, i, j), g, dir, fl);
+            fluxdef_eos(&m->tab, EAT(m->rR, i, j), g, dir, fr);
             for (int k = 0; k < NE; ++k) {
                 EAT(m->hL, i, j)[k] = EAT(m->rL, i, j)[k] - 0.5 * (dt / h) * (fr[k] - fl[k]);
                 EAT(m->hR, i, j)[k] = EAT(m->rR, i, j)[k] - 0.5 * (dt / h) * (fr[k] - fl[k]);
@@ -172,7 +313,7 @@ static void sweep(euler_t *m, const double *in, double *out, int dir) {
     ebc(m, m->hR);
     for (int j = 1; j < ny + 3; ++j)
         for (int i = 1; i < nx + 3; ++i)
-            lsc_oracle_euler_force(EAT(m->hR, i, j), EAT(m->hL, i + di, j + dj), h, dt, g, dir, EAT(m->flux, i, j));
+            force_eos(&m->tab, EAT(m->hR, i, j), EAT(m->hL, i + di, j + dj), h, dt, g, dir, EAT(m->flux, i, j));
     for (int j = 2; j < ny + 2; ++j)
         for (int i = 2; i < nx + 2; ++i)
             for (int k = 0; k < NE; ++k)
@@ -237,6 +378,50 @@ void lsc_oracle_euler_ic(const lsc_oracle_euler_cfg *c, int ic, double *u) {
     ebc(&tmp, u);
 }
 
+/* IC of TabEoS.cpp main(), T:918-941: four quadrants at rest, rho = 1, p = 0.01e5 (x > 0.5) / 1000e5 (x <= 0.5),
+ * PrimativeToConservative through the table, then the transmissive boundary fill (T:954). */
+void lsc_oracle_tabeos_ic(const lsc_oracle_euler_cfg *c, const double *dens, const double *pres, const double *sound,
+                          const double *en, double *u) {
+    eos_table_t tb = {dens, pres, sound, en};
+    const int nx = c->nx, ny = c->ny;
+    const double dx = (c->x1 - c->x0) / nx, dy = (c->y1 - c->y0) / ny;
+    for (int i = 0; i < nx + 4; ++i)
+        for (int j = 0; j < ny + 4; ++j) {
+            double x = c->x0 + (i - 1.5) * dx, y = c->y0 + (j - 1.5) * dy, pr[NE];
+            pr[0] = 1.0; pr[1] = 0; pr[2] = 0;
+            if (x > 0.5 && y > 0.5) pr[3] = 0.01 * 1e5;
+            else if (x <= 0.5 && y > 0.5) pr[3] = 1000 * 1e5;
+            else if (x <= 0.5 && y <= 0.5) pr[3] = 1000 * 1e5;
+            else pr[3] = 0.01 * 1e5;
+            lsc_oracle_tabeos_p2c(&tb, pr, EAT(u, i, j));
+        }
+    euler_t tmp;
+    tmp.c = *c;
+    tmp.c.bc = 1;
+    ebc(&tmp, u);
+}
+
+/* attach a copy of the four tables to an oracle instance: every flux and the time step then go through T's EoS */
+void lsc_oracle_euler_set_table(void *h, const double *dens, const double *pres, const double *sound, const double *en) {
+    euler_t *m = (euler_t *)h;
+    free(m->tab_store);
+    m->tab_store = (double *)malloc(sizeof(double) * (2 * NT + 2 * NT * NT));
+    memcpy(m->tab_store, dens, sizeof(double) * NT);
+    memcpy(m->tab_store + NT, pres, sizeof(double) * NT);
+    memcpy(m->tab_store + 2 * NT, sound, sizeof(double) * NT * NT);
+    memcpy(m->tab_store + 2 * NT + NT * NT, en, sizeof(double) * NT * NT);
+    m->tab.dens = m->tab_store;
+    m->tab.pres = m->tab_store + NT;
+    m->tab.sound = m->tab_store + 2 * NT;
+    m->tab.en = m->tab_store + 2 * NT + NT * NT;
+}
+
+void lsc_oracle_tabeos_c2p_flat(const double *dens, const double *pres, const double *sound, const double *en,
+                                const double *consv, double *prim) {
+    eos_table_t tb = {dens, pres, sound, en};
+    lsc_oracle_tabeos_c2p(&tb, consv, prim);
+}
+
 void *lsc_oracle_euler_create(const lsc_oracle_euler_cfg *c, const double *u0) {
     euler_t *m = (euler_t *)calloc(1, sizeof(euler_t));
     m->c = *c;
@@ -268,5 +453,6 @@ void lsc_oracle_euler_destroy(void *h) {
     euler_t *m = (euler_t *)h;
     double *arr[] = {m->u, m->A, m->B, m->flux, m->ubar, m->rL, m->rR, m->hL, m->hR};
     for (size_t a = 0; a < sizeof(arr) / sizeof(arr[0]); ++a) free(arr[a]);
+    free(m->tab_store);
     free(m);
 }

@@ -138,6 +138,11 @@ class OracleEuler:
         assert u0.shape == (cfg.nx + 4, cfg.ny + 4, 4)
         self.h = ctypes.c_void_p(self.lib.lsc_oracle_euler_create(ctypes.byref(cfg), _dp(u0)))
 
+    def set_table(self, dens, pres, sound, energies):
+        """switch this instance to TabEoS.cpp's equation of state (T:147-438)"""
+        args = [np.ascontiguousarray(a, dtype=np.float64) for a in (dens, pres, sound, energies)]
+        self.lib.lsc_oracle_euler_set_table(self.h, *[_dp(a) for a in args])
+
     def step(self, n=1):
         log = np.zeros((n, 2), dtype=np.float64)
         self.lib.lsc_oracle_euler_step(self.h, ctypes.c_long(n), _dp(log))
@@ -170,3 +175,80 @@ def run_euler_ref(which, nx, ny, dom, t_stop, cfl, gamma, nsteps, ic=0, cwd=None
         u = np.fromfile(st, dtype=np.float64).reshape(nx + 4, ny + 4, 4)
         log = np.fromfile(lg, dtype=np.float64).reshape(-1, 2)
     return u, log, r.stderr
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Tabulated EoS (MHD_codes/TabEoS.cpp = T).  The real Plasma19_EoS.txt is not in the reference tree (stripped
+# large blob), so every checker and the CUDA path run on a SYNTHETIC table in the same file format (T:36-128):
+# line 10 = 500 densities, line 12 = 500 pressures, lines 14-513 sound speed, 515-1014 specific internal energy,
+# 1016-1515 temperature, 1517-2016 electrical and 2018-2517 thermal conductivity; rows = pressure index, columns
+# = density index.  A gas whose adiabatic index drifts from 1.6 (low p) to 1.2 (high p): not an ideal gas (so the
+# lookup is really exercised), e(p) strictly increasing at fixed rho (T's reverse search needs that).
+# ---------------------------------------------------------------------------------------------------------
+def eos_table():
+    dens = np.logspace(-3.0, 2.0, 500)
+    pres = np.logspace(1.0, 10.0, 500)
+    g = 1.4 - 0.2 * np.tanh(np.log10(pres / 1.0e6))
+    P, R = pres[:, None], dens[None, :]
+    energies = P / ((g[:, None] - 1.0) * R)
+    sound = np.sqrt(g[:, None] * P / R)
+    return dens, pres, sound, energies
+
+
+def write_eos_table(path):
+    """Write the synthetic table as a Plasma19_EoS.txt look-alike and return the arrays AS PARSED BACK from it."""
+    dens, pres, sound, energies = eos_table()
+    temp = energies / 718.0
+    row = lambda v: " ".join(repr(float(x)) for x in v)  # noqa: E731
+    lines = ["# synthetic EoS table in the layout TabEoS.cpp parses (T:36-128)"] * 9
+    lines += [row(dens), "# pressures", row(pres), "# sound speed [p][rho]"]
+    lines += [row(r) for r in sound] + ["# specific internal energy [p][rho]"]
+    lines += [row(r) for r in energies] + ["# temperature"]
+    lines += [row(r) for r in temp] + ["# electrical conductivity"]
+    lines += [row(r) for r in np.ones_like(temp)] + ["# thermal conductivity"]
+    lines += [row(r) for r in np.ones_like(temp)]
+    assert len(lines) == 2517
+    with open(path, "w") as f:
+        f.write("\n".join(lines) + "\n")
+    return dens, pres, sound, energies
+
+
+def run_tabeos_ref(nx, ny, nsteps, dom=(0.0, 1.0, 0.0, 1.0), t_stop=1e9, cfl=0.8, workdir=None):
+    """Run oracle/_ref/tabeos_ref (the real TabEoS.cpp) on the synthetic table; returns (u, [(t, dt)...])."""
+    import tempfile
+    exe = os.path.join(REF_DIR, "tabeos_ref")
+    with tempfile.TemporaryDirectory() as td:
+        write_eos_table(os.path.join(td, "Plasma19_EoS.txt"))
+        dump, log = os.path.join(td, "u.bin"), os.path.join(td, "log.bin")
+        subprocess.run([exe, str(nx), str(ny)] + [repr(float(v)) for v in dom] + [repr(float(t_stop)), repr(float(cfl)),
+                       str(nsteps), "0", dump, log], cwd=td, check=True, capture_output=True)
+        u = np.fromfile(dump, dtype=np.float64).reshape(nx + 4, ny + 4, 4)
+        lg = np.fromfile(log, dtype=np.float64).reshape(-1, 2)
+    return u, lg
+
+
+def tabeos_ic(cfg, table):
+    """IC of TabEoS.cpp main() (T:918-941 + boundary fill T:954) through the oracle's table P2C."""
+    u = np.zeros((cfg.nx + 4, cfg.ny + 4, 4), dtype=np.float64)
+    args = [np.ascontiguousarray(a, dtype=np.float64) for a in table]
+    oracle_lib().lsc_oracle_tabeos_ic(ctypes.byref(cfg), *[_dp(a) for a in args], _dp(u))
+    return u
+
+
+_TABLE = None
+
+
+def parsed_eos_table():
+    """the synthetic table as the reference / the library parse it back from the text file (cached)"""
+    global _TABLE
+    if _TABLE is None:
+        with tempfile.TemporaryDirectory() as td:
+            path = os.path.join(td, "Plasma19_EoS.txt")
+            write_eos_table(path)
+            rows = open(path).read().split("\n")
+        num = lambda r: np.array([float(x) for x in r.split()])  # noqa: E731
+        dens, pres = num(rows[9]), num(rows[11])
+        sound = np.array([num(r) for r in rows[13:513]])
+        en = np.array([num(r) for r in rows[514:1014]])
+        _TABLE = (dens, pres, sound, en)
+    return _TABLE
