@@ -199,6 +199,9 @@ int lsc_kat_division(int device, unsigned long long seed, int mode, long nblocks
 #define LSC_EULER_IC_CYLINDER 2    /* cylindrical explosion of BASELINE config 3: rho,p = 1,1 inside
                                       (x-.5)^2+(y-.5)^2 <= 0.2^2, 0.125,0.1 outside, at rest (not in the reference) */
 
+#define LSC_EULER_IC_TABEOS 3       /* T:918-941: four quadrants at rest, rho = 1, p = 0.01e5 (x > 0.5) / 1000e5;
+                                      PrimativeToConservative through the EoS table (needs lsc_euler_set_eos_table) */
+
 /* Replaces the constants S:529-540 / G:565-577. */
 typedef struct lsc_euler_config {
     int nx, ny;
@@ -241,6 +244,27 @@ int lsc_euler_download(lsc_euler_ctx* ctx, double* aos);              /* u after
 /* S:621-642 (blank_line_per_row = 0, euler_<k>.dat) / G:645-667 (= 1, SLIC2d.dat) */
 int lsc_euler_write_dat(const lsc_euler_config* cfg, const double* aos, const char* path, int blank_line_per_row);
 long lsc_euler_ieee_fallback_count(const lsc_euler_ctx* ctx);
+
+/* ------------------------------------------------------------------------------------------------
+ * Tabulated equation of state (T = MHD_codes/TabEoS.cpp; SURVEY.md 8f row N2, BASELINE config 5): the same SLIC
+ * sweeps as G with every pressure / sound speed taken from a 500x500 table instead of the ideal-gas formulas:
+ * ConservativeToPrimative T:248-327 (two bisections + reverse bilinear interpolation) inside fluxX/Y_def
+ * T:408-438, SoundSpeed T:330-404 inside ComputeTimeStep T:494-526.  cfg.gamma is not used on this path.
+ * Tables are [pressure index][density index], 500 x 500 doubles; axes strictly ascending.
+ * ---------------------------------------------------------------------------------------------- */
+/* Plasma19(), T:18-133: parse a table file in the layout the reference reads (line 10 densities, 12 pressures,
+ * 14-513 sound speed, 515-1014 specific internal energy; the remaining blocks are unused by the solver). */
+int lsc_eos_table_read(const char* path, double* densities, double* pressures, double* sound_speeds,
+                       double* energies);
+/* replaces the globals T:135-144.  densities == NULL switches the context back to the ideal gas. */
+int lsc_euler_set_eos_table(lsc_euler_ctx* ctx, const double* densities, const double* pressures,
+                            const double* sound_speeds, const double* energies);
+/* IC loop T:912-952 + boundary fill T:954 into [(nx+4)][(ny+4)][4] (or the slab of cfg->rank) */
+int lsc_euler_tabeos_initial_condition(const lsc_euler_config* cfg, const double* densities, const double* pressures,
+                                       const double* energies, double* aos);
+/* T:974-999: SLIC2d.dat through the table's ConservativeToPrimative, blank line after each j row */
+int lsc_euler_tabeos_write_dat(const lsc_euler_config* cfg, const double* aos, const char* path,
+                               const double* densities, const double* pressures, const double* energies);
 int lsc_euler_set_profiling(lsc_euler_ctx* ctx, int enabled);
 int lsc_euler_kernel_times(lsc_euler_ctx* ctx, double ms[2], long launches[2]);
 

@@ -48,7 +48,7 @@ class EulerConfig(ctypes.Structure):
                 ("rank", ctypes.c_int), ("nranks", ctypes.c_int)]
 
 
-EULER_PROBLEMS = {"ot": 0, "orszag-tang": 0, "quadrants": 1, "cylinder": 2}
+EULER_PROBLEMS = {"ot": 0, "orszag-tang": 0, "quadrants": 1, "cylinder": 2, "tabeos": 3}
 EULER_LOG_CB = ctypes.CFUNCTYPE(None, ctypes.c_long, ctypes.c_double, ctypes.c_double, ctypes.c_void_p)
 
 DUMP_CB = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_double, ctypes.c_double,
@@ -67,7 +67,8 @@ EXPORTS = [
     "lsc_euler_init_problem", "lsc_euler_step", "lsc_euler_step_timed", "lsc_euler_run_until",
     "lsc_euler_get_scalars", "lsc_euler_download", "lsc_euler_write_dat", "lsc_euler_ieee_fallback_count",
     "lsc_euler_set_profiling", "lsc_euler_kernel_times", "lsc_euler_local_nx", "lsc_euler_local_i0",
-    "lsc_euler_comm_init", "lsc_euler_group_step",
+    "lsc_euler_comm_init", "lsc_euler_group_step", "lsc_eos_table_read", "lsc_euler_set_eos_table",
+    "lsc_euler_tabeos_initial_condition", "lsc_euler_tabeos_write_dat",
 ]
 
 _lib = None
@@ -117,6 +118,10 @@ def lib():
     ecfg = ctypes.POINTER(EulerConfig)
     L.lsc_euler_create.argtypes = [ecfg, ctypes.POINTER(vp)]
     L.lsc_euler_destroy.argtypes = [vp]
+    L.lsc_eos_table_read.argtypes = [ctypes.c_char_p, dp, dp, dp, dp]
+    L.lsc_euler_set_eos_table.argtypes = [vp, dp, dp, dp, dp]
+    L.lsc_euler_tabeos_initial_condition.argtypes = [ecfg, dp, dp, dp, dp]
+    L.lsc_euler_tabeos_write_dat.argtypes = [ecfg, dp, ctypes.c_char_p, dp, dp, dp]
     L.lsc_euler_local_nx.argtypes = [vp]
     L.lsc_euler_local_i0.argtypes = [vp]
     L.lsc_euler_comm_init.argtypes = [vp, vp]

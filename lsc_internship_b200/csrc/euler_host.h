@@ -7,4 +7,10 @@ void euler_slab_range(const lsc_euler_config& c, int& b0, int& b1);
 void euler_initial_condition(const lsc_euler_config& c, int problem, double* aos);
 void euler_fill_ghost_ring(const lsc_euler_config& c, double* a);
 int euler_write_dat(const lsc_euler_config& c, const double* a, const char* path, int blank_line_per_row);
+// tabulated EoS (MHD_codes/TabEoS.cpp): table file reader, IC, .dat writer
+int eos_table_read(const char* path, double* dens, double* pres, double* sound, double* en);
+void tabeos_initial_condition(const lsc_euler_config& c, const double* dens, const double* pres, const double* en,
+                              double* aos);
+int tabeos_write_dat(const lsc_euler_config& c, const double* a, const char* path, const double* dens,
+                     const double* pres, const double* en);
 }  // namespace lsc

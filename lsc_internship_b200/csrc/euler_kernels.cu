@@ -28,20 +28,32 @@ __device__ __forceinline__ void eload(const double* __restrict__ base, size_t pl
 // x sweep.  Ghost half states are boundary images of interior half states (S:297-298): periodic ones equal a
 // reconstruction from the ghost columns; transmissive (G:199-215) ones copy the first / last interior cell.
 // ---------------------------------------------------------------------------------------------------------
-template <class D>
-__device__ __noinline__ void euler_x_halfstates_global(D& dv, const GridDims g, const EulerParams p,
+template <class D, class EOS>
+__device__ __noinline__ void euler_x_halfstates_global(D& dv, const EOS eos, const GridDims g, const EulerParams p,
                                                        const double* __restrict__ cur, int i, int j,
                                                        double (&hL)[NE], double (&hR)[NE]) {
     double um[NE], u0[NE], up[NE];
     eload(cur, g.plane, cell_index(g, i - 1, j), um);
     eload(cur, g.plane, cell_index(g, i, j), u0);
     eload(cur, g.plane, cell_index(g, i + 1, j), up);
-    euler_halfstates<0>(dv, um, u0, up, p.gm1, p.cm, p.cp, p.hdtdx, hL, hR);
+    euler_halfstates<0>(dv, um, u0, up, eos, p.cm, p.cp, p.hdtdx, hL, hR);
+}
+
+// EoS policy object of a launch: ideal gas (S / G) or the table of T (EulerParams::tab_*)
+template <class EOS>
+__device__ __forceinline__ EOS make_eos(const EulerParams& p);
+template <>
+__device__ __forceinline__ IdealEos make_eos<IdealEos>(const EulerParams& p) {
+    return IdealEos{p.gm1, p.gamma};
+}
+template <>
+__device__ __forceinline__ TableEos make_eos<TableEos>(const EulerParams& p) {
+    return TableEos{p.tab_dens, p.tab_pres, p.tab_sound, p.tab_en};
 }
 
 constexpr long EFIX_GRID = 148 * 4;  // persistent grid of the fix kernels (see mhd_kernels.cu)
 
-template <class D>
+template <class D, class EOS>
 __device__ __forceinline__ bool euler_x_sweep_block(const GridDims& g, const EulerParams& p,
                                                     const double* __restrict__ cur, double* __restrict__ ubar,
                                                     const int bx, const int by, const int strip) {
@@ -52,11 +64,12 @@ __device__ __forceinline__ bool euler_x_sweep_block(const GridDims& g, const Eul
     const bool lo_image = (ia == 2) && (p.bcx_lo == BC_TRANSMISSIVE_E);
     const bool hi_image = (ib == g.nxl + 2) && (p.bcx_hi == BC_TRANSMISSIVE_E);
     D dv;
+    const EOS eos = make_eos<EOS>(p);
 
     double hRprev[NE], hLprev[NE], Fprev[NE];
     {
         double tL[NE], tR[NE];
-        euler_x_halfstates_global(dv, g, p, cur, lo_image ? 2 : ia - 1, j, tL, tR);
+        euler_x_halfstates_global(dv, eos, g, p, cur, lo_image ? 2 : ia - 1, j, tL, tR);
 #pragma unroll
         for (int k = 0; k < NE; ++k) {
             hRprev[k] = tR[k];
@@ -78,10 +91,10 @@ __device__ __forceinline__ bool euler_x_sweep_block(const GridDims& g, const Eul
                 hR[k] = hRprev[k];
             }
         } else {
-            euler_halfstates<0>(dv, uM, u0, uP, p.gm1, p.cm, p.cp, p.hdtdx, hL, hR);
+            euler_halfstates<0>(dv, uM, u0, uP, eos, p.cm, p.cp, p.hdtdx, hL, hR);
         }
         double F[NE];
-        euler_force<0>(dv, hRprev, hL, p.gm1, p.hdtdx, p.hdxdt, F);  // interface c-1/2, S:302
+        euler_force<0>(dv, hRprev, hL, eos, p.hdtdx, p.hdxdt, F);  // interface c-1/2, S:302
         if (c > ia) {
             const size_t o = cell_index(g, c - 1, j);
 #pragma unroll
@@ -100,17 +113,18 @@ __device__ __forceinline__ bool euler_x_sweep_block(const GridDims& g, const Eul
     return dv.bad();
 }
 
-template <class D>
+template <class D, class EOS>
 __global__ void __launch_bounds__(128, 4) euler_x_sweep_kernel(const GridDims g, const EulerParams p,
                                                                const double* __restrict__ cur,
                                                                double* __restrict__ ubar,
                                                                unsigned long long* __restrict__ status,
                                                                unsigned* __restrict__ fix_list, const int strip) {
-    const bool bad = euler_x_sweep_block<D>(g, p, cur, ubar, blockIdx.x, blockIdx.y, strip);
+    const bool bad = euler_x_sweep_block<D, EOS>(g, p, cur, ubar, blockIdx.x, blockIdx.y, strip);
     if (__syncthreads_or(bad) && threadIdx.x == 0)
         fix_list[atomicAdd(status + 1, 1ull)] = blockIdx.y * gridDim.x + blockIdx.x;
 }
 
+template <class EOS>
 __global__ void __launch_bounds__(128) euler_x_sweep_fix_kernel(const GridDims g, const EulerParams p,
                                                                 const double* __restrict__ cur,
                                                                 double* __restrict__ ubar,
@@ -120,7 +134,7 @@ __global__ void __launch_bounds__(128) euler_x_sweep_fix_kernel(const GridDims g
     const unsigned long long count = status[1];
     for (unsigned long long q = blockIdx.x; q < count; q += gridDim.x) {
         const unsigned bid = fix_list[q];
-        euler_x_sweep_block<IeeeDiv>(g, p, cur, ubar, (int)(bid % nbx), (int)(bid / nbx), strip);
+        euler_x_sweep_block<IeeeDiv, EOS>(g, p, cur, ubar, (int)(bid % nbx), (int)(bid / nbx), strip);
     }
 }
 
@@ -131,9 +145,14 @@ void launch_euler_x_sweep(const GridDims& g, const EulerParams& p, const double*
     int strip = 64;
     while (strip > 8 && (long)row_blocks * ((g.nxl + strip - 1) / strip) < 148L * 4 * 3) strip /= 2;
     dim3 grid(row_blocks, (g.nxl + strip - 1) / strip);
-    euler_x_sweep_kernel<EULER_FAST_POLICY><<<grid, block, 0, s>>>(g, p, cur, ubar, status, fix_list, strip);
     const unsigned nfix = (unsigned)std::min<long>(EFIX_GRID, (long)grid.x * grid.y);
-    euler_x_sweep_fix_kernel<<<nfix, block, 0, s>>>(g, p, cur, ubar, status, fix_list, strip, grid.x);
+    if (p.tab_dens) {  // tabulated EoS (T)
+        euler_x_sweep_kernel<EULER_FAST_POLICY, TableEos><<<grid, block, 0, s>>>(g, p, cur, ubar, status, fix_list, strip);
+        euler_x_sweep_fix_kernel<TableEos><<<nfix, block, 0, s>>>(g, p, cur, ubar, status, fix_list, strip, grid.x);
+    } else {
+        euler_x_sweep_kernel<EULER_FAST_POLICY, IdealEos><<<grid, block, 0, s>>>(g, p, cur, ubar, status, fix_list, strip);
+        euler_x_sweep_fix_kernel<IdealEos><<<nfix, block, 0, s>>>(g, p, cur, ubar, status, fix_list, strip, grid.x);
+    }
 }
 
 long euler_fix_list_entries(const GridDims& g) {
@@ -156,8 +175,8 @@ __device__ __forceinline__ int emap_row(int j, int ny, int bc) {
 
 // One y sweep of `in` for this thread's cell: returns the updated value of cell c in `out` (valid for
 // tid in [1, EBJ-2], c in [2, ny+1]).  sH / sF: shared exchange buffers [NE][EBJ].
-template <class D>
-__device__ __forceinline__ void euler_y_pass(D& dv, const GridDims& g, const EulerParams& p,
+template <class D, class EOS>
+__device__ __forceinline__ void euler_y_pass(D& dv, const EOS& eos, const GridDims& g, const EulerParams& p,
                                              const double* __restrict__ in, int i, int c, int tid,
                                              double (*sH)[EBJ], double (*sF)[EBJ], double (&out)[NE]) {
     const int ny = g.ny;
@@ -174,7 +193,7 @@ __device__ __forceinline__ void euler_y_pass(D& dv, const GridDims& g, const Eul
         eload(in, g.plane, cell_index(g, i, emap_row(s - 1, ny, p.bcy)), um);
         eload(in, g.plane, cell_index(g, i, emap_row(s, ny, p.bcy)), u0);
         eload(in, g.plane, cell_index(g, i, emap_row(s + 1, ny, p.bcy)), up);
-        euler_halfstates<1>(dv, um, u0, up, p.gm1, p.cm, p.cp, p.hdtdy, hB, hT);
+        euler_halfstates<1>(dv, um, u0, up, eos, p.cm, p.cp, p.hdtdy, hB, hT);
 #pragma unroll
         for (int k = 0; k < NE; ++k) sH[k][tid] = hB[k];
     }
@@ -187,7 +206,7 @@ __device__ __forceinline__ void euler_y_pass(D& dv, const GridDims& g, const Eul
         double nb[NE];
 #pragma unroll
         for (int k = 0; k < NE; ++k) nb[k] = sH[k][tid + 1];
-        euler_force<1>(dv, hT, nb, p.gm1, p.hdtdy, p.hdydt, F);  // getFluxY(top of c, bottom of c+1), S:361
+        euler_force<1>(dv, hT, nb, eos, p.hdtdy, p.hdydt, F);  // getFluxY(top of c, bottom of c+1), S:361
 #pragma unroll
         for (int k = 0; k < NE; ++k) sF[k][tid] = F[k];
     }
@@ -199,7 +218,7 @@ __device__ __forceinline__ void euler_y_pass(D& dv, const GridDims& g, const Eul
     __syncthreads();  // sH / sF are reused by the next pass
 }
 
-template <class D>
+template <class D, class EOS>
 __device__ __forceinline__ bool euler_y_sweep_block(const GridDims& g, const EulerParams& p,
                                                     const double* __restrict__ ubar, const double* __restrict__ cur,
                                                     double* __restrict__ next, const int bx, const int by,
@@ -211,11 +230,12 @@ __device__ __forceinline__ bool euler_y_sweep_block(const GridDims& g, const Eul
     const int jo = 2 + bx * (EBJ - 2);
     const int c = jo - 1 + tid;
     D dv;
+    const EOS eos = make_eos<EOS>(p);
     double A[NE], B[NE];
 #pragma unroll
     for (int k = 0; k < NE; ++k) A[k] = B[k] = 0.0;
-    euler_y_pass(dv, g, p, ubar, i, c, tid, sH, sF, A);  // XthenY: y sweep of ubar
-    euler_y_pass(dv, g, p, cur, i, c, tid, sH, sF, B);   // YthenX: y sweep of u (its x sweep is a no-op)
+    euler_y_pass(dv, eos, g, p, ubar, i, c, tid, sH, sF, A);  // XthenY: y sweep of ubar
+    euler_y_pass(dv, eos, g, p, cur, i, c, tid, sH, sF, B);   // YthenX: y sweep of u (its x sweep is a no-op)
 
     speed = 0.0;
     if (tid >= 1 && tid < EBJ - 1 && c <= g.ny + 1) {
@@ -228,7 +248,7 @@ __device__ __forceinline__ bool euler_y_sweep_block(const GridDims& g, const Eul
             un[k] = 0.5 * (A[k] + b);
             next[(size_t)k * g.plane + o] = un[k];
         }
-        const double sp = euler_cfl_speed(dv, un, p.gamma);
+        const double sp = eos.cfl_speed(dv, un);
         if (sp > speed) speed = sp;
     }
     return dv.bad();
@@ -256,7 +276,7 @@ __device__ __forceinline__ void euler_block_max(double speed, unsigned long long
     }
 }
 
-template <class D>
+template <class D, class EOS>
 __global__ void __launch_bounds__(EBJ, 4) euler_y_sweep_kernel(const GridDims g, const EulerParams p,
                                                                const double* __restrict__ ubar,
                                                                const double* __restrict__ cur,
@@ -264,7 +284,7 @@ __global__ void __launch_bounds__(EBJ, 4) euler_y_sweep_kernel(const GridDims g,
                                                                unsigned long long* __restrict__ status,
                                                                unsigned* __restrict__ fix_list) {
     double speed;
-    const bool bad = euler_y_sweep_block<D>(g, p, ubar, cur, next, blockIdx.x, blockIdx.y, speed);
+    const bool bad = euler_y_sweep_block<D, EOS>(g, p, ubar, cur, next, blockIdx.x, blockIdx.y, speed);
     if (__syncthreads_or(bad)) {
         if (threadIdx.x == 0) fix_list[atomicAdd(status + 2, 1ull)] = blockIdx.y * gridDim.x + blockIdx.x;
     } else {
@@ -272,6 +292,7 @@ __global__ void __launch_bounds__(EBJ, 4) euler_y_sweep_kernel(const GridDims g,
     }
 }
 
+template <class EOS>
 __global__ void __launch_bounds__(EBJ) euler_y_sweep_fix_kernel(const GridDims g, const EulerParams p,
                                                                 const double* __restrict__ ubar,
                                                                 const double* __restrict__ cur,
@@ -283,7 +304,7 @@ __global__ void __launch_bounds__(EBJ) euler_y_sweep_fix_kernel(const GridDims g
     for (unsigned long long q = blockIdx.x; q < count; q += gridDim.x) {
         const unsigned bid = fix_list[q];
         double speed;
-        euler_y_sweep_block<IeeeDiv>(g, p, ubar, cur, next, (int)(bid % nbx), (int)(bid / nbx), speed);
+        euler_y_sweep_block<IeeeDiv, EOS>(g, p, ubar, cur, next, (int)(bid % nbx), (int)(bid / nbx), speed);
         euler_block_max(speed, status);
         __syncthreads();
     }
@@ -293,14 +314,20 @@ void launch_euler_y_sweep(const GridDims& g, const EulerParams& p, const double*
                           unsigned long long* status, unsigned* fix_list, cudaStream_t s) {
     dim3 block(EBJ);
     dim3 grid((g.ny + (EBJ - 2) - 1) / (EBJ - 2), g.nxl);
-    euler_y_sweep_kernel<EULER_FAST_POLICY><<<grid, block, 0, s>>>(g, p, ubar, cur, next, status, fix_list);
     const unsigned nfix = (unsigned)std::min<long>(EFIX_GRID, (long)grid.x * grid.y);
-    euler_y_sweep_fix_kernel<<<nfix, block, 0, s>>>(g, p, ubar, cur, next, status, fix_list, grid.x);
+    if (p.tab_dens) {
+        euler_y_sweep_kernel<EULER_FAST_POLICY, TableEos><<<grid, block, 0, s>>>(g, p, ubar, cur, next, status, fix_list);
+        euler_y_sweep_fix_kernel<TableEos><<<nfix, block, 0, s>>>(g, p, ubar, cur, next, status, fix_list, grid.x);
+    } else {
+        euler_y_sweep_kernel<EULER_FAST_POLICY, IdealEos><<<grid, block, 0, s>>>(g, p, ubar, cur, next, status, fix_list);
+        euler_y_sweep_fix_kernel<IdealEos><<<nfix, block, 0, s>>>(g, p, ubar, cur, next, status, fix_list, grid.x);
+    }
 }
 
 // Stand-alone CFL reduction over [i_lo,i_hi] x [j_lo,j_hi]: the reference's range is [2,n+2] on the array as
 // it stands (S:173-174), ghost row/column n+2 included.
-__global__ void euler_max_speed_kernel(const GridDims g, double gamma, const double* __restrict__ u, int i_lo,
+template <class EOS>
+__global__ void euler_max_speed_kernel(const GridDims g, const EulerParams p, const double* __restrict__ u, int i_lo,
                                        int i_hi, int j_lo, int j_hi, unsigned long long* __restrict__ status) {
     const int j = j_lo + blockIdx.x * blockDim.x + threadIdx.x;
     double best = 0.0;
@@ -309,19 +336,20 @@ __global__ void euler_max_speed_kernel(const GridDims g, double gamma, const dou
             double q[NE];
             eload(u, g.plane, cell_index(g, i, j), q);
             IeeeDiv dv;
-            const double sp = euler_cfl_speed(dv, q, gamma);
+            const double sp = make_eos<EOS>(p).cfl_speed(dv, q);
             if (sp > best) best = sp;
         }
     }
     if (best > 0.0) atomicMax(status, (unsigned long long)__double_as_longlong(best));
 }
 
-void launch_euler_max_speed(const GridDims& g, double gamma, const double* u, int i_lo, int i_hi, int j_lo, int j_hi,
+void launch_euler_max_speed(const GridDims& g, const EulerParams& p, const double* u, int i_lo, int i_hi, int j_lo, int j_hi,
                             unsigned long long* status, cudaStream_t s) {
     dim3 block(128);
     const int nj = j_hi - j_lo + 1, ni = i_hi - i_lo + 1;
     dim3 grid((nj + 127) / 128, ni < 64 ? ni : 64);
-    euler_max_speed_kernel<<<grid, block, 0, s>>>(g, gamma, u, i_lo, i_hi, j_lo, j_hi, status);
+    if (p.tab_dens) euler_max_speed_kernel<TableEos><<<grid, block, 0, s>>>(g, p, u, i_lo, i_hi, j_lo, j_hi, status);
+    else euler_max_speed_kernel<IdealEos><<<grid, block, 0, s>>>(g, p, u, i_lo, i_hi, j_lo, j_hi, status);
 }
 
 // ghost columns, S:205-210 (periodic) / G:203-208 (transmissive: 0,1 <- 2 ; n+2,n+3 <- n+1)

@@ -14,6 +14,11 @@ struct EulerParams {
     double hdxdt, hdydt;  // 0.5*dx/dt, 0.5*dy/dt            (S:129, S:156)
     int bcx_lo, bcx_hi;   // physical x boundary type at each end of this slab, -1 at an inter-rank edge
     int bcy;
+    // tabulated EoS of MHD_codes/TabEoS.cpp (device pointers; tab_dens == nullptr: ideal gas, S / G)
+    const double* tab_dens;   // [500]
+    const double* tab_pres;   // [500]
+    const double* tab_sound;  // [500][500]  [pressure][density]
+    const double* tab_en;     // [500][500]
 };
 
 // status / fix_list as in mhd_kernels.cuh: [0] max speed bits, [1]/[2] x/y blocks recomputed with IEEE division
@@ -22,7 +27,7 @@ void launch_euler_x_sweep(const GridDims& g, const EulerParams& p, const double*
 void launch_euler_y_sweep(const GridDims& g, const EulerParams& p, const double* ubar, const double* cur, double* next,
                           unsigned long long* status, unsigned* fix_list, cudaStream_t s);
 long euler_fix_list_entries(const GridDims& g);
-void launch_euler_max_speed(const GridDims& g, double gamma, const double* u, int i_lo, int i_hi, int j_lo, int j_hi,
+void launch_euler_max_speed(const GridDims& g, const EulerParams& p, const double* u, int i_lo, int i_hi, int j_lo, int j_hi,
                             unsigned long long* status, cudaStream_t s);
 void launch_euler_x_ghosts(const GridDims& g, int bc_x, double* u, cudaStream_t s);
 void launch_euler_x_ghosts_side(const GridDims& g, int hi_side, double* u, cudaStream_t s);

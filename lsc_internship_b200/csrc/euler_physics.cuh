@@ -1,5 +1,6 @@
 // euler_physics.cuh -- per-cell / per-interface device arithmetic of the 2-D Euler SLIC scheme
-// (Euler_codes/SLIC_euler_2d.cpp = S; transmissive variant generaliseSLIC.cpp = G).  Bit-faithful: the
+// (Euler_codes/SLIC_euler_2d.cpp = S; transmissive variant generaliseSLIC.cpp = G; tabulated-EoS variant
+// MHD_codes/TabEoS.cpp = T).  Bit-faithful: the
 // reference's association, IEEE division (fp64_div.cuh), no FMA contraction.
 #pragma once
 #include <cuda_runtime.h>
@@ -10,16 +11,127 @@ namespace lsc {
 
 constexpr int NE = 4;  // rho, rho*vx, rho*vy, E  (S:10-17)
 
-// fluxX_def S:30-44 (DIR 0) / fluxY_def S:46-60 (DIR 1).  The reference evaluates this 16 times per cell
-// on identical inputs (S:292-293); here once per distinct state.
-template <int DIR, class D>
-__device__ __forceinline__ void euler_flux(D& dv, const double (&x)[NE], double gm1, double (&f)[NE]) {
+// ---- equation of state policies ---------------------------------------------------------------------------
+// The sweeps are templated on the EoS: IdealEos is S / G (p = (gamma-1)(E - KE)), TableEos is
+// MHD_codes/TabEoS.cpp = T (bilinear lookup in a 500x500 table, T:147-404).  Both take the state, the shared
+// reciprocal of rho and the velocities the flux function has already formed.
+
+struct IdealEos {
+    double gm1, gamma;
+
+    template <class D>
+    __device__ __forceinline__ double pressure(D&, const double (&x)[NE], const Rcp&, double vx, double vy) const {
+        const double KE = 0.5 * x[0] * (vx * vx + vy * vy);
+        return gm1 * (x[3] - KE);  // S:37-38
+    }
+
+    // Signal speed of ComputeTimeStep, S:175-184.
+    template <class D>
+    __device__ __forceinline__ double cfl_speed(D& dv, const double (&q)[NE]) const {
+        const double rho = q[0];
+        const Rcp ir = dv.rcp(rho);
+        const double vx = dv.div(q[1], ir);
+        const double vy = dv.div(q[2], ir);
+        const double speed = sqrt(vx * vx + vy * vy);
+        const double KE = 0.5 * rho * speed * speed;
+        const double p = (gamma - 1.0) * (q[3] - KE);
+        const double a = sqrt(dv.div(gamma * p, ir));
+        return speed + a;
+    }
+};
+
+constexpr int NT = 500;  // table axes, T:12
+
+struct TableEos {
+    const double* __restrict__ dens;   // [500] ascending densities (file line 10)
+    const double* __restrict__ pres;   // [500] ascending pressures (file line 12)
+    const double* __restrict__ sound;  // [500][500] sound speed, [pressure index][density index]
+    const double* __restrict__ en;     // [500][500] specific internal energy, same indexing
+
+    // The bisection every lookup of T starts with (T:257-275 etc.): brackets v in the ascending axis; point2
+    // starts at 499, or at 500 in SoundSpeed's pressure search (T:366; index 500 is never read).
+    __device__ __forceinline__ static void bracket(const double* __restrict__ a, double v, int point2, int& lo,
+                                                   int& hi) {
+        int point1 = 0;
+        while (abs(point1 - point2) > 1) {
+            const int half = (point1 + point2) / 2;
+            if (v > __ldg(a + half)) point1 = half;
+            else point2 = half;
+        }
+        lo = min(max(point1, 0), 499);  // T:271-275
+        hi = min(max(point2, 0), 499);
+    }
+
+    // ConservativeToPrimative's pressure, T:263-324.  Also returns the density bracket for SoundSpeed.
+    template <class D>
+    __device__ __forceinline__ double pressure_ex(D& dv, const double (&x)[NE], const Rcp& ir, double vx, double vy,
+                                                  int& db, int& dt, double& density_ratio) const {
+        const double rho = x[0];
+        bracket(dens, rho, 499, db, dt);
+        const double d_bottom = __ldg(dens + db), d_top = __ldg(dens + dt);
+        density_ratio = dv.div(rho - d_bottom, d_top - d_bottom);
+        if (d_bottom == d_top) density_ratio = 1;
+        const double e = dv.div(x[3] - 0.5 * rho * (vx * vx + vy * vy), ir);  // T:288
+        int point1 = 0, point2 = 499;
+        while (abs(point1 - point2) > 1) {  // T:291-299: bisection on the density-interpolated energy column
+            const int half = (point1 + point2) / 2;
+            const double eb = __ldg(en + half * NT + db), et = __ldg(en + half * NT + dt);
+            if (e > (eb + density_ratio * (et - eb))) point1 = half;
+            else point2 = half;
+        }
+        const int pt = point2, pb = point1;  // captured before the (no-op) clamps, T:303-310
+        const double f_NE = __ldg(en + pt * NT + dt), f_SE = __ldg(en + pb * NT + dt);
+        const double f_SW = __ldg(en + pb * NT + db), f_NW = __ldg(en + pt * NT + db);
+        // ReverseBilinearInterpolation, T:156-163
+        const double f_x_y1 = (1 - density_ratio) * f_SW + density_ratio * f_SE;
+        const double f_x_y2 = (1 - density_ratio) * f_NW + density_ratio * f_NE;
+        double y = dv.div(e - f_x_y1, f_x_y2 - f_x_y1);
+        if (f_x_y2 == f_x_y1) y = 1;
+        const double p_bottom = __ldg(pres + pb);
+        return y * (__ldg(pres + pt) - p_bottom) + p_bottom;  // T:322
+    }
+
+    template <class D>
+    __device__ __forceinline__ double pressure(D& dv, const double (&x)[NE], const Rcp& ir, double vx, double vy) const {
+        int db, dt;
+        double ratio;
+        return pressure_ex(dv, x, ir, vx, vy, db, dt, ratio);
+    }
+
+    // ComputeTimeStep's speed, T:505-521: |v| + SoundSpeed(u) (T:330-404; its ConservativeToPrimative and density
+    // bracket repeat the ones above on identical inputs)
+    template <class D>
+    __device__ __forceinline__ double cfl_speed(D& dv, const double (&q)[NE]) const {
+        const Rcp ir = dv.rcp(q[0]);
+        const double vx = dv.div(q[1], ir);
+        const double vy = dv.div(q[2], ir);
+        const double speed = sqrt(vx * vx + vy * vy);
+        int db, dt, pb, pt;
+        double density_ratio;
+        const double p = pressure_ex(dv, q, ir, vx, vy, db, dt, density_ratio);
+        bracket(pres, p, 500, pb, pt);  // T:366
+        const double p_bottom = __ldg(pres + pb), p_top = __ldg(pres + pt);
+        double pressure_ratio = dv.div(p - p_bottom, p_top - p_bottom);
+        if (p_bottom == p_top) pressure_ratio = 1;
+        const double ss_NE = __ldg(sound + pt * NT + dt), ss_SE = __ldg(sound + pb * NT + dt);
+        const double ss_SW = __ldg(sound + pb * NT + db), ss_NW = __ldg(sound + pt * NT + db);
+        // BilinearInterpolation, T:147-153
+        const double f_x_y1 = (1 - density_ratio) * ss_SW + density_ratio * ss_SE;
+        const double f_x_y2 = (1 - density_ratio) * ss_NW + density_ratio * ss_NE;
+        const double sound_speed = (1 - pressure_ratio) * f_x_y1 + pressure_ratio * f_x_y2;
+        return speed + sound_speed;
+    }
+};
+
+// fluxX_def S:30-44 / T:408-422 (DIR 0), fluxY_def S:46-60 / T:424-438 (DIR 1).  The reference evaluates this 16
+// times per cell on identical inputs (S:292-293); here once per distinct state.
+template <int DIR, class D, class EOS>
+__device__ __forceinline__ void euler_flux(D& dv, const double (&x)[NE], const EOS& eos, double (&f)[NE]) {
     const double rho = x[0];
     const Rcp ir = dv.rcp(x[0]);
     const double vx = dv.div(x[1], ir);
     const double vy = dv.div(x[2], ir);
-    const double KE = 0.5 * rho * (vx * vx + vy * vy);
-    const double p = gm1 * (x[3] - KE);
+    const double p = eos.pressure(dv, x, ir, vx, vy);
     if (DIR == 0) {
         f[0] = x[1];
         f[1] = rho * vx * vx + p;
@@ -56,15 +168,15 @@ __device__ __forceinline__ void euler_reconstruct1(D& dv, double um, double u0, 
 }
 
 // Reconstruct cell (um,u0,up) and advance both face states by half a step, S:260-296.  hdtdh = 0.5*(dt/h).
-template <int DIR, class D>
+template <int DIR, class D, class EOS>
 __device__ __forceinline__ void euler_halfstates(D& dv, const double (&um)[NE], const double (&u0)[NE],
-                                                 const double (&up)[NE], double gm1, double cm, double cp,
+                                                 const double (&up)[NE], const EOS& eos, double cm, double cp,
                                                  double hdtdh, double (&lo)[NE], double (&hi)[NE]) {
 #pragma unroll
     for (int k = 0; k < NE; ++k) euler_reconstruct1(dv, um[k], u0[k], up[k], cm, cp, lo[k], hi[k]);
     double fl[NE], fh[NE];
-    euler_flux<DIR>(dv, lo, gm1, fl);
-    euler_flux<DIR>(dv, hi, gm1, fh);
+    euler_flux<DIR>(dv, lo, eos, fl);
+    euler_flux<DIR>(dv, hi, eos, fh);
 #pragma unroll
     for (int k = 0; k < NE; ++k) {
         const double d = hdtdh * (fh[k] - fl[k]);
@@ -74,34 +186,20 @@ __device__ __forceinline__ void euler_halfstates(D& dv, const double (&um)[NE], 
 }
 
 // FORCE flux, getFluxX S:111-136 / getFluxY S:139-163.  hdtdh = 0.5*(dt/h), hhdt = 0.5*h/dt.
-template <int DIR, class D>
-__device__ __forceinline__ void euler_force(D& dv, const double (&a)[NE], const double (&b)[NE], double gm1,
+template <int DIR, class D, class EOS>
+__device__ __forceinline__ void euler_force(D& dv, const double (&a)[NE], const double (&b)[NE], const EOS& eos,
                                             double hdtdh, double hhdt, double (&F)[NE]) {
     double f1[NE], f2[NE], uh[NE], ri[NE];
-    euler_flux<DIR>(dv, a, gm1, f1);
-    euler_flux<DIR>(dv, b, gm1, f2);
+    euler_flux<DIR>(dv, a, eos, f1);
+    euler_flux<DIR>(dv, b, eos, f2);
 #pragma unroll
     for (int k = 0; k < NE; ++k) uh[k] = 0.5 * (a[k] + b[k]) - hdtdh * (f2[k] - f1[k]);
-    euler_flux<DIR>(dv, uh, gm1, ri);
+    euler_flux<DIR>(dv, uh, eos, ri);
 #pragma unroll
     for (int k = 0; k < NE; ++k) {
         const double lf = hhdt * (a[k] - b[k]) + 0.5 * (f1[k] + f2[k]);
         F[k] = 0.5 * (lf + ri[k]);
     }
-}
-
-// Signal speed of ComputeTimeStep, S:175-184.
-template <class D>
-__device__ __forceinline__ double euler_cfl_speed(D& dv, const double (&q)[NE], double gamma) {
-    const double rho = q[0];
-    const Rcp ir = dv.rcp(rho);
-    const double vx = dv.div(q[1], ir);
-    const double vy = dv.div(q[2], ir);
-    const double speed = sqrt(vx * vx + vy * vy);
-    const double KE = 0.5 * rho * speed * speed;
-    const double p = (gamma - 1.0) * (q[3] - KE);
-    const double a = sqrt(dv.div(gamma * p, ir));
-    return speed + a;
 }
 
 }  // namespace lsc

@@ -34,6 +34,8 @@ struct lsc_euler_ctx {
     bool uploaded = false;
     bool profiling = false;
     std::vector<cudaEvent_t> prof_events;
+    double* d_table = nullptr;         // tabulated EoS: dens[500] pres[500] sound[500*500] energies[500*500]
+    std::vector<double> h_table;       // host copy (IC, .dat output)
     lsc::Comm* comm = nullptr;         // NCCL mode (one process per GPU)
     bool in_group = false;             // driven by lsc_euler_group_step
     cudaEvent_t halo_event = nullptr;  // "new u complete" marker for neighbours in a group
@@ -42,6 +44,21 @@ struct lsc_euler_ctx {
 namespace {
 
 int kernel_bc(int bc) { return bc == LSC_BC_PERIODIC ? lsc::BC_PERIODIC : lsc::BC_TRANSMISSIVE_E; }
+
+constexpr size_t TAB_N = 500, TAB_DOUBLES = 2 * TAB_N + 2 * TAB_N * TAB_N;
+
+// EoS part of the kernel parameters: ideal gas, or the table once lsc_euler_set_eos_table was called
+void fill_eos(const lsc_euler_ctx* c, lsc::EulerParams& p) {
+    p.gamma = c->cfg.gamma;
+    p.gm1 = c->cfg.gamma - 1;
+    p.tab_dens = p.tab_pres = p.tab_sound = p.tab_en = nullptr;
+    if (c->d_table) {
+        p.tab_dens = c->d_table;
+        p.tab_pres = c->d_table + TAB_N;
+        p.tab_sound = c->d_table + 2 * TAB_N;
+        p.tab_en = c->d_table + 2 * TAB_N + TAB_N * TAB_N;
+    }
+}
 
 int e_read_status(lsc_euler_ctx* c) {
     LSC_CUDA_TRY(cudaMemcpyAsync(c->h_status, c->d_status, 32, cudaMemcpyDeviceToHost, c->stream));
@@ -125,8 +142,7 @@ int e_step_launch(lsc_euler_ctx* c) {
     c->dt = dt;
     c->t += dt;  // S:602
     lsc::EulerParams p{};
-    p.gamma = c->cfg.gamma;
-    p.gm1 = c->cfg.gamma - 1;
+    fill_eos(c, p);
     p.cm = 0.5 * (1 + c->cfg.omega);
     p.cp = 0.5 * (1 - c->cfg.omega);
     p.dtdx = dt / c->dx;
@@ -319,6 +335,7 @@ int lsc_euler_destroy(lsc_euler_ctx* c) {
     if (c->d_status) cudaFree(c->d_status);
     if (c->d_fix) cudaFree(c->d_fix);
     if (c->h_status) cudaFreeHost(c->h_status);
+    if (c->d_table) cudaFree(c->d_table);
     if (c->comm) lsc::comm_destroy(c->comm);
     if (c->halo_event) cudaEventDestroy(c->halo_event);
     for (auto e : c->prof_events) cudaEventDestroy(e);
@@ -330,8 +347,66 @@ int lsc_euler_destroy(lsc_euler_ctx* c) {
 int lsc_euler_initial_condition(const lsc_euler_config* cfg, int problem, double* aos) {
     if (!cfg || !aos) return lsc_fail(LSC_EINVAL, "null argument");
     if (problem < LSC_EULER_IC_ORSZAG_TANG || problem > LSC_EULER_IC_CYLINDER)
-        return lsc_fail(LSC_EINVAL, "unknown problem %d", problem);
+        return lsc_fail(LSC_EINVAL, "unknown problem %d (the table IC goes through lsc_euler_tabeos_initial_condition)",
+                        problem);
     lsc::euler_initial_condition(*cfg, problem, aos);
+    return LSC_OK;
+}
+
+int lsc_eos_table_read(const char* path, double* densities, double* pressures, double* sound_speeds,
+                       double* energies) {
+    if (!path || !densities || !pressures || !sound_speeds || !energies) return lsc_fail(LSC_EINVAL, "null argument");
+    const int bad = lsc::eos_table_read(path, densities, pressures, sound_speeds, energies);
+    if (bad < 0) return lsc_fail(LSC_EINVAL, "cannot open %s", path);
+    if (bad > 0) return lsc_fail(LSC_EINVAL, "%s: line %d does not hold the 500 values the table layout needs", path, bad);
+    return LSC_OK;
+}
+
+int lsc_euler_set_eos_table(lsc_euler_ctx* c, const double* densities, const double* pressures,
+                            const double* sound_speeds, const double* energies) {
+    if (!c) return lsc_fail(LSC_EINVAL, "null argument");
+    LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
+    if (!densities) {  // back to the ideal gas of S / G
+        if (c->d_table) cudaFree(c->d_table);
+        c->d_table = nullptr;
+        c->h_table.clear();
+        return LSC_OK;
+    }
+    if (!pressures || !sound_speeds || !energies) return lsc_fail(LSC_EINVAL, "null table");
+    for (size_t k = 1; k < TAB_N; ++k)
+        if (!(densities[k] > densities[k - 1]) || !(pressures[k] > pressures[k - 1]))
+            return lsc_fail(LSC_EINVAL, "table axes must be strictly ascending (entry %zu)", k);
+    try {
+        c->h_table.resize(TAB_DOUBLES);
+    } catch (...) {
+        return lsc_fail(LSC_ENOMEM, "host allocation failed");
+    }
+    double* t = c->h_table.data();
+    std::memcpy(t, densities, TAB_N * sizeof(double));
+    std::memcpy(t + TAB_N, pressures, TAB_N * sizeof(double));
+    std::memcpy(t + 2 * TAB_N, sound_speeds, TAB_N * TAB_N * sizeof(double));
+    std::memcpy(t + 2 * TAB_N + TAB_N * TAB_N, energies, TAB_N * TAB_N * sizeof(double));
+    if (!c->d_table && cudaMalloc(&c->d_table, TAB_DOUBLES * sizeof(double)) != cudaSuccess) {
+        cudaGetLastError();
+        c->d_table = nullptr;
+        return lsc_fail(LSC_ENOMEM, "device allocation of the EoS table failed");
+    }
+    LSC_CUDA_TRY(cudaMemcpy(c->d_table, t, TAB_DOUBLES * sizeof(double), cudaMemcpyHostToDevice));
+    return LSC_OK;
+}
+
+int lsc_euler_tabeos_initial_condition(const lsc_euler_config* cfg, const double* densities, const double* pressures,
+                                       const double* energies, double* aos) {
+    if (!cfg || !densities || !pressures || !energies || !aos) return lsc_fail(LSC_EINVAL, "null argument");
+    lsc::tabeos_initial_condition(*cfg, densities, pressures, energies, aos);
+    return LSC_OK;
+}
+
+int lsc_euler_tabeos_write_dat(const lsc_euler_config* cfg, const double* aos, const char* path,
+                               const double* densities, const double* pressures, const double* energies) {
+    if (!cfg || !aos || !path || !densities || !pressures || !energies) return lsc_fail(LSC_EINVAL, "null argument");
+    if (lsc::tabeos_write_dat(*cfg, aos, path, densities, pressures, energies))
+        return lsc_fail(LSC_EINVAL, "cannot write %s", path);
     return LSC_OK;
 }
 
@@ -354,8 +429,9 @@ int lsc_euler_upload(lsc_euler_ctx* c, const double* aos) {
     LSC_CUDA_TRY(cudaMemsetAsync(c->d_status, 0, 32, c->stream));
     // (a slab's share of that range: its own interior columns, plus global column nx+2 on the last rank)
     const int i_hi = c->nxl + ((c->cfg.rank == c->cfg.nranks - 1) ? 2 : 1);
-    lsc::launch_euler_max_speed(c->g, c->cfg.gamma, c->state[c->cur], 2, i_hi, 2, c->cfg.ny + 2, c->d_status,
-                                c->stream);
+    lsc::EulerParams ep{};
+    fill_eos(c, ep);
+    lsc::launch_euler_max_speed(c->g, ep, c->state[c->cur], 2, i_hi, 2, c->cfg.ny + 2, c->d_status, c->stream);
     lsc_count_launches(1);
     LSC_CUDA_TRY(cudaGetLastError());
     if (c->cfg.nranks <= 1) {
@@ -378,6 +454,12 @@ int lsc_euler_init_problem(lsc_euler_ctx* c, int problem) {
         host.resize((size_t)(c->nxl + 4) * (c->cfg.ny + 4) * 4);
     } catch (...) {
         return lsc_fail(LSC_ENOMEM, "host allocation failed");
+    }
+    if (problem == LSC_EULER_IC_TABEOS) {
+        if (c->h_table.empty()) return lsc_fail(LSC_ESTATE, "LSC_EULER_IC_TABEOS needs lsc_euler_set_eos_table first");
+        const double* t = c->h_table.data();
+        lsc::tabeos_initial_condition(c->cfg, t, t + TAB_N, t + 2 * TAB_N + TAB_N * TAB_N, host.data());
+        return lsc_euler_upload(c, host.data());
     }
     int rc = lsc_euler_initial_condition(&c->cfg, problem, host.data());
     if (rc) return rc;

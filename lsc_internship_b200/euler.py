@@ -38,6 +38,43 @@ class SlicEuler2d:
         self.nxl = lib().lsc_euler_local_nx(self._h)
         self.i0 = lib().lsc_euler_local_i0(self._h)
 
+    # -- tabulated equation of state (MHD_codes/TabEoS.cpp = T) -----------------------------------------
+    @staticmethod
+    def read_eos_table(path):
+        """Plasma19() of T:18-133: (densities[500], pressures[500], sound_speeds[500,500], energies[500,500])."""
+        dens, pres = np.empty(500), np.empty(500)
+        sound, en = np.empty((500, 500)), np.empty((500, 500))
+        check(lib().lsc_eos_table_read(os.fsencode(path), _dp(dens), _dp(pres), _dp(sound), _dp(en)))
+        return dens, pres, sound, en
+
+    def set_eos_table(self, densities, pressures, sound_speeds, energies):
+        """Every pressure / sound speed of the sweeps now comes from the table (T:248-404); gamma is unused."""
+        self.table = tuple(np.ascontiguousarray(a, dtype=np.float64) for a in
+                           (densities, pressures, sound_speeds, energies))
+        assert self.table[0].shape == (500,) and self.table[1].shape == (500,)
+        assert self.table[2].shape == (500, 500) and self.table[3].shape == (500, 500)
+        check(lib().lsc_euler_set_eos_table(self._h, *[_dp(a) for a in self.table]))
+
+    def tabeos_initial_condition(self):
+        """IC loop of T's main() (T:912-954) as a host array."""
+        u = np.empty(self.shape, dtype=np.float64)
+        d, p, _, e = self.table
+        check(lib().lsc_euler_tabeos_initial_condition(ctypes.byref(self.cfg), _dp(d), _dp(p), _dp(e), _dp(u)))
+        return u
+
+    def write_tabeos_dat(self, u, path):
+        """T:974-999 (SLIC2d.dat through the table's ConservativeToPrimative)."""
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        d, p, _, e = self.table
+        check(lib().lsc_euler_tabeos_write_dat(ctypes.byref(self.cfg), _dp(u), os.fsencode(path), _dp(d), _dp(p), _dp(e)))
+
+    def run_tabeos(self, outdir=None, log=None):
+        """main() of TabEoS.cpp from T:959: do{}while(t < tStop), then SLIC2d.dat (T:974-999)."""
+        n = self.run_until(self.tStop, log)
+        if outdir:
+            self.write_tabeos_dat(self.download(), os.path.join(outdir, "SLIC2d.dat"))
+        return n
+
     def comm_init(self, unique_id):
         """Join the NCCL communicator of the slab decomposition (id from lsc_comm_unique_id on rank 0)."""
         buf = ctypes.create_string_buffer(bytes(unique_id), 128)

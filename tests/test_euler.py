@@ -143,6 +143,51 @@ def test_slab_decomposition_does_not_change_a_bit(bc, ic, nx, ny, P, n):
 
 
 @gpu
+@pytest.mark.parametrize("nx,ny,n", [(40, 40, 6), (33, 21, 4), (130, 70, 3)])
+def test_tabeos_cuda_matches_oracle_and_reference(nx, ny, n, tmp_path):
+    """SURVEY 8f N2 / BASELINE config 5: the sweeps with T's table EoS (ConservativeToPrimative T:248-327 in every
+    flux, SoundSpeed T:330-404 in the time step) against oracle/euler_oracle.c and, where it is built, the REAL
+    TabEoS.cpp (oracle/_ref/tabeos_ref), on the synthetic Plasma19-format table: table parsing, IC, every (t, dt)
+    and the full state, bit for bit."""
+    import lsc_internship_b200 as lsc
+    from oracle_util import parsed_eos_table, run_tabeos_ref, tabeos_ic, write_eos_table
+    path = str(tmp_path / "Plasma19_EoS.txt")
+    write_eos_table(path)
+    table = lsc.SlicEuler2d.read_eos_table(path)
+    for a, b in zip(table, parsed_eos_table()):
+        assert np.array_equal(bits(a), bits(b)), "library table parser differs from strtod of the same file"
+    cfg = euler_cfg(nx, ny, DOM, bc="transmissive")
+    u0 = tabeos_ic(cfg, table)
+    s = lsc.SlicEuler2d(nx, ny, bc="transmissive", problem="tabeos", tStop=0.012 / 10 ** 2.5)
+    s.set_eos_table(*table)
+    assert np.array_equal(bits(s.tabeos_initial_condition()), bits(u0))
+    s.init_problem()
+    assert np.array_equal(bits(s.download()), bits(u0))
+    o = OracleEuler(cfg, u0)
+    o.set_table(*table)
+    for k in range(n):
+        lo = o.step(1)[0]
+        s.step(1)
+        t, dt, _ = s.scalars()
+        assert (t, dt) == tuple(lo), f"step {k}"
+    u = s.download()
+    assert np.array_equal(bits(u), bits(o.state()[0]))
+    if have_ref("tabeos_ref"):
+        ur, lg = run_tabeos_ref(nx, ny, n)
+        assert np.array_equal(bits(u), bits(ur))
+        assert (t, dt) == tuple(lg[-1])
+    # slabs: the table path through the decomposition
+    grp = lsc.SlicEuler2dGroup(2, nxCells=nx, nyCells=ny, bc="transmissive", problem="tabeos")
+    for part in grp.parts:
+        part.set_eos_table(*table)
+    grp.init_problem()
+    grp.step(n)
+    assert np.array_equal(bits(grp.download()), bits(u))
+    grp.close()
+    s.close()
+
+
+@gpu
 def test_random_state_parity():
     import lsc_internship_b200 as lsc
     nx, ny = 90, 70
