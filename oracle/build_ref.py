@@ -204,6 +204,11 @@ def build_all():
         build_euler()
     except ImportError:
         pass
+    try:
+        from build_ref_tabeos import build_tabeos  # noqa
+        build_tabeos()
+    except ImportError:
+        pass
     return True
 
 

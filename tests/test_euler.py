@@ -188,6 +188,46 @@ def test_tabeos_cuda_matches_oracle_and_reference(nx, ny, n, tmp_path):
 
 
 @gpu
+@pytest.mark.parametrize("name", ["40x40_s6", "33x21_s4", "130x70_s3"])
+def test_tabeos_cuda_matches_reference_golden(name, tmp_path):
+    """tests/golden/tabeos_*.npz: states and (t, dt) logs written by the real TabEoS.cpp on the synthetic table"""
+    import lsc_internship_b200 as lsc
+    from oracle_util import write_eos_table
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", f"tabeos_{name}.npz"))
+    nx, ny, n = int(z["nx"]), int(z["ny"]), int(z["nsteps"])
+    path = str(tmp_path / "Plasma19_EoS.txt")
+    write_eos_table(path)
+    s = lsc.SlicEuler2d(nx, ny, bc="transmissive", problem="tabeos")
+    s.set_eos_table(*lsc.SlicEuler2d.read_eos_table(path))
+    s.init_problem()
+    for k in range(n):
+        s.step(1)
+        t, dt, _ = s.scalars()
+        assert (t, dt) == tuple(z["log"][k]), f"step {k}"
+    assert np.array_equal(bits(s.download()), bits(z["u"]))
+    s.close()
+
+
+@gpu
+def test_tab_eos_driver_is_a_drop_in(tmp_path):
+    """drivers/tab_eos run like the reference program (table in the working directory): the same 't = .. dt = ..'
+    lines and a byte-identical SLIC2d.dat as the real TabEoS.cpp produced (tests/golden/tabeos_program_48x40.npz)."""
+    import subprocess
+    from oracle_util import write_eos_table
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "drivers", "_bin", "tab_eos")
+    if not os.path.exists(exe):
+        pytest.skip("drivers/_bin/tab_eos not built")
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "tabeos_program_48x40.npz"))
+    write_eos_table(str(tmp_path / "Plasma19_EoS.txt"))
+    r = subprocess.run([exe, "--nx", "48", "--ny", "40"], cwd=tmp_path, capture_output=True, text=True, check=True)
+    ref_lines = bytes(z["stdout"]).decode().splitlines()
+    mine = r.stdout.splitlines()
+    assert mine[0] == "finished loop!"
+    assert mine[1:] == [ln for ln in ref_lines if ln.startswith("t = ")]
+    assert (tmp_path / "SLIC2d.dat").read_bytes() == bytes(z["dat"])
+
+
+@gpu
 def test_random_state_parity():
     import lsc_internship_b200 as lsc
     nx, ny = 90, 70
