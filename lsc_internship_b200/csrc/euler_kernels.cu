@@ -29,14 +29,16 @@ __device__ __forceinline__ void eload(const double* __restrict__ base, size_t pl
 // reconstruction from the ghost columns; transmissive (G:199-215) ones copy the first / last interior cell.
 // ---------------------------------------------------------------------------------------------------------
 template <class D, class EOS>
-__device__ __noinline__ void euler_x_halfstates_global(D& dv, const EOS eos, const GridDims g, const EulerParams p,
+__device__ __noinline__ D euler_x_halfstates_global(const EOS eos, const GridDims g, const EulerParams p,
                                                        const double* __restrict__ cur, int i, int j,
                                                        double (&hL)[NE], double (&hR)[NE]) {
+    D dv;  // own guard state, handed back by value (see FastDiv::absorb)
     double um[NE], u0[NE], up[NE];
     eload(cur, g.plane, cell_index(g, i - 1, j), um);
     eload(cur, g.plane, cell_index(g, i, j), u0);
     eload(cur, g.plane, cell_index(g, i + 1, j), up);
     euler_halfstates<0>(dv, um, u0, up, eos, p.cm, p.cp, p.hdtdx, hL, hR);
+    return dv;
 }
 
 // EoS policy object of a launch: ideal gas (S / G) or the table of T (EulerParams::tab_*)
@@ -69,7 +71,7 @@ __device__ __forceinline__ bool euler_x_sweep_block(const GridDims& g, const Eul
     double hRprev[NE], hLprev[NE], Fprev[NE];
     {
         double tL[NE], tR[NE];
-        euler_x_halfstates_global(dv, eos, g, p, cur, lo_image ? 2 : ia - 1, j, tL, tR);
+        dv.absorb(euler_x_halfstates_global<D>(eos, g, p, cur, lo_image ? 2 : ia - 1, j, tL, tR));
 #pragma unroll
         for (int k = 0; k < NE; ++k) {
             hRprev[k] = tR[k];

@@ -94,10 +94,11 @@ constexpr long FIX_GRID = 148 * 4;  // persistent grid of the fix kernels
 // Half-step face states of cell i computed straight from global memory (strip warm-up and the
 // non-periodic boundary images of MUSCL_NEW.cpp:878-879).
 template <class D>
-__device__ __noinline__ void x_halfstates_global(D& dv, const GridDims g, const SweepParams p,
+__device__ __noinline__ D x_halfstates_global(const GridDims g, const SweepParams p,
                                                  const double* __restrict__ cur,
                                                  const double* __restrict__ prev, int i, int j,
                                                  double (&hL)[NV], double (&hR)[NV]) {
+    D dv;  // own guard state, handed back by value (see FastDiv::absorb)
     double um[NV], u0[NV], up[NV], pm[NV], p0[NV], pp[NV];
     load_cell(cur, g.plane, cell_index(g, i - 1, j), um);
     load_cell(cur, g.plane, cell_index(g, i, j), u0);
@@ -115,6 +116,7 @@ __device__ __noinline__ void x_halfstates_global(D& dv, const GridDims g, const 
 #pragma unroll
     for (int k = 0; k < NV; ++k) reconstruct1(dv, pm[k], p0[k], pp[k], um[k], u0[k], up[k], hL[k], hR[k]);
     predictor<0>(dv, hL, hR, p.gm1, p.ch2, p.hdtdh);
+    return dv;
 }
 
 __device__ __forceinline__ void prefetch_cell_l1(const double* __restrict__ base, size_t plane, size_t idx) {
@@ -154,7 +156,7 @@ __device__ __forceinline__ bool x_sweep_block(const GridDims& g, const SweepPara
         // face state R of cell ia-1; at a transmissive wall ghost cell 1 carries the half state of
         // cell 3 (u[1] = u[3] applied to the half-step arrays, MUSCL_NEW.cpp:617-622, :878-879)
         double tL[NV], tR[NV];
-        x_halfstates_global(dv, g, p, cur, prev, lo_image ? 3 : ia - 1, j, tL, tR);
+        dv.absorb(x_halfstates_global<D>(g, p, cur, prev, lo_image ? 3 : ia - 1, j, tL, tR));
 #pragma unroll
         for (int k = 0; k < NV; ++k) hRprev[k] = tR[k];
         double uM[NV];
@@ -171,7 +173,7 @@ __device__ __forceinline__ bool x_sweep_block(const GridDims& g, const SweepPara
         double hL[NV], hR[NV], P0nt[4];
         if (c == ib && hi_image) {
             double tL[NV], tR[NV];
-            x_halfstates_global(dv, g, p, cur, prev, g.nxl, j, tL, tR);  // u[nx+2] = u[nx]
+            dv.absorb(x_halfstates_global<D>(g, p, cur, prev, g.nxl, j, tL, tR));  // u[nx+2] = u[nx]
 #pragma unroll
             for (int k = 0; k < NV; ++k) {
                 hL[k] = tL[k];
@@ -321,10 +323,11 @@ __device__ __forceinline__ void load_row_cell(const double* __restrict__ base, c
 
 // Half-step face states (bottom, top) of cell j of column i straight from global memory.
 template <class D>
-__device__ __noinline__ void y_halfstates_global(D& dv, const GridDims g, const SweepParams p,
+__device__ __noinline__ D y_halfstates_global(const GridDims g, const SweepParams p,
                                                  const double* __restrict__ ubar,
                                                  const double* __restrict__ cur, int i, int j,
                                                  double (&hB)[NV], double (&hT)[NV]) {
+    D dv;
     double um[NV], u0[NV], up[NV], q[NV], pm[NV], p0[NV], pp[NV];
     load_row_cell(ubar, g, i, j - 1, p.bc_lo, um);
     load_row_cell(ubar, g, i, j, p.bc_lo, u0);
@@ -338,6 +341,7 @@ __device__ __noinline__ void y_halfstates_global(D& dv, const GridDims g, const 
 #pragma unroll
     for (int k = 0; k < NV; ++k) reconstruct1(dv, pm[k], p0[k], pp[k], um[k], u0[k], up[k], hB[k], hT[k]);
     predictor<1>(dv, hB, hT, p.gm1, p.ch2, p.hdtdh);
+    return dv;
 }
 
 // One block of the y sweep at block coordinates (bx, by).  Returns this thread's sticky division flag and its
@@ -389,7 +393,7 @@ __device__ __forceinline__ bool y_sweep_block(const GridDims& g, const SweepPara
             // ghost face states are the (sign-flipped) face states of cell 3 / ny: the reference
             // applies its boundary function to the half-step arrays (MUSCL_NEW.cpp:940-941)
             double tB[NV], tT[NV];
-            y_halfstates_global(dv, g, p, ubar, cur, i, (c == 1) ? 3 : g.ny, tB, tT);
+            dv.absorb(y_halfstates_global<D>(g, p, ubar, cur, i, (c == 1) ? 3 : g.ny, tB, tT));
 #pragma unroll
             for (int k = 0; k < NV; ++k) {
                 hB[k] = tB[k];

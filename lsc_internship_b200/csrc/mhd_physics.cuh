@@ -9,6 +9,17 @@
 // distinct value is computed once, and of the two star states only the one the
 // HLLC branch selects.  Every common sub-expression that is reused is an IDENTICAL
 // IEEE expression on identical inputs, so results are bit-identical.
+//
+// Exact scalings.  Multiplying by 0.5, 0.25 or 4 is exact in binary floating point (no rounding unless the
+// result is subnormal), so fl(0.5*a + 0.5*b) = 0.5*fl(a+b), fl(fl(0.5*x)*y) = 0.5*fl(x*y) and
+// fl(c - fl(0.5*w)) = fma(-0.5, w, c): where the reference multiplies by such a constant right before an
+// addition, the pair is issued as ONE explicit __fma_rn with the constant as multiplier (scaled_add below).
+// That is not a contraction of the reference's arithmetic -- the product is exact, the single rounding is the
+// reference's rounding of the sum -- and it removes ~55 of ~815 fp64 instructions per cell and sweep.  The
+// identity needs the scaled intermediate to be normal; a quantity below 2^-1021 that is not an exact zero
+// reaches these expressions only through operands the division guards already flag (fp64_div.cuh: nonzero
+// dividends below 2^-500), and flagged blocks are recomputed by the IeeeDiv instantiation of the same code, in
+// which the identity holds for the same reason.
 #pragma once
 #include <cuda_runtime.h>
 
@@ -16,6 +27,9 @@
 #include "mhd_kernels.cuh"
 
 namespace lsc {
+
+// fl(c + k*w) for k = +-0.5, +-0.25, +-4: the exact product k*w and the addition's single rounding
+__device__ __forceinline__ double scaled_add(double k, double w, double c) { return __fma_rn(k, w, c); }
 
 // std::min / std::max as libstdc++ defines them (first argument on ties / unordered)
 __device__ __forceinline__ double std_min(double a, double b) { return (b < a) ? b : a; }
@@ -25,7 +39,7 @@ __device__ __forceinline__ double std_max(double a, double b) { return (a < b) ?
 // MUSCL_NEW.cpp:22-34 (ConservativeToPrimitive); v0,v5..v8 are copies of u.
 struct Prim {
     double vx, vy, vz, p;
-    double ke;  // 0.5*rho*(vx*vx+vy*vy+vz*vz) as it appears in the pressure expression
+    double kw;  // rho*(vx*vx+vy*vy+vz*vz): twice the kinetic term 0.5*rho*(...) of the pressure expression
     Rcp irho;  // shared refined reciprocal of the density (fp64_div.cuh)
 };
 
@@ -36,8 +50,9 @@ __device__ __forceinline__ Prim c2p(D& dv, const double (&u)[NV], double gm1) {
     q.vx = dv.div(u[1], q.irho);
     q.vy = dv.div(u[2], q.irho);
     q.vz = dv.div(u[3], q.irho);
-    q.ke = 0.5 * u[0] * (q.vx * q.vx + q.vy * q.vy + q.vz * q.vz);
-    q.p = (u[4] - q.ke - 0.5 * (u[5] * u[5] + u[6] * u[6] + u[7] * u[7])) * gm1;
+    // v4 = (u4 - 0.5*v0*(v.v) - 0.5*(B.B))*(gamma-1), MUSCL_NEW.cpp:29-31: 0.5*v0*(v.v) = 0.5*fl(v0*(v.v)) exactly
+    q.kw = u[0] * (q.vx * q.vx + q.vy * q.vy + q.vz * q.vz);
+    q.p = scaled_add(-0.5, u[5] * u[5] + u[6] * u[6] + u[7] * u[7], scaled_add(-0.5, q.kw, u[4])) * gm1;
     return q;
 }
 
@@ -58,10 +73,10 @@ __device__ __forceinline__ void flux_from_prim(const double (&u)[NV], const Prim
     if (DIR == 0) {
         const double rvx = u[0] * q.vx;
         f[0] = u[1];
-        f[1] = rvx * q.vx + q.p + 0.5 * B2 - u[5] * u[5];
+        f[1] = scaled_add(0.5, B2, rvx * q.vx + q.p) - u[5] * u[5];
         f[2] = rvx * q.vy - u[5] * u[6];
         f[3] = rvx * q.vz - u[5] * u[7];
-        f[4] = (u[4] + q.p + 0.5 * B2) * q.vx - vB * u[5];
+        f[4] = scaled_add(0.5, B2, u[4] + q.p) * q.vx - vB * u[5];
         f[5] = u[8];
         f[6] = u[6] * q.vx - u[5] * q.vy;
         f[7] = u[7] * q.vx - u[5] * q.vz;
@@ -71,9 +86,9 @@ __device__ __forceinline__ void flux_from_prim(const double (&u)[NV], const Prim
         const double rvy = u[0] * q.vy;
         f[0] = u[2];
         f[1] = rvx * q.vy - u[5] * u[6];
-        f[2] = rvy * q.vy + q.p + 0.5 * B2 - u[6] * u[6];
+        f[2] = scaled_add(0.5, B2, rvy * q.vy + q.p) - u[6] * u[6];
         f[3] = rvy * q.vz - u[6] * u[7];
-        f[4] = (u[4] + q.p + 0.5 * B2) * q.vy - vB * u[6];
+        f[4] = scaled_add(0.5, B2, u[4] + q.p) * q.vy - vB * u[6];
         f[5] = u[5] * q.vy - u[6] * q.vx;
         f[6] = u[8];
         f[7] = u[7] * q.vy - u[6] * q.vz;
@@ -108,9 +123,11 @@ __device__ __forceinline__ void reconstruct1(D& dv, double pm, double p0, double
     } else {
         xi = dv.div((r <= 1.0) ? 2.0 * r : 2.0, 1 + r);
     }
-    const double Delta = 0.5 * dMinus + 0.5 * dPlus;
-    lo = u0 - 0.5 * xi * Delta;
-    hi = u0 + 0.5 * xi * Delta;
+    // Delta = 0.5*dMinus + 0.5*dPlus = 0.5*S exactly; 0.5*xi*Delta = 0.25*fl(xi*S) exactly (see the header)
+    const double S = dMinus + dPlus;
+    const double T = xi * S;
+    lo = scaled_add(-0.25, T, u0);
+    hi = scaled_add(0.25, T, u0);
 }
 
 // MUSCL-Hancock predictor: both face states advanced by half a step with the flux
@@ -136,7 +153,8 @@ template <class D>
 __device__ __forceinline__ double fast_speed_sq(D& dv, const Rcp& irho, double p, double B2, double Bn, double gamma) {
     const double cs2 = dv.div(gamma * p, irho);
     const double t = cs2 + dv.div(B2, irho);
-    return 0.5 * (t + sqrt(t * t - dv.div(4.0 * cs2 * Bn * Bn, irho)));
+    // 4.0*cs2*Bn*Bn/rho = 4*fl(fl(fl(cs2*Bn)*Bn)/rho) exactly
+    return 0.5 * (t + sqrt(scaled_add(-4.0, dv.div(cs2 * Bn * Bn, irho), t * t)));
 }
 
 // HLLC flux with mixed-GLM interface values.  FluxHLLCX MUSCL_NEW.cpp:483-515 /
@@ -152,8 +170,8 @@ __device__ __forceinline__ void hllc_flux(D& dv, const double (&L)[NV], const do
     constexpr int N = (DIR == 0) ? 5 : 6;  // normal field component
     // ---- mixed GLM interface values (:126-127 / :135-136)
     // inv2ch = 1.0/(2.0*ch), halfch = ch/2.0: per-step scalars, divided once on the host
-    const double BnT = 0.5 * (L[N] + R[N]) - inv2ch * (R[8] - L[8]);
-    const double psiT = 0.5 * (L[8] + R[8]) - halfch * (R[N] - L[N]);
+    const double BnT = scaled_add(0.5, L[N] + R[N], -(inv2ch * (R[8] - L[8])));
+    const double psiT = scaled_add(0.5, L[8] + R[8], -(halfch * (R[N] - L[N])));
 
     // ---- primitives of the ORIGINAL states
     const Prim qL = c2p(dv, L, gm1), qR = c2p(dv, R, gm1);
@@ -168,8 +186,8 @@ __device__ __forceinline__ void hllc_flux(D& dv, const double (&L)[NV], const do
     const double cmax = std_max(cfL, cfR);
     const double sL = std_min(vnL, vnR) - cmax;
     const double sR = std_max(vnL, vnR) + cmax;
-    const double pModL = (qL.p + 0.5 * B2L) - L[N] * L[N];
-    const double pModR = (qR.p + 0.5 * B2R) - R[N] * R[N];
+    const double pModL = scaled_add(0.5, B2L, qL.p) - L[N] * L[N];
+    const double pModR = scaled_add(0.5, B2R, qR.p) - R[N] * R[N];
     const double qS = dv.div(R[0] * vnR * (sR - vnR) - L[0] * vnL * (sL - vnL) + pModL - pModR,
                            R[0] * (sR - vnR) - L[0] * (sL - vnL));
 
@@ -197,7 +215,7 @@ __device__ __forceinline__ void hllc_flux(D& dv, const double (&L)[NV], const do
     double FS[NV];
     {
         Prim q1 = qs;  // S1[0..4] == S[0..4]: same velocities and kinetic term, new magnetic pressure
-        q1.p = (S1[4] - qs.ke - 0.5 * (S1[5] * S1[5] + S1[6] * S1[6] + S1[7] * S1[7])) * gm1;
+        q1.p = scaled_add(-0.5, S1[5] * S1[5] + S1[6] * S1[6] + S1[7] * S1[7], scaled_add(-0.5, qs.kw, S1[4])) * gm1;
         flux_from_prim<DIR>(S1, q1, ch2, FS);
     }
 
@@ -235,7 +253,7 @@ __device__ __forceinline__ void hllc_flux(D& dv, const double (&L)[NV], const do
     const double vz = qs.vz;
     // B2 with the cleaned normal component, summed in x,y,z order (:335-336 / :420-421)
     const double B2s = (DIR == 0) ? (BnT * BnT + Bt * Bt + Bz * Bz) : (Bt * Bt + BnT * BnT + Bz * Bz);
-    const double pT = qs.p + 0.5 * B2s;
+    const double pT = scaled_add(0.5, B2s, qs.p);
     const double pStar = S[0] * (ss - vn) * (qS - vn) + pT - BnT * BnT + BnS * BnS;
     const Rcp is = dv.rcp(ss - qS);  // shared by the four quotients over (s - qStar)
     const double rhoS = dv.div(S[0] * (ss - vn), is);
@@ -284,15 +302,16 @@ __device__ __forceinline__ double cfl_speed(D& dv, const double (&q)[NV], double
     const Rcp irho = dv.rcp(rho);
     const double ux = dv.div(q[1], irho), uy = dv.div(q[2], irho), uz = dv.div(q[3], irho);
     const double B2 = Bx * Bx + By * By + Bz * Bz;
-    const double ke = 0.5 * rho * (ux * ux + uy * uy + uz * uz) + 0.5 * B2;
-    const double p = (gamma - 1.0) * (q[4] - ke);
+    // ke = 0.5*rho*(u.u) + 0.5*B2 = 0.5*fl(rho*(u.u) + B2) exactly
+    const double p = (gamma - 1.0) * scaled_add(-0.5, rho * (ux * ux + uy * uy + uz * uz) + B2, q[4]);
     const double a = sqrt(dv.div(gamma * p, irho));
     const double a2 = a * a;
     const double s = a2 + dv.div(B2, irho);
     const double s2 = s * s;  // pow(s, 2)
-    const double cfx = sqrt(0.5 * (s + sqrt(s2 - dv.div(4 * a * a * Bx * Bx, irho))));
-    const double cfy = sqrt(0.5 * (s + sqrt(s2 - dv.div(4 * a * a * By * By, irho))));
-    const double cfz = sqrt(0.5 * (s + sqrt(s2 - dv.div(4 * a * a * Bz * Bz, irho))));
+    // 4*a*a*Bd*Bd/rho = 4*fl(fl(fl(a2*Bd)*Bd)/rho) exactly (4*a*a = 4*a2)
+    const double cfx = sqrt(0.5 * (s + sqrt(scaled_add(-4.0, dv.div(a2 * Bx * Bx, irho), s2))));
+    const double cfy = sqrt(0.5 * (s + sqrt(scaled_add(-4.0, dv.div(a2 * By * By, irho), s2))));
+    const double cfz = sqrt(0.5 * (s + sqrt(scaled_add(-4.0, dv.div(a2 * Bz * Bz, irho), s2))));
     return std_max(std_max(fabs(ux) + cfx, fabs(uy) + cfy), fabs(uz) + cfz);
 }
 
