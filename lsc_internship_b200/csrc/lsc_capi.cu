@@ -149,7 +149,7 @@ int lsc_mhd_create(const lsc_mhd_config* cfg, lsc_mhd_ctx** out) {
     c->dy = (cfg->y1 - cfg->y0) / cfg->ny;
     c->g.nxl = c->nxl;
     c->g.ny = cfg->ny;
-    c->g.pitch = ((cfg->ny + 4 + lsc::JOFF) + 15) / 16 * 16;
+    c->g.pitch = ((cfg->ny + 4 + lsc::JOFF) + lsc::JBLK - 1) / lsc::JBLK * lsc::JBLK;
     c->g.plane = (size_t)(c->nxl + 4) * (size_t)c->g.pitch;
     const size_t state_bytes = c->g.plane * lsc::NV * sizeof(double);
     for (int b = 0; b < 3; ++b) {
@@ -445,7 +445,8 @@ int group_halo(lsc_mhd_ctx** g, int n) {
         CUDA_TRY(cudaSetDevice(c->cfg.device));
         const int left = (r > 0) ? r - 1 : (ring ? n - 1 : -1);
         const int right = (r < n - 1) ? r + 1 : (ring ? 0 : -1);
-        const size_t bytes = 2 * (size_t)c->g.pitch * sizeof(double);
+        const size_t col = lsc::mhd_column_doubles(c->g);  // a column of the blocked layout is one contiguous run
+        const size_t bytes = 2 * col * sizeof(double);
         for (int side = 0; side < 2; ++side) {
             const int nb = side == 0 ? left : right;
             if (nb < 0) {
@@ -455,14 +456,10 @@ int group_halo(lsc_mhd_ctx** g, int n) {
             }
             lsc_mhd_ctx* o = g[nb];
             CUDA_TRY(cudaStreamWaitEvent(c->stream, o->halo_event, 0));
-            for (int k = 0; k < lsc::NV; ++k) {
-                double* dst = c->state[c->cur] + (size_t)k * c->g.plane +
-                              (side == 0 ? 0 : (size_t)(c->g.nxl + 2) * c->g.pitch);
-                // left ghost <- neighbour's last two interior columns; right ghost <- its first two
-                const double* src = o->state[o->cur] + (size_t)k * o->g.plane +
-                                    (side == 0 ? (size_t)o->g.nxl * o->g.pitch : (size_t)2 * o->g.pitch);
-                CUDA_TRY(cudaMemcpyPeerAsync(dst, c->cfg.device, src, o->cfg.device, bytes, c->stream));
-            }
+            double* dst = c->state[c->cur] + (side == 0 ? 0 : (size_t)(c->g.nxl + 2) * col);
+            // left ghost <- neighbour's last two interior columns; right ghost <- its first two
+            const double* src = o->state[o->cur] + (side == 0 ? (size_t)o->g.nxl * col : 2 * col);
+            CUDA_TRY(cudaMemcpyPeerAsync(dst, c->cfg.device, src, o->cfg.device, bytes, c->stream));
         }
     }
     CUDA_TRY(cudaGetLastError());

@@ -29,10 +29,9 @@
 
 namespace lsc {
 
-__device__ __forceinline__ void load_cell(const double* __restrict__ base, size_t plane, size_t idx,
-                                          double (&u)[NV]) {
+__device__ __forceinline__ void load_cell(const double* __restrict__ base, size_t idx, double (&u)[NV]) {
 #pragma unroll
-    for (int k = 0; k < NV; ++k) u[k] = __ldg(base + (size_t)k * plane + idx);
+    for (int k = 0; k < NV; ++k) u[k] = __ldg(base + idx + k * MHD_KSTR);
 }
 
 __device__ __forceinline__ void atomic_max_nonneg(unsigned long long* addr, double v) {
@@ -100,9 +99,9 @@ __device__ __noinline__ D x_halfstates_global(const GridDims g, const SweepParam
                                                  double (&hL)[NV], double (&hR)[NV]) {
     D dv;  // own guard state, handed back by value (see FastDiv::absorb)
     double um[NV], u0[NV], up[NV], pm[NV], p0[NV], pp[NV];
-    load_cell(cur, g.plane, cell_index(g, i - 1, j), um);
-    load_cell(cur, g.plane, cell_index(g, i, j), u0);
-    load_cell(cur, g.plane, cell_index(g, i + 1, j), up);
+    load_cell(cur, mhd_index(g, i - 1, j), um);
+    load_cell(cur, mhd_index(g, i, j), u0);
+    load_cell(cur, mhd_index(g, i + 1, j), up);
     c2p_full(dv, um, p.gm1, pm);
     c2p_full(dv, u0, p.gm1, p0);
     if (p.first_step) {
@@ -110,7 +109,7 @@ __device__ __noinline__ D x_halfstates_global(const GridDims g, const SweepParam
         for (int k = 0; k < NV; ++k) pp[k] = 0.0;
     } else {
         double q[NV];
-        load_cell(prev, g.plane, cell_index(g, i + 1, j), q);
+        load_cell(prev, mhd_index(g, i + 1, j), q);
         c2p_full(dv, q, p.gm1, pp);
     }
 #pragma unroll
@@ -119,9 +118,9 @@ __device__ __noinline__ D x_halfstates_global(const GridDims g, const SweepParam
     return dv;
 }
 
-__device__ __forceinline__ void prefetch_cell_l1(const double* __restrict__ base, size_t plane, size_t idx) {
+__device__ __forceinline__ void prefetch_cell_l1(const double* __restrict__ base, size_t idx) {
 #pragma unroll
-    for (int k = 0; k < NV; ++k) asm volatile("prefetch.global.L1 [%0];" ::"l"(base + (size_t)k * plane + idx));
+    for (int k = 0; k < NV; ++k) asm volatile("prefetch.global.L1 [%0];" ::"l"(base + idx + k * MHD_KSTR));
 }
 
 // The non-trivial primitives (vx, vy, vz, p) of a cell are carried from one column to the next; the five that
@@ -149,8 +148,8 @@ __device__ __forceinline__ bool x_sweep_block(const GridDims& g, const SweepPara
     const bool hi_image = (ib == g.nxl + 2) && (p.bc_hi == BC_TRANSMISSIVE);
     D dv;
 
-    prefetch_cell_l1(cur, g.plane, cell_index(g, ia + 1, j));
-    if (!p.first_step) prefetch_cell_l1(prev, g.plane, cell_index(g, ia + 1, j));
+    prefetch_cell_l1(cur, mhd_index(g, ia + 1, j));
+    if (!p.first_step) prefetch_cell_l1(prev, mhd_index(g, ia + 1, j));
     double hRprev[NV], Fprev[NV], PMnt[4];
     {
         // face state R of cell ia-1; at a transmissive wall ghost cell 1 carries the half state of
@@ -160,15 +159,15 @@ __device__ __forceinline__ bool x_sweep_block(const GridDims& g, const SweepPara
 #pragma unroll
         for (int k = 0; k < NV; ++k) hRprev[k] = tR[k];
         double uM[NV];
-        load_cell(cur, g.plane, cell_index(g, ia - 1, j), uM);
+        load_cell(cur, mhd_index(g, ia - 1, j), uM);
         const Prim q = c2p(dv, uM, p.gm1);
         PMnt[0] = q.vx; PMnt[1] = q.vy; PMnt[2] = q.vz; PMnt[3] = q.p;
     }
 
     for (int c = ia; c <= ib; ++c) {
         if (c + 2 <= g.nxl + 3) {
-            prefetch_cell_l1(cur, g.plane, cell_index(g, c + 2, j));
-            if (!p.first_step) prefetch_cell_l1(prev, g.plane, cell_index(g, c + 2, j));
+            prefetch_cell_l1(cur, mhd_index(g, c + 2, j));
+            if (!p.first_step) prefetch_cell_l1(prev, mhd_index(g, c + 2, j));
         }
         double hL[NV], hR[NV], P0nt[4];
         if (c == ib && hi_image) {
@@ -183,15 +182,15 @@ __device__ __forceinline__ bool x_sweep_block(const GridDims& g, const SweepPara
             for (int k = 0; k < 4; ++k) P0nt[k] = 0.0;  // last column of the strip: not carried further
         } else {
             double uM[NV], u0[NV], uP[NV], PM[NV], P0[NV], Pp[NV];
-            load_cell(cur, g.plane, cell_index(g, c - 1, j), uM);
-            load_cell(cur, g.plane, cell_index(g, c, j), u0);
-            load_cell(cur, g.plane, cell_index(g, c + 1, j), uP);
+            load_cell(cur, mhd_index(g, c - 1, j), uM);
+            load_cell(cur, mhd_index(g, c, j), u0);
+            load_cell(cur, mhd_index(g, c + 1, j), uP);
             if (p.first_step) {
 #pragma unroll
                 for (int k = 0; k < NV; ++k) Pp[k] = 0.0;
             } else {
                 double q[NV];
-                load_cell(prev, g.plane, cell_index(g, c + 1, j), q);
+                load_cell(prev, mhd_index(g, c + 1, j), q);
                 c2p_full(dv, q, p.gm1, Pp);
             }
             {
@@ -210,12 +209,12 @@ __device__ __forceinline__ bool x_sweep_block(const GridDims& g, const SweepPara
         hllc_flux<0>(dv, hRprev, hL, p.gamma, p.gm1, p.ch, p.ch2, p.inv2ch, p.halfch, F);
         if (c > ia) {
             // uBar[c-1] = u[c-1] - (dt/dx)(F[c-1/2] - F[c-3/2])   MUSCL_NEW.cpp:891; psi damping :900
-            const size_t o = cell_index(g, c - 1, j);
+            const size_t o = mhd_index(g, c - 1, j);
 #pragma unroll
             for (int k = 0; k < NV; ++k) {
-                double v = __ldg(cur + (size_t)k * g.plane + o) - p.dtdh * (F[k] - Fprev[k]);
+                double v = __ldg(cur + o + k * MHD_KSTR) - p.dtdh * (F[k] - Fprev[k]);
                 if (k == 8) v = v * p.psi_factor;
-                ubar[(size_t)k * g.plane + o] = v;
+                ubar[o + k * MHD_KSTR] = v;
             }
         }
 #pragma unroll
@@ -314,7 +313,7 @@ __device__ __forceinline__ void load_row_cell(const double* __restrict__ base, c
                                               int bc, double (&u)[NV]) {
     bool flip;
     const int js = map_row(j, g.ny, bc, flip);
-    load_cell(base, g.plane, cell_index(g, i, js), u);
+    load_cell(base, mhd_index(g, i, js), u);
     if (flip) {
         u[2] = -u[2];
         u[6] = -u[6];
@@ -437,13 +436,13 @@ __device__ __forceinline__ bool y_sweep_block(const GridDims& g, const SweepPara
     double un[NV];
     if (updates) {
         // u^{n+1} = uBar - (dt/dy)(F[j] - F[j-1])  MUSCL_NEW.cpp:953; psi damping :963
-        const size_t o = cell_index(g, i, c);
+        const size_t o = mhd_index(g, i, c);
 #pragma unroll
         for (int k = 0; k < NV; ++k) {
             double v = ub[k] - p.dtdh * (F[k] - sP[k][tid - 1]);
             if (k == 8) v = v * p.psi_factor;
             un[k] = v;
-            next[(size_t)k * g.plane + o] = v;
+            next[o + k * MHD_KSTR] = v;
         }
     }
     // Signal speed of the new state for the next step's CFL condition (MUSCL_NEW.cpp:75-111).  Only the global
@@ -533,9 +532,9 @@ __global__ void x_ghost_kernel(const GridDims g, int bc_x, double* __restrict__ 
     } else {
         src[0] = 2; src[1] = 3; src[2] = nx; src[3] = nx + 1;
     }
-    double* pl = u + (size_t)k * g.plane;
+    double* pl = u + k * MHD_KSTR;
 #pragma unroll
-    for (int q = 0; q < 4; ++q) pl[cell_index(g, dst[q], j)] = pl[cell_index(g, src[q], j)];
+    for (int q = 0; q < 4; ++q) pl[mhd_index(g, dst[q], j)] = pl[mhd_index(g, src[q], j)];
 }
 
 void launch_x_ghosts(const GridDims& g, int bc_x, double* u, cudaStream_t s) {
@@ -548,14 +547,14 @@ void launch_x_ghosts(const GridDims& g, int bc_x, double* u, cudaStream_t s) {
 __global__ void x_ghost_side_kernel(const GridDims g, int hi_side, double* __restrict__ u) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= g.ny + 4) return;
-    double* pl = u + (size_t)blockIdx.y * g.plane;
+    double* pl = u + blockIdx.y * MHD_KSTR;
     const int nx = g.nxl;
     if (hi_side) {
-        pl[cell_index(g, nx + 2, j)] = pl[cell_index(g, nx, j)];
-        pl[cell_index(g, nx + 3, j)] = pl[cell_index(g, nx + 1, j)];
+        pl[mhd_index(g, nx + 2, j)] = pl[mhd_index(g, nx, j)];
+        pl[mhd_index(g, nx + 3, j)] = pl[mhd_index(g, nx + 1, j)];
     } else {
-        pl[cell_index(g, 0, j)] = pl[cell_index(g, 2, j)];
-        pl[cell_index(g, 1, j)] = pl[cell_index(g, 3, j)];
+        pl[mhd_index(g, 0, j)] = pl[mhd_index(g, 2, j)];
+        pl[mhd_index(g, 1, j)] = pl[mhd_index(g, 3, j)];
     }
 }
 
@@ -574,7 +573,7 @@ __global__ void max_speed_kernel(const GridDims g, double gamma, const double* _
     if (j <= j_hi) {
         for (int i = i_lo + blockIdx.y; i <= i_hi; i += gridDim.y) {
             double q[NV];
-            load_cell(u, g.plane, cell_index(g, i, j), q);
+            load_cell(u, mhd_index(g, i, j), q);
             IeeeDiv dv;  // cold kernel (once per upload): plain IEEE division
             const double sp = cfl_speed(dv, q, gamma);
             if (sp > best) best = sp;
@@ -592,7 +591,7 @@ void launch_max_speed(const GridDims& g, double gamma, const double* u, int i_lo
 }
 
 // ------------------------------------------------------------------------------------
-// Reference array-of-structures [i][j][9] <-> device planes, for `ni` columns starting at i0.
+// Reference array-of-structures [i][j][9] <-> blocked device layout, for `ni` columns starting at i0.
 // The AoS chunk pointer addresses column i0 (chunk-local), rows 0..ny+3.
 // ------------------------------------------------------------------------------------
 __global__ void aos_to_soa_kernel(const GridDims g, const double* __restrict__ aos, int i0, int ni,
@@ -607,7 +606,7 @@ __global__ void aos_to_soa_kernel(const GridDims g, const double* __restrict__ a
     __syncthreads();
     for (int t = threadIdx.x; t < nj * NV; t += blockDim.x) {
         const int k = t / nj, jj = t - k * nj;
-        soa[(size_t)k * g.plane + cell_index(g, i0 + il, jb + jj)] = tile[jj * NV + k];
+        soa[mhd_index(g, i0 + il, jb + jj) + k * MHD_KSTR] = tile[jj * NV + k];
     }
 }
 
@@ -620,7 +619,7 @@ __global__ void soa_to_aos_kernel(const GridDims g, const double* __restrict__ s
     const int nj = min(32, nrow - jb);
     for (int t = threadIdx.x; t < nj * NV; t += blockDim.x) {
         const int k = t / nj, jj = t - k * nj;
-        tile[jj * NV + k] = soa[(size_t)k * g.plane + cell_index(g, i0 + il, jb + jj)];
+        tile[jj * NV + k] = soa[mhd_index(g, i0 + il, jb + jj) + k * MHD_KSTR];
     }
     __syncthreads();
     double* dst = aos + ((size_t)il * nrow + jb) * NV;

@@ -11,24 +11,39 @@ constexpr int NV = 9;  // rho, mx, my, mz, E, Bx, By, Bz, psi  (MUSCL_NEW.cpp:11
 // Boundary-condition codes (include/lsc_b200.h mirrors these values).
 enum : int { BC_PERIODIC = 0, BC_REFLECTIVE = 1, BC_TRANSMISSIVE = 2 };
 
-// Device layout of one 9-component state: structure-of-arrays, nine fp64 planes of
-// (nxl+4) x pitch doubles.  Cell (i,j) of plane k lives at
-//     base + k*plane + i*pitch + JOFF + j
-// i = x (slow), j = y (contiguous) -- the reference's [i][j] order (MUSCL_NEW.cpp:673-674),
-// with two ghost cells per side.  JOFF = 14 and pitch % 16 == 0 put the first interior cell
-// of every column (j = 2) on a 128-byte line.
+// Device layout of one 9-component MHD state: column-major blocks of 32 rows.  Column i (x index, the slow
+// axis of the reference's [i][j] order, MUSCL_NEW.cpp:673-674) is one contiguous run of NV*pitch doubles; inside
+// it rows are grouped 32 at a time and the nine components of a group are stored one after the other:
+//     base + i*(NV*pitch) + (jj/32)*(NV*32) + k*32 + jj%32,      jj = JOFF + j
+// so a warp's 32 adjacent rows of one component are one 256-byte run (coalesced exactly like a plane), the
+// nine components of a cell sit at COMPILE-TIME offsets k*256 bytes from one address (one 64-bit address per
+// cell instead of one per value: the separate planes cost ~140 integer instructions per cell in the x sweep),
+// and the two halo columns a neighbour rank needs are ONE contiguous message.  Two ghost cells per side;
+// JOFF = 14 and pitch % 32 == 0 put the first interior row (j = 2) on a 128-byte line.
+// The 4-component Euler states (euler_kernels.cu) keep separate planes: base + k*plane + i*pitch + JOFF + j.
 constexpr int JOFF = 14;
+constexpr int JBLK = 32;  // rows per layout block
 
 struct GridDims {
     int nxl;        // interior columns held by this rank (slab along x)
     int ny;         // interior rows
-    int pitch;      // doubles between consecutive i
-    size_t plane;   // doubles between consecutive components
+    int pitch;      // padded rows per column (doubles between consecutive i of one plane)
+    size_t plane;   // (nxl+4)*pitch: doubles of one component; the component stride of the plane layout
 };
 
+// plane layout (Euler)
 __host__ __device__ inline size_t cell_index(const GridDims& g, int i, int j) {
     return (size_t)i * (size_t)g.pitch + (size_t)(JOFF + j);
 }
+
+// blocked layout (MHD): index of component 0 of cell (i,j); component k is MHD_KSTR doubles further
+constexpr size_t MHD_KSTR = JBLK;
+__host__ __device__ inline size_t mhd_index(const GridDims& g, int i, int j) {
+    const int jj = JOFF + j;
+    return (size_t)i * (size_t)(NV * g.pitch) + (size_t)((jj >> 5) * (NV * JBLK) + (jj & (JBLK - 1)));
+}
+// doubles per column / offset of column i: halo messages and ghost copies move whole columns
+__host__ __device__ inline size_t mhd_column_doubles(const GridDims& g) { return (size_t)NV * (size_t)g.pitch; }
 
 struct SweepParams {
     double gamma, gm1;
