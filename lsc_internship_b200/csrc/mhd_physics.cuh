@@ -121,7 +121,7 @@ __device__ __forceinline__ void reconstruct1(D& dv, double pm, double p0, double
     if (r <= 0) {
         xi = 0;
     } else {
-        xi = dv.div((r <= 1.0) ? 2.0 * r : 2.0, 1 + r);
+        xi = dv.div_pos((r <= 1.0) ? 2.0 * r : 2.0, 1 + r);  // r > 0 (or NaN): 0 < dividend <= 2, divisor >= 1
     }
     // Delta = 0.5*dMinus + 0.5*dPlus = 0.5*S exactly; 0.5*xi*Delta = 0.25*fl(xi*S) exactly (see the header)
     const double S = dMinus + dPlus;
