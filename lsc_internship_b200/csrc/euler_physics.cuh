@@ -1,7 +1,9 @@
 // euler_physics.cuh -- per-cell / per-interface device arithmetic of the 2-D Euler SLIC scheme
 // (Euler_codes/SLIC_euler_2d.cpp = S; transmissive variant generaliseSLIC.cpp = G; tabulated-EoS variant
 // MHD_codes/TabEoS.cpp = T).  Bit-faithful: the
-// reference's association, IEEE division (fp64_div.cuh), no FMA contraction.
+// reference's association, IEEE division (fp64_div.cuh), no FMA contraction.  Multiplications by 0.5 are exact,
+// so where the reference adds such a product the pair is issued as one explicit FMA (escaled_add; the argument
+// is the one in the header of mhd_physics.cuh).
 #pragma once
 #include <cuda_runtime.h>
 
@@ -10,6 +12,9 @@
 namespace lsc {
 
 constexpr int NE = 4;  // rho, rho*vx, rho*vy, E  (S:10-17)
+
+// fl(c + k*w) for k = +-0.5: the exact product and the addition's single rounding
+__device__ __forceinline__ double escaled_add(double k, double w, double c) { return __fma_rn(k, w, c); }
 
 // ---- equation of state policies ---------------------------------------------------------------------------
 // The sweeps are templated on the EoS: IdealEos is S / G (p = (gamma-1)(E - KE)), TableEos is
@@ -21,8 +26,8 @@ struct IdealEos {
 
     template <class D>
     __device__ __forceinline__ double pressure(D&, const double (&x)[NE], const Rcp&, double vx, double vy) const {
-        const double KE = 0.5 * x[0] * (vx * vx + vy * vy);
-        return gm1 * (x[3] - KE);  // S:37-38
+        // KE = 0.5*rho*(vx*vx+vy*vy) = 0.5*fl(rho*(...)) exactly; p = (gamma-1)*(E - KE), S:37-38
+        return gm1 * escaled_add(-0.5, x[0] * (vx * vx + vy * vy), x[3]);
     }
 
     // Signal speed of ComputeTimeStep, S:175-184.
@@ -33,8 +38,8 @@ struct IdealEos {
         const double vx = dv.div(q[1], ir);
         const double vy = dv.div(q[2], ir);
         const double speed = sqrt(vx * vx + vy * vy);
-        const double KE = 0.5 * rho * speed * speed;
-        const double p = (gamma - 1.0) * (q[3] - KE);
+        // KE = 0.5*rho*speed*speed = 0.5*fl(fl(rho*speed)*speed) exactly
+        const double p = (gamma - 1.0) * escaled_add(-0.5, rho * speed * speed, q[3]);
         const double a = sqrt(dv.div(gamma * p, ir));
         return speed + a;
     }
@@ -71,7 +76,7 @@ struct TableEos {
         const double d_bottom = __ldg(dens + db), d_top = __ldg(dens + dt);
         density_ratio = dv.div(rho - d_bottom, d_top - d_bottom);
         if (d_bottom == d_top) density_ratio = 1;
-        const double e = dv.div(x[3] - 0.5 * rho * (vx * vx + vy * vy), ir);  // T:288
+        const double e = dv.div(escaled_add(-0.5, rho * (vx * vx + vy * vy), x[3]), ir);  // T:288
         int point1 = 0, point2 = 499;
         while (abs(point1 - point2) > 1) {  // T:291-299: bisection on the density-interpolated energy column
             const int half = (point1 + point2) / 2;
@@ -161,10 +166,11 @@ __device__ __forceinline__ void euler_reconstruct1(D& dv, double um, double u0, 
     } else if (r <= 1) {
         xi = r;
     } else {
-        xi = fmin(1.0, dv.div(2.0, 1 + r));
+        xi = fmin(1.0, dv.div_pos(2.0, 1 + r));  // r > 1 (or NaN): dividend 2, divisor > 2
     }
-    lo = u0 - 0.5 * xi * Delta;
-    hi = u0 + 0.5 * xi * Delta;
+    const double T = xi * Delta;  // 0.5*xi*Delta = 0.5*fl(xi*Delta) exactly
+    lo = escaled_add(-0.5, T, u0);
+    hi = escaled_add(0.5, T, u0);
 }
 
 // Reconstruct cell (um,u0,up) and advance both face states by half a step, S:260-296.  hdtdh = 0.5*(dt/h).
@@ -193,11 +199,11 @@ __device__ __forceinline__ void euler_force(D& dv, const double (&a)[NE], const 
     euler_flux<DIR>(dv, a, eos, f1);
     euler_flux<DIR>(dv, b, eos, f2);
 #pragma unroll
-    for (int k = 0; k < NE; ++k) uh[k] = 0.5 * (a[k] + b[k]) - hdtdh * (f2[k] - f1[k]);
+    for (int k = 0; k < NE; ++k) uh[k] = escaled_add(0.5, a[k] + b[k], -(hdtdh * (f2[k] - f1[k])));
     euler_flux<DIR>(dv, uh, eos, ri);
 #pragma unroll
     for (int k = 0; k < NE; ++k) {
-        const double lf = hhdt * (a[k] - b[k]) + 0.5 * (f1[k] + f2[k]);
+        const double lf = escaled_add(0.5, f1[k] + f2[k], hhdt * (a[k] - b[k]));
         F[k] = 0.5 * (lf + ri[k]);
     }
 }

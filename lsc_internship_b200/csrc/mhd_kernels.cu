@@ -63,6 +63,19 @@ __device__ __forceinline__ void block_max_to_global(double local, unsigned long 
     }
 }
 
+// Warp-level variant for the y sweep: with the fp32 CFL filter most warps carry no candidate at all (local == 0
+// in every lane) and leave after one vote; a warp that does hold one publishes it with its own atomic -- no
+// shared memory, no block barrier.
+__device__ __forceinline__ void warp_max_to_global(double local, unsigned long long* out) {
+    if (!__any_sync(0xffffffffu, local > 0.0)) return;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double other = __shfl_xor_sync(0xffffffffu, local, o);
+        local = (other > local) ? other : local;
+    }
+    if ((threadIdx.x & 31) == 0) atomic_max_nonneg(out, local);
+}
+
 #ifndef XS_BLOCK
 #define XS_BLOCK 128
 #endif
@@ -476,7 +489,7 @@ __global__ void __launch_bounds__(BJ, YS_MINB) y_sweep_kernel(const GridDims g, 
     if (__syncthreads_or(bad)) {  // whole block is recomputed by the fix kernel; its maximum must not count
         if (threadIdx.x == 0) fix_list[atomicAdd(status + 2, 1ull)] = blockIdx.y * gridDim.x + blockIdx.x;
     } else {
-        block_max_to_global(speed, status);
+        warp_max_to_global(speed, status);
     }
 }
 
