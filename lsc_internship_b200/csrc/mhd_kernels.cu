@@ -382,23 +382,45 @@ __device__ __forceinline__ bool y_sweep_block(const GridDims& g, const SweepPara
     const int bc = p.bc_lo;      // the reference uses one y boundary type for both ends
     D dv;
 
-    for (int t = tid; t < BJ + 2; t += BJ) {
+    // Tile of BJ+2 cells (rows jo-2 .. jo+BJ-1): uBar and the primitives of u^n go to shared memory for the
+    // neighbours.  A thread fills the tile entry of its OWN cell (t = tid+1) and keeps those 18 values in
+    // registers; the two end entries are an extra pass of threads 0 and 1.
+    auto fill_tile = [&](const int t, double (&qu)[NV], double (&v)[NV]) {
         const int jt = jo - 2 + t;
-        if (jt <= g.ny + 3) {
-            double q[NV], v[NV];
-            load_row_cell(ubar, g, i, jt, bc, q);
-#pragma unroll
-            for (int k = 0; k < NV; ++k) sU[k][t] = q[k];
-            load_row_cell(cur, g, i, jt, bc, q);
-            c2p_full(dv, q, p.gm1, v);
-#pragma unroll
-            for (int k = 0; k < NV; ++k) sP[k][t] = v[k];
+        if (jt > g.ny + 3) return;
+        // interior rows map to themselves; only ghost rows go through the boundary map.  Both states of the
+        // cell share one address computation.
+        bool flip = false;
+        int js = jt;
+        if (jt < 2 || jt > g.ny + 1) js = map_row(jt, g.ny, bc, flip);
+        const size_t idx = mhd_index(g, i, js);
+        load_cell(ubar, idx, qu);
+        if (flip) {
+            qu[2] = -qu[2];
+            qu[6] = -qu[6];
         }
+#pragma unroll
+        for (int k = 0; k < NV; ++k) sU[k][t] = qu[k];
+        double q[NV];
+        load_cell(cur, idx, q);
+        if (flip) {
+            q[2] = -q[2];
+            q[6] = -q[6];
+        }
+        c2p_full(dv, q, p.gm1, v);
+#pragma unroll
+        for (int k = 0; k < NV; ++k) sP[k][t] = v[k];
+    };
+    double ub[NV], p0[NV];
+    fill_tile(tid + 1, ub, p0);
+    if (tid < 2) {
+        double qe[NV], ve[NV];
+        fill_tile(tid == 0 ? 0 : BJ + 1, qe, ve);
     }
     __syncthreads();
 
     const bool active = (c <= g.ny + 2);
-    double hB[NV], hT[NV], ub[NV];
+    double hB[NV], hT[NV];
     if (active) {
         const bool image = (bc != BC_PERIODIC) && (c == 1 || c == g.ny + 2);
         if (image) {
@@ -419,11 +441,8 @@ __device__ __forceinline__ bool y_sweep_block(const GridDims& g, const SweepPara
         } else {
             const int t = tid + 1;
 #pragma unroll
-            for (int k = 0; k < NV; ++k) {
-                ub[k] = sU[k][t];
-                reconstruct1(dv, sP[k][t - 1], sP[k][t], sP[k][t + 1], sU[k][t - 1], ub[k], sU[k][t + 1], hB[k],
-                             hT[k]);
-            }
+            for (int k = 0; k < NV; ++k)
+                reconstruct1(dv, sP[k][t - 1], p0[k], sP[k][t + 1], sU[k][t - 1], ub[k], sU[k][t + 1], hB[k], hT[k]);
             predictor<1>(dv, hB, hT, p.gm1, p.ch2, p.hdtdh);
         }
 #pragma unroll
