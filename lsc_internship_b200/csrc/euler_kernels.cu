@@ -144,8 +144,7 @@ void launch_euler_x_sweep(const GridDims& g, const EulerParams& p, const double*
                           unsigned long long* status, unsigned* fix_list, cudaStream_t s) {
     dim3 block(128);
     const int row_blocks = (g.ny + block.x - 1) / block.x;
-    int strip = 64;
-    while (strip > 8 && (long)row_blocks * ((g.nxl + strip - 1) / strip) < 148L * 4 * 3) strip /= 2;
+    const int strip = choose_x_strip(row_blocks, g.nxl, 64, 148 * 4);
     dim3 grid(row_blocks, (g.nxl + strip - 1) / strip);
     const unsigned nfix = (unsigned)std::min<long>(EFIX_GRID, (long)grid.x * grid.y);
     if (p.tab_dens) {  // tabulated EoS (T)

@@ -276,12 +276,11 @@ __global__ void __launch_bounds__(XS_BLOCK) x_sweep_fix_kernel(const GridDims g,
 
 void launch_x_sweep(const GridDims& g, const SweepParams& p, const double* u_cur, const double* u_prev,
                     double* u_bar, unsigned long long* status, unsigned* x_flags, cudaStream_t s) {
-    // strip length along i: XS_STRIP columns per thread (3 warm-up cells amortised over the strip), shortened
-    // on small grids so that the launch still fills 148 SMs x 4 resident blocks a few times over
+    // strip length along i: at most XS_STRIP columns per thread (3 warm-up cells amortised over the strip),
+    // chosen so that the blocks fill whole rounds of the 148 SMs x XS_MINB resident blocks (choose_x_strip)
     dim3 block(XS_BLOCK);
     const int row_blocks = (g.ny + block.x - 1) / block.x;
-    int strip = XS_STRIP;
-    while (strip > 8 && (long)row_blocks * ((g.nxl + strip - 1) / strip) < 148L * 4 * 3) strip /= 2;
+    const int strip = choose_x_strip(row_blocks, g.nxl, XS_STRIP, 148 * XS_MINB);
     dim3 grid(row_blocks, (g.nxl + strip - 1) / strip);
     x_sweep_kernel<MHD_FAST_POLICY><<<grid, block, 0, s>>>(g, p, u_cur, u_prev, u_bar, x_flags, strip);
     const unsigned nblocks = grid.x * grid.y;
@@ -298,8 +297,7 @@ void launch_x_sweep_relaxed(const GridDims& g, const SweepParams& p, const doubl
                             double* u_bar, unsigned* x_flags, cudaStream_t s) {
     dim3 block(XS_BLOCK);
     const int row_blocks = (g.ny + block.x - 1) / block.x;
-    int strip = XS_STRIP;
-    while (strip > 8 && (long)row_blocks * ((g.nxl + strip - 1) / strip) < 148L * 4 * 3) strip /= 2;
+    const int strip = choose_x_strip(row_blocks, g.nxl, XS_STRIP, 148 * XS_MINB);
     dim3 grid(row_blocks, (g.nxl + strip - 1) / strip);
     x_sweep_kernel<RelaxedDiv><<<grid, block, 0, s>>>(g, p, u_cur, u_prev, u_bar, x_flags, strip);
 }

@@ -45,6 +45,28 @@ __host__ __device__ inline size_t mhd_index(const GridDims& g, int i, int j) {
 // doubles per column / offset of column i: halo messages and ghost copies move whole columns
 __host__ __device__ inline size_t mhd_column_doubles(const GridDims& g) { return (size_t)NV * (size_t)g.pitch; }
 
+// Columns per thread of an x sweep.  A block runs strip+1 loop iterations after a warm-up worth about half of one;
+// all blocks of a launch cost the same, so the launch takes ceil(blocks / resident) rounds of (strip + 1.5)
+// columns.  Picks the
+// strip in [8, max_strip] that minimises that product: e.g. a 2048-column slab (16384^2 on 8 GPUs) with
+// 128-column strips is 2048 blocks = 3.46 rounds of the 592 resident blocks (the 4th round 46 % full); 90-column
+// strips make it 2944 blocks = 4.97 rounds of shorter blocks, 12 % less time.  The decomposition does not touch
+// the arithmetic (tests/test_mhd_gpu.py compares different strip lengths bit for bit).
+inline int choose_x_strip(int row_blocks, int nxl, int max_strip, int resident_blocks) {
+    long best_cost = -1;
+    int best = max_strip;
+    for (int s = 8; s <= max_strip; ++s) {
+        const long blocks = (long)row_blocks * ((nxl + s - 1) / s);
+        const long rounds = (blocks + resident_blocks - 1) / resident_blocks;
+        const long cost = rounds * (2 * s + 3);
+        if (best_cost < 0 || cost < best_cost || (cost == best_cost && s > best)) {
+            best_cost = cost;
+            best = s;
+        }
+    }
+    return best;
+}
+
 struct SweepParams {
     double gamma, gm1;
     double inv2ch, halfch;  // 1.0/(2.0*ch) and ch/2.0 (MUSCL_NEW.cpp:126-127), divided on the host
