@@ -212,9 +212,11 @@ __device__ __forceinline__ bool x_sweep_block(const GridDims& g, const SweepPara
             }
             prim_vector(uM, PMnt, PM);
             prim_vector(u0, P0nt, P0);
+            double ratio[NV];
 #pragma unroll
-            for (int k = 0; k < NV; ++k)
-                reconstruct1(dv, PM[k], P0[k], Pp[k], uM[k], u0[k], uP[k], hL[k], hR[k]);
+            for (int k = 0; k < NV; ++k) ratio[k] = limiter_ratio(dv, PM[k], P0[k], Pp[k]);
+#pragma unroll
+            for (int k = 0; k < NV; ++k) reconstruct_with_ratio(dv, ratio[k], uM[k], u0[k], uP[k], hL[k], hR[k]);
             predictor<0>(dv, hL, hR, p.gm1, p.ch2, p.hdtdh);
         }
         double F[NV];
@@ -438,9 +440,12 @@ __device__ __forceinline__ bool y_sweep_block(const GridDims& g, const SweepPara
             }
         } else {
             const int t = tid + 1;
+            double ratio[NV];
+#pragma unroll
+            for (int k = 0; k < NV; ++k) ratio[k] = limiter_ratio(dv, sP[k][t - 1], p0[k], sP[k][t + 1]);
 #pragma unroll
             for (int k = 0; k < NV; ++k)
-                reconstruct1(dv, sP[k][t - 1], p0[k], sP[k][t + 1], sU[k][t - 1], ub[k], sU[k][t + 1], hB[k], hT[k]);
+                reconstruct_with_ratio(dv, ratio[k], sU[k][t - 1], ub[k], sU[k][t + 1], hB[k], hT[k]);
             predictor<1>(dv, hB, hT, p.gm1, p.ch2, p.hdtdh);
         }
 #pragma unroll

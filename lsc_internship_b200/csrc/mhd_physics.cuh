@@ -111,10 +111,16 @@ __device__ __forceinline__ void flux_def(D& dv, const double (&u)[NV], double gm
 // monotone in the numerator, so the minimum is fl(2r/d) when r <= 1 and fl(2/d)
 // otherwise (equal at r == 1; for r = +inf the reference's fmin(NaN, 0) = 0 = 2/inf;
 // NaN r gives NaN both ways).
+// Split in two so that the sweeps can form the nine limiter ratios back to back (nine independent Newton chains
+// the scheduler can interleave) before the branchy second quotient of each component.
 template <class D>
-__device__ __forceinline__ void reconstruct1(D& dv, double pm, double p0, double pp, double um, double u0,
-                                             double up, double& lo, double& hi) {
-    const double r = dv.div(p0 - pm, (pp - p0) + 1e-8);
+__device__ __forceinline__ double limiter_ratio(D& dv, double pm, double p0, double pp) {
+    return dv.div(p0 - pm, (pp - p0) + 1e-8);
+}
+
+template <class D>
+__device__ __forceinline__ void reconstruct_with_ratio(D& dv, double r, double um, double u0, double up,
+                                                       double& lo, double& hi) {
     const double dPlus = up - u0;
     const double dMinus = u0 - um;
     double xi;
@@ -128,6 +134,12 @@ __device__ __forceinline__ void reconstruct1(D& dv, double pm, double p0, double
     const double T = xi * S;
     lo = scaled_add(-0.25, T, u0);
     hi = scaled_add(0.25, T, u0);
+}
+
+template <class D>
+__device__ __forceinline__ void reconstruct1(D& dv, double pm, double p0, double pp, double um, double u0,
+                                             double up, double& lo, double& hi) {
+    reconstruct_with_ratio(dv, limiter_ratio(dv, pm, p0, pp), um, u0, up, lo, hi);
 }
 
 // MUSCL-Hancock predictor: both face states advanced by half a step with the flux
