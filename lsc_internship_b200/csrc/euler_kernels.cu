@@ -53,6 +53,10 @@ __device__ __forceinline__ TableEos make_eos<TableEos>(const EulerParams& p) {
     return TableEos{p.tab_dens, p.tab_pres, p.tab_sound, p.tab_en};
 }
 
+#ifndef EULER_X_UNROLL
+#define EULER_X_UNROLL 2
+#endif
+constexpr int EX_UNROLL = EULER_X_UNROLL;  // copies of the march-loop body: the 20 carried doubles are renamed, not moved
 constexpr long EFIX_GRID = 148 * 4;  // persistent grid of the fix kernels (see mhd_kernels.cu)
 
 template <class D, class EOS>
@@ -84,6 +88,7 @@ __device__ __forceinline__ bool euler_x_sweep_block(const GridDims& g, const Eul
     eload(cur, g.plane, cell_index(g, ia, j), u0);
     eload(cur, g.plane, cell_index(g, ia + 1, j), uP);
 
+#pragma unroll EX_UNROLL
     for (int c = ia; c <= ib; ++c) {
         double hL[NE], hR[NE];
         if (c == ib && hi_image) {
@@ -182,9 +187,7 @@ __device__ __forceinline__ void euler_y_pass(D& dv, const EOS& eos, const GridDi
                                              double (*sH)[EBJ], double (*sF)[EBJ], double (&out)[NE]) {
     const int ny = g.ny;
     const bool active = (c <= ny + 2);
-    double hB[NE], hT[NE], u0[NE];
-#pragma unroll
-    for (int k = 0; k < NE; ++k) hB[k] = hT[k] = u0[k] = 0.0;
+    double hB[NE], hT[NE], u0[NE];  // written and read only by active threads
     if (active) {
         // ghost cells carry the half states of their boundary image: periodic -> same stencil through the wrap,
         // transmissive -> the first / last interior cell (S:356-357 with G:208-214)
@@ -201,8 +204,6 @@ __device__ __forceinline__ void euler_y_pass(D& dv, const EOS& eos, const GridDi
     __syncthreads();
     const bool has_flux = (tid < EBJ - 1) && (c <= ny + 1);
     double F[NE];
-#pragma unroll
-    for (int k = 0; k < NE; ++k) F[k] = 0.0;
     if (has_flux) {
         double nb[NE];
 #pragma unroll
@@ -232,9 +233,7 @@ __device__ __forceinline__ bool euler_y_sweep_block(const GridDims& g, const Eul
     const int c = jo - 1 + tid;
     D dv;
     const EOS eos = make_eos<EOS>(p);
-    double A[NE], B[NE];
-#pragma unroll
-    for (int k = 0; k < NE; ++k) A[k] = B[k] = 0.0;
+    double A[NE], B[NE];  // valid for the threads that update a cell (the only ones that read them)
     euler_y_pass(dv, eos, g, p, ubar, i, c, tid, sH, sF, A);  // XthenY: y sweep of ubar
     euler_y_pass(dv, eos, g, p, cur, i, c, tid, sH, sF, B);   // YthenX: y sweep of u (its x sweep is a no-op)
 
