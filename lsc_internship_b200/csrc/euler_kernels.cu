@@ -19,9 +19,11 @@
 
 namespace lsc {
 
-__device__ __forceinline__ void eload(const double* __restrict__ base, size_t plane, size_t idx, double (&u)[NE]) {
+__host__ __device__ inline size_t euler_index(const GridDims& g, int i, int j) { return blocked_index<NE>(g, i, j); }
+
+__device__ __forceinline__ void eload(const double* __restrict__ base, size_t idx, double (&u)[NE]) {
 #pragma unroll
-    for (int k = 0; k < NE; ++k) u[k] = __ldg(base + (size_t)k * plane + idx);
+    for (int k = 0; k < NE; ++k) u[k] = __ldg(base + idx + k * KSTR);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -34,9 +36,9 @@ __device__ __noinline__ D euler_x_halfstates_global(const EOS eos, const GridDim
                                                        double (&hL)[NE], double (&hR)[NE]) {
     D dv;  // own guard state, handed back by value (see FastDiv::absorb)
     double um[NE], u0[NE], up[NE];
-    eload(cur, g.plane, cell_index(g, i - 1, j), um);
-    eload(cur, g.plane, cell_index(g, i, j), u0);
-    eload(cur, g.plane, cell_index(g, i + 1, j), up);
+    eload(cur, euler_index(g, i - 1, j), um);
+    eload(cur, euler_index(g, i, j), u0);
+    eload(cur, euler_index(g, i + 1, j), up);
     euler_halfstates<0>(dv, um, u0, up, eos, p.cm, p.cp, p.hdtdx, hL, hR);
     return dv;
 }
@@ -84,9 +86,9 @@ __device__ __forceinline__ bool euler_x_sweep_block(const GridDims& g, const Eul
         }
     }
     double uM[NE], u0[NE], uP[NE];
-    eload(cur, g.plane, cell_index(g, ia - 1, j), uM);
-    eload(cur, g.plane, cell_index(g, ia, j), u0);
-    eload(cur, g.plane, cell_index(g, ia + 1, j), uP);
+    eload(cur, euler_index(g, ia - 1, j), uM);
+    eload(cur, euler_index(g, ia, j), u0);
+    eload(cur, euler_index(g, ia + 1, j), uP);
 
 #pragma unroll EX_UNROLL
     for (int c = ia; c <= ib; ++c) {
@@ -103,9 +105,9 @@ __device__ __forceinline__ bool euler_x_sweep_block(const GridDims& g, const Eul
         double F[NE];
         euler_force<0>(dv, hRprev, hL, eos, p.hdtdx, p.hdxdt, F);  // interface c-1/2, S:302
         if (c > ia) {
-            const size_t o = cell_index(g, c - 1, j);
+            const size_t o = euler_index(g, c - 1, j);
 #pragma unroll
-            for (int k = 0; k < NE; ++k) ubar[(size_t)k * g.plane + o] = uM[k] - p.dtdx * (F[k] - Fprev[k]);  // S:309
+            for (int k = 0; k < NE; ++k) ubar[o + k * KSTR] = uM[k] - p.dtdx * (F[k] - Fprev[k]);  // S:309
         }
 #pragma unroll
         for (int k = 0; k < NE; ++k) {
@@ -115,7 +117,7 @@ __device__ __forceinline__ bool euler_x_sweep_block(const GridDims& g, const Eul
             uM[k] = u0[k];
             u0[k] = uP[k];
         }
-        if (c < ib) eload(cur, g.plane, cell_index(g, c + 2, j), uP);
+        if (c < ib) eload(cur, euler_index(g, c + 2, j), uP);
     }
     return dv.bad();
 }
@@ -194,9 +196,9 @@ __device__ __forceinline__ void euler_y_pass(D& dv, const EOS& eos, const GridDi
         int s = c;
         if (p.bcy != BC_PERIODIC) s = min(max(c, 2), ny + 1);
         double um[NE], up[NE];
-        eload(in, g.plane, cell_index(g, i, emap_row(s - 1, ny, p.bcy)), um);
-        eload(in, g.plane, cell_index(g, i, emap_row(s, ny, p.bcy)), u0);
-        eload(in, g.plane, cell_index(g, i, emap_row(s + 1, ny, p.bcy)), up);
+        eload(in, euler_index(g, i, emap_row(s - 1, ny, p.bcy)), um);
+        eload(in, euler_index(g, i, emap_row(s, ny, p.bcy)), u0);
+        eload(in, euler_index(g, i, emap_row(s + 1, ny, p.bcy)), up);
         euler_halfstates<1>(dv, um, u0, up, eos, p.cm, p.cp, p.hdtdy, hB, hT);
 #pragma unroll
         for (int k = 0; k < NE; ++k) sH[k][tid] = hB[k];
@@ -240,13 +242,13 @@ __device__ __forceinline__ bool euler_y_sweep_block(const GridDims& g, const Eul
     speed = 0.0;
     if (tid >= 1 && tid < EBJ - 1 && c <= g.ny + 1) {
         double un[NE];
-        const size_t o = cell_index(g, i, c);
+        const size_t o = euler_index(g, i, c);
 #pragma unroll
         for (int k = 0; k < NE; ++k) {
             // uPlus1 = uPlus1Bar - (dt/dx)*(fluxX - fluxX) with fluxX == 0 (S:519), then the average S:612
             const double b = B[k] - p.dtdx * (0.0 - 0.0);
             un[k] = 0.5 * (A[k] + b);
-            next[(size_t)k * g.plane + o] = un[k];
+            next[o + k * KSTR] = un[k];
         }
         const double sp = eos.cfl_speed(dv, un);
         if (sp > speed) speed = sp;
@@ -334,7 +336,7 @@ __global__ void euler_max_speed_kernel(const GridDims g, const EulerParams p, co
     if (j <= j_hi) {
         for (int i = i_lo + blockIdx.y; i <= i_hi; i += gridDim.y) {
             double q[NE];
-            eload(u, g.plane, cell_index(g, i, j), q);
+            eload(u, euler_index(g, i, j), q);
             IeeeDiv dv;
             const double sp = make_eos<EOS>(p).cfl_speed(dv, q);
             if (sp > best) best = sp;
@@ -356,7 +358,7 @@ void launch_euler_max_speed(const GridDims& g, const EulerParams& p, const doubl
 __global__ void euler_x_ghost_kernel(const GridDims g, int bc_x, double* __restrict__ u) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= g.ny + 4) return;
-    double* pl = u + (size_t)blockIdx.y * g.plane;
+    double* pl = u + blockIdx.y * KSTR;
     const int nx = g.nxl;
     int src[4];
     if (bc_x == BC_PERIODIC) {
@@ -366,7 +368,7 @@ __global__ void euler_x_ghost_kernel(const GridDims g, int bc_x, double* __restr
     }
     const int dst[4] = {0, 1, nx + 2, nx + 3};
 #pragma unroll
-    for (int q = 0; q < 4; ++q) pl[cell_index(g, dst[q], j)] = pl[cell_index(g, src[q], j)];
+    for (int q = 0; q < 4; ++q) pl[euler_index(g, dst[q], j)] = pl[euler_index(g, src[q], j)];
 }
 
 void launch_euler_x_ghosts(const GridDims& g, int bc_x, double* u, cudaStream_t s) {
@@ -378,16 +380,16 @@ void launch_euler_x_ghosts(const GridDims& g, int bc_x, double* u, cudaStream_t 
 __global__ void euler_x_ghost_side_kernel(const GridDims g, int hi_side, double* __restrict__ u) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= g.ny + 4) return;
-    double* pl = u + (size_t)blockIdx.y * g.plane;
+    double* pl = u + blockIdx.y * KSTR;
     const int nx = g.nxl;
     if (hi_side) {
-        const double v = pl[cell_index(g, nx + 1, j)];
-        pl[cell_index(g, nx + 2, j)] = v;
-        pl[cell_index(g, nx + 3, j)] = v;
+        const double v = pl[euler_index(g, nx + 1, j)];
+        pl[euler_index(g, nx + 2, j)] = v;
+        pl[euler_index(g, nx + 3, j)] = v;
     } else {
-        const double v = pl[cell_index(g, 2, j)];
-        pl[cell_index(g, 0, j)] = v;
-        pl[cell_index(g, 1, j)] = v;
+        const double v = pl[euler_index(g, 2, j)];
+        pl[euler_index(g, 0, j)] = v;
+        pl[euler_index(g, 1, j)] = v;
     }
 }
 
@@ -396,7 +398,7 @@ void launch_euler_x_ghosts_side(const GridDims& g, int hi_side, double* u, cudaS
     euler_x_ghost_side_kernel<<<grid, block, 0, s>>>(g, hi_side, u);
 }
 
-// reference array-of-structures [i][j][4] <-> device planes for `ni` columns starting at i0
+// reference array-of-structures [i][j][4] <-> blocked device layout for `ni` columns starting at i0
 __global__ void euler_aos_to_soa_kernel(const GridDims g, const double* __restrict__ aos, int i0,
                                         double* __restrict__ soa) {
     __shared__ double tile[32 * NE];
@@ -407,7 +409,7 @@ __global__ void euler_aos_to_soa_kernel(const GridDims g, const double* __restri
     __syncthreads();
     for (int t = threadIdx.x; t < nj * NE; t += blockDim.x) {
         const int k = t / nj, jj = t - k * nj;
-        soa[(size_t)k * g.plane + cell_index(g, i0 + il, jb + jj)] = tile[jj * NE + k];
+        soa[euler_index(g, i0 + il, jb + jj) + k * KSTR] = tile[jj * NE + k];
     }
 }
 
@@ -418,7 +420,7 @@ __global__ void euler_soa_to_aos_kernel(const GridDims g, const double* __restri
     const int nj = min(32, nrow - jb);
     for (int t = threadIdx.x; t < nj * NE; t += blockDim.x) {
         const int k = t / nj, jj = t - k * nj;
-        tile[jj * NE + k] = soa[(size_t)k * g.plane + cell_index(g, i0 + il, jb + jj)];
+        tile[jj * NE + k] = soa[euler_index(g, i0 + il, jb + jj) + k * KSTR];
     }
     __syncthreads();
     double* dst = aos + ((size_t)il * nrow + jb) * NE;

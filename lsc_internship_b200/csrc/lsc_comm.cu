@@ -66,22 +66,17 @@ int comm_exchange_halos(Comm* c, const GridDims& g, int bc_x, double* u, cudaStr
     const bool ring = (bc_x == BC_PERIODIC);
     const int left = (c->rank > 0) ? c->rank - 1 : (ring ? c->nranks - 1 : -1);
     const int right = (c->rank < c->nranks - 1) ? c->rank + 1 : (ring ? 0 : -1);
-    // Two adjacent columns are contiguous: per plane in the Euler layout (nvar messages of 2*pitch doubles per
-    // neighbour), as ONE run of 2*NV*pitch doubles in the blocked MHD layout (mhd_kernels.cuh).
-    const bool blocked = (c->nvar == NV);
-    const int nmsg = blocked ? 1 : c->nvar;
-    const size_t col = blocked ? mhd_column_doubles(g) : (size_t)g.pitch;
+    // A column of the blocked layout (mhd_kernels.cuh) is one contiguous run of nvar*pitch doubles, so the two
+    // halo columns a neighbour needs are ONE message per direction.
+    const size_t col = column_doubles(g, c->nvar);
     const size_t n = 2 * col;
     NCCL_TRY(ncclGroupStart(), -1);
-    for (int k = 0; k < nmsg; ++k) {
-        double* pl = u + (size_t)k * g.plane;
-        // Posting order matters when left == right (two ranks on a periodic ring): NCCL matches the sends and
-        // receives of a pair in order, so "my low columns" must meet the peer's "high ghost" receive.
-        if (left >= 0) NCCL_TRY(ncclSend(pl + 2 * col, n, ncclDouble, left, c->nccl, s), -1);
-        if (right >= 0) NCCL_TRY(ncclRecv(pl + (size_t)(g.nxl + 2) * col, n, ncclDouble, right, c->nccl, s), -1);
-        if (right >= 0) NCCL_TRY(ncclSend(pl + (size_t)g.nxl * col, n, ncclDouble, right, c->nccl, s), -1);
-        if (left >= 0) NCCL_TRY(ncclRecv(pl, n, ncclDouble, left, c->nccl, s), -1);
-    }
+    // Posting order matters when left == right (two ranks on a periodic ring): NCCL matches the sends and
+    // receives of a pair in order, so "my low columns" must meet the peer's "high ghost" receive.
+    if (left >= 0) NCCL_TRY(ncclSend(u + 2 * col, n, ncclDouble, left, c->nccl, s), -1);
+    if (right >= 0) NCCL_TRY(ncclRecv(u + (size_t)(g.nxl + 2) * col, n, ncclDouble, right, c->nccl, s), -1);
+    if (right >= 0) NCCL_TRY(ncclSend(u + (size_t)g.nxl * col, n, ncclDouble, right, c->nccl, s), -1);
+    if (left >= 0) NCCL_TRY(ncclRecv(u, n, ncclDouble, left, c->nccl, s), -1);
     NCCL_TRY(ncclGroupEnd(), -1);
     // end ranks of a non-periodic decomposition: the boundary image of that side (MHD: M:617-622, 4 variables:
     // the Euler map G:203-208)

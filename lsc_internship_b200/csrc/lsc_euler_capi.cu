@@ -180,7 +180,8 @@ int eg_halo(lsc_euler_ctx** g, int n) {
         LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
         const int left = (r > 0) ? r - 1 : (ring ? n - 1 : -1);
         const int right = (r < n - 1) ? r + 1 : (ring ? 0 : -1);
-        const size_t bytes = 2 * (size_t)c->g.pitch * sizeof(double);
+        const size_t col = lsc::column_doubles(c->g, 4);  // a column of the blocked layout is one contiguous run
+        const size_t bytes = 2 * col * sizeof(double);
         for (int side = 0; side < 2; ++side) {
             const int nb = side == 0 ? left : right;
             if (nb < 0) {
@@ -190,13 +191,9 @@ int eg_halo(lsc_euler_ctx** g, int n) {
             }
             lsc_euler_ctx* o = g[nb];
             LSC_CUDA_TRY(cudaStreamWaitEvent(c->stream, o->halo_event, 0));
-            for (int k = 0; k < 4; ++k) {
-                double* dst = c->state[c->cur] + (size_t)k * c->g.plane +
-                              (side == 0 ? 0 : (size_t)(c->g.nxl + 2) * c->g.pitch);
-                const double* src = o->state[o->cur] + (size_t)k * o->g.plane +
-                                    (side == 0 ? (size_t)o->g.nxl * o->g.pitch : (size_t)2 * o->g.pitch);
-                LSC_CUDA_TRY(cudaMemcpyPeerAsync(dst, c->cfg.device, src, o->cfg.device, bytes, c->stream));
-            }
+            double* dst = c->state[c->cur] + (side == 0 ? 0 : (size_t)(c->g.nxl + 2) * col);
+            const double* src = o->state[o->cur] + (side == 0 ? (size_t)o->g.nxl * col : 2 * col);
+            LSC_CUDA_TRY(cudaMemcpyPeerAsync(dst, c->cfg.device, src, o->cfg.device, bytes, c->stream));
         }
     }
     LSC_CUDA_TRY(cudaGetLastError());
@@ -297,7 +294,7 @@ int lsc_euler_create(const lsc_euler_config* cfg, lsc_euler_ctx** out) {
     c->dy = (cfg->y1 - cfg->y0) / cfg->ny;
     c->g.nxl = c->nxl;
     c->g.ny = cfg->ny;
-    c->g.pitch = ((cfg->ny + 4 + lsc::JOFF) + 15) / 16 * 16;
+    c->g.pitch = ((cfg->ny + 4 + lsc::JOFF) + lsc::JBLK - 1) / lsc::JBLK * lsc::JBLK;
     c->g.plane = (size_t)(c->nxl + 4) * (size_t)c->g.pitch;
     const size_t state_bytes = c->g.plane * 4 * sizeof(double);
     const size_t col_bytes = (size_t)(cfg->ny + 4) * 4 * sizeof(double);

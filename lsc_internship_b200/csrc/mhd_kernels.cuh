@@ -20,7 +20,7 @@ enum : int { BC_PERIODIC = 0, BC_REFLECTIVE = 1, BC_TRANSMISSIVE = 2 };
 // cell instead of one per value: the separate planes cost ~140 integer instructions per cell in the x sweep),
 // and the two halo columns a neighbour rank needs are ONE contiguous message.  Two ghost cells per side;
 // JOFF = 14 and pitch % 32 == 0 put the first interior row (j = 2) on a 128-byte line.
-// The 4-component Euler states (euler_kernels.cu) keep separate planes: base + k*plane + i*pitch + JOFF + j.
+// The 4-component Euler states (euler_kernels.cu) use the same layout with 4 components per group of 32 rows.
 constexpr int JOFF = 14;
 constexpr int JBLK = 32;  // rows per layout block
 
@@ -28,22 +28,21 @@ struct GridDims {
     int nxl;        // interior columns held by this rank (slab along x)
     int ny;         // interior rows
     int pitch;      // padded rows per column (doubles between consecutive i of one plane)
-    size_t plane;   // (nxl+4)*pitch: doubles of one component; the component stride of the plane layout
+    size_t plane;   // (nxl+4)*pitch: doubles of one component of a state
 };
 
-// plane layout (Euler)
-__host__ __device__ inline size_t cell_index(const GridDims& g, int i, int j) {
-    return (size_t)i * (size_t)g.pitch + (size_t)(JOFF + j);
-}
-
-// blocked layout (MHD): index of component 0 of cell (i,j); component k is MHD_KSTR doubles further
-constexpr size_t MHD_KSTR = JBLK;
-__host__ __device__ inline size_t mhd_index(const GridDims& g, int i, int j) {
+// index of component 0 of cell (i,j) of an NC-component state; component k is KSTR doubles further
+constexpr size_t KSTR = JBLK;
+template <int NC>
+__host__ __device__ inline size_t blocked_index(const GridDims& g, int i, int j) {
     const int jj = JOFF + j;
-    return (size_t)i * (size_t)(NV * g.pitch) + (size_t)((jj >> 5) * (NV * JBLK) + (jj & (JBLK - 1)));
+    return (size_t)i * (size_t)(NC * g.pitch) + (size_t)((jj >> 5) * (NC * JBLK) + (jj & (JBLK - 1)));
 }
-// doubles per column / offset of column i: halo messages and ghost copies move whole columns
-__host__ __device__ inline size_t mhd_column_doubles(const GridDims& g) { return (size_t)NV * (size_t)g.pitch; }
+constexpr size_t MHD_KSTR = KSTR;
+__host__ __device__ inline size_t mhd_index(const GridDims& g, int i, int j) { return blocked_index<NV>(g, i, j); }
+// doubles per column of an nvar-component state: halo messages and ghost copies move whole columns
+__host__ __device__ inline size_t column_doubles(const GridDims& g, int nvar) { return (size_t)nvar * (size_t)g.pitch; }
+__host__ __device__ inline size_t mhd_column_doubles(const GridDims& g) { return column_doubles(g, NV); }
 
 // Columns per thread of an x sweep.  A block runs strip+1 loop iterations after a warm-up worth about half of one;
 // all blocks of a launch cost the same, so the launch takes ceil(blocks / resident) rounds of (strip + 1.5)
