@@ -265,6 +265,11 @@ int lsc_euler_tabeos_initial_condition(const lsc_euler_config* cfg, const double
 /* T:974-999: SLIC2d.dat through the table's ConservativeToPrimative, blank line after each j row */
 int lsc_euler_tabeos_write_dat(const lsc_euler_config* cfg, const double* aos, const char* path,
                                const double* densities, const double* pressures, const double* energies);
+/* Test hook for the Euler y sweep's CFL filter (csrc/euler_physics.cuh: IdealEos::cfl_speed_over_max_f32), as
+ * lsc_mhd_kat_cfl_bound: U holds n states of 4 doubles; exact_and_bound[2t] = ComputeTimeStep's speed + a
+ * (SLIC_euler_2d.cpp:175-184), [2t+1] = the fp32 upper bound of it in units of run_max (NaN = not trusted). */
+int lsc_euler_kat_cfl_bound(int device, long n, const double* U, double gamma, double run_max,
+                            double* exact_and_bound);
 int lsc_euler_set_profiling(lsc_euler_ctx* ctx, int enabled);
 int lsc_euler_kernel_times(lsc_euler_ctx* ctx, double ms[2], long launches[2]);
 

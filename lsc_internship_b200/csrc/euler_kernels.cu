@@ -8,7 +8,9 @@
 // Same structure as the MHD kernels (mhd_kernels.cu): x marches along i with the stencil in registers, y is one
 // thread per cell with face states and fluxes exchanged through shared memory; division policy as there.
 #include <algorithm>
+#include <type_traits>
 
+#include "cfl_reduce.cuh"
 #include "euler_kernels.cuh"
 #include "euler_physics.cuh"
 
@@ -226,7 +228,12 @@ template <class D, class EOS>
 __device__ __forceinline__ bool euler_y_sweep_block(const GridDims& g, const EulerParams& p,
                                                     const double* __restrict__ ubar, const double* __restrict__ cur,
                                                     double* __restrict__ next, const int bx, const int by,
-                                                    double& speed) {
+                                                    double& speed, const unsigned long long* status) {
+    // fast instantiation with an EoS that has a cheap bound: fp32 filter of the CFL reduction (see the MHD y
+    // sweep): the running exact maximum of the blocks that already finished, read first to hide its latency
+    constexpr bool FILTER = !std::is_same<D, IeeeDiv>::value && EOS::kHasCflBound;
+    float inv_run_max = 0.0f;
+    if (FILTER) inv_run_max = inv_running_max_f32(status);
     __shared__ double sH[NE][EBJ];
     __shared__ double sF[NE][EBJ];
     const int tid = threadIdx.x;
@@ -240,8 +247,9 @@ __device__ __forceinline__ bool euler_y_sweep_block(const GridDims& g, const Eul
     euler_y_pass(dv, eos, g, p, cur, i, c, tid, sH, sF, B);   // YthenX: y sweep of u (its x sweep is a no-op)
 
     speed = 0.0;
-    if (tid >= 1 && tid < EBJ - 1 && c <= g.ny + 1) {
-        double un[NE];
+    const bool updates = (tid >= 1 && tid < EBJ - 1 && c <= g.ny + 1);
+    double un[NE];
+    if (updates) {
         const size_t o = euler_index(g, i, c);
 #pragma unroll
         for (int k = 0; k < NE; ++k) {
@@ -250,6 +258,18 @@ __device__ __forceinline__ bool euler_y_sweep_block(const GridDims& g, const Eul
             un[k] = 0.5 * (A[k] + b);
             next[o + k * KSTR] = un[k];
         }
+    }
+    // Only the global maximum of the signal speed is consumed: a warp evaluates the exact fp64 expression only if
+    // one of its cells is not provably (fp32 upper bound) below the running exact maximum.  Skipped cells are
+    // below the final maximum, so the result is the same bit pattern whatever the block order.
+    bool evaluate = updates;
+    if (FILTER) {
+        bool candidate = false;
+        if (updates) candidate = !(eos.cfl_speed_over_max_f32(un, inv_run_max) < 1.0f);
+        const bool warp_has_candidate = __any_sync(0xffffffffu, candidate);  // every lane votes (no short circuit)
+        evaluate = updates && warp_has_candidate;
+    }
+    if (evaluate) {
         const double sp = eos.cfl_speed(dv, un);
         if (sp > speed) speed = sp;
     }
@@ -286,9 +306,11 @@ __global__ void __launch_bounds__(EBJ, 4) euler_y_sweep_kernel(const GridDims g,
                                                                unsigned long long* __restrict__ status,
                                                                unsigned* __restrict__ fix_list) {
     double speed;
-    const bool bad = euler_y_sweep_block<D, EOS>(g, p, ubar, cur, next, blockIdx.x, blockIdx.y, speed);
-    if (__syncthreads_or(bad)) {
+    const bool bad = euler_y_sweep_block<D, EOS>(g, p, ubar, cur, next, blockIdx.x, blockIdx.y, speed, status);
+    if (__syncthreads_or(bad)) {  // whole block is recomputed by the fix kernel; its maximum must not count
         if (threadIdx.x == 0) fix_list[atomicAdd(status + 2, 1ull)] = blockIdx.y * gridDim.x + blockIdx.x;
+    } else if (!std::is_same<D, IeeeDiv>::value && EOS::kHasCflBound) {
+        warp_max_to_global(speed, status);
     } else {
         euler_block_max(speed, status);
     }
@@ -306,7 +328,7 @@ __global__ void __launch_bounds__(EBJ) euler_y_sweep_fix_kernel(const GridDims g
     for (unsigned long long q = blockIdx.x; q < count; q += gridDim.x) {
         const unsigned bid = fix_list[q];
         double speed;
-        euler_y_sweep_block<IeeeDiv, EOS>(g, p, ubar, cur, next, (int)(bid % nbx), (int)(bid / nbx), speed);
+        euler_y_sweep_block<IeeeDiv, EOS>(g, p, ubar, cur, next, (int)(bid % nbx), (int)(bid / nbx), speed, status);
         euler_block_max(speed, status);
         __syncthreads();
     }
@@ -435,6 +457,24 @@ void launch_euler_aos_to_soa(const GridDims& g, const double* aos, int i0, int n
 void launch_euler_soa_to_aos(const GridDims& g, const double* soa, int i0, int ni, double* aos, cudaStream_t s) {
     dim3 grid((g.ny + 4 + 31) / 32, ni);
     euler_soa_to_aos_kernel<<<grid, 128, 0, s>>>(g, soa, i0, aos);
+}
+
+// Test hook: exact signal speed (S:175-184) and the fp32 upper bound of speed/run_max of the y sweep's filter.
+__global__ void euler_kat_cfl_bound_kernel(long n, const double* __restrict__ U, double gamma, double run_max,
+                                           double* __restrict__ out) {
+    const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    double u[NE];
+#pragma unroll
+    for (int k = 0; k < NE; ++k) u[k] = U[t * NE + k];
+    const IdealEos eos{gamma - 1, gamma};
+    IeeeDiv dv;
+    out[2 * t] = eos.cfl_speed(dv, u);
+    out[2 * t + 1] = (double)eos.cfl_speed_over_max_f32(u, __frcp_ru(__double2float_rd(run_max)));
+}
+
+void launch_euler_kat_cfl_bound(long n, const double* U, double gamma, double run_max, double* out) {
+    euler_kat_cfl_bound_kernel<<<(unsigned)((n + 127) / 128), 128>>>(n, U, gamma, run_max, out);
 }
 
 }  // namespace lsc

@@ -34,4 +34,7 @@ void launch_euler_x_ghosts_side(const GridDims& g, int hi_side, double* u, cudaS
 void launch_euler_aos_to_soa(const GridDims& g, const double* aos, int i0, int ni, double* soa, cudaStream_t s);
 void launch_euler_soa_to_aos(const GridDims& g, const double* soa, int i0, int ni, double* aos, cudaStream_t s);
 
+// test hook (device pointers): out[2t] = exact cfl speed, out[2t+1] = fp32 bound of speed / run_max
+void launch_euler_kat_cfl_bound(long n, const double* U, double gamma, double run_max, double* out);
+
 }  // namespace lsc

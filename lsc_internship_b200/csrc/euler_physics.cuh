@@ -23,6 +23,33 @@ __device__ __forceinline__ double escaled_add(double k, double w, double c) { re
 
 struct IdealEos {
     double gm1, gamma;
+    static constexpr bool kHasCflBound = true;
+
+    // Single-precision UPPER BOUND of cfl_speed(q) / R for the y sweep's warp filter (the construction and its
+    // safety argument are those of cfl_speed_over_max_f32 in mhd_physics.cuh): everything in units of the running
+    // maximum R (inv_r = 1/R rounded up) so that the estimate is invariant under rescaling of the state; the
+    // pressure -- the one cancellation-prone term -- gets +1e-6*(|E| + kinetic) before use; the total is inflated
+    // by 2^-10; scale factors outside [1e-25, 1e25] and any NaN/inf (negative pressure, R = 0) give NaN, and the
+    // caller evaluates exactly unless `bound < 1`.  tests/test_euler_gpu.py::test_euler_cfl_upper_bound.
+    __device__ __forceinline__ float cfl_speed_over_max_f32(const double (&q)[NE], float inv_r) const {
+        const float gamma_up = __double2float_ru(gamma), gm1_up = __double2float_ru(gamma - 1.0);
+        const float rho = (float)q[0];
+        float ir;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ir) : "f"(rho));
+        const float kv = ir * inv_r;  // momentum -> velocity / R
+        const float k = kv * inv_r;   // energy density -> speed^2 / R^2
+        const float vx = fabsf((float)q[1]) * kv, vy = fabsf((float)q[2]) * kv;
+        const float v2 = vx * vx + vy * vy;
+        const float e = (float)q[3] * k;
+        const float ke = 0.5f * v2;
+        const float pk = gm1_up * ((e - ke) + 1e-6f * (fabsf(e) + ke));  // p / (rho R^2), upper bound
+        float sp, a;
+        asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sp) : "f"(v2));
+        asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(a) : "f"(gamma_up * pk));
+        const float best = (sp + a) * 1.0009765625f;
+        const bool scales_ok = fminf(k, kv) > 1e-25f && fmaxf(k, kv) < 1e25f;
+        return scales_ok ? best : __int_as_float(0x7fc00000);
+    }
 
     template <class D>
     __device__ __forceinline__ double pressure(D&, const double (&x)[NE], const Rcp&, double vx, double vy) const {
@@ -48,6 +75,10 @@ struct IdealEos {
 constexpr int NT = 500;  // table axes, T:12
 
 struct TableEos {
+    static constexpr bool kHasCflBound = false;  // every cell evaluates its table lookup
+    __device__ __forceinline__ float cfl_speed_over_max_f32(const double (&)[NE], float) const {
+        return __int_as_float(0x7fc00000);
+    }
     const double* __restrict__ dens;   // [500] ascending densities (file line 10)
     const double* __restrict__ pres;   // [500] ascending pressures (file line 12)
     const double* __restrict__ sound;  // [500][500] sound speed, [pressure index][density index]

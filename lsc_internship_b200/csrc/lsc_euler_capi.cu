@@ -578,3 +578,26 @@ int lsc_euler_kernel_times(lsc_euler_ctx* c, double ms[2], long launches[2]) {
 }
 
 }  // extern "C"
+
+extern "C" int lsc_euler_kat_cfl_bound(int device, long n, const double* U, double gamma, double run_max,
+                                       double* exact_and_bound) {
+    if (n <= 0 || !U || !exact_and_bound) return LSC_EINVAL;
+    if (cudaSetDevice(device) != cudaSuccess) return LSC_ECUDA;
+    double *du = nullptr, *dout = nullptr;
+    int rc = LSC_OK;
+    if (cudaMalloc(&du, (size_t)n * 32) != cudaSuccess || cudaMalloc(&dout, (size_t)n * 16) != cudaSuccess) {
+        rc = LSC_ENOMEM;
+    } else {
+        cudaMemcpy(du, U, (size_t)n * 32, cudaMemcpyHostToDevice);
+        lsc::launch_euler_kat_cfl_bound(n, du, gamma, run_max, dout);
+        lsc_count_launches(1);
+        if (cudaDeviceSynchronize() != cudaSuccess ||
+            cudaMemcpy(exact_and_bound, dout, (size_t)n * 16, cudaMemcpyDeviceToHost) != cudaSuccess) {
+            cudaGetLastError();
+            rc = LSC_ECUDA;
+        }
+    }
+    cudaFree(du);
+    cudaFree(dout);
+    return rc;
+}

@@ -19,6 +19,7 @@
 #include <algorithm>
 #include <type_traits>
 
+#include "cfl_reduce.cuh"
 #include "mhd_kernels.cuh"
 #include "mhd_physics.cuh"
 
@@ -32,11 +33,6 @@ namespace lsc {
 __device__ __forceinline__ void load_cell(const double* __restrict__ base, size_t idx, double (&u)[NV]) {
 #pragma unroll
     for (int k = 0; k < NV; ++k) u[k] = __ldg(base + idx + k * MHD_KSTR);
-}
-
-__device__ __forceinline__ void atomic_max_nonneg(unsigned long long* addr, double v) {
-    // v >= 0 and not NaN: the IEEE bit pattern is monotone in the value
-    atomicMax(addr, (unsigned long long)__double_as_longlong(v));
 }
 
 // Reduce a per-thread running maximum (started from 0.0, updated only with `>` so NaNs
@@ -61,19 +57,6 @@ __device__ __forceinline__ void block_max_to_global(double local, unsigned long 
         }
         if (lane == 0 && v > 0.0) atomic_max_nonneg(out, v);
     }
-}
-
-// Warp-level variant for the y sweep: with the fp32 CFL filter most warps carry no candidate at all (local == 0
-// in every lane) and leave after one vote; a warp that does hold one publishes it with its own atomic -- no
-// shared memory, no block barrier.
-__device__ __forceinline__ void warp_max_to_global(double local, unsigned long long* out) {
-    if (!__any_sync(0xffffffffu, local > 0.0)) return;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        const double other = __shfl_xor_sync(0xffffffffu, local, o);
-        local = (other > local) ? other : local;
-    }
-    if ((threadIdx.x & 31) == 0) atomic_max_nonneg(out, local);
 }
 
 #ifndef XS_BLOCK
@@ -368,8 +351,7 @@ __device__ __forceinline__ bool y_sweep_block(const GridDims& g, const SweepPara
     constexpr bool FILTER = !std::is_same<D, IeeeDiv>::value;
     float inv_run_max = 0.0f;  // 1/R rounded up (R = 0 -> +inf -> every warp evaluates)
     if (FILTER) {
-        const float r = __double2float_rd(__longlong_as_double((long long)*(const volatile unsigned long long*)status));
-        inv_run_max = __frcp_ru(r);
+        inv_run_max = inv_running_max_f32(status);
     }
     __shared__ double sU[NV][BJ + 2];  // uBar of cells jo-2 .. jo+BJ-1
     __shared__ double sP[NV][BJ + 2];  // primitives of u^n there; later the interface fluxes

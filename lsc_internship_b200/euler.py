@@ -182,6 +182,15 @@ class SlicEuler2d:
         return n
 
 
+def euler_kat_cfl_bound(U, gamma, run_max, device=0):
+    """(exact fp64 signal speed S:175-184, fp32 upper bound of speed/run_max used by the Euler y sweep's warp
+    filter) per state; U is (n, 4) conserved states."""
+    U = np.ascontiguousarray(U, dtype=np.float64)
+    out = np.empty((U.shape[0], 2), dtype=np.float64)
+    check(lib().lsc_euler_kat_cfl_bound(device, U.shape[0], _dp(U), float(gamma), float(run_max), _dp(out)))
+    return out[:, 0], out[:, 1]
+
+
 class SlicEuler2dGroup:
     """The n slabs of one grid advanced in lock step inside ONE process (lsc_euler_group_step): halos by peer
     copies, the CFL maximum on the host.  Same kernels and slab-edge code path as the NCCL mode; used to check

@@ -246,6 +246,43 @@ def test_random_state_parity():
     s.close()
 
 
+
+@pytest.mark.gpu
+def test_euler_cfl_upper_bound():
+    """The Euler y sweep skips the exact signal speed for warps whose fp32 upper bound of speed/run_max is < 1
+    (euler_physics.cuh: IdealEos::cfl_speed_over_max_f32).  bound*run_max must be >= the exact speed (up to 1e-12
+    of run_max, the fp32 underflow floor) wherever the bound is finite, and a state that could raise the maximum is
+    never skipped.  Regimes: solver range, pressure = tiny remainder of E, at rest, scales around the fp32 range."""
+    import lsc_internship_b200 as lsc
+    rng = np.random.default_rng(77)
+    n = 300000
+    g = 1.4
+    rho = 10.0 ** rng.uniform(-3, 3, n)
+    v = rng.uniform(-3, 3, (n, 2)) * 10.0 ** rng.uniform(-6, 2, (n, 1))
+    p = 10.0 ** rng.uniform(-9, 3, n)
+    q = n // 4
+    v[:q] = 0.0
+    scale = np.ones(n)
+    scale[q:2 * q] = 10.0 ** rng.uniform(-30, 30, q)
+    U = np.empty((n, 4))
+    U[:, 0] = rho * scale
+    U[:, 1:3] = rho[:, None] * v * scale[:, None]
+    U[:, 3] = (p / (g - 1) + 0.5 * rho * (v * v).sum(1)) * scale
+    med = float(np.median(np.sqrt(g * p / rho)))
+    for run_max in (med, 1e-3 * med, 1e3 * med, 1e-20, 1e20, 0.0):
+        exact, bound = lsc.euler_kat_cfl_bound(U, g, run_max)
+        trusted = np.isfinite(bound)
+        ok = ~np.isfinite(exact) | ~trusted | (bound * run_max >= exact - 1e-12 * run_max)
+        assert ok.all(), f"run_max={run_max}: {(~ok).sum()} states with bound < exact"
+        assert not np.any((bound < 1.0) & (exact >= run_max))
+        if run_max == 0.0:
+            assert not trusted.any()
+    exact, bound = lsc.euler_kat_cfl_bound(U, g, med)
+    ordinary = np.isfinite(bound) & np.isfinite(exact) & (scale == 1.0) & (p > 1e-3 * U[:, 3])
+    assert ordinary.sum() > n // 4
+    assert np.median(bound[ordinary] * med / exact[ordinary]) < 1.01
+
+
 @gpu
 def test_out_of_window_operands_take_the_ieee_path():
     import lsc_internship_b200 as lsc
