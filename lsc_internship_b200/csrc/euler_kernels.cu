@@ -94,6 +94,13 @@ __device__ __forceinline__ bool euler_x_sweep_block(const GridDims& g, const Eul
 
 #pragma unroll EX_UNROLL
     for (int c = ia; c <= ib; ++c) {
+        // the column loaded at the end of this iteration is consumed at the start of the next one: pull the one
+        // after it into L1 now, a whole iteration ahead
+        if (c + 3 <= g.nxl + 3) {
+            const double* pf = cur + euler_index(g, c + 3, j);
+#pragma unroll
+            for (int k = 0; k < NE; ++k) asm volatile("prefetch.global.L1 [%0];" ::"l"(pf + k * KSTR));
+        }
         double hL[NE], hR[NE];
         if (c == ib && hi_image) {
 #pragma unroll
