@@ -228,7 +228,6 @@ __device__ __forceinline__ void euler_y_pass(D& dv, const EOS& eos, const GridDi
 #pragma unroll
         for (int k = 0; k < NE; ++k) out[k] = u0[k] - p.dtdy * (F[k] - sF[k][tid - 1]);  // S:370
     }
-    __syncthreads();  // sH / sF are reused by the next pass
 }
 
 template <class D, class EOS>
@@ -241,8 +240,8 @@ __device__ __forceinline__ bool euler_y_sweep_block(const GridDims& g, const Eul
     constexpr bool FILTER = !std::is_same<D, IeeeDiv>::value && EOS::kHasCflBound;
     float inv_run_max = 0.0f;
     if (FILTER) inv_run_max = inv_running_max_f32(status);
-    __shared__ double sH[NE][EBJ];
-    __shared__ double sF[NE][EBJ];
+    __shared__ double sH[2][NE][EBJ];  // one pair of exchange buffers per pass: no barrier between the passes
+    __shared__ double sF[2][NE][EBJ];
     const int tid = threadIdx.x;
     const int i = 2 + by;
     const int jo = 2 + bx * (EBJ - 2);
@@ -250,8 +249,8 @@ __device__ __forceinline__ bool euler_y_sweep_block(const GridDims& g, const Eul
     D dv;
     const EOS eos = make_eos<EOS>(p);
     double A[NE], B[NE];  // valid for the threads that update a cell (the only ones that read them)
-    euler_y_pass(dv, eos, g, p, ubar, i, c, tid, sH, sF, A);  // XthenY: y sweep of ubar
-    euler_y_pass(dv, eos, g, p, cur, i, c, tid, sH, sF, B);   // YthenX: y sweep of u (its x sweep is a no-op)
+    euler_y_pass(dv, eos, g, p, ubar, i, c, tid, sH[0], sF[0], A);  // XthenY: y sweep of ubar
+    euler_y_pass(dv, eos, g, p, cur, i, c, tid, sH[1], sF[1], B);   // YthenX: y sweep of u (its x sweep is a no-op)
 
     speed = 0.0;
     const bool updates = (tid >= 1 && tid < EBJ - 1 && c <= g.ny + 1);
