@@ -260,6 +260,13 @@ int lsc_eos_table_read(const char* path, double* densities, double* pressures, d
 int lsc_euler_set_eos_table(lsc_euler_ctx* ctx, const double* densities, const double* pressures,
                             const double* sound_speeds, const double* energies);
 /* IC loop T:912-952 + boundary fill T:954 into [(nx+4)][(ny+4)][4] (or the slab of cfg->rank) */
+/* The table searches of T (T:257-275, :291-299, :366-376) are bisections.  When the table passes the library's
+ * monotonicity check (axes strictly ascending -- required -- and energy columns ascending by more than the rounding
+ * of the density interpolation) the bracket a bisection ends in is unique, and the kernels find it by first trying
+ * the bracket of the thread's previous lookup (bit-identical results, ~2.5x faster); otherwise, or after
+ * lsc_euler_set_eos_search(ctx, 0), every search is the reference's bisection. */
+int lsc_euler_set_eos_search(lsc_euler_ctx* ctx, int warm_start);
+int lsc_euler_eos_search_is_warm(const lsc_euler_ctx* ctx);
 int lsc_euler_tabeos_initial_condition(const lsc_euler_config* cfg, const double* densities, const double* pressures,
                                        const double* energies, double* aos);
 /* T:974-999: SLIC2d.dat through the table's ConservativeToPrimative, blank line after each j row */

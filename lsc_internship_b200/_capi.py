@@ -68,7 +68,7 @@ EXPORTS = [
     "lsc_euler_get_scalars", "lsc_euler_download", "lsc_euler_write_dat", "lsc_euler_ieee_fallback_count",
     "lsc_euler_set_profiling", "lsc_euler_kernel_times", "lsc_euler_local_nx", "lsc_euler_local_i0",
     "lsc_euler_comm_init", "lsc_euler_group_step", "lsc_eos_table_read", "lsc_euler_set_eos_table",
-    "lsc_euler_tabeos_initial_condition", "lsc_euler_tabeos_write_dat", "lsc_euler_kat_cfl_bound",
+    "lsc_euler_tabeos_initial_condition", "lsc_euler_tabeos_write_dat", "lsc_euler_kat_cfl_bound", "lsc_euler_set_eos_search", "lsc_euler_eos_search_is_warm",
 ]
 
 _lib = None
@@ -120,6 +120,8 @@ def lib():
     L.lsc_euler_destroy.argtypes = [vp]
     L.lsc_eos_table_read.argtypes = [ctypes.c_char_p, dp, dp, dp, dp]
     L.lsc_euler_set_eos_table.argtypes = [vp, dp, dp, dp, dp]
+    L.lsc_euler_set_eos_search.argtypes = [vp, ctypes.c_int]
+    L.lsc_euler_eos_search_is_warm.argtypes = [vp]
     L.lsc_euler_tabeos_initial_condition.argtypes = [ecfg, dp, dp, dp, dp]
     L.lsc_euler_tabeos_write_dat.argtypes = [ecfg, dp, ctypes.c_char_p, dp, dp, dp]
     L.lsc_euler_kat_cfl_bound.argtypes = [ctypes.c_int, ctypes.c_long, dp, ctypes.c_double, ctypes.c_double, dp]

@@ -278,4 +278,21 @@ int tabeos_write_dat(const lsc_euler_config& c, const double* a, const char* pat
     return output.good() ? 0 : -1;
 }
 
+bool eos_table_is_monotone(const double* en) {
+    constexpr int N = 500;
+    const double tol = std::ldexp(1.0, -49);  // 16 u: the three roundings of the interpolation are < 4 u * mag
+    for (int p = 0; p + 1 < N; ++p) {
+        for (int d = 0; d < N; ++d) {
+            const int d2 = (d + 1 < N) ? d + 1 : d;
+            const double a0 = en[p * N + d], a1 = en[(p + 1) * N + d];
+            const double b0 = en[p * N + d2], b1 = en[(p + 1) * N + d2];
+            const double gap = std::fmin(a1 - a0, b1 - b0);
+            const double mag = std::fmax(std::fmax(std::fabs(a0), std::fabs(a1)), std::fmax(std::fabs(b0), std::fabs(b1))) +
+                               2.0 * std::fmax(std::fabs(b0 - a0), std::fabs(b1 - a1));
+            if (!(gap > tol * mag)) return false;  // also false for NaN
+        }
+    }
+    return true;
+}
+
 }  // namespace lsc

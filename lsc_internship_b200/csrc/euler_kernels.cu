@@ -54,7 +54,7 @@ __device__ __forceinline__ IdealEos make_eos<IdealEos>(const EulerParams& p) {
 }
 template <>
 __device__ __forceinline__ TableEos make_eos<TableEos>(const EulerParams& p) {
-    return TableEos{p.tab_dens, p.tab_pres, p.tab_sound, p.tab_en};
+    return TableEos{p.tab_dens, p.tab_pres, p.tab_sound, p.tab_en, p.tab_warm};
 }
 
 #ifndef EULER_X_UNROLL

@@ -19,6 +19,7 @@ struct EulerParams {
     const double* tab_pres;   // [500]
     const double* tab_sound;  // [500][500]  [pressure][density]
     const double* tab_en;     // [500][500]
+    int tab_warm;             // 1: the table passed eos_table_is_monotone -> warm-started searches (TableEos)
 };
 
 // status / fix_list as in mhd_kernels.cuh: [0] max speed bits, [1]/[2] x/y blocks recomputed with IEEE division

@@ -83,19 +83,46 @@ struct TableEos {
     const double* __restrict__ pres;   // [500] ascending pressures (file line 12)
     const double* __restrict__ sound;  // [500][500] sound speed, [pressure index][density index]
     const double* __restrict__ en;     // [500][500] specific internal energy, same indexing
+    // Host-verified (eos_table_is_monotone, euler_host.cpp): both axes strictly ascending and every energy column
+    // ascending by more than the rounding of the interpolation.  Then each search predicate of T is monotone in
+    // the index and the bracket its bisection ends in is unique -- (last index whose entry is below the value,
+    // that index + 1) -- so it can be FOUND any way: here by checking the bracket of the thread's previous lookup
+    // first (consecutive lookups are the face states of one cell) and bisecting only on a miss.  With
+    // warm == 0 every search is the reference's bisection.
+    int warm;
+    mutable int hint_d = 249, hint_e = 249, hint_p = 249;  // previous brackets (density axis, energy column, pressure axis)
 
     // The bisection every lookup of T starts with (T:257-275 etc.): brackets v in the ascending axis; point2
-    // starts at 499, or at 500 in SoundSpeed's pressure search (T:366; index 500 is never read).
-    __device__ __forceinline__ static void bracket(const double* __restrict__ a, double v, int point2, int& lo,
-                                                   int& hi) {
+    // starts at 499, or at 500 in SoundSpeed's pressure search (T:366; index 500 is never read).  Returns the
+    // unclamped point1 (point2 = point1 + 1 on exit).
+    __device__ __forceinline__ static int bisect_axis(const double* __restrict__ a, double v, int point2) {
         int point1 = 0;
-        while (abs(point1 - point2) > 1) {
-            const int half = (point1 + point2) / 2;
+        while (point2 - point1 > 1) {
+            const int half = (point1 + point2) >> 1;
             if (v > __ldg(a + half)) point1 = half;
             else point2 = half;
         }
-        lo = min(max(point1, 0), 499);  // T:271-275
-        hi = min(max(point2, 0), 499);
+        return point1;
+    }
+    __device__ __forceinline__ void bracket(const double* __restrict__ a, double v, int point2, int& hint, int& lo,
+                                            int& hi) const {
+        int p1 = hint;
+        bool hit = false;
+        if (warm) {
+            // p1 is the answer iff (p1 == 0 or v > a[p1]) and (p1 + 1 == point2 or not v > a[p1 + 1])
+            const double below = __ldg(a + p1), above = __ldg(a + min(p1 + 1, NT - 1));
+            hit = (p1 == 0 || v > below) && (p1 + 1 >= point2 || !(v > above));
+        }
+        if (!hit) p1 = bisect_axis(a, v, point2);
+        hint = p1;
+        lo = min(max(p1, 0), 499);  // T:271-275
+        hi = min(max(p1 + 1, 0), 499);
+    }
+
+    // density-interpolated energy at pressure index h (the bisection's comparand, T:293-296)
+    __device__ __forceinline__ double energy_at(int h, int db, int dt, double density_ratio) const {
+        const double eb = __ldg(en + h * NT + db), et = __ldg(en + h * NT + dt);
+        return eb + density_ratio * (et - eb);
     }
 
     // ConservativeToPrimative's pressure, T:263-324.  Also returns the density bracket for SoundSpeed.
@@ -103,19 +130,30 @@ struct TableEos {
     __device__ __forceinline__ double pressure_ex(D& dv, const double (&x)[NE], const Rcp& ir, double vx, double vy,
                                                   int& db, int& dt, double& density_ratio) const {
         const double rho = x[0];
-        bracket(dens, rho, 499, db, dt);
+        bracket(dens, rho, 499, hint_d, db, dt);
         const double d_bottom = __ldg(dens + db), d_top = __ldg(dens + dt);
         density_ratio = dv.div(rho - d_bottom, d_top - d_bottom);
         if (d_bottom == d_top) density_ratio = 1;
         const double e = dv.div(escaled_add(-0.5, rho * (vx * vx + vy * vy), x[3]), ir);  // T:288
-        int point1 = 0, point2 = 499;
-        while (abs(point1 - point2) > 1) {  // T:291-299: bisection on the density-interpolated energy column
-            const int half = (point1 + point2) / 2;
-            const double eb = __ldg(en + half * NT + db), et = __ldg(en + half * NT + dt);
-            if (e > (eb + density_ratio * (et - eb))) point1 = half;
-            else point2 = half;
+        // T:291-299: bisection on the density-interpolated energy column (monotone for 0 <= ratio <= 1 when the
+        // table passed the host check; outside that range -- extrapolation -- always the reference's bisection)
+        int point1 = hint_e;
+        bool hit = false;
+        if (warm && density_ratio >= 0.0 && density_ratio <= 1.0) {
+            hit = (point1 == 0 || e > energy_at(point1, db, dt, density_ratio)) &&
+                  (point1 + 1 >= 499 || !(e > energy_at(point1 + 1, db, dt, density_ratio)));
         }
-        const int pt = point2, pb = point1;  // captured before the (no-op) clamps, T:303-310
+        if (!hit) {
+            point1 = 0;
+            int point2 = 499;
+            while (point2 - point1 > 1) {
+                const int half = (point1 + point2) >> 1;
+                if (e > energy_at(half, db, dt, density_ratio)) point1 = half;
+                else point2 = half;
+            }
+        }
+        hint_e = point1;
+        const int pt = point1 + 1, pb = point1;  // captured before the (no-op) clamps, T:303-310
         const double f_NE = __ldg(en + pt * NT + dt), f_SE = __ldg(en + pb * NT + dt);
         const double f_SW = __ldg(en + pb * NT + db), f_NW = __ldg(en + pt * NT + db);
         // ReverseBilinearInterpolation, T:156-163
@@ -145,7 +183,7 @@ struct TableEos {
         int db, dt, pb, pt;
         double density_ratio;
         const double p = pressure_ex(dv, q, ir, vx, vy, db, dt, density_ratio);
-        bracket(pres, p, 500, pb, pt);  // T:366
+        bracket(pres, p, 500, hint_p, pb, pt);  // T:366
         const double p_bottom = __ldg(pres + pb), p_top = __ldg(pres + pt);
         double pressure_ratio = dv.div(p - p_bottom, p_top - p_bottom);
         if (p_bottom == p_top) pressure_ratio = 1;

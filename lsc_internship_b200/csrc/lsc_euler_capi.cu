@@ -36,6 +36,8 @@ struct lsc_euler_ctx {
     std::vector<cudaEvent_t> prof_events;
     double* d_table = nullptr;         // tabulated EoS: dens[500] pres[500] sound[500*500] energies[500*500]
     std::vector<double> h_table;       // host copy (IC, .dat output)
+    bool table_monotone = false;       // energy columns ascending with margin: searches may be warm-started
+    bool warm_search = true;           // lsc_euler_set_eos_search
     lsc::Comm* comm = nullptr;         // NCCL mode (one process per GPU)
     bool in_group = false;             // driven by lsc_euler_group_step
     cudaEvent_t halo_event = nullptr;  // "new u complete" marker for neighbours in a group
@@ -58,6 +60,7 @@ void fill_eos(const lsc_euler_ctx* c, lsc::EulerParams& p) {
         p.tab_sound = c->d_table + 2 * TAB_N;
         p.tab_en = c->d_table + 2 * TAB_N + TAB_N * TAB_N;
     }
+    p.tab_warm = (c->d_table && c->table_monotone && c->warm_search) ? 1 : 0;
 }
 
 int e_read_status(lsc_euler_ctx* c) {
@@ -389,7 +392,19 @@ int lsc_euler_set_eos_table(lsc_euler_ctx* c, const double* densities, const dou
         return lsc_fail(LSC_ENOMEM, "device allocation of the EoS table failed");
     }
     LSC_CUDA_TRY(cudaMemcpy(c->d_table, t, TAB_DOUBLES * sizeof(double), cudaMemcpyHostToDevice));
+    c->table_monotone = lsc::eos_table_is_monotone(energies);
     return LSC_OK;
+}
+
+int lsc_euler_set_eos_search(lsc_euler_ctx* c, int warm_start) {
+    if (!c) return lsc_fail(LSC_EINVAL, "null argument");
+    c->warm_search = (warm_start != 0);
+    return LSC_OK;
+}
+
+int lsc_euler_eos_search_is_warm(const lsc_euler_ctx* c) {
+    if (!c) return 0;
+    return (c->d_table && c->table_monotone && c->warm_search) ? 1 : 0;
 }
 
 int lsc_euler_tabeos_initial_condition(const lsc_euler_config* cfg, const double* densities, const double* pressures,

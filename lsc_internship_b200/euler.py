@@ -55,6 +55,15 @@ class SlicEuler2d:
         assert self.table[2].shape == (500, 500) and self.table[3].shape == (500, 500)
         check(lib().lsc_euler_set_eos_table(self._h, *[_dp(a) for a in self.table]))
 
+    def set_eos_search(self, warm_start):
+        """warm_start=False: every table search is the reference's bisection; True (default): warm-started searches
+        when the table passed the library's monotonicity check (bit-identical results either way)."""
+        check(lib().lsc_euler_set_eos_search(self._h, 1 if warm_start else 0))
+
+    @property
+    def eos_search_is_warm(self):
+        return bool(lib().lsc_euler_eos_search_is_warm(self._h))
+
     def tabeos_initial_condition(self):
         """IC loop of T's main() (T:912-954) as a host array."""
         u = np.empty(self.shape, dtype=np.float64)

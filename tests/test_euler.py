@@ -176,6 +176,18 @@ def test_tabeos_cuda_matches_oracle_and_reference(nx, ny, n, tmp_path):
         ur, lg = run_tabeos_ref(nx, ny, n)
         assert np.array_equal(bits(u), bits(ur))
         assert (t, dt) == tuple(lg[-1])
+    # the searches were warm-started (the synthetic table passes the monotonicity check); the reference's plain
+    # bisection must give the same bits
+    assert s.eos_search_is_warm
+    cold = lsc.SlicEuler2d(nx, ny, bc="transmissive", problem="tabeos")
+    cold.set_eos_table(*table)
+    cold.set_eos_search(False)
+    assert not cold.eos_search_is_warm
+    cold.init_problem()
+    cold.step(n)
+    assert cold.scalars()[:2] == (t, dt)
+    assert np.array_equal(bits(cold.download()), bits(u))
+    cold.close()
     # slabs: the table path through the decomposition
     grp = lsc.SlicEuler2dGroup(2, nxCells=nx, nyCells=ny, bc="transmissive", problem="tabeos")
     for part in grp.parts:
@@ -184,6 +196,37 @@ def test_tabeos_cuda_matches_oracle_and_reference(nx, ny, n, tmp_path):
     grp.step(n)
     assert np.array_equal(bits(grp.download()), bits(u))
     grp.close()
+    s.close()
+
+
+@gpu
+def test_tabeos_non_monotone_table_falls_back_to_the_bisection(tmp_path):
+    """A table whose energy columns are not ascending (two pressure rows swapped) fails the library's check: the
+    searches are then the reference's bisections, whose result depends on the path -- compare with the oracle, which
+    runs T's loops literally, on that same table."""
+    import lsc_internship_b200 as lsc
+    from oracle_util import tabeos_ic, write_eos_table
+    path = str(tmp_path / "Plasma19_EoS.txt")
+    write_eos_table(path)
+    d, p, ss, en = lsc.SlicEuler2d.read_eos_table(path)
+    en = en.copy()
+    for row in range(40, 460, 7):  # inversions all over the pressure range
+        en[[row, row + 1]] = en[[row + 1, row]]
+    table = (d, p, ss, en)
+    nx, ny, n = 48, 36, 4
+    cfg = euler_cfg(nx, ny, DOM, bc="transmissive")
+    u0 = tabeos_ic(cfg, table)
+    s = lsc.SlicEuler2d(nx, ny, bc="transmissive", problem="tabeos")
+    s.set_eos_table(*table)
+    assert not s.eos_search_is_warm
+    s.upload(u0)
+    o = OracleEuler(cfg, u0)
+    o.set_table(*table)
+    for k in range(n):
+        lo = o.step(1)[0]
+        s.step(1)
+        assert s.scalars()[:2] == tuple(lo), f"step {k}"
+    assert np.array_equal(bits(s.download()), bits(o.state()[0]))
     s.close()
 
 
