@@ -104,19 +104,26 @@ struct TableEos {
         }
         return point1;
     }
+    // lo / hi: the clamped bracket (T:271-275); a_lo / a_hi: the axis values there
     __device__ __forceinline__ void bracket(const double* __restrict__ a, double v, int point2, int& hint, int& lo,
-                                            int& hi) const {
+                                            int& hi, double& a_lo, double& a_hi) const {
         int p1 = hint;
         bool hit = false;
         if (warm) {
-            // p1 is the answer iff (p1 == 0 or v > a[p1]) and (p1 + 1 == point2 or not v > a[p1 + 1])
-            const double below = __ldg(a + p1), above = __ldg(a + min(p1 + 1, NT - 1));
-            hit = (p1 == 0 || v > below) && (p1 + 1 >= point2 || !(v > above));
+            // p1 is the answer iff (p1 == 0 or v > a[p1]) and (p1 + 1 == point2 or not v > a[p1 + 1]); the two
+            // entries read for the test are the bracket's axis values
+            a_lo = __ldg(a + p1);
+            a_hi = __ldg(a + min(p1 + 1, NT - 1));
+            hit = (p1 == 0 || v > a_lo) && (p1 + 1 >= point2 || !(v > a_hi));
         }
-        if (!hit) p1 = bisect_axis(a, v, point2);
+        if (!hit) {
+            p1 = bisect_axis(a, v, point2);
+            a_lo = __ldg(a + p1);
+            a_hi = __ldg(a + min(p1 + 1, NT - 1));
+        }
         hint = p1;
-        lo = min(max(p1, 0), 499);  // T:271-275
-        hi = min(max(p1 + 1, 0), 499);
+        lo = p1;  // 0 <= p1 <= 499 and p1 + 1 >= 1: only the upper clamp of T:271-275 can act
+        hi = min(p1 + 1, NT - 1);
     }
 
     // density-interpolated energy at pressure index h (the bisection's comparand, T:293-296)
@@ -130,18 +137,24 @@ struct TableEos {
     __device__ __forceinline__ double pressure_ex(D& dv, const double (&x)[NE], const Rcp& ir, double vx, double vy,
                                                   int& db, int& dt, double& density_ratio) const {
         const double rho = x[0];
-        bracket(dens, rho, 499, hint_d, db, dt);
-        const double d_bottom = __ldg(dens + db), d_top = __ldg(dens + dt);
+        double d_bottom, d_top;
+        bracket(dens, rho, 499, hint_d, db, dt, d_bottom, d_top);
         density_ratio = dv.div(rho - d_bottom, d_top - d_bottom);
         if (d_bottom == d_top) density_ratio = 1;
         const double e = dv.div(escaled_add(-0.5, rho * (vx * vx + vy * vy), x[3]), ir);  // T:288
         // T:291-299: bisection on the density-interpolated energy column (monotone for 0 <= ratio <= 1 when the
-        // table passed the host check; outside that range -- extrapolation -- always the reference's bisection)
+        // table passed the host check; outside that range -- extrapolation -- always the reference's bisection).
+        // The four entries the warm test reads are the corners of the interpolation cell.
         int point1 = hint_e;
         bool hit = false;
+        double f_SW, f_SE, f_NW, f_NE;
         if (warm && density_ratio >= 0.0 && density_ratio <= 1.0) {
-            hit = (point1 == 0 || e > energy_at(point1, db, dt, density_ratio)) &&
-                  (point1 + 1 >= 499 || !(e > energy_at(point1 + 1, db, dt, density_ratio)));
+            f_SW = __ldg(en + point1 * NT + db);
+            f_SE = __ldg(en + point1 * NT + dt);
+            f_NW = __ldg(en + (point1 + 1) * NT + db);  // hint_e <= 498
+            f_NE = __ldg(en + (point1 + 1) * NT + dt);
+            hit = (point1 == 0 || e > (f_SW + density_ratio * (f_SE - f_SW))) &&
+                  (point1 + 1 >= 499 || !(e > (f_NW + density_ratio * (f_NE - f_NW))));
         }
         if (!hit) {
             point1 = 0;
@@ -151,11 +164,13 @@ struct TableEos {
                 if (e > energy_at(half, db, dt, density_ratio)) point1 = half;
                 else point2 = half;
             }
+            f_SW = __ldg(en + point1 * NT + db);
+            f_SE = __ldg(en + point1 * NT + dt);
+            f_NW = __ldg(en + (point1 + 1) * NT + db);
+            f_NE = __ldg(en + (point1 + 1) * NT + dt);
         }
         hint_e = point1;
         const int pt = point1 + 1, pb = point1;  // captured before the (no-op) clamps, T:303-310
-        const double f_NE = __ldg(en + pt * NT + dt), f_SE = __ldg(en + pb * NT + dt);
-        const double f_SW = __ldg(en + pb * NT + db), f_NW = __ldg(en + pt * NT + db);
         // ReverseBilinearInterpolation, T:156-163
         const double f_x_y1 = (1 - density_ratio) * f_SW + density_ratio * f_SE;
         const double f_x_y2 = (1 - density_ratio) * f_NW + density_ratio * f_NE;
@@ -183,8 +198,8 @@ struct TableEos {
         int db, dt, pb, pt;
         double density_ratio;
         const double p = pressure_ex(dv, q, ir, vx, vy, db, dt, density_ratio);
-        bracket(pres, p, 500, hint_p, pb, pt);  // T:366
-        const double p_bottom = __ldg(pres + pb), p_top = __ldg(pres + pt);
+        double p_bottom, p_top;
+        bracket(pres, p, 500, hint_p, pb, pt, p_bottom, p_top);  // T:366
         double pressure_ratio = dv.div(p - p_bottom, p_top - p_bottom);
         if (p_bottom == p_top) pressure_ratio = 1;
         const double ss_NE = __ldg(sound + pt * NT + dt), ss_SE = __ldg(sound + pb * NT + dt);
