@@ -90,8 +90,9 @@ if "c5" in which:
                 "ms_per_step": ms / 20, "cell_updates_per_s": v, "algorithmic_bytes_per_cell_update": 160,
                 "hbm_frac_of_measured": v * 160 / (PEAK * 1e9), "x_sweep_ms": mx / kx, "y_sweep_ms": my / ky,
                 "ieee_fallback_blocks": s.ieee_fallback_count(),
-                "note": "13 EoS lookups per cell-update, each two 9-step bisections (dependent L2/L1 loads) + reverse "
-                        "bilinear interpolation: latency bound, not HBM bound"}
+                "eos_search": "warm-started" if s.eos_search_is_warm else "bisection",
+                "note": "13 EoS lookups per cell-update (density axis search, energy-column search, reverse bilinear "
+                        "interpolation): instruction bound, not HBM bound"}
         s.close()
         exe = os.path.join(ROOT, "oracle", "_ref", "tabeos_ref")
         if os.path.exists(exe):
