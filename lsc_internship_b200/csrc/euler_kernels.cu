@@ -183,6 +183,8 @@ long euler_fix_list_entries(const GridDims& g) {
 // ---------------------------------------------------------------------------------------------------------
 constexpr int EBJ = 128;
 
+long euler_y_block_count(const GridDims& g) { return (long)((g.ny + (EBJ - 2) - 1) / (EBJ - 2)) * g.nxl; }
+
 // stored row that a (possibly ghost) row index refers to: periodic S:217-225, transmissive G:208-214
 __device__ __forceinline__ int emap_row(int j, int ny, int bc) {
     if (j >= 2 && j <= ny + 1) return j;
@@ -248,6 +250,9 @@ __device__ __forceinline__ bool euler_y_sweep_block(const GridDims& g, const Eul
     const int c = jo - 1 + tid;
     D dv;
     const EOS eos = make_eos<EOS>(p);
+    const int nbx = (g.ny + (EBJ - 2) - 1) / (EBJ - 2);  // blocks per column (also in the fix kernel's grid)
+    int* const block_hints = p.tab_hints ? p.tab_hints + 3 * ((size_t)by * nbx + bx) : nullptr;
+    eos.load_hints(block_hints);
     double A[NE], B[NE];  // valid for the threads that update a cell (the only ones that read them)
     euler_y_pass(dv, eos, g, p, ubar, i, c, tid, sH[0], sF[0], A);  // XthenY: y sweep of ubar
     euler_y_pass(dv, eos, g, p, cur, i, c, tid, sH[1], sF[1], B);   // YthenX: y sweep of u (its x sweep is a no-op)
@@ -279,6 +284,7 @@ __device__ __forceinline__ bool euler_y_sweep_block(const GridDims& g, const Eul
         const double sp = eos.cfl_speed(dv, un);
         if (sp > speed) speed = sp;
     }
+    if (tid == EBJ / 2 && updates) eos.store_hints(block_hints);
     return dv.bad();
 }
 

@@ -19,6 +19,7 @@ struct EulerParams {
     const double* tab_pres;   // [500]
     const double* tab_sound;  // [500][500]  [pressure][density]
     const double* tab_en;     // [500][500]
+    int* tab_hints;           // 3 ints per y-sweep block: search brackets carried from step to step (or nullptr)
     int tab_warm;             // 1: the table passed eos_table_is_monotone -> warm-started searches (TableEos)
 };
 
@@ -28,6 +29,7 @@ void launch_euler_x_sweep(const GridDims& g, const EulerParams& p, const double*
 void launch_euler_y_sweep(const GridDims& g, const EulerParams& p, const double* ubar, const double* cur, double* next,
                           unsigned long long* status, unsigned* fix_list, cudaStream_t s);
 long euler_fix_list_entries(const GridDims& g);
+long euler_y_block_count(const GridDims& g);  // blocks of one y-sweep launch (size of EulerParams::tab_hints / 3)
 void launch_euler_max_speed(const GridDims& g, const EulerParams& p, const double* u, int i_lo, int i_hi, int j_lo, int j_hi,
                             unsigned long long* status, cudaStream_t s);
 void launch_euler_x_ghosts(const GridDims& g, int bc_x, double* u, cudaStream_t s);

@@ -24,6 +24,8 @@ __device__ __forceinline__ double escaled_add(double k, double w, double c) { re
 struct IdealEos {
     double gm1, gamma;
     static constexpr bool kHasCflBound = true;
+    __device__ __forceinline__ void load_hints(const int*) const {}
+    __device__ __forceinline__ void store_hints(int*) const {}
 
     // Single-precision UPPER BOUND of cfl_speed(q) / R for the y sweep's warp filter (the construction and its
     // safety argument are those of cfl_speed_over_max_f32 in mhd_physics.cuh): everything in units of the running
@@ -91,6 +93,22 @@ struct TableEos {
     // warm == 0 every search is the reference's bisection.
     int warm;
     mutable int hint_d = 249, hint_e = 249, hint_p = 249;  // previous brackets (density axis, energy column, pressure axis)
+
+    // The y sweep is one thread per cell: its first lookup would have no previous bracket.  Each block therefore
+    // starts from the brackets one of its threads ended with in the previous step (3 ints per block, written
+    // at the end of the kernel; any values in range are valid starting points, a stale hint only costs a miss).
+    __device__ __forceinline__ void load_hints(const int* h) const {
+        if (!warm || !h) return;
+        hint_d = min(max(__ldg(h), 0), 498);
+        hint_e = min(max(__ldg(h + 1), 0), 498);
+        hint_p = min(max(__ldg(h + 2), 0), 499);
+    }
+    __device__ __forceinline__ void store_hints(int* h) const {
+        if (!warm || !h) return;
+        h[0] = hint_d;
+        h[1] = hint_e;
+        h[2] = hint_p;
+    }
 
     // The bisection every lookup of T starts with (T:257-275 etc.): brackets v in the ascending axis; point2
     // starts at 499, or at 500 in SoundSpeed's pressure search (T:366; index 500 is never read).  Returns the

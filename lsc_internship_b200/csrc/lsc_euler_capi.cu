@@ -34,6 +34,7 @@ struct lsc_euler_ctx {
     bool uploaded = false;
     bool profiling = false;
     std::vector<cudaEvent_t> prof_events;
+    int* d_hints = nullptr;            // 3 search brackets per y-sweep block, carried from step to step
     double* d_table = nullptr;         // tabulated EoS: dens[500] pres[500] sound[500*500] energies[500*500]
     std::vector<double> h_table;       // host copy (IC, .dat output)
     bool table_monotone = false;       // energy columns ascending with margin: searches may be warm-started
@@ -54,6 +55,7 @@ void fill_eos(const lsc_euler_ctx* c, lsc::EulerParams& p) {
     p.gamma = c->cfg.gamma;
     p.gm1 = c->cfg.gamma - 1;
     p.tab_dens = p.tab_pres = p.tab_sound = p.tab_en = nullptr;
+    p.tab_hints = nullptr;
     if (c->d_table) {
         p.tab_dens = c->d_table;
         p.tab_pres = c->d_table + TAB_N;
@@ -61,6 +63,7 @@ void fill_eos(const lsc_euler_ctx* c, lsc::EulerParams& p) {
         p.tab_en = c->d_table + 2 * TAB_N + TAB_N * TAB_N;
     }
     p.tab_warm = (c->d_table && c->table_monotone && c->warm_search) ? 1 : 0;
+    p.tab_hints = p.tab_warm ? c->d_hints : nullptr;
 }
 
 int e_read_status(lsc_euler_ctx* c) {
@@ -336,6 +339,7 @@ int lsc_euler_destroy(lsc_euler_ctx* c) {
     if (c->d_fix) cudaFree(c->d_fix);
     if (c->h_status) cudaFreeHost(c->h_status);
     if (c->d_table) cudaFree(c->d_table);
+    if (c->d_hints) cudaFree(c->d_hints);
     if (c->comm) lsc::comm_destroy(c->comm);
     if (c->halo_event) cudaEventDestroy(c->halo_event);
     for (auto e : c->prof_events) cudaEventDestroy(e);
@@ -393,6 +397,15 @@ int lsc_euler_set_eos_table(lsc_euler_ctx* c, const double* densities, const dou
     }
     LSC_CUDA_TRY(cudaMemcpy(c->d_table, t, TAB_DOUBLES * sizeof(double), cudaMemcpyHostToDevice));
     c->table_monotone = lsc::eos_table_is_monotone(energies);
+    if (!c->d_hints) {  // any in-range bracket is a valid starting point: 0 will do
+        const size_t bytes = 3 * sizeof(int) * (size_t)lsc::euler_y_block_count(c->g);
+        if (cudaMalloc(&c->d_hints, bytes) != cudaSuccess) {
+            cudaGetLastError();
+            c->d_hints = nullptr;
+            return lsc_fail(LSC_ENOMEM, "device allocation of the search hints failed");
+        }
+        LSC_CUDA_TRY(cudaMemset(c->d_hints, 0, bytes));
+    }
     return LSC_OK;
 }
 
