@@ -82,7 +82,7 @@ int lsc_device_count(void);
 int lsc_host_alloc(void** ptr, unsigned long long bytes);
 int lsc_host_free(void* ptr);
 
-/* allocate the 15 work arrays of M:673-713 -- here: 3 device-resident SoA states */
+/* allocate the 15 work arrays of M:673-713 -- here: 3 device-resident states (blocked component-major layout, csrc/mhd_kernels.cuh) */
 int lsc_mhd_create(const lsc_mhd_config* cfg, lsc_mhd_ctx** out);
 int lsc_mhd_destroy(lsc_mhd_ctx* ctx);
 

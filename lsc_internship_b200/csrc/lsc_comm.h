@@ -14,7 +14,7 @@ const char* comm_error();
 int comm_unique_id(void* id128);
 Comm* comm_create(const void* id128, int rank, int nranks, const GridDims& g, int nvar);
 void comm_destroy(Comm* c);
-// Fill the ghost columns 0,1 and nxl+2,nxl+3 of every plane of `u`: neighbour ranks' edge columns
+// Fill the ghost columns 0,1 and nxl+2,nxl+3 of `u` (one contiguous run each in the blocked layout): neighbour ranks' edge columns
 // (a ring when bc_x is periodic), boundary images on the end ranks otherwise.
 int comm_exchange_halos(Comm* c, const GridDims& g, int bc_x, double* u, cudaStream_t s);
 // In-place max over ranks of `count` unsigned 64-bit words on the device (bit pattern of a

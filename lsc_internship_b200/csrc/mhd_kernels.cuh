@@ -27,7 +27,7 @@ constexpr int JBLK = 32;  // rows per layout block
 struct GridDims {
     int nxl;        // interior columns held by this rank (slab along x)
     int ny;         // interior rows
-    int pitch;      // padded rows per column (doubles between consecutive i of one plane)
+    int pitch;      // padded rows per column (a column of an NC-component state is NC*pitch doubles)
     size_t plane;   // (nxl+4)*pitch: doubles of one component of a state
 };
 
