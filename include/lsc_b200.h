@@ -136,6 +136,9 @@ int lsc_mhd_step_timed(lsc_mhd_ctx* ctx, long nsteps, float* ms);
  * ms[0] = x sweeps, ms[1] = y sweeps, launches[0..1] = how many of each. */
 int lsc_mhd_set_profiling(lsc_mhd_ctx* ctx, int enabled);
 int lsc_mhd_kernel_times(lsc_mhd_ctx* ctx, double ms[2], long launches[2]);
+/* with profiling enabled and nranks > 1: device time of the NCCL halo exchanges (ms[0], calls[0]) and of the
+ * max-allreduces (ms[1], calls[1]) since the last call (CUDA events on the solver's stream) */
+int lsc_mhd_comm_times(lsc_mhd_ctx* ctx, double ms[2], long calls[2]);
 
 /* How many thread blocks the device-side IEEE fix kernels had to recompute so far because a fast
  * shared-reciprocal division saw an operand outside its guarded exponent window (csrc/fp64_div.cuh; e.g. the

@@ -90,6 +90,7 @@ struct lsc_mhd_ctx {
     bool profiling = false;
     bool relaxed = false;  // LSC_ARITH_RELAXED: FMA-contracted sweeps with 1-multiply quotients (not the parity path)
     std::vector<cudaEvent_t> prof_events;  // quadruples: x begin, x end, y begin, y end
+    std::vector<cudaEvent_t> halo_events, reduce_events;  // pairs around the NCCL halo exchange / max-allreduce
 };
 
 extern "C" {
@@ -312,8 +313,19 @@ int fill_x_ghosts(lsc_mhd_ctx* c, int b) {
         return LSC_OK;
     }
     if (!c->comm) return fail(LSC_ESTATE, "nranks > 1 but lsc_mhd_comm_init was not called");
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (c->profiling) {
+        CUDA_TRY(cudaEventCreate(&e0));
+        CUDA_TRY(cudaEventCreate(&e1));
+        CUDA_TRY(cudaEventRecord(e0, c->stream));
+    }
     int rc = lsc::comm_exchange_halos(c->comm, c->g, to_kernel_bc(c->cfg.bc_x), c->state[b], c->stream);
     if (rc) return fail(LSC_ECOMM, "halo exchange failed: %s", lsc::comm_error());
+    if (c->profiling) {
+        CUDA_TRY(cudaEventRecord(e1, c->stream));
+        c->halo_events.push_back(e0);
+        c->halo_events.push_back(e1);
+    }
     return LSC_OK;
 }
 
@@ -332,8 +344,19 @@ int resolve_pending(lsc_mhd_ctx* c) {
     if (c->in_group) return fail(LSC_ESTATE, "context belongs to a group: use the lsc_mhd_group_* calls");
     if (c->cfg.nranks > 1) {
         if (!c->comm) return fail(LSC_ESTATE, "nranks > 1 but lsc_mhd_comm_init was not called");
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        if (c->profiling) {
+            CUDA_TRY(cudaEventCreate(&e0));
+            CUDA_TRY(cudaEventCreate(&e1));
+            CUDA_TRY(cudaEventRecord(e0, c->stream));
+        }
         if (lsc::comm_allreduce_max_u64(c->comm, c->d_max, 1, c->stream))
             return fail(LSC_ECOMM, "allreduce failed: %s", lsc::comm_error());
+        if (c->profiling) {
+            CUDA_TRY(cudaEventRecord(e1, c->stream));
+            c->reduce_events.push_back(e0);
+            c->reduce_events.push_back(e1);
+        }
     }
     int rc = read_status_local(c);
     if (rc) return rc;
@@ -581,6 +604,26 @@ int lsc_mhd_kernel_times(lsc_mhd_ctx* c, double ms[2], long launches[2]) {
     }
     for (auto e : c->prof_events) cudaEventDestroy(e);
     c->prof_events.clear();
+    return LSC_OK;
+}
+
+int lsc_mhd_comm_times(lsc_mhd_ctx* c, double ms[2], long calls[2]) {
+    if (!c || !ms || !calls) return fail(LSC_EINVAL, "null argument");
+    CUDA_TRY(cudaSetDevice(c->cfg.device));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    std::vector<cudaEvent_t>* lists[2] = {&c->halo_events, &c->reduce_events};
+    for (int w = 0; w < 2; ++w) {
+        ms[w] = 0;
+        calls[w] = 0;
+        for (size_t q = 0; q + 1 < lists[w]->size(); q += 2) {
+            float a = 0;
+            CUDA_TRY(cudaEventElapsedTime(&a, (*lists[w])[q], (*lists[w])[q + 1]));
+            ms[w] += a;
+            calls[w] += 1;
+        }
+        for (auto e : *lists[w]) cudaEventDestroy(e);
+        lists[w]->clear();
+    }
     return LSC_OK;
 }
 

@@ -118,6 +118,13 @@ class MusclNew:
         check(lib().lsc_mhd_kernel_times(self._h, ms, n))
         return ms[0], ms[1], n[0], n[1]
 
+    def comm_times(self):
+        """(halo exchange ms, allreduce ms, halo calls, allreduce calls) since the last call (profiling, nranks > 1)"""
+        ms = (ctypes.c_double * 2)()
+        n = (ctypes.c_long * 2)()
+        check(lib().lsc_mhd_comm_times(self._h, ms, n))
+        return ms[0], ms[1], n[0], n[1]
+
     def ieee_fallback_count(self):
         """Steps recomputed with IEEE division because a fast division flagged an operand."""
         return lib().lsc_mhd_ieee_fallback_count(self._h)
