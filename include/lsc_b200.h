@@ -139,6 +139,12 @@ int lsc_mhd_kernel_times(lsc_mhd_ctx* ctx, double ms[2], long launches[2]);
 /* with profiling enabled and nranks > 1: device time of the NCCL halo exchanges (ms[0], calls[0]) and of the
  * max-allreduces (ms[1], calls[1]) since the last call (CUDA events on the solver's stream) */
 int lsc_mhd_comm_times(lsc_mhd_ctx* ctx, double ms[2], long calls[2]);
+/* Halo/compute overlap (default on).  With nranks > 1 and a slab of >= 8 columns a step
+ * sweeps the four slab-edge columns in y first and issues their NCCL exchange on a second, high-priority stream
+ * while the interior columns are still being swept; the next call that needs the ghost columns waits for it on
+ * the device.  0 restores the serial order (y sweep, then exchange); 2 splits the y sweep on a single rank too
+ * (the ghost-column kernel then takes the place of the exchange; for tests).  Bit-identical in every mode. */
+int lsc_mhd_set_overlap(lsc_mhd_ctx* ctx, int enabled);
 
 /* How many thread blocks the device-side IEEE fix kernels had to recompute so far because a fast
  * shared-reciprocal division saw an operand outside its guarded exponent window (csrc/fp64_div.cuh; e.g. the

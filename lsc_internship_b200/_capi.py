@@ -62,7 +62,7 @@ EXPORTS = [
     "lsc_mhd_initial_condition", "lsc_mhd_upload", "lsc_mhd_init_problem", "lsc_mhd_step",
     "lsc_mhd_run_until", "lsc_mhd_get_scalars", "lsc_mhd_download", "lsc_mhd_write_dat",
     "lsc_comm_unique_id", "lsc_mhd_comm_init", "lsc_mhd_kat_hllc", "lsc_mhd_kat_fluxdef", "lsc_mhd_kat_cfl_bound", "lsc_mhd_set_arithmetic",
-    "lsc_kernel_launch_count", "lsc_mhd_step_timed", "lsc_mhd_set_profiling", "lsc_mhd_kernel_times", "lsc_mhd_comm_times", "lsc_kat_division", "lsc_mhd_ieee_fallback_count", "lsc_mhd_group_step", "lsc_mhd_fill_ghost_ring",
+    "lsc_kernel_launch_count", "lsc_mhd_step_timed", "lsc_mhd_set_profiling", "lsc_mhd_kernel_times", "lsc_mhd_comm_times", "lsc_mhd_set_overlap", "lsc_kat_division", "lsc_mhd_ieee_fallback_count", "lsc_mhd_group_step", "lsc_mhd_fill_ghost_ring",
     "lsc_euler_create", "lsc_euler_destroy", "lsc_euler_initial_condition", "lsc_euler_upload",
     "lsc_euler_init_problem", "lsc_euler_step", "lsc_euler_step_timed", "lsc_euler_run_until",
     "lsc_euler_get_scalars", "lsc_euler_download", "lsc_euler_write_dat", "lsc_euler_ieee_fallback_count",
@@ -99,6 +99,7 @@ def lib():
     L.lsc_mhd_step.argtypes = [vp, ctypes.c_long]
     L.lsc_mhd_step_timed.argtypes = [vp, ctypes.c_long, ctypes.POINTER(ctypes.c_float)]
     L.lsc_mhd_set_profiling.argtypes = [vp, ctypes.c_int]
+    L.lsc_mhd_set_overlap.argtypes = [vp, ctypes.c_int]
     L.lsc_mhd_kernel_times.argtypes = [vp, dp, ctypes.POINTER(ctypes.c_long)]
     L.lsc_mhd_comm_times.argtypes = [vp, dp, ctypes.POINTER(ctypes.c_long)]
     L.lsc_mhd_run_until.argtypes = [vp, ctypes.c_double, DUMP_CB, LOG_CB, vp, ctypes.POINTER(ctypes.c_long)]

@@ -59,6 +59,13 @@ int lsc_fail(int code, const char* fmt, ...) {
     return code;
 }
 
+static cudaError_t create_comm_stream(cudaStream_t* s) {
+    int lo = 0, hi = 0;  // numerically lowest = highest priority: the few NCCL blocks go ahead of queued sweep blocks
+    cudaError_t e = cudaDeviceGetStreamPriorityRange(&lo, &hi);
+    if (e != cudaSuccess) return e;
+    return cudaStreamCreateWithPriority(s, cudaStreamNonBlocking, hi);
+}
+
 struct lsc_mhd_ctx {
     lsc_mhd_config cfg;
     int nxl = 0, i0 = 0;  // slab: interior columns, first global interior column (0-based)
@@ -68,7 +75,7 @@ struct lsc_mhd_ctx {
     double* state[3] = {nullptr, nullptr, nullptr};
     int cur = 0, bar = 1, prev = 2;
     // status words: [0] bit pattern of the max signal speed of state[cur], [1]/[2] number of x/y sweep blocks
-    // recomputed with IEEE division in the last step (mhd_kernels.cu), [3] unused
+    // recomputed with IEEE division in the last step (mhd_kernels.cu), [3] the same for the slab-edge y launch
     unsigned long long* d_max = nullptr;
     unsigned long long* h_max = nullptr;  // pinned copy
     unsigned* d_fix = nullptr;            // y-sweep block indices flagged by the fast sweep
@@ -80,6 +87,11 @@ struct lsc_mhd_ctx {
     double* d_stage = nullptr;            // AoS staging for transfers
     int stage_cols = 0;
     cudaStream_t stream = nullptr;
+    // halo/compute overlap: the exchange runs on its own high-priority stream behind the
+    // slab-edge columns of the y sweep while `stream` sweeps the interior
+    cudaStream_t comm_stream = nullptr;
+    cudaEvent_t edges_done = nullptr, halo_done = nullptr;
+    int overlap = 1;  // 0 off, 1 when the slab has NCCL neighbours, 2 always (single rank: the ghost kernel overlaps)
     double t = 0, dt = 0, ch = 0;
     long step = 0;
     bool uploaded = false;
@@ -169,12 +181,16 @@ int lsc_mhd_create(const lsc_mhd_config* cfg, lsc_mhd_ctx** out) {
     c->stage_cols = (int)cols;
     if (cudaMalloc(&c->d_stage, col_bytes * (size_t)cols) != cudaSuccess ||
         cudaMalloc(&c->d_max, STATUS_BYTES) != cudaSuccess ||
-        cudaMalloc(&c->d_fix, sizeof(unsigned) * (size_t)lsc::y_sweep_block_count(c->g)) != cudaSuccess ||
+        cudaMalloc(&c->d_fix, sizeof(unsigned) * (size_t)(lsc::y_sweep_block_count(c->g) +
+                                                          lsc::y_edge_block_count(c->g))) != cudaSuccess ||
         cudaMalloc(&c->d_xflags, sizeof(unsigned) * (size_t)lsc::x_sweep_block_count(c->g)) != cudaSuccess ||
         cudaMemset(c->d_xflags, 0, sizeof(unsigned) * (size_t)lsc::x_sweep_block_count(c->g)) != cudaSuccess ||
         cudaHostAlloc(&c->h_max, STATUS_BYTES, cudaHostAllocDefault) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreateWithFlags(&c->halo_event, cudaEventDisableTiming) != cudaSuccess) {
+        cudaEventCreateWithFlags(&c->halo_event, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->edges_done, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->halo_done, cudaEventDisableTiming) != cudaSuccess ||
+        create_comm_stream(&c->comm_stream) != cudaSuccess) {
         cudaGetLastError();
         lsc_mhd_destroy(c);
         return fail(LSC_ENOMEM, "allocation of staging / scalars / stream failed");
@@ -196,6 +212,9 @@ int lsc_mhd_destroy(lsc_mhd_ctx* c) {
     if (c->d_max) cudaFree(c->d_max);
     if (c->h_max) cudaFreeHost(c->h_max);
     if (c->halo_event) cudaEventDestroy(c->halo_event);
+    if (c->edges_done) cudaEventDestroy(c->edges_done);
+    if (c->halo_done) cudaEventDestroy(c->halo_done);
+    if (c->comm_stream) cudaStreamDestroy(c->comm_stream);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
     return LSC_OK;
@@ -305,9 +324,10 @@ int lsc_mhd_get_scalars(const lsc_mhd_ctx* c, double* t, double* dt, double* ch,
 namespace {
 
 // Boundary images / neighbour data into the two ghost columns on each side of state b.
-int fill_x_ghosts(lsc_mhd_ctx* c, int b) {
+int fill_x_ghosts(lsc_mhd_ctx* c, int b, cudaStream_t s = nullptr) {
+    if (!s) s = c->stream;
     if (c->cfg.nranks == 1) {
-        lsc::launch_x_ghosts(c->g, to_kernel_bc(c->cfg.bc_x), c->state[b], c->stream);
+        lsc::launch_x_ghosts(c->g, to_kernel_bc(c->cfg.bc_x), c->state[b], s);
         lsc_count_launches(1);
         CUDA_TRY(cudaGetLastError());
         return LSC_OK;
@@ -317,16 +337,22 @@ int fill_x_ghosts(lsc_mhd_ctx* c, int b) {
     if (c->profiling) {
         CUDA_TRY(cudaEventCreate(&e0));
         CUDA_TRY(cudaEventCreate(&e1));
-        CUDA_TRY(cudaEventRecord(e0, c->stream));
+        CUDA_TRY(cudaEventRecord(e0, s));
     }
-    int rc = lsc::comm_exchange_halos(c->comm, c->g, to_kernel_bc(c->cfg.bc_x), c->state[b], c->stream);
+    int rc = lsc::comm_exchange_halos(c->comm, c->g, to_kernel_bc(c->cfg.bc_x), c->state[b], s);
     if (rc) return fail(LSC_ECOMM, "halo exchange failed: %s", lsc::comm_error());
     if (c->profiling) {
-        CUDA_TRY(cudaEventRecord(e1, c->stream));
+        CUDA_TRY(cudaEventRecord(e1, s));
         c->halo_events.push_back(e0);
         c->halo_events.push_back(e1);
     }
     return LSC_OK;
+}
+
+// Halo exchange overlapped with the interior of the y sweep: NCCL slabs wide enough to have an interior.
+bool overlap_active(const lsc_mhd_ctx* c) {
+    if (c->in_group || c->nxl < 8) return false;
+    return c->overlap == 2 || (c->overlap == 1 && c->cfg.nranks > 1 && c->comm);
 }
 
 // 16-byte readback of {max signal speed bits, fast-division flag} of this context (no communication).
@@ -360,7 +386,7 @@ int resolve_pending(lsc_mhd_ctx* c) {
     }
     int rc = read_status_local(c);
     if (rc) return rc;
-    if (c->pending_step) c->ieee_redos += (long)(c->h_max[1] + c->h_max[2]);
+    if (c->pending_step) c->ieee_redos += (long)(c->h_max[1] + c->h_max[2] + c->h_max[3]);
     std::memcpy(&c->max_speed, &c->h_max[0], sizeof(double));
     c->pending = false;
     return LSC_OK;
@@ -415,14 +441,34 @@ int launch_sweeps(lsc_mhd_ctx* c) {
     p.hdtdh = 0.5 * (dt / c->dy);
     p.bc_lo = p.bc_hi = to_kernel_bc(c->cfg.bc_y);
     if (c->profiling) CUDA_TRY(cudaEventRecord(ev[2], c->stream));
-    if (c->relaxed)
-        lsc::launch_y_sweep_relaxed(c->g, p, c->state[c->bar], c->state[c->cur], c->state[c->prev], c->d_max,
-                                    c->d_fix, c->stream);
-    else
-        lsc::launch_y_sweep(c->g, p, c->state[c->bar], c->state[c->cur], c->state[c->prev], c->d_max, c->d_fix,
-                            c->stream);
+    auto y_launch = [&](int part) {
+        if (c->relaxed)
+            lsc::launch_y_sweep_relaxed(c->g, p, c->state[c->bar], c->state[c->cur], c->state[c->prev], c->d_max,
+                                        c->d_fix, c->stream, part);
+        else
+            lsc::launch_y_sweep(c->g, p, c->state[c->bar], c->state[c->cur], c->state[c->prev], c->d_max, c->d_fix,
+                                c->stream, part);
+    };
+    const bool overlapped = overlap_active(c);
+    if (overlapped) {
+        // The four slab-edge columns of u^{n+1} (what the x neighbours need) first; their halo exchange (:971 for
+        // the ghost columns) then runs on comm_stream while this stream sweeps the interior columns.  The interior
+        // launch neither reads nor writes the edge or ghost columns of the new state.
+        y_launch(lsc::Y_EDGES);
+        CUDA_TRY(cudaEventRecord(c->edges_done, c->stream));
+        y_launch(lsc::Y_INTERIOR);
+        if (c->profiling) CUDA_TRY(cudaEventRecord(ev[3], c->stream));  // y time = both launches, not the halo wait
+        CUDA_TRY(cudaStreamWaitEvent(c->comm_stream, c->edges_done, 0));
+        int rc = fill_x_ghosts(c, c->prev, c->comm_stream);
+        if (rc) return rc;
+        CUDA_TRY(cudaEventRecord(c->halo_done, c->comm_stream));
+        CUDA_TRY(cudaStreamWaitEvent(c->stream, c->halo_done, 0));  // everything later on `stream` sees the halos
+        lsc_count_launches(2);
+    } else {
+        y_launch(lsc::Y_ALL);
+        if (c->profiling) CUDA_TRY(cudaEventRecord(ev[3], c->stream));
+    }
     if (c->profiling) {
-        CUDA_TRY(cudaEventRecord(ev[3], c->stream));
         for (auto e : ev) c->prof_events.push_back(e);
     }
     lsc_count_launches(4);
@@ -447,8 +493,10 @@ int step_once(lsc_mhd_ctx* c) {
         if (rc) return rc;
         c->ghosts_current = true;
     }
+    const bool overlapped = overlap_active(c);
     rc = launch_sweeps(c);
     if (rc) return rc;
+    if (overlapped) return LSC_OK;    // the exchange was issued behind the slab-edge columns of the y sweep
     return fill_x_ghosts(c, c->cur);  // applyBoundaryConditions(u) (:971)
 }
 
@@ -498,7 +546,7 @@ int group_resolve(lsc_mhd_ctx** g, int n) {
         mx = std::max(mx, g[r]->h_max[0]);
     }
     for (int r = 0; r < n; ++r) {
-        if (g[r]->pending_step) g[r]->ieee_redos += (long)(g[r]->h_max[1] + g[r]->h_max[2]);
+        if (g[r]->pending_step) g[r]->ieee_redos += (long)(g[r]->h_max[1] + g[r]->h_max[2] + g[r]->h_max[3]);
         std::memcpy(&g[r]->max_speed, &mx, sizeof(double));
         g[r]->pending = false;
     }
@@ -580,6 +628,13 @@ int lsc_mhd_step_timed(lsc_mhd_ctx* c, long nsteps, float* ms) {
 }
 
 long lsc_mhd_ieee_fallback_count(const lsc_mhd_ctx* c) { return c ? c->ieee_redos : -1; }
+
+int lsc_mhd_set_overlap(lsc_mhd_ctx* c, int enabled) {
+    if (!c) return fail(LSC_EINVAL, "null context");
+    if (enabled < 0 || enabled > 2) return fail(LSC_EINVAL, "overlap mode %d", enabled);
+    c->overlap = enabled;
+    return LSC_OK;
+}
 
 int lsc_mhd_set_profiling(lsc_mhd_ctx* c, int enabled) {
     if (!c) return fail(LSC_EINVAL, "null argument");

@@ -487,11 +487,13 @@ __global__ void __launch_bounds__(BJ, YS_MINB) y_sweep_kernel(const GridDims g, 
                                                               const double* __restrict__ cur,
                                                               double* __restrict__ next,
                                                               unsigned long long* __restrict__ status,
-                                                              unsigned* __restrict__ fix_list) {
+                                                              unsigned* __restrict__ fix_list, const YCols yc) {
     double speed;
-    const bool bad = y_sweep_block<D>(g, p, ubar, cur, next, blockIdx.x, blockIdx.y, speed, status);
+    // column of this block row: a launch covers all columns, the four slab-edge columns or the rest (YCols)
+    const int col = yc.c0 + (int)blockIdx.y + ((int)blockIdx.y >= yc.jump_at ? yc.jump : 0);
+    const bool bad = y_sweep_block<D>(g, p, ubar, cur, next, blockIdx.x, col, speed, status);
     if (__syncthreads_or(bad)) {  // whole block is recomputed by the fix kernel; its maximum must not count
-        if (threadIdx.x == 0) fix_list[atomicAdd(status + 2, 1ull)] = blockIdx.y * gridDim.x + blockIdx.x;
+        if (threadIdx.x == 0) fix_list[atomicAdd(status + yc.counter, 1ull)] = col * gridDim.x + blockIdx.x;
     } else {
         warp_max_to_global(speed, status);
     }
@@ -502,8 +504,9 @@ __global__ void __launch_bounds__(BJ) y_sweep_fix_kernel(const GridDims g, const
                                                          const double* __restrict__ ubar,
                                                          const double* __restrict__ cur, double* __restrict__ next,
                                                          unsigned long long* __restrict__ status,
-                                                         const unsigned* __restrict__ fix_list, const unsigned nbx) {
-    const unsigned long long count = status[2];
+                                                         const unsigned* __restrict__ fix_list, const unsigned nbx,
+                                                         const int counter) {
+    const unsigned long long count = status[counter];
     for (unsigned long long q = blockIdx.x; q < count; q += gridDim.x) {
         const unsigned bid = fix_list[q];
         double speed;
@@ -514,21 +517,28 @@ __global__ void __launch_bounds__(BJ) y_sweep_fix_kernel(const GridDims g, const
 }
 
 void launch_y_sweep(const GridDims& g, const SweepParams& p, const double* u_bar, const double* u_cur,
-                    double* u_next, unsigned long long* status, unsigned* fix_list, cudaStream_t s) {
+                    double* u_next, unsigned long long* status, unsigned* fix_list, cudaStream_t s,
+                    int part) {
     dim3 block(BJ);
-    dim3 grid((g.ny + (BJ - 2) - 1) / (BJ - 2), g.nxl);
-    y_sweep_kernel<MHD_FAST_POLICY><<<grid, block, 0, s>>>(g, p, u_bar, u_cur, u_next, status, fix_list);
+    const YCols yc = y_columns(g, part);
+    // the slab-edge launch keeps its own list (behind the y_sweep_block_count entries of the others) and counter
+    unsigned* list = fix_list + (part == Y_EDGES ? y_sweep_block_count(g) : 0);
+    dim3 grid((g.ny + (BJ - 2) - 1) / (BJ - 2), yc.ncols);
+    y_sweep_kernel<MHD_FAST_POLICY><<<grid, block, 0, s>>>(g, p, u_bar, u_cur, u_next, status, list, yc);
     const unsigned nfix = (unsigned)std::min<long>(FIX_GRID, (long)grid.x * grid.y);
-    y_sweep_fix_kernel<<<nfix, block, 0, s>>>(g, p, u_bar, u_cur, u_next, status, fix_list, grid.x);
+    y_sweep_fix_kernel<<<nfix, block, 0, s>>>(g, p, u_bar, u_cur, u_next, status, list, grid.x, yc.counter);
 }
 
 long y_sweep_block_count(const GridDims& g) { return (long)((g.ny + (BJ - 2) - 1) / (BJ - 2)) * g.nxl; }
+long y_edge_block_count(const GridDims& g) { return (long)((g.ny + (BJ - 2) - 1) / (BJ - 2)) * 4; }
 #else  // LSC_RELAXED_TU
 void launch_y_sweep_relaxed(const GridDims& g, const SweepParams& p, const double* u_bar, const double* u_cur,
-                            double* u_next, unsigned long long* status, unsigned* fix_list, cudaStream_t s) {
+                            double* u_next, unsigned long long* status, unsigned* fix_list, cudaStream_t s,
+                            int part) {
     dim3 block(BJ);
-    dim3 grid((g.ny + (BJ - 2) - 1) / (BJ - 2), g.nxl);
-    y_sweep_kernel<RelaxedDiv><<<grid, block, 0, s>>>(g, p, u_bar, u_cur, u_next, status, fix_list);
+    const YCols yc = y_columns(g, part);
+    dim3 grid((g.ny + (BJ - 2) - 1) / (BJ - 2), yc.ncols);
+    y_sweep_kernel<RelaxedDiv><<<grid, block, 0, s>>>(g, p, u_bar, u_cur, u_next, status, fix_list, yc);
 }
 #endif
 #ifndef LSC_RELAXED_TU

@@ -82,18 +82,35 @@ struct SweepParams {
 // blocks in which a fast division saw an operand outside its guarded window; those block indices are in
 // recomputed with IEEE division by the fix kernel launched right behind each sweep.  The x sweep marks them in
 // x_flags (x_sweep_block_count entries, all zero on entry and again on exit), the y sweep lists them in fix_list
-// (y_sweep_block_count entries).
+// (y_sweep_block_count entries, plus y_edge_block_count for the slab-edge launch, which counts in status[3]).
 void launch_x_sweep(const GridDims& g, const SweepParams& p, const double* u_cur, const double* u_prev,
                     double* u_bar, unsigned long long* status, unsigned* x_flags, cudaStream_t s);
+// `part` selects the columns of one y-sweep launch (halo/compute overlap): Y_ALL, or
+// Y_EDGES (local columns 0,1 and nxl-2,nxl-1: what the x neighbours need) followed by Y_INTERIOR (the rest), so
+// that the halo exchange of the edge columns runs while the interior is still being swept.  Needs nxl >= 8.
+enum : int { Y_ALL = 0, Y_EDGES = 1, Y_INTERIOR = 2 };
+struct YCols {
+    int c0, jump_at, jump;  // local column of block row by: c0 + by + (by >= jump_at ? jump : 0)
+    int ncols;              // block rows of the launch
+    int counter;            // status word that counts this launch's flagged blocks (2, slab edges: 3)
+};
+inline YCols y_columns(const GridDims& g, int part) {
+    if (part == Y_EDGES) return YCols{0, 2, g.nxl - 4, 4, 3};
+    if (part == Y_INTERIOR) return YCols{2, 0x7fffffff, 0, g.nxl - 4, 2};
+    return YCols{0, 0x7fffffff, 0, g.nxl, 2};
+}
 void launch_y_sweep(const GridDims& g, const SweepParams& p, const double* u_bar, const double* u_cur,
-                    double* u_next, unsigned long long* status, unsigned* fix_list, cudaStream_t s);
+                    double* u_next, unsigned long long* status, unsigned* fix_list, cudaStream_t s,
+                    int part = Y_ALL);
 // relaxed-arithmetic instantiations (mhd_kernels_relaxed.cu: FMA contraction, 1-multiply quotients; no fix pass)
 void launch_x_sweep_relaxed(const GridDims& g, const SweepParams& p, const double* u_cur, const double* u_prev,
                             double* u_bar, unsigned* x_flags, cudaStream_t s);
 void launch_y_sweep_relaxed(const GridDims& g, const SweepParams& p, const double* u_bar, const double* u_cur,
-                            double* u_next, unsigned long long* status, unsigned* fix_list, cudaStream_t s);
+                            double* u_next, unsigned long long* status, unsigned* fix_list, cudaStream_t s,
+                            int part = Y_ALL);
 long x_sweep_block_count(const GridDims& g);
 long y_sweep_block_count(const GridDims& g);
+long y_edge_block_count(const GridDims& g);
 void launch_x_ghosts(const GridDims& g, int bc_x, double* u, cudaStream_t s);
 // transmissive image of ONE side (0 = low, 1 = high): end ranks of a non-periodic slab decomposition
 void launch_x_ghosts_side(const GridDims& g, int hi_side, double* u, cudaStream_t s);

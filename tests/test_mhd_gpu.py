@@ -305,6 +305,33 @@ def test_slab_decomposition_is_bit_invariant(prob, nx, ny, dom, bcx, bcy, nslabs
     g.close()
 
 
+@pytest.mark.parametrize("prob,nx,ny,dom,bcx,bcy", [
+    ("ot", 96, 64, (0.0, 1.0, 0.0, 1.0), "periodic", "periodic"),
+    ("kh", 70, 130, (0.0, 1.0, -1.0, 1.0), "transmissive", "reflective"),
+    ("ot", 8, 40, (0.0, 1.0, 0.0, 1.0), "periodic", "periodic"),   # narrowest slab that is split (4 + 4 columns)
+])
+def test_split_y_sweep_with_overlapped_ghost_fill(prob, nx, ny, dom, bcx, bcy):
+    """The halo/compute overlap order: slab-edge columns of the y sweep first, ghost/halo fill on the
+    second stream while the interior is swept.  Mode 2 runs that order on one rank; it must not change a bit,
+    including when out-of-window operands put edge AND interior blocks on the IEEE fix lists."""
+    cfg = mhd_cfg(nx, ny, dom, bcx=bcx, bcy=bcy)
+    u0 = mhd_ic(cfg, prob)
+    u0[2:4, 7:30, 3] = 1e-200       # first edge columns
+    u0[nx // 2, 5:9, 7] = -1e-180   # interior
+    u0[nx + 1, 12:20, 3] = 1e-200   # last edge column
+    o = OracleMhd(cfg, u0)
+    s = lsc.MusclNew(nx, ny, dom[0], dom[1], dom[2], dom[3], bc_x=bcx, bc_y=bcy, problem=prob)
+    s.set_overlap(2)
+    s.upload(u0)
+    log = o.step(6)
+    s.step(6)
+    t, dt, ch, n = s.scalars()
+    assert (t, dt, ch) == tuple(log[-1]) and n == 6
+    assert s.ieee_fallback_count() >= 3
+    assert np.array_equal(bits(s.download()), bits(o.state()[0]))
+    s.close()
+
+
 def test_nccl_slab_path_is_bit_invariant():
     """One process per GPU over NCCL (the bench.py --gpus N path).  Needs >= 2 GPUs; skipped otherwise."""
     import subprocess
