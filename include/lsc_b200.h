@@ -287,6 +287,7 @@ int lsc_euler_tabeos_write_dat(const lsc_euler_config* cfg, const double* aos, c
 int lsc_euler_kat_cfl_bound(int device, long n, const double* U, double gamma, double run_max,
                             double* exact_and_bound);
 int lsc_euler_set_profiling(lsc_euler_ctx* ctx, int enabled);
+int lsc_euler_set_overlap(lsc_euler_ctx* ctx, int enabled);   /* as lsc_mhd_set_overlap: 0 serial, 1 default, 2 always */
 int lsc_euler_kernel_times(lsc_euler_ctx* ctx, double ms[2], long launches[2]);
 
 /* number of kernels this library has launched in this process (for bench.py's gpu_launches) */

@@ -66,7 +66,7 @@ EXPORTS = [
     "lsc_euler_create", "lsc_euler_destroy", "lsc_euler_initial_condition", "lsc_euler_upload",
     "lsc_euler_init_problem", "lsc_euler_step", "lsc_euler_step_timed", "lsc_euler_run_until",
     "lsc_euler_get_scalars", "lsc_euler_download", "lsc_euler_write_dat", "lsc_euler_ieee_fallback_count",
-    "lsc_euler_set_profiling", "lsc_euler_kernel_times", "lsc_euler_local_nx", "lsc_euler_local_i0",
+    "lsc_euler_set_profiling", "lsc_euler_set_overlap", "lsc_euler_kernel_times", "lsc_euler_local_nx", "lsc_euler_local_i0",
     "lsc_euler_comm_init", "lsc_euler_group_step", "lsc_eos_table_read", "lsc_euler_set_eos_table",
     "lsc_euler_tabeos_initial_condition", "lsc_euler_tabeos_write_dat", "lsc_euler_kat_cfl_bound", "lsc_euler_set_eos_search", "lsc_euler_eos_search_is_warm",
 ]
@@ -143,6 +143,7 @@ def lib():
     L.lsc_euler_ieee_fallback_count.argtypes = [vp]
     L.lsc_euler_ieee_fallback_count.restype = ctypes.c_long
     L.lsc_euler_set_profiling.argtypes = [vp, ctypes.c_int]
+    L.lsc_euler_set_overlap.argtypes = [vp, ctypes.c_int]
     L.lsc_euler_kernel_times.argtypes = [vp, dp, ctypes.POINTER(ctypes.c_long)]
     L.lsc_mhd_fill_ghost_ring.argtypes = [ctypes.POINTER(MhdConfig), dp]
     L.lsc_mhd_ieee_fallback_count.argtypes = [vp]

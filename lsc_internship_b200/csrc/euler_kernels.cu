@@ -172,6 +172,8 @@ void launch_euler_x_sweep(const GridDims& g, const EulerParams& p, const double*
     }
 }
 
+long euler_edge_list_entries(const GridDims& g) { return (long)((g.ny + 125) / 126) * 4; }
+
 long euler_fix_list_entries(const GridDims& g) {
     const long xb = (long)((g.ny + 127) / 128) * ((g.nxl + 7) / 8);
     const long yb = (long)((g.ny + 125) / 126) * g.nxl;
@@ -316,11 +318,13 @@ __global__ void __launch_bounds__(EBJ, 4) euler_y_sweep_kernel(const GridDims g,
                                                                const double* __restrict__ cur,
                                                                double* __restrict__ next,
                                                                unsigned long long* __restrict__ status,
-                                                               unsigned* __restrict__ fix_list) {
+                                                               unsigned* __restrict__ fix_list, const YCols yc) {
     double speed;
-    const bool bad = euler_y_sweep_block<D, EOS>(g, p, ubar, cur, next, blockIdx.x, blockIdx.y, speed, status);
+    // column of this block row: all columns, the four slab-edge columns or the rest (YCols, mhd_kernels.cuh)
+    const int col = yc.c0 + (int)blockIdx.y + ((int)blockIdx.y >= yc.jump_at ? yc.jump : 0);
+    const bool bad = euler_y_sweep_block<D, EOS>(g, p, ubar, cur, next, blockIdx.x, col, speed, status);
     if (__syncthreads_or(bad)) {  // whole block is recomputed by the fix kernel; its maximum must not count
-        if (threadIdx.x == 0) fix_list[atomicAdd(status + 2, 1ull)] = blockIdx.y * gridDim.x + blockIdx.x;
+        if (threadIdx.x == 0) fix_list[atomicAdd(status + yc.counter, 1ull)] = col * gridDim.x + blockIdx.x;
     } else if (!std::is_same<D, IeeeDiv>::value && EOS::kHasCflBound) {
         warp_max_to_global(speed, status);
     } else {
@@ -335,8 +339,8 @@ __global__ void __launch_bounds__(EBJ) euler_y_sweep_fix_kernel(const GridDims g
                                                                 double* __restrict__ next,
                                                                 unsigned long long* __restrict__ status,
                                                                 const unsigned* __restrict__ fix_list,
-                                                                const unsigned nbx) {
-    const unsigned long long count = status[2];
+                                                                const unsigned nbx, const int counter) {
+    const unsigned long long count = status[counter];
     for (unsigned long long q = blockIdx.x; q < count; q += gridDim.x) {
         const unsigned bid = fix_list[q];
         double speed;
@@ -347,16 +351,19 @@ __global__ void __launch_bounds__(EBJ) euler_y_sweep_fix_kernel(const GridDims g
 }
 
 void launch_euler_y_sweep(const GridDims& g, const EulerParams& p, const double* ubar, const double* cur, double* next,
-                          unsigned long long* status, unsigned* fix_list, cudaStream_t s) {
+                          unsigned long long* status, unsigned* fix_list, cudaStream_t s, int part) {
     dim3 block(EBJ);
-    dim3 grid((g.ny + (EBJ - 2) - 1) / (EBJ - 2), g.nxl);
+    const YCols yc = y_columns(g, part);
+    // the slab-edge launch keeps its own list (behind the euler_fix_list_entries of the others) and counter
+    unsigned* list = fix_list + (part == Y_EDGES ? euler_fix_list_entries(g) : 0);
+    dim3 grid((g.ny + (EBJ - 2) - 1) / (EBJ - 2), yc.ncols);
     const unsigned nfix = (unsigned)std::min<long>(EFIX_GRID, (long)grid.x * grid.y);
     if (p.tab_dens) {
-        euler_y_sweep_kernel<EULER_FAST_POLICY, TableEos><<<grid, block, 0, s>>>(g, p, ubar, cur, next, status, fix_list);
-        euler_y_sweep_fix_kernel<TableEos><<<nfix, block, 0, s>>>(g, p, ubar, cur, next, status, fix_list, grid.x);
+        euler_y_sweep_kernel<EULER_FAST_POLICY, TableEos><<<grid, block, 0, s>>>(g, p, ubar, cur, next, status, list, yc);
+        euler_y_sweep_fix_kernel<TableEos><<<nfix, block, 0, s>>>(g, p, ubar, cur, next, status, list, grid.x, yc.counter);
     } else {
-        euler_y_sweep_kernel<EULER_FAST_POLICY, IdealEos><<<grid, block, 0, s>>>(g, p, ubar, cur, next, status, fix_list);
-        euler_y_sweep_fix_kernel<IdealEos><<<nfix, block, 0, s>>>(g, p, ubar, cur, next, status, fix_list, grid.x);
+        euler_y_sweep_kernel<EULER_FAST_POLICY, IdealEos><<<grid, block, 0, s>>>(g, p, ubar, cur, next, status, list, yc);
+        euler_y_sweep_fix_kernel<IdealEos><<<nfix, block, 0, s>>>(g, p, ubar, cur, next, status, list, grid.x, yc.counter);
     }
 }
 

@@ -26,9 +26,12 @@ struct EulerParams {
 // status / fix_list as in mhd_kernels.cuh: [0] max speed bits, [1]/[2] x/y blocks recomputed with IEEE division
 void launch_euler_x_sweep(const GridDims& g, const EulerParams& p, const double* cur, double* ubar,
                           unsigned long long* status, unsigned* fix_list, cudaStream_t s);
+// part: Y_ALL, or Y_EDGES then Y_INTERIOR for the halo/compute overlap (mhd_kernels.cuh); the edge launch counts its
+// flagged blocks in status[3] and lists them behind the euler_fix_list_entries of the other launches
 void launch_euler_y_sweep(const GridDims& g, const EulerParams& p, const double* ubar, const double* cur, double* next,
-                          unsigned long long* status, unsigned* fix_list, cudaStream_t s);
+                          unsigned long long* status, unsigned* fix_list, cudaStream_t s, int part = Y_ALL);
 long euler_fix_list_entries(const GridDims& g);
+long euler_edge_list_entries(const GridDims& g);
 long euler_y_block_count(const GridDims& g);  // blocks of one y-sweep launch (size of EulerParams::tab_hints / 3)
 void launch_euler_max_speed(const GridDims& g, const EulerParams& p, const double* u, int i_lo, int i_hi, int j_lo, int j_hi,
                             unsigned long long* status, cudaStream_t s);

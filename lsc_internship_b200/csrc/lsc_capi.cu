@@ -13,6 +13,7 @@
 
 #include "../../include/lsc_b200.h"
 #include "lsc_comm.h"
+#include "lsc_common.h"
 #include "mhd_host.h"
 #include "mhd_kernels.cuh"
 
@@ -57,13 +58,6 @@ int lsc_fail(int code, const char* fmt, ...) {
     vsnprintf(g_err, sizeof g_err, fmt, ap);
     va_end(ap);
     return code;
-}
-
-static cudaError_t create_comm_stream(cudaStream_t* s) {
-    int lo = 0, hi = 0;  // numerically lowest = highest priority: the few NCCL blocks go ahead of queued sweep blocks
-    cudaError_t e = cudaDeviceGetStreamPriorityRange(&lo, &hi);
-    if (e != cudaSuccess) return e;
-    return cudaStreamCreateWithPriority(s, cudaStreamNonBlocking, hi);
 }
 
 struct lsc_mhd_ctx {
@@ -190,7 +184,7 @@ int lsc_mhd_create(const lsc_mhd_config* cfg, lsc_mhd_ctx** out) {
         cudaEventCreateWithFlags(&c->halo_event, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->edges_done, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->halo_done, cudaEventDisableTiming) != cudaSuccess ||
-        create_comm_stream(&c->comm_stream) != cudaSuccess) {
+        lsc_create_comm_stream(&c->comm_stream) != cudaSuccess) {
         cudaGetLastError();
         lsc_mhd_destroy(c);
         return fail(LSC_ENOMEM, "allocation of staging / scalars / stream failed");

@@ -7,6 +7,15 @@
 void lsc_count_launches(unsigned long long n);
 int lsc_fail(int code, const char* fmt, ...);  // records the message lsc_last_error() returns
 
+// stream for the halo exchange that overlaps a sweep: highest priority, so that the few NCCL / ghost-column blocks
+// are scheduled ahead of the queued sweep blocks
+static inline cudaError_t lsc_create_comm_stream(cudaStream_t* s) {
+    int lo = 0, hi = 0;  // numerically lowest = highest priority
+    cudaError_t e = cudaDeviceGetStreamPriorityRange(&lo, &hi);
+    if (e != cudaSuccess) return e;
+    return cudaStreamCreateWithPriority(s, cudaStreamNonBlocking, hi);
+}
+
 #define LSC_CUDA_TRY(expr)                                                                                   \
     do {                                                                                                     \
         cudaError_t e_ = (expr);                                                                             \

@@ -29,6 +29,10 @@ struct lsc_euler_ctx {
     double* d_stage = nullptr;
     int stage_cols = 0;
     cudaStream_t stream = nullptr;
+    // halo/compute overlap as in the MHD solver (lsc_capi.cu): exchange on comm_stream behind the slab-edge columns
+    cudaStream_t comm_stream = nullptr;
+    cudaEvent_t edges_done = nullptr, halo_done = nullptr;
+    int overlap = 1;  // 0 off, 1 with NCCL neighbours, 2 always
     double t = 0, dt = 0;
     long step = 0;
     bool uploaded = false;
@@ -73,18 +77,24 @@ int e_read_status(lsc_euler_ctx* c) {
 }
 
 // boundary images / neighbour data into the two ghost columns on each side of state b
-int e_fill_x_ghosts(lsc_euler_ctx* c, int b) {
+int e_fill_x_ghosts(lsc_euler_ctx* c, int b, cudaStream_t s = nullptr) {
+    if (!s) s = c->stream;
     if (c->cfg.nranks <= 1) {
-        lsc::launch_euler_x_ghosts(c->g, kernel_bc(c->cfg.bc), c->state[b], c->stream);
+        lsc::launch_euler_x_ghosts(c->g, kernel_bc(c->cfg.bc), c->state[b], s);
         lsc_count_launches(1);
         LSC_CUDA_TRY(cudaGetLastError());
         return LSC_OK;
     }
     if (!c->comm) return lsc_fail(LSC_ESTATE, "nranks > 1 but lsc_euler_comm_init was not called");
     const int bc = c->cfg.bc == LSC_BC_PERIODIC ? lsc::BC_PERIODIC : lsc::BC_TRANSMISSIVE;
-    if (lsc::comm_exchange_halos(c->comm, c->g, bc, c->state[b], c->stream))
+    if (lsc::comm_exchange_halos(c->comm, c->g, bc, c->state[b], s))
         return lsc_fail(LSC_ECOMM, "halo exchange failed: %s", lsc::comm_error());
     return LSC_OK;
+}
+
+bool e_overlap_active(const lsc_euler_ctx* c) {
+    if (c->in_group || c->g.nxl < 8) return false;
+    return c->overlap == 2 || (c->overlap == 1 && c->cfg.nranks > 1 && c->comm);
 }
 
 int e_launch(lsc_euler_ctx* c, const lsc::EulerParams& p, int in, int out) {
@@ -100,14 +110,35 @@ int e_launch(lsc_euler_ctx* c, const lsc::EulerParams& p, int in, int out) {
         LSC_CUDA_TRY(cudaEventRecord(ev[1], c->stream));
         LSC_CUDA_TRY(cudaEventRecord(ev[2], c->stream));
     }
-    lsc::launch_euler_y_sweep(c->g, p, c->state[c->bar], c->state[in], c->state[out], c->d_status, c->d_fix,
-                              c->stream);
+    auto y_launch = [&](int part) {
+        lsc::launch_euler_y_sweep(c->g, p, c->state[c->bar], c->state[in], c->state[out], c->d_status, c->d_fix,
+                                  c->stream, part);
+    };
+    const bool overlapped = e_overlap_active(c);
+    if (overlapped) {
+        // slab-edge columns of the new u first; their exchange (S:616 for the ghost columns) runs on comm_stream
+        // while this stream sweeps the interior, which touches neither the edge nor the ghost columns of `out`
+        y_launch(lsc::Y_EDGES);
+        LSC_CUDA_TRY(cudaEventRecord(c->edges_done, c->stream));
+        y_launch(lsc::Y_INTERIOR);
+        lsc_count_launches(2);
+    } else {
+        y_launch(lsc::Y_ALL);
+    }
     if (prof) {
         LSC_CUDA_TRY(cudaEventRecord(ev[3], c->stream));
         for (auto e : ev) c->prof_events.push_back(e);
     }
     lsc_count_launches(4);
     LSC_CUDA_TRY(cudaGetLastError());
+    if (overlapped) {
+        LSC_CUDA_TRY(cudaStreamWaitEvent(c->comm_stream, c->edges_done, 0));
+        int rc = e_fill_x_ghosts(c, out, c->comm_stream);
+        if (rc) return rc;
+        LSC_CUDA_TRY(cudaEventRecord(c->halo_done, c->comm_stream));
+        LSC_CUDA_TRY(cudaStreamWaitEvent(c->stream, c->halo_done, 0));  // later work on `stream` sees the halos
+        return LSC_OK;
+    }
     // applyBoundaryConditions(u) after the average (S:616): only x ghost columns are read on the device
     return c->in_group ? LSC_OK : e_fill_x_ghosts(c, out);
 }
@@ -123,7 +154,7 @@ int e_resolve(lsc_euler_ctx* c) {
     }
     int rc = e_read_status(c);
     if (rc) return rc;
-    if (c->pending_step) c->ieee_redos += (long)(c->h_status[1] + c->h_status[2]);
+    if (c->pending_step) c->ieee_redos += (long)(c->h_status[1] + c->h_status[2] + c->h_status[3]);
     std::memcpy(&c->max_speed, &c->h_status[0], sizeof(double));
     c->pending = false;
     return LSC_OK;
@@ -216,7 +247,7 @@ int eg_resolve(lsc_euler_ctx** g, int n) {
         if (g[r]->h_status[0] > mx) mx = g[r]->h_status[0];
     }
     for (int r = 0; r < n; ++r) {
-        if (g[r]->pending_step) g[r]->ieee_redos += (long)(g[r]->h_status[1] + g[r]->h_status[2]);
+        if (g[r]->pending_step) g[r]->ieee_redos += (long)(g[r]->h_status[1] + g[r]->h_status[2] + g[r]->h_status[3]);
         std::memcpy(&g[r]->max_speed, &mx, sizeof(double));
         g[r]->pending = false;
     }
@@ -315,10 +346,14 @@ int lsc_euler_create(const lsc_euler_config* cfg, lsc_euler_ctx** out) {
     }
     ok = ok && cudaMalloc(&c->d_stage, col_bytes * (size_t)cols) == cudaSuccess &&
          cudaMalloc(&c->d_status, 32) == cudaSuccess &&
-         cudaMalloc(&c->d_fix, sizeof(unsigned) * (size_t)lsc::euler_fix_list_entries(c->g)) == cudaSuccess &&
+         cudaMalloc(&c->d_fix, sizeof(unsigned) * (size_t)(lsc::euler_fix_list_entries(c->g) +
+                                                           lsc::euler_edge_list_entries(c->g))) == cudaSuccess &&
          cudaHostAlloc(&c->h_status, 32, cudaHostAllocDefault) == cudaSuccess &&
          cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess &&
-         cudaEventCreateWithFlags(&c->halo_event, cudaEventDisableTiming) == cudaSuccess;
+         cudaEventCreateWithFlags(&c->halo_event, cudaEventDisableTiming) == cudaSuccess &&
+         cudaEventCreateWithFlags(&c->edges_done, cudaEventDisableTiming) == cudaSuccess &&
+         cudaEventCreateWithFlags(&c->halo_done, cudaEventDisableTiming) == cudaSuccess &&
+         lsc_create_comm_stream(&c->comm_stream) == cudaSuccess;
     if (!ok) {
         cudaGetLastError();
         lsc_euler_destroy(c);
@@ -342,6 +377,9 @@ int lsc_euler_destroy(lsc_euler_ctx* c) {
     if (c->d_hints) cudaFree(c->d_hints);
     if (c->comm) lsc::comm_destroy(c->comm);
     if (c->halo_event) cudaEventDestroy(c->halo_event);
+    if (c->edges_done) cudaEventDestroy(c->edges_done);
+    if (c->halo_done) cudaEventDestroy(c->halo_done);
+    if (c->comm_stream) cudaStreamDestroy(c->comm_stream);
     for (auto e : c->prof_events) cudaEventDestroy(e);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -578,6 +616,13 @@ int lsc_euler_write_dat(const lsc_euler_config* cfg, const double* aos, const ch
 }
 
 long lsc_euler_ieee_fallback_count(const lsc_euler_ctx* c) { return c ? c->ieee_redos : -1; }
+
+int lsc_euler_set_overlap(lsc_euler_ctx* c, int enabled) {
+    if (!c) return lsc_fail(LSC_EINVAL, "null context");
+    if (enabled < 0 || enabled > 2) return lsc_fail(LSC_EINVAL, "overlap mode %d", enabled);
+    c->overlap = enabled;
+    return LSC_OK;
+}
 
 int lsc_euler_set_profiling(lsc_euler_ctx* c, int enabled) {
     if (!c) return lsc_fail(LSC_EINVAL, "null argument");

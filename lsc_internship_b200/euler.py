@@ -138,6 +138,11 @@ class SlicEuler2d:
         check(lib().lsc_euler_step_timed(self._h, int(nsteps), ctypes.byref(ms)))
         return ms.value
 
+    def set_overlap(self, mode=1):
+        """0: y sweep, then halo exchange; 1 (default): exchange overlapped with the interior of the y sweep when
+        the slab has NCCL neighbours; 2: split the y sweep on a single rank too (tests)."""
+        check(lib().lsc_euler_set_overlap(self._h, int(mode)))
+
     def set_profiling(self, enabled=True):
         check(lib().lsc_euler_set_profiling(self._h, 1 if enabled else 0))
 

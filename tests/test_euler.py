@@ -344,6 +344,35 @@ def test_out_of_window_operands_take_the_ieee_path():
 
 
 @gpu
+@pytest.mark.parametrize("bc,ic,nx,ny", [
+    ("periodic", "ot", 96, 64),
+    ("transmissive", "cylinder", 70, 130),
+    ("transmissive", "quadrants", 8, 40),             # narrowest slab that is split (4 + 4 columns)
+])
+def test_split_y_sweep_with_overlapped_ghost_fill(bc, ic, nx, ny):
+    """Halo/compute overlap order on one rank (lsc_euler_set_overlap(ctx, 2)): slab-edge columns of the y sweep
+    first, ghost fill on the second stream while the interior is swept; edge and interior blocks on the IEEE fix
+    lists.  Must not change a bit."""
+    import lsc_internship_b200 as lsc
+    cfg = euler_cfg(nx, ny, DOM, bc=bc)
+    u0 = euler_ic(cfg, ic)
+    u0[2:4, 6:20, 1] = 1e-210
+    u0[nx // 2, 5:9, 2] = 1e-210
+    u0[nx + 1, 12:20, 1] = 1e-210
+    o = OracleEuler(cfg, u0)
+    s = lsc.SlicEuler2d(nx, ny, bc=bc, problem=ic)
+    s.set_overlap(2)
+    s.upload(u0)
+    log = o.step(6)
+    s.step(6)
+    t, dt, _ = s.scalars()
+    assert (t, dt) == tuple(log[-1])
+    assert s.ieee_fallback_count() >= 3
+    assert np.array_equal(bits(s.download()), bits(o.state()[0]))
+    s.close()
+
+
+@gpu
 def test_committed_program_reproduces_reference_dat_files(tmp_path, golden_dir):
     """SlicEuler2d().run() = main() of SLIC_euler_2d.cpp as committed: all twenty euler_<k>.dat must be
     byte-identical to the files committed in the reference repo (MHD_plot_data/euler_*.dat)."""
