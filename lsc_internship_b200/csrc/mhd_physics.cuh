@@ -169,53 +169,19 @@ __device__ __forceinline__ double fast_speed_sq(D& dv, const Rcp& irho, double p
     return 0.5 * (t + sqrt(scaled_add(-4.0, dv.div(cs2 * Bn * Bn, irho), t * t)));
 }
 
-// HLLC flux with mixed-GLM interface values.  FluxHLLCX MUSCL_NEW.cpp:483-515 /
-// FluxHLLCY :517-549, together with everything they call:
-//   psiAndBx/psiAndBy :121-138, wavespeedx/y :167-253, uHLLx/y :255-307,
-//   uStarX :309-395, uStarY :397-481 (incl. the :442 quirk: the RIGHT star
-//   z-momentum in y is built from the LEFT quantities).
-// L is the state left/below the interface, R the one right/above.
-template <int DIR, class D>
-__device__ __forceinline__ void hllc_flux(D& dv, const double (&L)[NV], const double (&R)[NV], double gamma,
-                                          double gm1, double ch, double ch2, double inv2ch, double halfch,
-                                          double (&F)[NV]) {
+// Second half of hllc_flux for the side the HLLC branch selects (LEFT: flux built from the left state, regions
+// sL >= 0 and sL <= 0 <= qStar; otherwise from the right state): flux of the modified state, and in the two star
+// regions (`star`) the HLL tangential fields, the star state uStarX/uStarY and F = F(S1) + s (U* - S1).
+template <int DIR, bool LEFT, class D>
+__device__ __forceinline__ void hllc_side(D& dv, const double (&L)[NV], const double (&R)[NV], const Prim& qL,
+                                          const Prim& qR, double sL, double sR, double qS, double BnT, double psiT,
+                                          bool star, double gm1, double ch2, double (&F)[NV]) {
     constexpr int N = (DIR == 0) ? 5 : 6;  // normal field component
-    // ---- mixed GLM interface values (:126-127 / :135-136)
-    // inv2ch = 1.0/(2.0*ch), halfch = ch/2.0: per-step scalars, divided once on the host
-    const double BnT = scaled_add(0.5, L[N] + R[N], -(inv2ch * (R[8] - L[8])));
-    const double psiT = scaled_add(0.5, L[8] + R[8], -(halfch * (R[N] - L[N])));
-
-    // ---- primitives of the ORIGINAL states
-    const Prim qL = c2p(dv, L, gm1), qR = c2p(dv, R, gm1);
-    const double vnL = (DIR == 0) ? qL.vx : qL.vy;
-    const double vnR = (DIR == 0) ? qR.vx : qR.vy;
-    const double B2L = L[5] * L[5] + L[6] * L[6] + L[7] * L[7];
-    const double B2R = R[5] * R[5] + R[6] * R[6] + R[7] * R[7];
-
-    // ---- wave speeds (:178-192 / :235-250)
-    const double cfL = sqrt(fast_speed_sq(dv, qL.irho, qL.p, B2L, L[N], gamma));
-    const double cfR = sqrt(fast_speed_sq(dv, qR.irho, qR.p, B2R, R[N], gamma));
-    const double cmax = std_max(cfL, cfR);
-    const double sL = std_min(vnL, vnR) - cmax;
-    const double sR = std_max(vnL, vnR) + cmax;
-    const double pModL = scaled_add(0.5, B2L, qL.p) - L[N] * L[N];
-    const double pModR = scaled_add(0.5, B2R, qR.p) - R[N] * R[N];
-    const double qS = dv.div(R[0] * vnR * (sR - vnR) - L[0] * vnL * (sL - vnL) + pModL - pModR,
-                           R[0] * (sR - vnR) - L[0] * (sL - vnL));
-
-    // ---- which of the four HLLC regions (:502-512 / :536-546), evaluated in the reference's order
-    const bool regA = (sL >= 0);
-    const bool regB = !regA && (sL <= 0 && qS >= 0);
-    const bool regC = !regA && !regB && (qS <= 0 && sR >= 0);
-    const bool left = regA || regB;  // flux built from the left (modified) state
-
-    // ---- the side the branch selects; modified state S1 has S1[N]=BnT, S1[8]=psiT
-    double S[NV];
-#pragma unroll
-    for (int k = 0; k < NV; ++k) S[k] = left ? L[k] : R[k];
-    const Prim qs = left ? qL : qR;
-    const double ss = left ? sL : sR;
-    const double vn = left ? vnL : vnR;
+    const double (&S)[NV] = LEFT ? L : R;
+    const Prim& qs = LEFT ? qL : qR;
+    const double ss = LEFT ? sL : sR;
+    const double vn = (DIR == 0) ? qs.vx : qs.vy;
+    // modified state S1: S with S1[N]=BnT, S1[8]=psiT
     double S1[NV];
 #pragma unroll
     for (int k = 0; k < NV; ++k) S1[k] = S[k];
@@ -231,7 +197,7 @@ __device__ __forceinline__ void hllc_flux(D& dv, const double (&L)[NV], const do
         flux_from_prim<DIR>(S1, q1, ch2, FS);
     }
 
-    if (!(regB || regC)) {
+    if (!star) {
 #pragma unroll
         for (int k = 0; k < NV; ++k) F[k] = FS[k];
         return;
@@ -273,10 +239,10 @@ __device__ __forceinline__ void hllc_flux(D& dv, const double (&L)[NV], const do
     // tangential momenta (:353-357 / :437-442)
     const double mtS = vt * rhoS - dv.div(BnS * BtH - BnT * Bt, is);
     double mzS;
-    if (DIR == 1 && !left) {
+    if (DIR == 1 && !LEFT) {
         // MUSCL_NEW.cpp:442: momzStarR = rhoStarL*u_zL - (ByStar*BzHLL - ByL*BzL)/(sL - qStar)
         const Rcp isl = dv.rcp(sL - qS);
-        const double rhoSL = dv.div(L[0] * (sL - vnL), isl);
+        const double rhoSL = dv.div(L[0] * (sL - qL.vy), isl);
         mzS = rhoSL * qL.vz - dv.div(BnS * BzH - BnT * L[7], isl);
     } else {
         mzS = vz * rhoS - dv.div(BnS * BzH - BnT * Bz, is);
@@ -305,6 +271,55 @@ __device__ __forceinline__ void hllc_flux(D& dv, const double (&L)[NV], const do
     US[8] = psiT;
 #pragma unroll
     for (int k = 0; k < NV; ++k) F[k] = FS[k] + ss * (US[k] - S1[k]);
+}
+
+// HLLC flux with mixed-GLM interface values.  FluxHLLCX MUSCL_NEW.cpp:483-515 /
+// FluxHLLCY :517-549, together with everything they call:
+//   psiAndBx/psiAndBy :121-138, wavespeedx/y :167-253, uHLLx/y :255-307,
+//   uStarX :309-395, uStarY :397-481 (incl. the :442 quirk: the RIGHT star
+//   z-momentum in y is built from the LEFT quantities).
+// L is the state left/below the interface, R the one right/above.
+template <int DIR, class D>
+__device__ __forceinline__ void hllc_flux(D& dv, const double (&L)[NV], const double (&R)[NV], double gamma,
+                                          double gm1, double ch, double ch2, double inv2ch, double halfch,
+                                          double (&F)[NV]) {
+    constexpr int N = (DIR == 0) ? 5 : 6;  // normal field component
+    // ---- mixed GLM interface values (:126-127 / :135-136)
+    // inv2ch = 1.0/(2.0*ch), halfch = ch/2.0: per-step scalars, divided once on the host
+    const double BnT = scaled_add(0.5, L[N] + R[N], -(inv2ch * (R[8] - L[8])));
+    const double psiT = scaled_add(0.5, L[8] + R[8], -(halfch * (R[N] - L[N])));
+
+    // ---- primitives of the ORIGINAL states
+    const Prim qL = c2p(dv, L, gm1), qR = c2p(dv, R, gm1);
+    const double vnL = (DIR == 0) ? qL.vx : qL.vy;
+    const double vnR = (DIR == 0) ? qR.vx : qR.vy;
+    const double B2L = L[5] * L[5] + L[6] * L[6] + L[7] * L[7];
+    const double B2R = R[5] * R[5] + R[6] * R[6] + R[7] * R[7];
+
+    // ---- wave speeds (:178-192 / :235-250)
+    const double cfL = sqrt(fast_speed_sq(dv, qL.irho, qL.p, B2L, L[N], gamma));
+    const double cfR = sqrt(fast_speed_sq(dv, qR.irho, qR.p, B2R, R[N], gamma));
+    const double cmax = std_max(cfL, cfR);
+    const double sL = std_min(vnL, vnR) - cmax;
+    const double sR = std_max(vnL, vnR) + cmax;
+    const double pModL = scaled_add(0.5, B2L, qL.p) - L[N] * L[N];
+    const double pModR = scaled_add(0.5, B2R, qR.p) - R[N] * R[N];
+    const double qS = dv.div(R[0] * vnR * (sR - vnR) - L[0] * vnL * (sL - vnL) + pModL - pModR,
+                           R[0] * (sR - vnR) - L[0] * (sL - vnL));
+
+    // ---- which of the four HLLC regions (:502-512 / :536-546), evaluated in the reference's order
+    const bool regA = (sL >= 0);
+    const bool regB = !regA && (sL <= 0 && qS >= 0);
+    const bool regC = !regA && !regB && (qS <= 0 && sR >= 0);
+    const bool left = regA || regB;  // flux built from the left (modified) state
+
+    // ---- the side the branch selects.  Two instantiations of the remainder behind ONE branch instead of ~20
+    // selected doubles (state, primitives, reciprocal, speed): the branch is warp-uniform except where the
+    // contact speed changes sign, and each instantiation reads its side's registers directly.
+    if (left)
+        hllc_side<DIR, true>(dv, L, R, qL, qR, sL, sR, qS, BnT, psiT, regB || regC, gm1, ch2, F);
+    else
+        hllc_side<DIR, false>(dv, L, R, qL, qR, sL, sR, qS, BnT, psiT, regB || regC, gm1, ch2, F);
 }
 
 // Local signal speed for the CFL condition.  ComputeTimeStep MUSCL_NEW.cpp:75-109.
