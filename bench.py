@@ -157,7 +157,7 @@ def run_reference_sample(n, steps):
     return n * n * steps / secs, secs
 
 
-def cpu_baseline(n=768, steps=12):
+def cpu_baseline(n=1024, steps=16):
     try:
         v, secs = run_reference_sample(n, steps)
         return {"value": v, "unit": UNIT, "cores": 1, "kind": "reference",
@@ -356,7 +356,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--grid", "--n", dest="n", type=int, default=16384, help="grid edge (default: the named 16384)")
-    ap.add_argument("--ref-n", type=int, default=768, help="grid edge of the bounded CPU reference sample")
+    ap.add_argument("--ref-n", type=int, default=1024, help="grid edge of the bounded CPU reference sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--arithmetic", default="reference", choices=["reference", "relaxed"],
                     help="reference = bit-identical IEEE path (default, the one that is judged); relaxed = N3 variant")

@@ -68,6 +68,9 @@ __device__ __forceinline__ void block_max_to_global(double local, unsigned long 
 #ifndef XS_STRIP
 #define XS_STRIP 128
 #endif
+#ifndef XS_PF
+#define XS_PF 2  // the x march prefetches column c + XS_PF into L1 while it works on column c
+#endif
 #ifndef YS_MINB
 #define YS_MINB 4
 #endif
@@ -144,8 +147,11 @@ __device__ __forceinline__ bool x_sweep_block(const GridDims& g, const SweepPara
     const bool hi_image = (ib == g.nxl + 2) && (p.bc_hi == BC_TRANSMISSIVE);
     D dv;
 
-    prefetch_cell_l1(cur, mhd_index(g, ia + 1, j));
-    if (!p.first_step) prefetch_cell_l1(prev, mhd_index(g, ia + 1, j));
+#pragma unroll
+    for (int a = 1; a < XS_PF; ++a) {
+        prefetch_cell_l1(cur, mhd_index(g, ia + a, j));
+        if (!p.first_step) prefetch_cell_l1(prev, mhd_index(g, ia + a, j));
+    }
     double hRprev[NV], Fprev[NV], PMnt[4];
     {
         // face state R of cell ia-1; at a transmissive wall ghost cell 1 carries the half state of
@@ -161,9 +167,9 @@ __device__ __forceinline__ bool x_sweep_block(const GridDims& g, const SweepPara
     }
 
     for (int c = ia; c <= ib; ++c) {
-        if (c + 2 <= g.nxl + 3) {
-            prefetch_cell_l1(cur, mhd_index(g, c + 2, j));
-            if (!p.first_step) prefetch_cell_l1(prev, mhd_index(g, c + 2, j));
+        if (c + XS_PF <= g.nxl + 3) {
+            prefetch_cell_l1(cur, mhd_index(g, c + XS_PF, j));
+            if (!p.first_step) prefetch_cell_l1(prev, mhd_index(g, c + XS_PF, j));
         }
         double hL[NV], hR[NV], P0nt[4];
         if (c == ib && hi_image) {
@@ -197,7 +203,7 @@ __device__ __forceinline__ bool x_sweep_block(const GridDims& g, const SweepPara
             prim_vector(u0, P0nt, P0);
             double ratio[NV];
 #pragma unroll
-            for (int k = 0; k < NV; ++k) ratio[k] = limiter_ratio(dv, PM[k], P0[k], Pp[k]);
+            for (int k = 0; k < NV; ++k) ratio[k] = limiter_ratio_k(dv, k, PM[k], P0[k], Pp[k]);
 #pragma unroll
             for (int k = 0; k < NV; ++k) reconstruct_with_ratio(dv, ratio[k], uM[k], u0[k], uP[k], hL[k], hR[k]);
             predictor<0>(dv, hL, hR, p.gm1, p.ch2, p.hdtdh);
@@ -424,7 +430,7 @@ __device__ __forceinline__ bool y_sweep_block(const GridDims& g, const SweepPara
             const int t = tid + 1;
             double ratio[NV];
 #pragma unroll
-            for (int k = 0; k < NV; ++k) ratio[k] = limiter_ratio(dv, sP[k][t - 1], p0[k], sP[k][t + 1]);
+            for (int k = 0; k < NV; ++k) ratio[k] = limiter_ratio_k(dv, k, sP[k][t - 1], p0[k], sP[k][t + 1]);
 #pragma unroll
             for (int k = 0; k < NV; ++k)
                 reconstruct_with_ratio(dv, ratio[k], sU[k][t - 1], ub[k], sU[k][t + 1], hB[k], hT[k]);

@@ -118,6 +118,28 @@ __device__ __forceinline__ double limiter_ratio(D& dv, double pm, double p0, dou
     return dv.div(p0 - pm, (pp - p0) + 1e-8);
 }
 
+// The same ratio for the components that are identically zero in planar problems (v_z, B_z: OT, KH and every
+// other committed initial condition): a zero numerator over a non-zero, non-NaN denominator gives r = +-0, which
+// the limiter maps to xi = 0 whatever its sign, so the reciprocal refinement and the quotient (8 fp64
+// instructions + guards) are skipped behind a branch that is warp-uniform in such problems.  Any other operand
+// pair (incl. 0/0 and 0/NaN, which must stay NaN) takes the division.
+template <class D>
+__device__ __forceinline__ double limiter_ratio_zskip(D& dv, double pm, double p0, double pp) {
+    const double num = p0 - pm;
+    const double den = (pp - p0) + 1e-8;
+#ifndef MHD_NO_ZSKIP
+    if (num == 0.0 && (den < 0.0 || den > 0.0)) return 0.0;
+#endif
+    return dv.div(num, den);
+}
+
+// limiter ratio of component k as the sweeps form it
+// (k is a compile-time constant after unrolling)
+template <class D>
+__device__ __forceinline__ double limiter_ratio_k(D& dv, int k, double pm, double p0, double pp) {
+    return (k == 3 || k == 7) ? limiter_ratio_zskip(dv, pm, p0, pp) : limiter_ratio(dv, pm, p0, pp);
+}
+
 template <class D>
 __device__ __forceinline__ void reconstruct_with_ratio(D& dv, double r, double um, double u0, double up,
                                                        double& lo, double& hi) {
