@@ -77,6 +77,9 @@ __device__ __forceinline__ void block_max_to_global(double local, unsigned long 
 #ifndef YS_BJ
 #define YS_BJ 128
 #endif
+#ifndef YS_PF_BLOCKS
+#define YS_PF_BLOCKS (148 * YS_MINB)  // y sweep: L2 prefetch distance in blocks = one resident wave (0 = off)
+#endif
 
 constexpr long FIX_GRID = 148 * 4;  // persistent grid of the fix kernels
 
@@ -367,6 +370,25 @@ __device__ __forceinline__ bool y_sweep_block(const GridDims& g, const SweepPara
     const int i = 2 + by;
     const int jo = 2 + bx * (BJ - 2);
     const int c = jo - 1 + tid;  // this thread's cell
+#if YS_PF_BLOCKS > 0
+    // The tile a block loads first thing is what its warps wait for longest (ncu: the first reciprocal behind the
+    // tile load holds 10 % of the sweep's warp samples).  Blocks are dispatched in launch order, so the block that
+    // will take this one's place on the SM is about one resident wave (YS_PF_BLOCKS) further on: ask for its tile
+    // -- the same rows, pf_cols columns on; in the blocked layout the rows of a tile are ONE contiguous run per
+    // state -- to be brought into L2 now, with one bulk prefetch per state.
+    if (FILTER && tid == BJ - 1) {
+        const int pf_cols = (YS_PF_BLOCKS + (int)gridDim.x - 1) / (int)gridDim.x;
+        const int ip = i + pf_cols;
+        if (ip <= g.nxl + 1) {
+            const int g0 = (JOFF + jo - 2) >> 5;
+            const int g1 = (JOFF + min(jo + BJ - 1, g.ny + 3)) >> 5;
+            const size_t off = (size_t)ip * mhd_column_doubles(g) + (size_t)g0 * (NV * JBLK);
+            const unsigned bytes = (unsigned)(g1 - g0 + 1) * (NV * JBLK * 8);
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ubar + off), "r"(bytes) : "memory");
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(cur + off), "r"(bytes) : "memory");
+        }
+    }
+#endif
     const int bc = p.bc_lo;      // the reference uses one y boundary type for both ends
     D dv;
 
