@@ -184,6 +184,9 @@ long euler_fix_list_entries(const GridDims& g) {
 // y sweep (both of them) + average + CFL maximum.
 // ---------------------------------------------------------------------------------------------------------
 constexpr int EBJ = 128;
+#ifndef EULER_YS_PREFETCH
+#define EULER_YS_PREFETCH 1  // 0: no L2 prefetch of the successor block's tile
+#endif
 
 long euler_y_block_count(const GridDims& g) { return (long)((g.ny + (EBJ - 2) - 1) / (EBJ - 2)) * g.nxl; }
 
@@ -250,6 +253,24 @@ __device__ __forceinline__ bool euler_y_sweep_block(const GridDims& g, const Eul
     const int i = 2 + by;
     const int jo = 2 + bx * (EBJ - 2);
     const int c = jo - 1 + tid;
+#if EULER_YS_PREFETCH
+    if (!std::is_same<D, IeeeDiv>::value) {
+        // as in the MHD y sweep: ask L2 for the tile (both states; one contiguous run each in the blocked layout) of
+        // the block one resident wave further on, which will take this block's place on the SM
+        if (tid == EBJ - 1) {
+            const int pf_cols = (148 * 4 + (int)gridDim.x - 1) / (int)gridDim.x;
+            const int ip = i + pf_cols;
+            if (ip <= g.nxl + 1) {
+                const int g0 = (JOFF + jo - 2) >> 5;
+                const int g1 = (JOFF + min(jo + EBJ - 1, g.ny + 3)) >> 5;
+                const size_t off = (size_t)ip * column_doubles(g, NE) + (size_t)g0 * (NE * JBLK);
+                const unsigned bytes = (unsigned)(g1 - g0 + 1) * (NE * JBLK * 8);
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ubar + off), "r"(bytes) : "memory");
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(cur + off), "r"(bytes) : "memory");
+            }
+        }
+    }
+#endif
     D dv;
     const EOS eos = make_eos<EOS>(p);
     const int nbx = (g.ny + (EBJ - 2) - 1) / (EBJ - 2);  // blocks per column (also in the fix kernel's grid)
