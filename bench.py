@@ -304,7 +304,7 @@ def main_gpu(args):
     achieved = cells_local * B_ALG_X / (dom_ms * 1e-3) / 1e9
     traffic, traffic_src = None, None
     try:  # dram bytes per cell of that kernel from the committed ncu --set full capture, scaled to this launch
-        with open(os.path.join(ROOT, "profiles", "r1_v4_traffic.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r1_v5_traffic.json")) as f:
             tj = json.load(f)
         traffic = tj[dom_name]["bytes_per_cell"] * cells_local
         traffic_src = tj["source"]
@@ -338,7 +338,7 @@ def main_gpu(args):
                      "whole_step_frac_of_measured": value * B_ALG / world / (peak * 1e9),
                      "whole_step_frac_of_nominal_8TBs": value * B_ALG / world / (NOMINAL_HBM_GBS * 1e9),
                      "note": "bound by the fp64 pipe / issue port, not HBM (no FMA contraction, IEEE div/sqrt): ncu "
-                             "sm__inst_executed_pipe_fp64 64 % (x) / 59 % (y) of peak, profiles/r1_v4_summary.md"},
+                             "sm__inst_executed_pipe_fp64 65 % (x) / 61 % (y) of peak, profiles/r1_v5_summary.md"},
         "sim": {"t": t_sim, "dt": dt_sim, "ch": ch_sim, "steps_taken": nstep},
     }
     if world == 1 and not args.no_cpu_baseline:

@@ -241,7 +241,8 @@ template <class D, class EOS>
 __device__ __forceinline__ bool euler_y_sweep_block(const GridDims& g, const EulerParams& p,
                                                     const double* __restrict__ ubar, const double* __restrict__ cur,
                                                     double* __restrict__ next, const int bx, const int by,
-                                                    double& speed, const unsigned long long* status) {
+                                                    double& speed, const unsigned long long* status,
+                                                    const int pf_cols = 0) {
     // fast instantiation with an EoS that has a cheap bound: fp32 filter of the CFL reduction (see the MHD y
     // sweep): the running exact maximum of the blocks that already finished, read first to hide its latency
     constexpr bool FILTER = !std::is_same<D, IeeeDiv>::value && EOS::kHasCflBound;
@@ -257,9 +258,8 @@ __device__ __forceinline__ bool euler_y_sweep_block(const GridDims& g, const Eul
     if (!std::is_same<D, IeeeDiv>::value) {
         // as in the MHD y sweep: ask L2 for the tile (both states; one contiguous run each in the blocked layout) of
         // the block one resident wave further on, which will take this block's place on the SM
-        if (tid == EBJ - 1) {
-            const int pf_cols = (148 * 4 + (int)gridDim.x - 1) / (int)gridDim.x;
-            const int ip = i + pf_cols;
+        if (pf_cols > 0 && tid == EBJ - 1) {
+            const int ip = i + pf_cols;  // pf_cols: one resident wave of blocks in columns, from the launch (YCols)
             if (ip <= g.nxl + 1) {
                 const int g0 = (JOFF + jo - 2) >> 5;
                 const int g1 = (JOFF + min(jo + EBJ - 1, g.ny + 3)) >> 5;
@@ -343,7 +343,7 @@ __global__ void __launch_bounds__(EBJ, 4) euler_y_sweep_kernel(const GridDims g,
     double speed;
     // column of this block row: all columns, the four slab-edge columns or the rest (YCols, mhd_kernels.cuh)
     const int col = yc.c0 + (int)blockIdx.y + ((int)blockIdx.y >= yc.jump_at ? yc.jump : 0);
-    const bool bad = euler_y_sweep_block<D, EOS>(g, p, ubar, cur, next, blockIdx.x, col, speed, status);
+    const bool bad = euler_y_sweep_block<D, EOS>(g, p, ubar, cur, next, blockIdx.x, col, speed, status, yc.pf_cols);
     if (__syncthreads_or(bad)) {  // whole block is recomputed by the fix kernel; its maximum must not count
         if (threadIdx.x == 0) fix_list[atomicAdd(status + yc.counter, 1ull)] = col * gridDim.x + blockIdx.x;
     } else if (!std::is_same<D, IeeeDiv>::value && EOS::kHasCflBound) {
@@ -374,10 +374,11 @@ __global__ void __launch_bounds__(EBJ) euler_y_sweep_fix_kernel(const GridDims g
 void launch_euler_y_sweep(const GridDims& g, const EulerParams& p, const double* ubar, const double* cur, double* next,
                           unsigned long long* status, unsigned* fix_list, cudaStream_t s, int part) {
     dim3 block(EBJ);
-    const YCols yc = y_columns(g, part);
+    YCols yc = y_columns(g, part);
     // the slab-edge launch keeps its own list (behind the euler_fix_list_entries of the others) and counter
     unsigned* list = fix_list + (part == Y_EDGES ? euler_fix_list_entries(g) : 0);
     dim3 grid((g.ny + (EBJ - 2) - 1) / (EBJ - 2), yc.ncols);
+    yc.pf_cols = (148 * 4 + (int)grid.x - 1) / (int)grid.x;
     const unsigned nfix = (unsigned)std::min<long>(EFIX_GRID, (long)grid.x * grid.y);
     if (p.tab_dens) {
         euler_y_sweep_kernel<EULER_FAST_POLICY, TableEos><<<grid, block, 0, s>>>(g, p, ubar, cur, next, status, list, yc);

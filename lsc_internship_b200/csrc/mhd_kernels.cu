@@ -354,7 +354,8 @@ template <class D>
 __device__ __forceinline__ bool y_sweep_block(const GridDims& g, const SweepParams& p,
                                               const double* __restrict__ ubar, const double* __restrict__ cur,
                                               double* __restrict__ next, const int bx, const int by,
-                                              double& speed, const unsigned long long* status) {
+                                              double& speed, const unsigned long long* status,
+                                              const int pf_cols = 0) {
     // Fast instantiation only: the running exact maximum of the blocks that already finished (stale is fine,
     // it only grows), rounded down to fp32.  Read first so that its latency hides behind the tile load.
     constexpr bool FILTER = !std::is_same<D, IeeeDiv>::value;
@@ -376,9 +377,8 @@ __device__ __forceinline__ bool y_sweep_block(const GridDims& g, const SweepPara
     // will take this one's place on the SM is about one resident wave (YS_PF_BLOCKS) further on: ask for its tile
     // -- the same rows, pf_cols columns on; in the blocked layout the rows of a tile are ONE contiguous run per
     // state -- to be brought into L2 now, with one bulk prefetch per state.
-    if (FILTER && tid == BJ - 1) {
-        const int pf_cols = (YS_PF_BLOCKS + (int)gridDim.x - 1) / (int)gridDim.x;
-        const int ip = i + pf_cols;
+    if (FILTER && pf_cols > 0 && tid == BJ - 1) {
+        const int ip = i + pf_cols;  // pf_cols: YS_PF_BLOCKS in columns, from the launch (YCols)
         if (ip <= g.nxl + 1) {
             const int g0 = (JOFF + jo - 2) >> 5;
             const int g1 = (JOFF + min(jo + BJ - 1, g.ny + 3)) >> 5;
@@ -535,7 +535,7 @@ __global__ void __launch_bounds__(BJ, YS_MINB) y_sweep_kernel(const GridDims g, 
     double speed;
     // column of this block row: a launch covers all columns, the four slab-edge columns or the rest (YCols)
     const int col = yc.c0 + (int)blockIdx.y + ((int)blockIdx.y >= yc.jump_at ? yc.jump : 0);
-    const bool bad = y_sweep_block<D>(g, p, ubar, cur, next, blockIdx.x, col, speed, status);
+    const bool bad = y_sweep_block<D>(g, p, ubar, cur, next, blockIdx.x, col, speed, status, yc.pf_cols);
     if (__syncthreads_or(bad)) {  // whole block is recomputed by the fix kernel; its maximum must not count
         if (threadIdx.x == 0) fix_list[atomicAdd(status + yc.counter, 1ull)] = col * gridDim.x + blockIdx.x;
     } else {
@@ -564,10 +564,11 @@ void launch_y_sweep(const GridDims& g, const SweepParams& p, const double* u_bar
                     double* u_next, unsigned long long* status, unsigned* fix_list, cudaStream_t s,
                     int part) {
     dim3 block(BJ);
-    const YCols yc = y_columns(g, part);
+    YCols yc = y_columns(g, part);
     // the slab-edge launch keeps its own list (behind the y_sweep_block_count entries of the others) and counter
     unsigned* list = fix_list + (part == Y_EDGES ? y_sweep_block_count(g) : 0);
     dim3 grid((g.ny + (BJ - 2) - 1) / (BJ - 2), yc.ncols);
+    yc.pf_cols = (YS_PF_BLOCKS + (int)grid.x - 1) / (int)grid.x;  // L2 prefetch distance: one resident wave of blocks
     y_sweep_kernel<MHD_FAST_POLICY><<<grid, block, 0, s>>>(g, p, u_bar, u_cur, u_next, status, list, yc);
     const unsigned nfix = (unsigned)std::min<long>(FIX_GRID, (long)grid.x * grid.y);
     y_sweep_fix_kernel<<<nfix, block, 0, s>>>(g, p, u_bar, u_cur, u_next, status, list, grid.x, yc.counter);

@@ -93,6 +93,7 @@ struct YCols {
     int c0, jump_at, jump;  // local column of block row by: c0 + by + (by >= jump_at ? jump : 0)
     int ncols;              // block rows of the launch
     int counter;            // status word that counts this launch's flagged blocks (2, slab edges: 3)
+    int pf_cols = 0;        // columns between a block and the one whose tile it asks L2 to fetch (0: none)
 };
 inline YCols y_columns(const GridDims& g, int part) {
     if (part == Y_EDGES) return YCols{0, 2, g.nxl - 4, 4, 3};

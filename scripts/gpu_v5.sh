@@ -17,5 +17,5 @@ done
 timeout 500 python bench.py > gpurun_out/bench_n1.json 2> gpurun_out/bench_n1.err; echo "bench exit $?"
 tail -1 gpurun_out/bench_n1.json | cut -c1-300
 timeout 200 python bench.py --impl reference --steps 12 --warmup 1 > gpurun_out/bench_ref.json 2>&1; tail -1 gpurun_out/bench_ref.json | cut -c1-200
-timeout 300 python scripts/bench_configs.py c2 > gpurun_out/secondary_configs.jsonl 2> gpurun_out/secondary.err; cut -c1-300 gpurun_out/secondary_configs.jsonl
+timeout 500 python scripts/bench_configs.py > gpurun_out/secondary_configs.jsonl 2> gpurun_out/secondary.err; cut -c1-300 gpurun_out/secondary_configs.jsonl
 bash scripts/gpu_ncu.sh 4096
