@@ -29,8 +29,15 @@ __device__ __forceinline__ void warp_max_to_global(double local, unsigned long l
 
 // 1/R rounded up, R = the running exact maximum (a bit pattern in *status) rounded down to fp32; R = 0 gives
 // +inf and every bound becomes NaN/inf, i.e. every warp evaluates.  Stale values are fine: R only grows.
-__device__ __forceinline__ float inv_running_max_f32(const unsigned long long* status) {
-    const float r = __double2float_rd(__longlong_as_double((long long)*(const volatile unsigned long long*)status));
+// In two halves, so that a kernel can issue the load first thing and convert where the value is needed:
+// a warp that converts right behind the load sits out a whole L2 round trip before it has issued its tile loads.
+// The conversion is a volatile asm so that it stays behind the barrier it is placed after.
+__device__ __forceinline__ unsigned long long running_max_bits(const unsigned long long* status) {
+    return *(const volatile unsigned long long*)status;
+}
+__device__ __forceinline__ float inv_running_max_from_bits(unsigned long long bits) {
+    float r;
+    asm volatile("cvt.rm.f32.f64 %0, %1;" : "=f"(r) : "d"(__longlong_as_double((long long)bits)));
     return __frcp_ru(r);
 }
 

@@ -247,7 +247,8 @@ __device__ __forceinline__ bool euler_y_sweep_block(const GridDims& g, const Eul
     // sweep): the running exact maximum of the blocks that already finished, read first to hide its latency
     constexpr bool FILTER = !std::is_same<D, IeeeDiv>::value && EOS::kHasCflBound;
     float inv_run_max = 0.0f;
-    if (FILTER) inv_run_max = inv_running_max_f32(status);
+    unsigned long long run_bits = 0;  // loaded first thing, converted where the filter needs it (cfl_reduce.cuh)
+    if (FILTER) run_bits = running_max_bits(status);
     __shared__ double sH[2][NE][EBJ];  // one pair of exchange buffers per pass: no barrier between the passes
     __shared__ double sF[2][NE][EBJ];
     const int tid = threadIdx.x;
@@ -298,6 +299,7 @@ __device__ __forceinline__ bool euler_y_sweep_block(const GridDims& g, const Eul
     // below the final maximum, so the result is the same bit pattern whatever the block order.
     bool evaluate = updates;
     if (FILTER) {
+        inv_run_max = inv_running_max_from_bits(run_bits);
         bool candidate = false;
         if (updates) candidate = !(eos.cfl_speed_over_max_f32(un, inv_run_max) < 1.0f);
         const bool warp_has_candidate = __any_sync(0xffffffffu, candidate);  // every lane votes (no short circuit)

@@ -360,9 +360,8 @@ __device__ __forceinline__ bool y_sweep_block(const GridDims& g, const SweepPara
     // it only grows), rounded down to fp32.  Read first so that its latency hides behind the tile load.
     constexpr bool FILTER = !std::is_same<D, IeeeDiv>::value;
     float inv_run_max = 0.0f;  // 1/R rounded up (R = 0 -> +inf -> every warp evaluates)
-    if (FILTER) {
-        inv_run_max = inv_running_max_f32(status);
-    }
+    unsigned long long run_bits = 0;
+    if (FILTER) run_bits = running_max_bits(status);
     __shared__ double sU[NV][BJ + 2];  // uBar of cells jo-2 .. jo+BJ-1
     __shared__ double sP[NV][BJ + 2];  // primitives of u^n there; later the interface fluxes
     __shared__ double sH[NV][BJ];      // bottom face state of each thread's cell
@@ -444,6 +443,9 @@ __device__ __forceinline__ bool y_sweep_block(const GridDims& g, const SweepPara
         if (have_e) tile_put(te, flip_e, ue, qe, ve);
     }
     __syncthreads();
+    // loaded first thing, converted behind the tile loads: a warp that converts right behind the load sits out an L2
+    // round trip before it has issued its tile loads
+    if (FILTER) inv_run_max = inv_running_max_from_bits(run_bits);
 
     const bool active = (c <= g.ny + 2);
     double hB[NV], hT[NV];
