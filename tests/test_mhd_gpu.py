@@ -215,6 +215,12 @@ def test_cuda_matches_reference_golden(path):
     ("kh", 67, 129, (0.0, 1.0, -1.0, 1.0), "transmissive", "reflective", 6),
     ("kh", 64, 126, (0.0, 1.0, -1.0, 1.0), "transmissive", "transmissive", 6),  # ny = exactly one y block
     ("ot", 4, 4, (0.0, 1.0, 0.0, 1.0), "periodic", "periodic", 3),             # minimum size
+    # non-periodic y: the ghost face states come from threads of the same y block (cells 3 and ny); these sizes put
+    # the top ghost at the last thread of a block, at thread 0 of the next one (fallback path) and on a 4-row grid
+    ("kh", 40, 252, (0.0, 1.0, -1.0, 1.0), "periodic", "reflective", 5),
+    ("kh", 36, 125, (0.0, 1.0, -1.0, 1.0), "transmissive", "reflective", 5),
+    ("kh", 33, 127, (0.0, 1.0, -1.0, 1.0), "periodic", "transmissive", 5),
+    ("kh", 4, 4, (0.0, 1.0, -1.0, 1.0), "transmissive", "reflective", 3),
 ])
 def test_cuda_matches_oracle(prob, nx, ny, dom, bcx, bcy, n):
     cfg = mhd_cfg(nx, ny, dom, bcx=bcx, bcy=bcy)
