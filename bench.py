@@ -341,6 +341,12 @@ def main_gpu(args):
                              "sm__inst_executed_pipe_fp64 65 % (x) / 61 % (y) of peak, profiles/r1_v5_summary.md"},
         "sim": {"t": t_sim, "dt": dt_sim, "ch": ch_sim, "steps_taken": nstep},
     }
+    try:  # the 16384^2 run is power-capped and boxes settle at different clocks: the same metric per SM clock
+        mhz = clocks.get("sm_mhz") if isinstance(clocks, dict) else None
+        if mhz:
+            line["roofline"]["cell_updates_per_gpu_per_sm_clock"] = value / world / (float(mhz) * 1e6)
+    except Exception:
+        pass
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline()
     print(json.dumps(line))
