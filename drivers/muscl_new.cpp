@@ -25,9 +25,10 @@ struct Run {
     int last_counter = 0;
 };
 
-void on_log(long, double t, double dt, double ch, void* user) {
+int on_log(long, double t, double dt, double ch, void* user) {
     if (!static_cast<Run*>(user)->quiet)
         std::cout << "t= " << t << " dt= " << dt << " ch= " << ch << std::endl;  // MUSCL_NEW.cpp:836
+    return 0;
 }
 
 int on_dump(lsc_mhd_ctx* ctx, int counter, double, double, void* user) {

@@ -16,8 +16,9 @@
 
 #include "lsc_b200.h"
 
-static void log_line(long, double t, double dt, void* quiet) {
+static int log_line(long, double t, double dt, void* quiet) {
     if (!*static_cast<bool*>(quiet)) std::cout << "t = " << t << " dt = " << dt << std::endl;  // T:963
+    return 0;
 }
 
 int main(int argc, char** argv) {

@@ -42,6 +42,7 @@ extern "C" {
 #define LSC_ESTATE (-4)  /* call out of order (e.g. step before upload) */
 #define LSC_ENAN (-5)    /* max signal speed is not finite / not positive */
 #define LSC_ECOMM (-6)   /* NCCL failure */
+#define LSC_ECALLBACK (-7) /* a log callback returned non-zero: the loop stopped after that step */
 
 /* boundary types.  M:607-655 selects these by (un)commenting loops. */
 #define LSC_BC_PERIODIC 0     /* M:609-614 (x), M:641-646 (y); S:205-225 */
@@ -72,8 +73,9 @@ typedef struct lsc_mhd_ctx lsc_mhd_ctx;
 
 /* Called at the dump cadence of M:975 (t crossed 0.1*counter) from lsc_mhd_run_until. */
 typedef int (*lsc_mhd_dump_cb)(lsc_mhd_ctx* ctx, int counter, double t, double dt, void* user);
-/* Called once per step with the values of the log line M:836 ("t= .. dt= .. ch= .."). */
-typedef void (*lsc_mhd_log_cb)(long step, double t, double dt, double ch, void* user);
+/* Called once per step with the values of the log line M:836 ("t= .. dt= .. ch= ..").  Return 0 to continue; any
+ * other value stops the loop (lsc_mhd_run_until then returns LSC_ECALLBACK). */
+typedef int (*lsc_mhd_log_cb)(long step, double t, double dt, double ch, void* user);
 
 const char* lsc_last_error(void);
 int lsc_device_count(void);
@@ -159,6 +161,13 @@ int lsc_mhd_get_scalars(const lsc_mhd_ctx* ctx, double* t, double* dt, double* c
  * cells [nx+2..nx+3][ny+2..ny+3] are zero once a step has been taken). */
 int lsc_mhd_download(lsc_mhd_ctx* ctx, double* aos);
 
+/* Decomposition-independent 64-bit fingerprint of the INTERIOR of the current state (M:673 `u` after M:969), computed
+ * on the device: sum modulo 2^64 over interior values of splitmix64(bit pattern + 0x9E3779B97F4A7C15 * (global cell
+ * number * NVAR + k + 1)), global cell number = i*ny + j (0-based interior indices).  *hash receives THIS slab's
+ * contribution; the fingerprint of a decomposed grid is the sum of its slabs' words modulo 2^64, and equals the
+ * single-context value exactly when every interior bit agrees. */
+int lsc_mhd_state_hash(lsc_mhd_ctx* ctx, unsigned long long* hash);
+
 /* Host helper for callers that assemble a full-grid array from slabs: rebuilds the ghost ring the
  * reference's `u` holds after M:971 (boundary images per cfg->bc_x / bc_y with the reference's loop bounds,
  * the four never-written corner cells zero) from the interior of `aos` [(nx+4)][(ny+4)][9]. */
@@ -227,7 +236,7 @@ typedef struct lsc_euler_config {
 } lsc_euler_config;
 
 typedef struct lsc_euler_ctx lsc_euler_ctx;
-typedef void (*lsc_euler_log_cb)(long step, double t, double dt, void* user); /* G:631 "t = .. dt = .." */
+typedef int (*lsc_euler_log_cb)(long step, double t, double dt, void* user); /* G:631 "t = .. dt = .."; non-zero stops the loop */
 
 int lsc_euler_create(const lsc_euler_config* cfg, lsc_euler_ctx** out);
 int lsc_euler_destroy(lsc_euler_ctx* ctx);
@@ -253,6 +262,7 @@ int lsc_euler_download(lsc_euler_ctx* ctx, double* aos);              /* u after
 /* S:621-642 (blank_line_per_row = 0, euler_<k>.dat) / G:645-667 (= 1, SLIC2d.dat) */
 int lsc_euler_write_dat(const lsc_euler_config* cfg, const double* aos, const char* path, int blank_line_per_row);
 long lsc_euler_ieee_fallback_count(const lsc_euler_ctx* ctx);
+int lsc_euler_state_hash(lsc_euler_ctx* ctx, unsigned long long* hash); /* as lsc_mhd_state_hash, NVAR = 4 */
 
 /* ------------------------------------------------------------------------------------------------
  * Tabulated equation of state (T = MHD_codes/TabEoS.cpp; SURVEY.md 8f row N2, BASELINE config 5): the same SLIC

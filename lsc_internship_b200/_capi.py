@@ -49,11 +49,11 @@ class EulerConfig(ctypes.Structure):
 
 
 EULER_PROBLEMS = {"ot": 0, "orszag-tang": 0, "quadrants": 1, "cylinder": 2, "tabeos": 3}
-EULER_LOG_CB = ctypes.CFUNCTYPE(None, ctypes.c_long, ctypes.c_double, ctypes.c_double, ctypes.c_void_p)
+EULER_LOG_CB = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_long, ctypes.c_double, ctypes.c_double, ctypes.c_void_p)
 
 DUMP_CB = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_double, ctypes.c_double,
                            ctypes.c_void_p)
-LOG_CB = ctypes.CFUNCTYPE(None, ctypes.c_long, ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_void_p)
+LOG_CB = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_long, ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_void_p)
 
 # every symbol include/lsc_b200.h declares
 EXPORTS = [
@@ -62,7 +62,7 @@ EXPORTS = [
     "lsc_mhd_initial_condition", "lsc_mhd_upload", "lsc_mhd_init_problem", "lsc_mhd_step",
     "lsc_mhd_run_until", "lsc_mhd_get_scalars", "lsc_mhd_download", "lsc_mhd_write_dat",
     "lsc_comm_unique_id", "lsc_mhd_comm_init", "lsc_mhd_kat_hllc", "lsc_mhd_kat_fluxdef", "lsc_mhd_kat_cfl_bound", "lsc_mhd_set_arithmetic",
-    "lsc_kernel_launch_count", "lsc_mhd_step_timed", "lsc_mhd_set_profiling", "lsc_mhd_kernel_times", "lsc_mhd_comm_times", "lsc_mhd_set_overlap", "lsc_kat_division", "lsc_mhd_ieee_fallback_count", "lsc_mhd_group_step", "lsc_mhd_fill_ghost_ring",
+    "lsc_kernel_launch_count", "lsc_mhd_step_timed", "lsc_mhd_set_profiling", "lsc_mhd_kernel_times", "lsc_mhd_comm_times", "lsc_mhd_set_overlap", "lsc_kat_division", "lsc_mhd_ieee_fallback_count", "lsc_mhd_group_step", "lsc_mhd_fill_ghost_ring", "lsc_mhd_state_hash", "lsc_euler_state_hash",
     "lsc_euler_create", "lsc_euler_destroy", "lsc_euler_initial_condition", "lsc_euler_upload",
     "lsc_euler_init_problem", "lsc_euler_step", "lsc_euler_step_timed", "lsc_euler_run_until",
     "lsc_euler_get_scalars", "lsc_euler_download", "lsc_euler_write_dat", "lsc_euler_ieee_fallback_count",
@@ -146,10 +146,33 @@ def lib():
     L.lsc_euler_set_overlap.argtypes = [vp, ctypes.c_int]
     L.lsc_euler_kernel_times.argtypes = [vp, dp, ctypes.POINTER(ctypes.c_long)]
     L.lsc_mhd_fill_ghost_ring.argtypes = [ctypes.POINTER(MhdConfig), dp]
+    L.lsc_mhd_state_hash.argtypes = [vp, ctypes.POINTER(ctypes.c_ulonglong)]
+    L.lsc_euler_state_hash.argtypes = [vp, ctypes.POINTER(ctypes.c_ulonglong)]
     L.lsc_mhd_ieee_fallback_count.argtypes = [vp]
     L.lsc_mhd_ieee_fallback_count.restype = ctypes.c_long
     _lib = L
     return L
+
+
+_M64 = (1 << 64) - 1
+
+
+def state_hash_host(u_interior, i0_global=0, ny_total=None):
+    """lsc_mhd_state_hash / lsc_euler_state_hash evaluated with numpy on a host array [nxl][ny][nvar] of interior
+    values (include/lsc_b200.h): the same splitmix64 sum modulo 2^64.  For checking the device fingerprint."""
+    import numpy as np
+    a = np.ascontiguousarray(u_interior, dtype=np.float64)
+    nxl, ny, nv = a.shape
+    ny_total = ny if ny_total is None else ny_total
+    with np.errstate(over="ignore"):
+        cell = (np.arange(nxl, dtype=np.uint64)[:, None] + np.uint64(i0_global)) * np.uint64(ny_total) + \
+            np.arange(ny, dtype=np.uint64)[None, :]
+        idx = cell[:, :, None] * np.uint64(nv) + (np.arange(nv, dtype=np.uint64) + np.uint64(1))[None, None, :]
+        z = a.view(np.uint64) + np.uint64(0x9E3779B97F4A7C15) * idx
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        z = z ^ (z >> np.uint64(31))
+        return int(z.sum(dtype=np.uint64)) & _M64
 
 
 def check(rc):

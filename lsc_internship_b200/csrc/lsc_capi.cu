@@ -16,6 +16,7 @@
 #include "lsc_common.h"
 #include "mhd_host.h"
 #include "mhd_kernels.cuh"
+#include "state_hash.h"
 
 namespace {
 
@@ -687,7 +688,8 @@ int lsc_mhd_run_until(lsc_mhd_ctx* c, double t_stop, lsc_mhd_dump_cb dump_cb, ls
         int rc = step_once(c);
         if (rc) return rc;
         ++n;
-        if (log_cb) log_cb(c->step, c->t, c->dt, c->ch, user);  // :836
+        if (log_cb && log_cb(c->step, c->t, c->dt, c->ch, user))  // :836
+            return fail(LSC_ECALLBACK, "log callback stopped the loop at step %ld", c->step);
         if (c->t > 0.1 * counter && c->t - c->dt <= 0.1 * counter) {  // :975
             if (dump_cb) {
                 rc = dump_cb(c, counter, c->t, c->dt, user);
@@ -727,6 +729,26 @@ int lsc_mhd_download(lsc_mhd_ctx* c, double* aos) {
             lsc::mhd_apply_bc_y(c->cfg, c->nxl + 4, aos);
         }
     }
+    return LSC_OK;
+}
+
+int lsc_mhd_state_hash(lsc_mhd_ctx* c, unsigned long long* hash) {
+    if (!c || !hash) return fail(LSC_EINVAL, "null argument");
+    if (!c->uploaded) return fail(LSC_ESTATE, "lsc_mhd_state_hash before lsc_mhd_upload");
+    CUDA_TRY(cudaSetDevice(c->cfg.device));
+    if (c->pending && c->pending_step) {  // a launched step may still have to be recomputed (IEEE path)
+        int rc = resolve_pending(c);
+        if (rc) return rc;
+    }
+    unsigned long long* d = nullptr;
+    CUDA_TRY(cudaMalloc(&d, sizeof *d));
+    cudaMemsetAsync(d, 0, sizeof *d, c->stream);
+    lsc::launch_state_hash(c->g, lsc::NV, c->state[c->cur], c->i0, d, c->stream);
+    lsc_count_launches(1);
+    cudaError_t e = cudaMemcpyAsync(hash, d, sizeof *d, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d);
+    CUDA_TRY(e);
     return LSC_OK;
 }
 

@@ -10,6 +10,7 @@
 #include "euler_kernels.cuh"
 #include "lsc_comm.h"
 #include "lsc_common.h"
+#include "state_hash.h"
 
 struct lsc_euler_ctx {
     lsc_euler_config cfg;
@@ -571,7 +572,8 @@ int lsc_euler_run_until(lsc_euler_ctx* c, double t_stop, lsc_euler_log_cb log_cb
         int rc = e_step_once(c);
         if (rc) return rc;
         ++n;
-        if (log_cb) log_cb(c->step, c->t, c->dt, user);  // G:631
+        if (log_cb && log_cb(c->step, c->t, c->dt, user))  // G:631
+            return lsc_fail(LSC_ECALLBACK, "log callback stopped the loop at step %ld", c->step);
     } while (c->t < t_stop);  // S:617 / G:646
     if (steps_out) *steps_out = n;
     return e_resolve(c);
@@ -606,6 +608,26 @@ int lsc_euler_download(lsc_euler_ctx* c, double* aos) {
     }
     // y ghost rows are never stored on the device: rebuild the reference's ghost ring (S:616) on the host
     if (c->step > 0) lsc::euler_fill_ghost_ring(c->cfg, aos);
+    return LSC_OK;
+}
+
+int lsc_euler_state_hash(lsc_euler_ctx* c, unsigned long long* hash) {
+    if (!c || !hash) return lsc_fail(LSC_EINVAL, "null argument");
+    if (!c->uploaded) return lsc_fail(LSC_ESTATE, "lsc_euler_state_hash before lsc_euler_upload");
+    LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
+    if (c->pending && c->pending_step && !c->in_group) {
+        int rc = e_resolve(c);
+        if (rc) return rc;
+    }
+    unsigned long long* d = nullptr;
+    LSC_CUDA_TRY(cudaMalloc(&d, sizeof *d));
+    cudaMemsetAsync(d, 0, sizeof *d, c->stream);
+    lsc::launch_state_hash(c->g, 4, c->state[c->cur], c->i0, d, c->stream);
+    lsc_count_launches(1);
+    cudaError_t e = cudaMemcpyAsync(hash, d, sizeof *d, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d);
+    LSC_CUDA_TRY(e);
     return LSC_OK;
 }
 

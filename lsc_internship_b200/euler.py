@@ -127,8 +127,17 @@ class SlicEuler2d:
 
     def download(self, out=None):
         u = np.empty(self.shape, dtype=np.float64) if out is None else out
+        if not (isinstance(u, np.ndarray) and u.dtype == np.float64 and u.shape == self.shape
+                and u.flags["C_CONTIGUOUS"] and u.flags["WRITEABLE"]):
+            raise ValueError(f"out must be a writeable C-contiguous float64 array of shape {self.shape}")
         check(lib().lsc_euler_download(self._h, _dp(u)))
         return u
+
+    def state_hash(self):
+        """this slab's word of the decomposition-independent interior fingerprint (lsc_euler_state_hash)"""
+        h = ctypes.c_ulonglong()
+        check(lib().lsc_euler_state_hash(self._h, ctypes.byref(h)))
+        return h.value
 
     def step(self, nsteps=1):
         check(lib().lsc_euler_step(self._h, int(nsteps)))
@@ -163,9 +172,22 @@ class SlicEuler2d:
 
     def run_until(self, t_stop, log=None):
         """do { step } while (t < t_stop) -- S:600-617 / G:627-646.  Returns the number of steps."""
-        cb = _capi.EULER_LOG_CB((lambda n, t, dt, _u: log(n, t, dt))) if log else ctypes.cast(None, _capi.EULER_LOG_CB)
+        err = []
+
+        def on_log(n, t, dt, _u):  # an exception in a ctypes callback would be swallowed: keep it, stop the loop
+            try:
+                log(n, t, dt)
+                return 0
+            except BaseException as e:  # noqa: BLE001
+                err.append(e)
+                return 1
+
+        cb = _capi.EULER_LOG_CB(on_log) if log else ctypes.cast(None, _capi.EULER_LOG_CB)
         n = ctypes.c_long()
-        check(lib().lsc_euler_run_until(self._h, float(t_stop), cb, None, ctypes.byref(n)))
+        rc = lib().lsc_euler_run_until(self._h, float(t_stop), cb, None, ctypes.byref(n))
+        if err:
+            raise err[0]
+        check(rc)
         return n.value
 
     def write_dat(self, u, path, blank_line_per_row=False):

@@ -91,8 +91,18 @@ class MusclNew:
 
     def download(self, out=None):
         u = np.empty(self.shape, dtype=np.float64) if out is None else out
+        if not (isinstance(u, np.ndarray) and u.dtype == np.float64 and u.shape == self.shape
+                and u.flags["C_CONTIGUOUS"] and u.flags["WRITEABLE"]):
+            raise ValueError(f"out must be a writeable C-contiguous float64 array of shape {self.shape}")
         check(lib().lsc_mhd_download(self._h, _dp(u)))
         return u
+
+    def state_hash(self):
+        """This slab's word of the decomposition-independent interior fingerprint (lsc_mhd_state_hash); the
+        fingerprint of the whole grid is the sum of the slabs' words modulo 2^64."""
+        h = ctypes.c_ulonglong()
+        check(lib().lsc_mhd_state_hash(self._h, ctypes.byref(h)))
+        return h.value
 
     def comm_init(self, unique_id: bytes):
         buf = ctypes.create_string_buffer(unique_id, 128)
@@ -149,20 +159,38 @@ class MusclNew:
         state = {"counter": 0}
         buf = np.empty(self.shape, dtype=np.float64) if outdir else None
 
+        # an exception inside a ctypes callback would be printed and swallowed: keep it, make the C loop stop
+        # (non-zero return from the dump callback aborts lsc_mhd_run_until), re-raise once the call has returned
         def on_dump(_ctx, counter, t, dt, _user):
-            if outdir:
-                self.download(buf)
-                self.write_dat(buf, os.path.join(outdir, f"MHD{counter}.dat"))
-            state["counter"] = counter + 1
-            return 0
+            if "error" in state:
+                return -1
+            try:
+                if outdir:
+                    self.download(buf)
+                    self.write_dat(buf, os.path.join(outdir, f"MHD{counter}.dat"))
+                state["counter"] = counter + 1
+                return 0
+            except BaseException as e:  # noqa: BLE001
+                state["error"] = e
+                return -1
 
         def on_log(step, t, dt, ch, _user):
-            log(step, t, dt, ch)
+            if "error" in state:
+                return 1
+            try:
+                log(step, t, dt, ch)
+                return 0
+            except BaseException as e:  # noqa: BLE001
+                state["error"] = e
+                return 1
 
         dump_cb = _capi.DUMP_CB(on_dump)
         log_cb = _capi.LOG_CB(on_log) if log else ctypes.cast(None, _capi.LOG_CB)
         n = ctypes.c_long()
-        check(lib().lsc_mhd_run_until(self._h, tStop, dump_cb, log_cb, None, ctypes.byref(n)))
+        rc = lib().lsc_mhd_run_until(self._h, tStop, dump_cb, log_cb, None, ctypes.byref(n))
+        if "error" in state:
+            raise state["error"]
+        check(rc)
         if outdir:
             self.download(buf)
             self.write_dat(buf, os.path.join(outdir, f"MHD{state['counter']}.dat"))
@@ -223,6 +251,9 @@ class MusclNewGroup:
 
     def scalars(self):
         return self.parts[0].scalars()
+
+    def state_hash(self):
+        return sum(p.state_hash() for p in self.parts) & ((1 << 64) - 1)
 
     def download(self):
         """The full-grid array in the reference layout, ghost ring rebuilt as the reference holds it."""

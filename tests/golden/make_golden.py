@@ -6,7 +6,7 @@ oracle/build_ref.py).  Writes
   tests/golden/mhd_<case>.npz      final conserved state incl. ghost ring after N steps of the
                                    reference program + its per-step (t, dt, ch) log
   tests/golden/dat_sha256.json     sha256 of the reference's own committed output files
-                                   MHD_plot_data/MHD{0,1,2,60,121}.dat and euler_{1,20}.dat
+                                   MHD_plot_data/MHD{0..121}.dat and euler_{1..20}.dat
 The GPU box has no /root/reference; the tests there read only these fixtures.
 """
 import hashlib
@@ -56,7 +56,7 @@ def main():
                                                  cfl=0.8, gamma="5/3")))
         print(name, u.shape, log[-1])
     sha = {}
-    for f in ["MHD0.dat", "MHD1.dat", "MHD2.dat", "MHD60.dat", "MHD121.dat"] + [f"euler_{k}.dat" for k in range(1, 21)]:
+    for f in [f"MHD{k}.dat" for k in range(122)] + [f"euler_{k}.dat" for k in range(1, 21)]:
         with open(os.path.join(REF, "MHD_plot_data", f), "rb") as fh:
             sha[f] = hashlib.sha256(fh.read()).hexdigest()
     # the reference program itself (committed config) run to tStop = 0.25: its stdout log and final dump
