@@ -5,6 +5,12 @@
 // stdout log (:836) and the same MHD<counter>.dat files (:975-1001, :1006-1032), byte for byte.  The
 // constants the reference makes you edit in source are command-line options here.  All numerics run on
 // the GPU behind the C ABI of include/lsc_b200.h; this file holds no arithmetic of its own.
+//
+// --gpus N: still ONE process, as the reference is (MUSCL_NEW.cpp:658-1034) -- the grid is cut into N slabs along x,
+// one context per GPU (lsc_mhd_group_*: halos by peer copies over NVLink, device-side max reduction, one host
+// synchronisation per batch of steps).  --slabs N with fewer GPUs puts several slabs on one device (tests).
+// stdout and the .dat files do not depend on N.
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -18,6 +24,7 @@ namespace {
 
 struct Run {
     lsc_mhd_config cfg;
+    std::vector<lsc_mhd_ctx*> slabs;
     std::vector<double> host;
     std::string outdir;
     bool quiet = false;
@@ -31,11 +38,11 @@ int on_log(long, double t, double dt, double ch, void* user) {
     return 0;
 }
 
-int on_dump(lsc_mhd_ctx* ctx, int counter, double, double, void* user) {
+int on_dump(lsc_mhd_ctx*, int counter, double, double, void* user) {
     Run* r = static_cast<Run*>(user);
     r->last_counter = counter + 1;
     if (r->nodat) return 0;
-    if (int rc = lsc_mhd_download(ctx, r->host.data())) return rc;
+    if (int rc = lsc_mhd_group_download(r->slabs.data(), (int)r->slabs.size(), r->host.data())) return rc;
     const std::string name = r->outdir + "MHD" + std::to_string(counter) + ".dat";  // :990
     return lsc_mhd_write_dat(&r->cfg, r->host.data(), name.c_str());
 }
@@ -53,10 +60,12 @@ int parse_bc(const char* s) {
 int main(int argc, char** argv) {
     Run run;
     // committed constants, MUSCL_NEW.cpp:659-668
-    run.cfg = {128, 256, 0.0, 1.0, -1.0, 1.0, 5.0 / 3.0, 0.8, LSC_BC_PERIODIC, LSC_BC_REFLECTIVE, 0, 0, 1};
+    run.cfg = {128, 256, 0.0, 1.0, -1.0, 1.0, 5.0 / 3.0, 0.8, LSC_BC_PERIODIC, LSC_BC_REFLECTIVE, 0, 0, 1, 0, 0};
     double tStop = 12.0;
     int problem = LSC_MHD_IC_KELVIN_HELMHOLTZ;
     long nsteps = -1;
+    int nslabs = 1, ngpus = 0;
+    bool timing = false;
     for (int a = 1; a < argc; ++a) {
         auto val = [&](const char* name) -> const char* {
             if (a + 1 >= argc) { std::fprintf(stderr, "%s needs a value\n", name); std::exit(2); }
@@ -76,6 +85,9 @@ int main(int argc, char** argv) {
         else if (o == "--bcy") run.cfg.bc_y = parse_bc(val("--bcy"));
         else if (o == "--device") run.cfg.device = std::atoi(val("--device"));
         else if (o == "--steps") nsteps = std::atol(val("--steps"));
+        else if (o == "--gpus") { ngpus = std::atoi(val("--gpus")); nslabs = ngpus; }
+        else if (o == "--slabs") nslabs = std::atoi(val("--slabs"));
+        else if (o == "--time") timing = true;
         else if (o == "--outdir") run.outdir = std::string(val("--outdir")) + "/";
         else if (o == "--quiet") run.quiet = true;
         else if (o == "--no-dat") run.nodat = true;
@@ -89,40 +101,61 @@ int main(int argc, char** argv) {
                          "usage: muscl_new [--problem kh|ot] [--nx N] [--ny N] [--x0 v --x1 v --y0 v --y1 v]\n"
                          "                 [--tstop t] [--cfl C] [--gamma g] [--bcx periodic|transmissive]\n"
                          "                 [--bcy reflective|periodic|transmissive] [--steps n] [--outdir d]\n"
-                         "                 [--device k] [--quiet] [--no-dat]\n");
+                         "                 [--device k] [--gpus N | --slabs N] [--time] [--quiet] [--no-dat]\n");
             return 2;
         }
     }
 
-    lsc_mhd_ctx* ctx = nullptr;
-    if (lsc_mhd_create(&run.cfg, &ctx)) { std::fprintf(stderr, "%s\n", lsc_last_error()); return 1; }
-    run.host.resize((size_t)(run.cfg.nx + 4) * (run.cfg.ny + 4) * LSC_MHD_NVAR);
-    // initial conditions: MUSCL_NEW.cpp:719-825, evaluated on the host with the same libm
-    if (lsc_mhd_initial_condition(ctx, problem, run.host.data()) || lsc_mhd_upload(ctx, run.host.data())) {
-        std::fprintf(stderr, "%s\n", lsc_last_error());
-        return 1;
+    if (nslabs < 1) { std::fprintf(stderr, "--gpus / --slabs must be >= 1\n"); return 2; }
+    const int ndev = lsc_device_count();
+    if (ngpus > ndev) { std::fprintf(stderr, "--gpus %d but only %d CUDA device(s) are visible\n", ngpus, ndev); return 1; }
+    auto die = [] { std::fprintf(stderr, "%s\n", lsc_last_error()); return 1; };
+    // one context per slab; slab r of N owns columns [r nx/N, (r+1) nx/N) and lives on GPU (device + r) mod #GPUs
+    for (int r = 0; r < nslabs; ++r) {
+        lsc_mhd_config c = run.cfg;
+        c.rank = r;
+        c.nranks = nslabs;
+        c.device = ndev > 0 ? (run.cfg.device + r) % ndev : 0;
+        lsc_mhd_ctx* ctx = nullptr;
+        if (lsc_mhd_create(&c, &ctx)) return die();
+        run.slabs.push_back(ctx);
+        // initial conditions: MUSCL_NEW.cpp:719-825, evaluated on the host with the same libm, slab by slab
+        if (lsc_mhd_init_problem(ctx, problem)) return die();
     }
+    lsc_mhd_ctx** g = run.slabs.data();
+    if (!run.nodat) run.host.resize((size_t)(run.cfg.nx + 4) * (run.cfg.ny + 4) * LSC_MHD_NVAR);
+    const auto t0 = std::chrono::steady_clock::now();
+    long steps_taken = 0;
     int rc;
     if (nsteps >= 0) {
-        rc = 0;
-        for (long s = 0; s < nsteps && !rc; ++s) {
-            rc = lsc_mhd_step(ctx, 1);
-            double t, dt, ch;
-            lsc_mhd_get_scalars(ctx, &t, &dt, &ch, nullptr);
-            on_log(s, t, dt, ch, &run);
+        if (run.quiet) {
+            rc = lsc_mhd_group_step(g, nslabs, nsteps);
+        } else {
+            rc = 0;
+            for (long s = 0; s < nsteps && !rc; ++s) {
+                rc = lsc_mhd_group_step(g, nslabs, 1);
+                double t, dt, ch;
+                lsc_mhd_get_scalars(g[0], &t, &dt, &ch, nullptr);
+                on_log(s, t, dt, ch, &run);
+            }
         }
+        steps_taken = nsteps;
     } else {
-        rc = lsc_mhd_run_until(ctx, tStop, on_dump, on_log, &run, nullptr);  // :831-1003
+        rc = lsc_mhd_group_run_until(g, nslabs, tStop, on_dump, run.quiet ? nullptr : on_log, &run, &steps_taken);  // :831-1003
     }
-    if (rc) { std::fprintf(stderr, "%s\n", lsc_last_error()); return 1; }
+    if (rc) return die();
+    if (timing) {
+        const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        long syncs = 0, misses = 0;
+        lsc_mhd_loop_stats(g[0], &syncs, &misses);
+        std::fprintf(stderr, "steps=%ld elapsed_s=%.6f cell_updates_per_s=%.6e slabs=%d host_syncs=%ld exp_table_misses=%ld\n",
+                     steps_taken, secs, (double)run.cfg.nx * run.cfg.ny * steps_taken / secs, nslabs, syncs, misses);
+    }
     if (!run.nodat) {  // final dump, :1006-1032
-        if (lsc_mhd_download(ctx, run.host.data())) { std::fprintf(stderr, "%s\n", lsc_last_error()); return 1; }
+        if (lsc_mhd_group_download(g, nslabs, run.host.data())) return die();
         const std::string name = run.outdir + "MHD" + std::to_string(run.last_counter) + ".dat";
-        if (lsc_mhd_write_dat(&run.cfg, run.host.data(), name.c_str())) {
-            std::fprintf(stderr, "%s\n", lsc_last_error());
-            return 1;
-        }
+        if (lsc_mhd_write_dat(&run.cfg, run.host.data(), name.c_str())) return die();
     }
-    lsc_mhd_destroy(ctx);
+    for (auto c : run.slabs) lsc_mhd_destroy(c);
     return 0;
 }

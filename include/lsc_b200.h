@@ -67,6 +67,10 @@ typedef struct lsc_mhd_config {
      * columns [r*nx/nranks, (r+1)*nx/nranks) plus two halo columns per side.  nranks = 1:
      * the whole grid.  For nranks > 1 call lsc_mhd_comm_init() before upload. */
     int rank, nranks;
+    /* optional explicit slab bounds (uneven decompositions, e.g. sized by a calibration pass): this rank owns
+     * interior columns [slab_i0, slab_i0 + slab_nx).  slab_nx = 0 (the default of a zero-initialised struct):
+     * the even split above.  The caller makes the slabs of the ranks tile [0, nx) in rank order. */
+    int slab_i0, slab_nx;
 } lsc_mhd_config;
 
 typedef struct lsc_mhd_ctx lsc_mhd_ctx;
@@ -123,11 +127,26 @@ int lsc_mhd_step(lsc_mhd_ctx* ctx, long nsteps);
 int lsc_mhd_run_until(lsc_mhd_ctx* ctx, double t_stop, lsc_mhd_dump_cb dump_cb, lsc_mhd_log_cb log_cb,
                       void* user, long* steps_out);
 
-/* Single-process slab group: `n` contexts created with nranks = n, rank = 0..n-1 (on one or several GPUs
- * of this process; cfg.device per context) are advanced in lock step.  Halo columns move by peer copies
- * between the contexts' buffers, the signal speed is reduced on the host.  Same kernels and slab-edge code
- * as the NCCL mode; results are bit-identical to the single-context run for any n. */
+/* Single-process slab group -- how ONE program (the reference is one process, M:658-1034) uses the 8 GPUs of a box:
+ * `n` contexts created with nranks = n, rank = 0..n-1 (cfg.device per context: one GPU each, or several slabs on one
+ * GPU) are advanced in lock step by the calling thread.  Halo columns move by peer copies between the contexts'
+ * buffers over NVLink; the signal speed is max-reduced through 8-byte peer copies and a one-thread kernel on the
+ * first context's GPU.  Everything is stream-ordered by events: like the plain calls, a group call synchronises with
+ * the host once per batch of steps, not per step.  Same kernels and slab-edge code as the NCCL mode; results are
+ * bit-identical to the single-context run for any n.  lsc_mhd_group_run_until hands ctxs[0] to the callbacks. */
 int lsc_mhd_group_step(lsc_mhd_ctx** ctxs, int n, long nsteps);
+int lsc_mhd_group_step_timed(lsc_mhd_ctx** ctxs, int n, long nsteps, float* ms);
+int lsc_mhd_group_run_until(lsc_mhd_ctx** ctxs, int n, double t_stop, lsc_mhd_dump_cb dump_cb, lsc_mhd_log_cb log_cb,
+                            void* user, long* steps_out);
+/* lsc_mhd_download for a group: the WHOLE grid [(nx+4)][(ny+4)][9] assembled from the slabs, ghost ring as the
+ * reference's `u` holds it after M:971 -- what lsc_mhd_write_dat takes. */
+int lsc_mhd_group_download(lsc_mhd_ctx** ctxs, int n, double* aos);
+
+/* The time loop is device-resident (csrc/step_ctl.cuh): dt, ch, t, the psi factor and the loop predicates of
+ * M:831-1003 are formed on the device and the host synchronises once per batch of steps.  *host_syncs = number of
+ * batches so far; *exp_table_misses = how often the psi-damping argument was not in the host-made {argument ->
+ * glibc exp} table and the host had to supply it (each miss costs one extra synchronisation, never accuracy). */
+int lsc_mhd_loop_stats(const lsc_mhd_ctx* ctx, long* host_syncs, long* exp_table_misses);
 
 /* As lsc_mhd_step, bracketed by CUDA events on the context's own stream; *ms receives the device
  * time of the whole call (kernels, the per-step 8-byte readback of the signal speed, ghost/halo fill). */
@@ -158,7 +177,10 @@ int lsc_mhd_get_scalars(const lsc_mhd_ctx* ctx, double* t, double* dt, double* c
 
 /* Copy this rank's slab back in the reference layout, ghost ring included, with exactly the ghost
  * contents the reference's `u` holds after M:971 (boundary images; the four never-written corner
- * cells [nx+2..nx+3][ny+2..ny+3] are zero once a step has been taken). */
+ * cells [nx+2..nx+3][ny+2..ny+3] are zero once a step has been taken).
+ * nranks > 1: the slab's interior and halo columns as they are on the device, y ghost rows as plain boundary images
+ * over ALL nxl+4 columns -- the reference's loop bounds (i < nx+2) and zero corners belong to the assembled grid:
+ * copy the interior columns of every slab into one [(nx+4)][(ny+4)][9] array and call lsc_mhd_fill_ghost_ring. */
 int lsc_mhd_download(lsc_mhd_ctx* ctx, double* aos);
 
 /* Decomposition-independent 64-bit fingerprint of the INTERIOR of the current state (M:673 `u` after M:969), computed

@@ -30,6 +30,44 @@
 
 namespace lsc {
 
+// Per-context step scalars (step_ctl.cuh).  Indexed with a kernel parameter, i.e. a uniform value: ptxas loads the
+// entry with LDCU into uniform registers once per kernel (checked in the SASS) -- no per-thread registers.
+static __constant__ StepScalars c_step[STEP_SLOTS];
+
+#define LSC_RETURN_IF_HALTED(slot) \
+    if (c_step[slot].halt) return
+
+template <int DIR>
+__device__ __forceinline__ SweepParams make_params(const SweepArgs& a) {
+    const StepScalars& sc = c_step[a.slot];
+    SweepParams p;
+    p.gamma = a.gamma;
+    p.gm1 = a.gm1;
+    p.first_step = a.first_step;
+    p.bc_lo = a.bc_lo;
+    p.bc_hi = a.bc_hi;
+    p.ch = sc.ch;
+    p.ch2 = sc.ch2;
+    p.inv2ch = sc.inv2ch;
+    p.halfch = sc.halfch;
+    p.dtdh = DIR == 0 ? sc.dtdx : sc.dtdy;
+    p.hdtdh = DIR == 0 ? sc.hdtdx : sc.hdtdy;
+    p.psi_factor = sc.psi_factor;
+    return p;
+}
+
+#ifndef LSC_RELAXED_TU
+cudaError_t publish_step_scalars(const StepCtl* ctl, int slot, cudaStream_t s) {
+    return cudaMemcpyToSymbolAsync(c_step, &ctl->sc, sizeof(StepScalars), (size_t)slot * sizeof(StepScalars),
+                                   cudaMemcpyDeviceToDevice, s);
+}
+#else
+cudaError_t publish_step_scalars_relaxed(const StepCtl* ctl, int slot, cudaStream_t s) {
+    return cudaMemcpyToSymbolAsync(c_step, &ctl->sc, sizeof(StepScalars), (size_t)slot * sizeof(StepScalars),
+                                   cudaMemcpyDeviceToDevice, s);
+}
+#endif
+
 __device__ __forceinline__ void load_cell(const double* __restrict__ base, size_t idx, double (&u)[NV]) {
 #pragma unroll
     for (int k = 0; k < NV; ++k) u[k] = __ldg(base + idx + k * MHD_KSTR);
@@ -236,20 +274,105 @@ __device__ __forceinline__ bool x_sweep_block(const GridDims& g, const SweepPara
 }
 
 template <class D>
-__global__ void __launch_bounds__(XS_BLOCK, XS_MINB) x_sweep_kernel(const GridDims g, const SweepParams p,
+__global__ void __launch_bounds__(XS_BLOCK, XS_MINB) x_sweep_kernel(const GridDims g, const SweepArgs a,
                                                                     const double* __restrict__ cur,
                                                                     const double* __restrict__ prev,
                                                                     double* __restrict__ ubar,
                                                                     unsigned* __restrict__ block_flags,
                                                                     const int strip) {
+    LSC_RETURN_IF_HALTED(a.slot);
+    const SweepParams p = make_params<0>(a);
     // threads of the x sweep are independent: no barrier, a flagged thread just marks its block
     if (x_sweep_block<D>(g, p, cur, prev, ubar, blockIdx.x, blockIdx.y, strip))
         block_flags[blockIdx.y * gridDim.x + blockIdx.x] = 1u;
 }
 
 #ifndef LSC_RELAXED_TU
+// ------------------------------------------------------------------------------------
+// Head of a step (step_ctl.cuh): ComputeTimeStep's scalars MUSCL_NEW.cpp:117-118, `ch = maxSpeed; t += dt`
+// :834-835, psiUpdate's factor :66-69 and the loop predicates :975 / :1003, by one thread.  status[0] holds the
+// bit pattern of the max signal speed of the current state (the previous y sweep's fused reduction, or the
+// stand-alone reduction after an upload; already max-reduced over ranks), status[1..3] the fix kernels' counts.
+// ------------------------------------------------------------------------------------
+__global__ void prepare_kernel(StepCtl* __restrict__ ctl, const StepCmd* __restrict__ cmd,
+                               unsigned long long* __restrict__ status, double* __restrict__ log_ring) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    StepCtl& c = *ctl;
+    bool fresh = false;
+    if (c.batch_seen != cmd->batch) {  // first step of a batch: the host has handled whatever stopped the last one
+        c.batch_seen = cmd->batch;
+        c.halt = HALT_NONE;
+        c.log_count = 0;
+        fresh = true;
+    }
+    if (c.halt != HALT_NONE) return;  // c.sc.halt is set already: the rest of this step does nothing
+    int halt = HALT_NONE;
+    if (!fresh && pause_due(c.t, c.dt, cmd->t_stop, cmd->dump_counter)) halt = HALT_PAUSE;
+    else if (c.step >= cmd->step_limit) halt = HALT_LIMIT;
+    else if (cmd->keep_log && c.log_count >= STEP_LOG_CAP) halt = HALT_LOG_FULL;
+    if (halt == HALT_NONE) {
+        const double ms = __longlong_as_double((long long)status[0]);
+        if (!(ms > 0.0) || !(ms <= 1.7976931348623157e308)) {
+            c.max_speed = ms;
+            halt = HALT_NAN;
+        } else {
+            const double dt = c.cfl * c.dspace / ms;  // :118
+            const double arg = psi_argument(dt, ms);  // psiUpdate(psi, maxSpeed, 0.5*dt), :67, :900
+            const unsigned long long abits = (unsigned long long)__double_as_longlong(arg);
+            int hit = -1;
+            for (int q = 0; q < c.ntab; ++q)
+                if (c.tab_arg[q] == abits) hit = q;
+            if (hit < 0) {
+                c.miss_arg = abits;
+                halt = HALT_EXP_MISS;  // status stays as it is: the resumed prepare consumes it
+            } else {
+                c.max_speed = ms;
+                c.dt = dt;
+                c.t += dt;  // :835
+                c.step += 1;
+                StepScalars& sc = c.sc;
+                sc.ch = ms;  // :834
+                sc.ch2 = ms * ms;
+                sc.inv2ch = 1.0 / (2.0 * ms);  // :126
+                sc.halfch = ms / 2.0;          // :127
+                sc.dtdx = dt / c.dx;
+                sc.hdtdx = 0.5 * (dt / c.dx);
+                sc.dtdy = dt / c.dy;
+                sc.hdtdy = 0.5 * (dt / c.dy);
+                sc.psi_factor = c.tab_val[hit];
+                c.redo_total += status[1] + status[2] + status[3];
+                status[0] = status[1] = status[2] = status[3] = 0ull;
+                if (cmd->keep_log) {
+                    double* rec = log_ring + 3 * c.log_count;
+                    rec[0] = c.t;
+                    rec[1] = dt;
+                    rec[2] = ms;
+                    c.log_count += 1;
+                }
+            }
+        }
+    }
+    c.halt = halt;
+    c.sc.halt = halt;
+}
+
+void launch_prepare(StepCtl* ctl, const StepCmd* cmd, unsigned long long* status, double* log_ring, cudaStream_t s) {
+    prepare_kernel<<<1, 32, 0, s>>>(ctl, cmd, status, log_ring);
+}
+
+// words[n] = max(words[0..n)): the slabs of a single-process team bring their status[0] words to the leader
+// (bit patterns of non-negative doubles order like the values)
+__global__ void max_words_kernel(unsigned long long* __restrict__ words, int n) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    unsigned long long m = 0;
+    for (int q = 0; q < n; ++q) m = words[q] > m ? words[q] : m;
+    words[n] = m;
+}
+
+void launch_max_words(unsigned long long* words, int n, cudaStream_t s) { max_words_kernel<<<1, 32, 0, s>>>(words, n); }
+
 // Recompute the blocks a fast sweep flagged, with IEEE division (persistent grid over the device-side list).
-__global__ void __launch_bounds__(XS_BLOCK) x_sweep_fix_kernel(const GridDims g, const SweepParams p,
+__global__ void __launch_bounds__(XS_BLOCK) x_sweep_fix_kernel(const GridDims g, const SweepArgs a,
                                                                const double* __restrict__ cur,
                                                                const double* __restrict__ prev,
                                                                double* __restrict__ ubar,
@@ -257,6 +380,8 @@ __global__ void __launch_bounds__(XS_BLOCK) x_sweep_fix_kernel(const GridDims g,
                                                                unsigned* __restrict__ block_flags,
                                                                const int strip, const unsigned nbx,
                                                                const unsigned nblocks) {
+    LSC_RETURN_IF_HALTED(a.slot);
+    const SweepParams p = make_params<0>(a);
     for (unsigned bid = blockIdx.x; bid < nblocks; bid += gridDim.x) {
         if (block_flags[bid] == 0u) continue;  // uniform across the block
         x_sweep_block<IeeeDiv>(g, p, cur, prev, ubar, (int)(bid % nbx), (int)(bid / nbx), strip);
@@ -268,7 +393,7 @@ __global__ void __launch_bounds__(XS_BLOCK) x_sweep_fix_kernel(const GridDims g,
     }
 }
 
-void launch_x_sweep(const GridDims& g, const SweepParams& p, const double* u_cur, const double* u_prev,
+void launch_x_sweep(const GridDims& g, const SweepArgs& p, const double* u_cur, const double* u_prev,
                     double* u_bar, unsigned long long* status, unsigned* x_flags, cudaStream_t s) {
     // strip length along i: at most XS_STRIP columns per thread (3 warm-up cells amortised over the strip),
     // chosen so that the blocks fill whole rounds of the 148 SMs x XS_MINB resident blocks (choose_x_strip)
@@ -287,7 +412,7 @@ long x_sweep_block_count(const GridDims& g) {
     return (long)row_blocks * ((g.nxl + 7) / 8);  // strip is never shorter than 8
 }
 #else  // LSC_RELAXED_TU
-void launch_x_sweep_relaxed(const GridDims& g, const SweepParams& p, const double* u_cur, const double* u_prev,
+void launch_x_sweep_relaxed(const GridDims& g, const SweepArgs& p, const double* u_cur, const double* u_prev,
                             double* u_bar, unsigned* x_flags, cudaStream_t s) {
     dim3 block(XS_BLOCK);
     const int row_blocks = (g.ny + block.x - 1) / block.x;
@@ -569,12 +694,14 @@ __device__ __forceinline__ bool y_sweep_block(const GridDims& g, const SweepPara
 }
 
 template <class D, bool NONPER>
-__global__ void __launch_bounds__(BJ, YS_MINB) y_sweep_kernel(const GridDims g, const SweepParams p,
+__global__ void __launch_bounds__(BJ, YS_MINB) y_sweep_kernel(const GridDims g, const SweepArgs a,
                                                               const double* __restrict__ ubar,
                                                               const double* __restrict__ cur,
                                                               double* __restrict__ next,
                                                               unsigned long long* __restrict__ status,
                                                               unsigned* __restrict__ fix_list, const YCols yc) {
+    LSC_RETURN_IF_HALTED(a.slot);
+    const SweepParams p = make_params<1>(a);
     double speed;
     // column of this block row: a launch covers all columns, the four slab-edge columns or the rest (YCols)
     const int col = yc.c0 + (int)blockIdx.y + ((int)blockIdx.y >= yc.jump_at ? yc.jump : 0);
@@ -588,12 +715,14 @@ __global__ void __launch_bounds__(BJ, YS_MINB) y_sweep_kernel(const GridDims g, 
 
 #ifndef LSC_RELAXED_TU
 template <bool NONPER>
-__global__ void __launch_bounds__(BJ) y_sweep_fix_kernel(const GridDims g, const SweepParams p,
+__global__ void __launch_bounds__(BJ) y_sweep_fix_kernel(const GridDims g, const SweepArgs a,
                                                          const double* __restrict__ ubar,
                                                          const double* __restrict__ cur, double* __restrict__ next,
                                                          unsigned long long* __restrict__ status,
                                                          const unsigned* __restrict__ fix_list, const unsigned nbx,
                                                          const int counter) {
+    LSC_RETURN_IF_HALTED(a.slot);
+    const SweepParams p = make_params<1>(a);
     const unsigned long long count = status[counter];
     for (unsigned long long q = blockIdx.x; q < count; q += gridDim.x) {
         const unsigned bid = fix_list[q];
@@ -604,7 +733,7 @@ __global__ void __launch_bounds__(BJ) y_sweep_fix_kernel(const GridDims g, const
     }
 }
 
-void launch_y_sweep(const GridDims& g, const SweepParams& p, const double* u_bar, const double* u_cur,
+void launch_y_sweep(const GridDims& g, const SweepArgs& p, const double* u_bar, const double* u_cur,
                     double* u_next, unsigned long long* status, unsigned* fix_list, cudaStream_t s,
                     int part) {
     dim3 block(BJ);
@@ -627,7 +756,7 @@ void launch_y_sweep(const GridDims& g, const SweepParams& p, const double* u_bar
 long y_sweep_block_count(const GridDims& g) { return (long)((g.ny + (BJ - 2) - 1) / (BJ - 2)) * g.nxl; }
 long y_edge_block_count(const GridDims& g) { return (long)((g.ny + (BJ - 2) - 1) / (BJ - 2)) * 4; }
 #else  // LSC_RELAXED_TU
-void launch_y_sweep_relaxed(const GridDims& g, const SweepParams& p, const double* u_bar, const double* u_cur,
+void launch_y_sweep_relaxed(const GridDims& g, const SweepArgs& p, const double* u_bar, const double* u_cur,
                             double* u_next, unsigned long long* status, unsigned* fix_list, cudaStream_t s,
                             int part) {
     dim3 block(BJ);

@@ -4,6 +4,8 @@
 #include <cstdint>
 #include <cuda_runtime.h>
 
+#include "step_ctl.cuh"
+
 namespace lsc {
 
 constexpr int NV = 9;  // rho, mx, my, mz, E, Bx, By, Bz, psi  (MUSCL_NEW.cpp:11-19)
@@ -66,24 +68,42 @@ inline int choose_x_strip(int row_blocks, int nxl, int max_strip, int resident_b
     return best;
 }
 
-struct SweepParams {
+// What a sweep needs besides the state.  The HOST knows the first six fields when it enqueues a step (SweepArgs,
+// kernel parameters); the rest are the step's scalars, computed on the device by the prepare kernel and read from
+// the context's __constant__ slot (step_ctl.cuh) -- the kernels assemble a SweepParams from both.
+struct SweepArgs {
     double gamma, gm1;
-    double inv2ch, halfch;  // 1.0/(2.0*ch) and ch/2.0 (MUSCL_NEW.cpp:126-127), divided on the host
-    double ch, ch2;      // GLM wave speed = max signal speed of this step (MUSCL_NEW.cpp:834)
-    double dtdh;         // dt/dx (x sweep) or dt/dy (y sweep)
-    double hdtdh;        // 0.5*(dt/dx)
-    double psi_factor;   // exp(-(0.5 dt) ch / 0.18), host libm (MUSCL_NEW.cpp:66-69)
     int first_step;      // 1: limiter's "previous primitives" are all zero (MUSCL_NEW.cpp:676-677, :845)
     int bc_lo, bc_hi;    // physical boundary type at the low/high end of the sweep axis, or -1 when the
                          // end is an inter-rank slab edge (ghost columns then hold neighbour data)
+    int slot;            // which c_step[] entry holds this context's scalars
 };
+struct SweepParams {
+    double gamma, gm1;
+    double inv2ch, halfch;  // 1.0/(2.0*ch) and ch/2.0 (MUSCL_NEW.cpp:126-127)
+    double ch, ch2;      // GLM wave speed = max signal speed of this step (MUSCL_NEW.cpp:834)
+    double dtdh;         // dt/dx (x sweep) or dt/dy (y sweep)
+    double hdtdh;        // 0.5*(dt/dx)
+    double psi_factor;   // exp(-(0.5 dt) ch / 0.18), glibc's value through the host-made table (MUSCL_NEW.cpp:66-69)
+    int first_step;
+    int bc_lo, bc_hi;
+};
+
+// Head of a step on the stream: (1) the one-thread prepare kernel -- consumes status[0] (max signal speed of the
+// current state), forms the step's scalars in ctl->sc, accumulates and clears the status words, evaluates the
+// pause conditions (step_ctl.cuh); (2) ctl->sc -> c_step[slot] of the translation unit that holds the sweeps
+// (`relaxed`: mhd_kernels_relaxed.cu keeps its own copy).
+void launch_prepare(StepCtl* ctl, const StepCmd* cmd, unsigned long long* status, double* log_ring, cudaStream_t s);
+void launch_max_words(unsigned long long* words, int n, cudaStream_t s);  // words[n] = max(words[0..n))
+cudaError_t publish_step_scalars(const StepCtl* ctl, int slot, cudaStream_t s);
+cudaError_t publish_step_scalars_relaxed(const StepCtl* ctl, int slot, cudaStream_t s);
 
 // status[0] = bit pattern of the max signal speed (y sweep), status[1] / status[2] = number of x / y sweep
 // blocks in which a fast division saw an operand outside its guarded window; those block indices are in
 // recomputed with IEEE division by the fix kernel launched right behind each sweep.  The x sweep marks them in
 // x_flags (x_sweep_block_count entries, all zero on entry and again on exit), the y sweep lists them in fix_list
 // (y_sweep_block_count entries, plus y_edge_block_count for the slab-edge launch, which counts in status[3]).
-void launch_x_sweep(const GridDims& g, const SweepParams& p, const double* u_cur, const double* u_prev,
+void launch_x_sweep(const GridDims& g, const SweepArgs& p, const double* u_cur, const double* u_prev,
                     double* u_bar, unsigned long long* status, unsigned* x_flags, cudaStream_t s);
 // `part` selects the columns of one y-sweep launch (halo/compute overlap): Y_ALL, or
 // Y_EDGES (local columns 0,1 and nxl-2,nxl-1: what the x neighbours need) followed by Y_INTERIOR (the rest), so
@@ -100,13 +120,13 @@ inline YCols y_columns(const GridDims& g, int part) {
     if (part == Y_INTERIOR) return YCols{2, 0x7fffffff, 0, g.nxl - 4, 2};
     return YCols{0, 0x7fffffff, 0, g.nxl, 2};
 }
-void launch_y_sweep(const GridDims& g, const SweepParams& p, const double* u_bar, const double* u_cur,
+void launch_y_sweep(const GridDims& g, const SweepArgs& p, const double* u_bar, const double* u_cur,
                     double* u_next, unsigned long long* status, unsigned* fix_list, cudaStream_t s,
                     int part = Y_ALL);
 // relaxed-arithmetic instantiations (mhd_kernels_relaxed.cu: FMA contraction, 1-multiply quotients; no fix pass)
-void launch_x_sweep_relaxed(const GridDims& g, const SweepParams& p, const double* u_cur, const double* u_prev,
+void launch_x_sweep_relaxed(const GridDims& g, const SweepArgs& p, const double* u_cur, const double* u_prev,
                             double* u_bar, unsigned* x_flags, cudaStream_t s);
-void launch_y_sweep_relaxed(const GridDims& g, const SweepParams& p, const double* u_bar, const double* u_cur,
+void launch_y_sweep_relaxed(const GridDims& g, const SweepArgs& p, const double* u_bar, const double* u_cur,
                             double* u_next, unsigned long long* status, unsigned* fix_list, cudaStream_t s,
                             int part = Y_ALL);
 long x_sweep_block_count(const GridDims& g);

@@ -32,12 +32,14 @@ class MusclNew:
 
     def __init__(self, nxCells=128, nyCells=256, x0=0.0, x1=1.0, y0=-1.0, y1=1.0, tStop=12.0, C=0.8,
                  gamma=5.0 / 3.0, bc_x="periodic", bc_y="reflective", problem="kh", device=0, rank=0, nranks=1,
-                 arithmetic="reference"):
+                 arithmetic="reference", slab=None):
         self.tStop = float(tStop)
         self.problem = _capi.MHD_PROBLEMS[problem] if isinstance(problem, str) else int(problem)
+        # slab = (first interior column, width): explicit bounds of this rank's slab (default: the even split)
+        slab_i0, slab_nx = (0, 0) if slab is None else (int(slab[0]), int(slab[1]))
         self.cfg = MhdConfig(int(nxCells), int(nyCells), float(x0), float(x1), float(y0), float(y1),
                              float(gamma), float(C), _capi.BC_NAMES[bc_x], _capi.BC_NAMES[bc_y],
-                             int(device), int(rank), int(nranks))
+                             int(device), int(rank), int(nranks), slab_i0, slab_nx)
         self._h = ctypes.c_void_p()
         check(lib().lsc_mhd_create(ctypes.byref(self.cfg), ctypes.byref(self._h)))
         self.nxl = lib().lsc_mhd_local_nx(self._h)
@@ -151,6 +153,15 @@ class MusclNew:
                                         ctypes.byref(n)))
         return t.value, dt.value, ch.value, n.value
 
+    def loop_stats(self):
+        """(host synchronisations of the time loop so far, psi-damping exp-table misses) -- lsc_mhd_loop_stats"""
+        a, b = ctypes.c_long(), ctypes.c_long()
+        check(lib().lsc_mhd_loop_stats(self._h, ctypes.byref(a), ctypes.byref(b)))
+        return a.value, b.value
+
+    def _run_until(self, tStop, dump_cb, log_cb, n):
+        return lib().lsc_mhd_run_until(self._h, tStop, dump_cb, log_cb, None, ctypes.byref(n))
+
     def run(self, tStop=None, outdir=None, log=None):
         """The do{}while loop MUSCL_NEW.cpp:831-1003 followed by the final dump :1006-1032.
         Writes MHD<counter>.dat into `outdir` at the reference's cadence when given; `log`
@@ -187,7 +198,7 @@ class MusclNew:
         dump_cb = _capi.DUMP_CB(on_dump)
         log_cb = _capi.LOG_CB(on_log) if log else ctypes.cast(None, _capi.LOG_CB)
         n = ctypes.c_long()
-        rc = lib().lsc_mhd_run_until(self._h, tStop, dump_cb, log_cb, None, ctypes.byref(n))
+        rc = self._run_until(tStop, dump_cb, log_cb, n)
         if "error" in state:
             raise state["error"]
         check(rc)
@@ -223,13 +234,19 @@ class MusclNewGroup:
     """P slabs of one grid driven in lock step from this process (lsc_mhd_group_step): on one GPU for
     decomposition-invariance tests, or one slab per GPU with peer copies over NVLink."""
 
-    def __init__(self, nslabs, devices=None, **kw):
+    def __init__(self, nslabs, devices=None, _parts=None, **kw):
         ndev = lib().lsc_device_count()
         devices = devices if devices is not None else [r % max(ndev, 1) for r in range(nslabs)]
-        self.parts = [MusclNew(device=devices[r], rank=r, nranks=nslabs, **kw) for r in range(nslabs)]
+        self.parts = _parts if _parts is not None else \
+            [MusclNew(device=devices[r], rank=r, nranks=nslabs, **kw) for r in range(nslabs)]
         self.cfg = MhdConfig.from_buffer_copy(self.parts[0].cfg)
-        self.cfg.rank, self.cfg.nranks = 0, 1
+        self.cfg.rank, self.cfg.nranks, self.cfg.slab_i0, self.cfg.slab_nx = 0, 1, 0, 0
         self._arr = (ctypes.c_void_p * nslabs)(*[p._h for p in self.parts])
+
+    @classmethod
+    def from_parts(cls, parts):
+        """a team of contexts the caller created itself (e.g. with explicit, uneven slab bounds)"""
+        return cls(len(parts), _parts=list(parts))
 
     @property
     def shape(self):
@@ -249,23 +266,71 @@ class MusclNewGroup:
     def step(self, nsteps=1):
         check(lib().lsc_mhd_group_step(self._arr, len(self.parts), int(nsteps)))
 
+    def step_timed(self, nsteps=1):
+        ms = ctypes.c_float()
+        check(lib().lsc_mhd_group_step_timed(self._arr, len(self.parts), int(nsteps), ctypes.byref(ms)))
+        return ms.value
+
     def scalars(self):
         return self.parts[0].scalars()
+
+    def loop_stats(self):
+        return self.parts[0].loop_stats()
+
+    def ieee_fallback_count(self):
+        return sum(p.ieee_fallback_count() for p in self.parts)
+
+    def run(self, tStop=12.0, outdir=None, log=None):
+        """MusclNew.run for the slabs of this process: the loop M:831-1003 through lsc_mhd_group_run_until, the
+        MHD<counter>.dat files from the assembled grid."""
+        state = {"counter": 0}
+
+        def on_dump(_ctx, counter, t, dt, _user):
+            if "error" in state:
+                return -1
+            try:
+                if outdir:
+                    self.write_dat(self.download(), os.path.join(outdir, f"MHD{counter}.dat"))
+                state["counter"] = counter + 1
+                return 0
+            except BaseException as e:  # noqa: BLE001
+                state["error"] = e
+                return -1
+
+        def on_log(step, t, dt, ch, _user):
+            if "error" in state:
+                return 1
+            try:
+                log(step, t, dt, ch)
+                return 0
+            except BaseException as e:  # noqa: BLE001
+                state["error"] = e
+                return 1
+
+        dump_cb = _capi.DUMP_CB(on_dump)
+        log_cb = _capi.LOG_CB(on_log) if log else ctypes.cast(None, _capi.LOG_CB)
+        n = ctypes.c_long()
+        rc = lib().lsc_mhd_group_run_until(self._arr, len(self.parts), float(tStop), dump_cb, log_cb, None,
+                                           ctypes.byref(n))
+        if "error" in state:
+            raise state["error"]
+        check(rc)
+        if outdir:
+            self.write_dat(self.download(), os.path.join(outdir, f"MHD{state['counter']}.dat"))
+        return n.value
+
+    def write_dat(self, u, path):
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        check(lib().lsc_mhd_write_dat(ctypes.byref(self.cfg), _dp(u), os.fsencode(path)))
 
     def state_hash(self):
         return sum(p.state_hash() for p in self.parts) & ((1 << 64) - 1)
 
-    def download(self):
-        """The full-grid array in the reference layout, ghost ring rebuilt as the reference holds it."""
-        u = np.zeros(self.shape, dtype=np.float64)
-        stepped = self.parts[0].scalars()[3] > 0
-        for p in self.parts:
-            s = p.download()
-            lo = 0 if p.cfg.rank == 0 else 2
-            hi = p.nxl + 4 if p.cfg.rank == p.cfg.nranks - 1 else p.nxl + 2
-            u[p.i0 + lo:p.i0 + hi] = s[lo:hi]
-        if stepped:
-            check(lib().lsc_mhd_fill_ghost_ring(ctypes.byref(self.cfg), _dp(u)))
+    def download(self, out=None):
+        """The full-grid array in the reference layout, ghost ring rebuilt as the reference holds it
+        (lsc_mhd_group_download)."""
+        u = np.zeros(self.shape, dtype=np.float64) if out is None else out
+        check(lib().lsc_mhd_group_download(self._arr, len(self.parts), _dp(u)))
         return u
 
     def close(self):

@@ -115,7 +115,7 @@ def patch_gslic(src):
     return body[:-1] + "    g_finish(u, t);\n}\n"
 
 
-def build_euler(opt="-O2"):
+def build_euler(opt="-O3"):
     with open(os.path.join(REF, "Euler_codes", "SLIC_euler_2d.cpp")) as f:
         compile_stdin(patch_slic(f.read()), os.path.join(OUT, "slic_ref"), opt)
     with open(os.path.join(REF, "Euler_codes", "generaliseSLIC.cpp")) as f:

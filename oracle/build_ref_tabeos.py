@@ -65,7 +65,7 @@ def patch_tabeos(src):
     return body[:-1] + "    g_finish(u, t);\n}\n"
 
 
-def build_tabeos(opt="-O2"):
+def build_tabeos(opt="-O3"):
     with open(os.path.join(REF, "MHD_codes", "TabEoS.cpp")) as f:
         compile_stdin(patch_tabeos(f.read()), os.path.join(OUT, "tabeos_ref"), opt)
 

@@ -185,32 +185,7 @@ def run_euler_ref(which, nx, ny, dom, t_stop, cfl, gamma, nsteps, ic=0, cwd=None
 # = density index.  A gas whose adiabatic index drifts from 1.6 (low p) to 1.2 (high p): not an ideal gas (so the
 # lookup is really exercised), e(p) strictly increasing at fixed rho (T's reverse search needs that).
 # ---------------------------------------------------------------------------------------------------------
-def eos_table():
-    dens = np.logspace(-3.0, 2.0, 500)
-    pres = np.logspace(1.0, 10.0, 500)
-    g = 1.4 - 0.2 * np.tanh(np.log10(pres / 1.0e6))
-    P, R = pres[:, None], dens[None, :]
-    energies = P / ((g[:, None] - 1.0) * R)
-    sound = np.sqrt(g[:, None] * P / R)
-    return dens, pres, sound, energies
-
-
-def write_eos_table(path):
-    """Write the synthetic table as a Plasma19_EoS.txt look-alike and return the arrays AS PARSED BACK from it."""
-    dens, pres, sound, energies = eos_table()
-    temp = energies / 718.0
-    row = lambda v: " ".join(repr(float(x)) for x in v)  # noqa: E731
-    lines = ["# synthetic EoS table in the layout TabEoS.cpp parses (T:36-128)"] * 9
-    lines += [row(dens), "# pressures", row(pres), "# sound speed [p][rho]"]
-    lines += [row(r) for r in sound] + ["# specific internal energy [p][rho]"]
-    lines += [row(r) for r in energies] + ["# temperature"]
-    lines += [row(r) for r in temp] + ["# electrical conductivity"]
-    lines += [row(r) for r in np.ones_like(temp)] + ["# thermal conductivity"]
-    lines += [row(r) for r in np.ones_like(temp)]
-    assert len(lines) == 2517
-    with open(path, "w") as f:
-        f.write("\n".join(lines) + "\n")
-    return dens, pres, sound, energies
+from lsc_internship_b200.synthetic_eos import eos_table, write_eos_table  # noqa: E402,F401  (the synthetic table)
 
 
 def run_tabeos_ref(nx, ny, nsteps, dom=(0.0, 1.0, 0.0, 1.0), t_stop=1e9, cfl=0.8, workdir=None):

@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol():
 
 
 def test_config_struct_layout():
-    assert ctypes.sizeof(_capi.MhdConfig) == 4 + 4 + 6 * 8 + 5 * 4 + 4  # trailing pad to 8
+    assert ctypes.sizeof(_capi.MhdConfig) == 4 + 4 + 6 * 8 + 7 * 4 + 4  # trailing pad to 8
 
 
 @pytest.mark.parametrize("bc", ["periodic", "transmissive"])

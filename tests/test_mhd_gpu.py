@@ -485,3 +485,121 @@ def test_relaxed_arithmetic_deviation():
     for k in (0, 1, 2, 4, 5, 6):                          # the variables that are not identically ~0 in OT
         assert rel[k] < 2e-2, (k, rel[k])
         assert l1[k] < 2e-3, (k, l1[k])
+
+
+def test_time_loop_is_device_resident():
+    """The loop state (dt, ch, t, psi factor, stop / dump predicates) lives on the device (csrc/step_ctl.cuh): a call
+    that advances many steps synchronises with the host ONCE, and the per-step scalars it leaves behind are the
+    reference's bit for bit (the oracle's log)."""
+    nx, ny, n = 64, 48, 57
+    cfg = mhd_cfg(nx, ny)
+    u0 = mhd_ic(cfg, "ot")
+    o = OracleMhd(cfg, u0)
+    log = o.step(n)
+    s = lsc.MusclNew(nx, ny, 0, 1, 0, 1, bc_x="periodic", bc_y="periodic", problem="ot")
+    s.upload(u0)
+    syncs0, _ = s.loop_stats()
+    s.step(n)
+    syncs1, misses = s.loop_stats()
+    assert syncs1 - syncs0 == 1 and misses == 0
+    t, dt, ch, k = s.scalars()
+    assert (t, dt, ch) == tuple(log[-1]) and k == n
+    assert np.array_equal(bits(s.download()), bits(o.state()[0]))
+    # run(): batches end where the reference dumps or stops, and the log callback sees every step's values
+    s.upload(u0)
+    o2 = OracleMhd(cfg, u0)
+    lines = []
+    nrun = s.run(tStop=0.35, log=lambda k, t, dt, ch: lines.append((t, dt, ch)))
+    ref = o2.step(nrun)
+    assert np.array_equal(bits(np.array(lines)), bits(ref))
+    assert ref[-1][0] >= 0.35 > ref[-2][0]                      # stopped at the first step past tStop (M:1003)
+    syncs2, _ = s.loop_stats()
+    assert syncs2 - syncs1 <= 6                                  # dumps at t = 0+, 0.1, 0.2, 0.3, the stop (+1 spare)
+    assert np.array_equal(bits(s.download()), bits(o2.state()[0]))
+    s.close()
+
+
+def test_psi_factor_table_miss_path(monkeypatch):
+    """exp() of psiUpdate (M:67) comes from a host-made {argument bits -> glibc exp} table.  With the table emptied
+    (test hook) every distinct argument takes the miss path -- the device halts, the host supplies exp of that very
+    argument, the step is re-issued -- and nothing changes in the result."""
+    nx, ny, n = 40, 36, 12
+    cfg = mhd_cfg(nx, ny, (0.0, 1.0, -1.0, 1.0), bcx="periodic", bcy="reflective")
+    u0 = mhd_ic(cfg, "kh")
+    o = OracleMhd(cfg, u0)
+    log = o.step(n)
+    monkeypatch.setenv("LSC_EXP_TABLE_EMPTY", "1")
+    s = lsc.MusclNew(nx, ny, 0.0, 1.0, -1.0, 1.0, bc_x="periodic", bc_y="reflective", problem="kh")
+    monkeypatch.delenv("LSC_EXP_TABLE_EMPTY")
+    s.upload(u0)
+    s.step(n)
+    _, misses = s.loop_stats()
+    assert 1 <= misses <= 4                                      # a handful of adjacent doubles (SURVEY B16)
+    assert s.scalars()[:3] == tuple(log[-1])
+    assert np.array_equal(bits(s.download()), bits(o.state()[0]))
+    s.close()
+
+
+def test_nan_signal_speed_is_reported():
+    """ComputeTimeStep with a non-finite maximum: the device-side loop halts and the call fails with LSC_ENAN."""
+    nx, ny = 32, 32
+    cfg = mhd_cfg(nx, ny)
+    u0 = mhd_ic(cfg, "ot")
+    u0[..., 0] = 0.0  # zero density everywhere: every speed is NaN, the running maximum stays 0
+    s = lsc.MusclNew(nx, ny, 0, 1, 0, 1, bc_x="periodic", bc_y="periodic", problem="ot")
+    s.upload(u0)
+    with pytest.raises(lsc.LscError) as e:
+        s.step(3)
+    assert e.value.code == -5
+    s.close()
+
+
+@pytest.mark.parametrize("nslabs", [2, 3])
+def test_group_run_reproduces_reference_files(tmp_path, golden_dir, nslabs):
+    """The committed program through the single-process slab group (what drivers/muscl_new --gpus N runs): the same
+    61 steps, the same MHD0..3.dat bytes as the reference, whatever the number of slabs."""
+    sha = json.load(open(os.path.join(golden_dir, "dat_sha256.json")))
+    g = lsc.MusclNewGroup(nslabs)  # committed defaults
+    g.init_problem()
+    lines = []
+    n = g.run(tStop=0.25, outdir=str(tmp_path), log=lambda k, t, dt, ch: lines.append((t, dt, ch)))
+    g.close()
+    assert n == 61 and len(lines) == 61
+    for k, key in ((0, "MHD0.dat"), (1, "MHD1.dat"), (2, "MHD2.dat"), (3, "MHD3.dat@tStop=0.25")):
+        h = hashlib.sha256(open(tmp_path / f"MHD{k}.dat", "rb").read()).hexdigest()
+        assert h == sha[key], f"MHD{k}.dat differs with {nslabs} slabs"
+
+
+def test_cpp_driver_with_slabs_is_the_same_program(tmp_path, golden_dir):
+    """drivers/muscl_new --slabs 3 (on a multi-GPU box: --gpus N): stdout and files identical to the reference's."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "drivers", "_bin", "muscl_new")
+    ndev = lsc.lib().lsc_device_count()
+    opt = ["--gpus", str(min(ndev, 4))] if ndev >= 2 else ["--slabs", "3"]
+    r = subprocess.run([exe, "--tstop", "0.25"] + opt, cwd=tmp_path, check=True, capture_output=True, text=True)
+    assert r.stdout == open(os.path.join(golden_dir, "muscl_new_stdout_t025.txt")).read()
+    sha = json.load(open(os.path.join(golden_dir, "dat_sha256.json")))
+    for k, key in ((0, "MHD0.dat"), (1, "MHD1.dat"), (2, "MHD2.dat"), (3, "MHD3.dat@tStop=0.25")):
+        h = hashlib.sha256(open(tmp_path / f"MHD{k}.dat", "rb").read()).hexdigest()
+        assert h == sha[key], f"MHD{k}.dat differs"
+
+
+def test_uneven_slabs_do_not_change_a_bit():
+    """Explicit slab bounds (lsc_mhd_config.slab_i0 / slab_nx): a 3-slab team of widths 10 / 57 / 29."""
+    nx, ny = 96, 64
+    cfg = mhd_cfg(nx, ny)
+    u0 = mhd_ic(cfg, "ot")
+    o = OracleMhd(cfg, u0)
+    o.step(6)
+    bounds = [(0, 10), (10, 57), (67, 29)]
+    parts = [lsc.MusclNew(nx, ny, 0, 1, 0, 1, bc_x="periodic", bc_y="periodic", problem="ot", rank=r, nranks=3, slab=b)
+             for r, b in enumerate(bounds)]
+    assert [(p.i0, p.nxl) for p in parts] == bounds
+    g = lsc.MusclNewGroup.from_parts(parts)
+    g.upload(u0)
+    g.step(6)
+    assert np.array_equal(bits(g.download()), bits(o.state()[0]))
+    g.close()
+    with pytest.raises(lsc.LscError):
+        lsc.MusclNew(nx, ny, 0, 1, 0, 1, bc_x="periodic", bc_y="periodic", problem="ot", rank=0, nranks=3, slab=(5, 10))
