@@ -338,6 +338,48 @@ def main_gpu(args):
     if args.warmup > 0:
         s.step(args.warmup)
 
+    # ---- slab calibration (MHD, N > 1): every step ends in a max-allreduce, so the slowest GPU paces all ranks, and
+    # under the board power cap individual GPUs differ by a few per cent.  Measure each rank's sweep time over the
+    # warm-up steps and size the slabs in proportion to its speed (explicit bounds, lsc_mhd_config.slab_i0/slab_nx).
+    # The decomposition does not touch the arithmetic: sim.state_hash is the same for any widths.
+    slabs = None
+    if world > 1 and args.workload == "mhd" and args.balance:
+        import torch
+        s.set_profiling(True)
+        s.kernel_times()
+        s.step(max(args.warmup, 3))
+        mx, my, kx, ky = s.kernel_times()
+        s.set_profiling(False)
+        mine = torch.tensor([(mx + my) / max(kx, 1), float(s.nxl)], dtype=torch.float64, device="cuda")
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        times = [float(a[0].item()) for a in allr]
+        widths = [float(a[1].item()) for a in allr]
+        speed = [wd / tm for wd, tm in zip(widths, times)]          # columns per ms of each GPU
+        share = [n * sp / sum(speed) for sp in speed]
+        new_w = [max(4, int(round(x))) for x in share]
+        new_w[new_w.index(max(new_w))] += n - sum(new_w)             # rounding remainder to the widest slab
+        slabs = {"sweep_ms_even_split": times, "widths": new_w,
+                 "spread_even_split": (max(times) - min(times)) / max(times)}
+        if max(abs(a - b) for a, b in zip(new_w, widths)) >= 2:
+            s.close()
+            i0 = sum(new_w[:rank])
+            s = lsc.MusclNew(n, n, 0.0, 1.0, 0.0, 1.0, tStop=0.5, C=0.8, bc_x="periodic", bc_y="periodic",
+                             problem="ot", device=local_rank, rank=rank, nranks=world, arithmetic=args.arithmetic,
+                             slab=(i0, new_w[rank]))
+            idbuf = ctypes.create_string_buffer(128)
+            if rank == 0:
+                lsc._capi.check(L.lsc_comm_unique_id(ctypes.cast(idbuf, ctypes.c_void_p)))
+            t = torch.tensor(list(idbuf.raw), dtype=torch.uint8, device="cuda")
+            dist.broadcast(t, 0)
+            s.comm_init(bytes(t.cpu().tolist()))
+        else:
+            slabs["widths"] = [int(x) for x in widths]
+        # start over from the initial condition: every N then hashes the state after exactly warmup + K steps
+        s.init_problem()
+        if args.warmup > 0:
+            s.step(args.warmup)
+
     # ---- device-resident throughput: K steps as one enqueued batch, CUDA events on the solver's stream
     sampler = ClockSampler(local_rank)
     barrier()
@@ -408,7 +450,7 @@ def main_gpu(args):
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": w["name"].format(n=n),
-                   "grid": [n, n], "parallelism": f"slab-x{world}",
+                   "grid": [n, n], "parallelism": f"slab-x{world}", "slabs": slabs,
                    "cache": "inputs larger than L2 (3 states x %.2f GB per GPU vs 126 MB L2), no flush needed"
                             % (cells_local * 8 * w["nvar"] / 1e9),
                    "arithmetic": ("reference: fp64, no FMA contraction, IEEE division, reference operation order "
@@ -471,6 +513,8 @@ def main():
     ap.add_argument("--grid", "--n", dest="n", type=int, default=0, help="grid edge (default: the named size)")
     ap.add_argument("--ref-n", type=int, default=0, help="grid edge of the bounded CPU reference sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-balance", dest="balance", action="store_false",
+                    help="N > 1: keep the even slab split instead of sizing slabs by the measured sweep time of each GPU")
     ap.add_argument("--arithmetic", default="reference", choices=["reference", "relaxed"],
                     help="reference = bit-identical IEEE path (default, the one that is judged); relaxed = N3 variant")
     args = ap.parse_args()

@@ -12,6 +12,7 @@
 #include <cstring>
 #include <iostream>
 #include <string>
+#include <chrono>
 #include <vector>
 
 #include "lsc_b200.h"
@@ -25,7 +26,8 @@ int main(int argc, char** argv) {
     lsc_euler_config cfg = {100, 100, 0.0, 1.0, 0.0, 1.0, 1.4, 0.8, 0.0, LSC_BC_PERIODIC, 0};  // S:529-539
     double tStop = 0.5;
     int problem = -1;
-    bool generalise = false, quiet = false, nodat = false;
+    bool generalise = false, quiet = false, nodat = false, timing = false;
+    int nslabs = 1, ngpus = 0;  // --gpus N: one process, N slabs along x, one GPU each (lsc_euler_group_*)
     std::string outdir;
     for (int a = 1; a < argc; ++a) {
         auto val = [&](const char* name) -> const char* {
@@ -48,6 +50,9 @@ int main(int argc, char** argv) {
         else if (o == "--outdir") outdir = std::string(val("--outdir")) + "/";
         else if (o == "--quiet") quiet = true;
         else if (o == "--no-dat") nodat = true;
+        else if (o == "--gpus") { ngpus = std::atoi(val("--gpus")); nslabs = ngpus; }
+        else if (o == "--slabs") nslabs = std::atoi(val("--slabs"));
+        else if (o == "--time") timing = true;
         else if (o == "--bc") {
             const std::string b = val("--bc");
             if (b == "periodic") cfg.bc = LSC_BC_PERIODIC;
@@ -63,7 +68,7 @@ int main(int argc, char** argv) {
             std::fprintf(stderr,
                          "usage: slic_euler_2d [--generalise] [--problem ot|quadrants|cylinder] [--bc periodic|transmissive]\n"
                          "       [--nx N --ny N --x0 v --x1 v --y0 v --y1 v] [--tstop t] [--cfl C] [--gamma g] [--omega w]\n"
-                         "       [--outdir d] [--device k] [--quiet] [--no-dat]\n");
+                         "       [--outdir d] [--device k] [--gpus N | --slabs N] [--time] [--quiet] [--no-dat]\n");
             return 2;
         }
     }
@@ -75,39 +80,44 @@ int main(int argc, char** argv) {
     }
     if (problem < 0) problem = LSC_EULER_IC_ORSZAG_TANG;
 
-    lsc_euler_ctx* ctx = nullptr;
-    if (lsc_euler_create(&cfg, &ctx) || lsc_euler_init_problem(ctx, problem)) {
-        std::fprintf(stderr, "%s\n", lsc_last_error());
-        return 1;
+    const int ndev = lsc_device_count();
+    if (nslabs < 1 || ngpus > ndev) { std::fprintf(stderr, "--gpus %d: %d CUDA device(s) visible\n", ngpus, ndev); return 1; }
+    auto die = [] { std::fprintf(stderr, "%s\n", lsc_last_error()); return 1; };
+    std::vector<lsc_euler_ctx*> slabs(nslabs, nullptr);
+    for (int r = 0; r < nslabs; ++r) {
+        lsc_euler_config c = cfg;
+        c.rank = r;
+        c.nranks = nslabs;
+        c.device = ndev > 0 ? (cfg.device + r) % ndev : 0;
+        if (lsc_euler_create(&c, &slabs[r]) || lsc_euler_init_problem(slabs[r], problem)) return die();
     }
-    std::vector<double> host((size_t)(cfg.nx + 4) * (cfg.ny + 4) * LSC_EULER_NVAR);
+    lsc_euler_ctx** g = slabs.data();
+    std::vector<double> host(nodat ? 0 : (size_t)(cfg.nx + 4) * (cfg.ny + 4) * LSC_EULER_NVAR);
+    const auto t0 = std::chrono::steady_clock::now();
+    long steps = 0, k = 0;
     if (generalise) {
-        if (lsc_euler_run_until(ctx, tStop, log_line, &quiet, nullptr)) {  // G:627-646
-            std::fprintf(stderr, "%s\n", lsc_last_error());
-            return 1;
-        }
-        if (!nodat && (lsc_euler_download(ctx, host.data()) ||
-                       lsc_euler_write_dat(&cfg, host.data(), (outdir + "SLIC2d.dat").c_str(), 1))) {
-            std::fprintf(stderr, "%s\n", lsc_last_error());
-            return 1;
-        }
+        if (lsc_euler_group_run_until(g, nslabs, tStop, log_line, &quiet, &steps)) return die();  // G:627-646
+        if (!nodat && (lsc_euler_group_download(g, nslabs, host.data()) ||
+                       lsc_euler_write_dat(&cfg, host.data(), (outdir + "SLIC2d.dat").c_str(), 1)))
+            return die();
     } else {
         for (int counter = 1; counter <= 20; ++counter) {  // S:599
             const double seg = tStop / (21 - counter);
-            if (lsc_euler_run_until(ctx, seg, nullptr, nullptr, nullptr)) {  // S:600-617
-                std::fprintf(stderr, "%s\n", lsc_last_error());
-                return 1;
-            }
+            if (lsc_euler_group_run_until(g, nslabs, seg, nullptr, nullptr, &k)) return die();  // S:600-617
+            steps += k;
             const double time = tStop / (21 - counter);  // S:618
             if (!quiet) std::cout << time << std::endl;  // S:619
             if (nodat) continue;
             const std::string name = outdir + "euler_" + std::to_string(counter) + ".dat";  // S:632
-            if (lsc_euler_download(ctx, host.data()) || lsc_euler_write_dat(&cfg, host.data(), name.c_str(), 0)) {
-                std::fprintf(stderr, "%s\n", lsc_last_error());
-                return 1;
-            }
+            if (lsc_euler_group_download(g, nslabs, host.data()) || lsc_euler_write_dat(&cfg, host.data(), name.c_str(), 0))
+                return die();
         }
     }
-    lsc_euler_destroy(ctx);
+    if (timing) {
+        const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        std::fprintf(stderr, "steps=%ld elapsed_s=%.6f cell_updates_per_s=%.6e slabs=%d\n", steps, secs,
+                     (double)cfg.nx * cfg.ny * steps / secs, nslabs);
+    }
+    for (auto c : slabs) lsc_euler_destroy(c);
     return 0;
 }

@@ -12,6 +12,7 @@
 #include <cstring>
 #include <iostream>
 #include <string>
+#include <chrono>
 #include <vector>
 
 #include "lsc_b200.h"
@@ -24,7 +25,8 @@ static int log_line(long, double t, double dt, void* quiet) {
 int main(int argc, char** argv) {
     lsc_euler_config cfg = {100, 100, 0.0, 1.0, 0.0, 1.0, 1.4, 0.8, 0.0, LSC_BC_TRANSMISSIVE_E, 0};  // T:896-905
     double tStop = 0.012 / std::pow(10, 2.5);                                                         // T:903
-    bool quiet = false, nodat = false;
+    bool quiet = false, nodat = false, timing = false;
+    int nslabs = 1, ngpus = 0;  // --gpus N: one process, N slabs along x, one GPU each (lsc_euler_group_*)
     std::string outdir, table = "Plasma19_EoS.txt";
     for (int a = 1; a < argc; ++a) {
         auto val = [&](const char* name) -> const char* {
@@ -46,10 +48,14 @@ int main(int argc, char** argv) {
         else if (o == "--table") table = val("--table");
         else if (o == "--quiet") quiet = true;
         else if (o == "--no-dat") nodat = true;
+        else if (o == "--gpus") { ngpus = std::atoi(val("--gpus")); nslabs = ngpus; }
+        else if (o == "--slabs") nslabs = std::atoi(val("--slabs"));
+        else if (o == "--time") timing = true;
         else {
             std::fprintf(stderr,
                          "usage: tab_eos [--table Plasma19_EoS.txt] [--nx N --ny N --x0 v --x1 v --y0 v --y1 v]\n"
-                         "       [--tstop t] [--cfl C] [--omega w] [--outdir d] [--device k] [--quiet] [--no-dat]\n");
+                         "       [--tstop t] [--cfl C] [--omega w] [--outdir d] [--device k] [--gpus N | --slabs N] [--time]\n"
+                         "       [--quiet] [--no-dat]\n");
             return 2;
         }
     }
@@ -58,24 +64,36 @@ int main(int argc, char** argv) {
         std::fprintf(stderr, "%s\n", lsc_last_error());
         return 1;
     }
-    lsc_euler_ctx* ctx = nullptr;
-    if (lsc_euler_create(&cfg, &ctx) || lsc_euler_set_eos_table(ctx, dens.data(), pres.data(), sound.data(), en.data()) ||
-        lsc_euler_init_problem(ctx, LSC_EULER_IC_TABEOS)) {
-        std::fprintf(stderr, "%s\n", lsc_last_error());
-        return 1;
+    const int ndev = lsc_device_count();
+    if (nslabs < 1 || ngpus > ndev) { std::fprintf(stderr, "--gpus %d: %d CUDA device(s) visible\n", ngpus, ndev); return 1; }
+    auto die = [] { std::fprintf(stderr, "%s\n", lsc_last_error()); return 1; };
+    std::vector<lsc_euler_ctx*> slabs(nslabs, nullptr);
+    for (int r = 0; r < nslabs; ++r) {
+        lsc_euler_config c = cfg;
+        c.rank = r;
+        c.nranks = nslabs;
+        c.device = ndev > 0 ? (cfg.device + r) % ndev : 0;
+        if (lsc_euler_create(&c, &slabs[r]) ||
+            lsc_euler_set_eos_table(slabs[r], dens.data(), pres.data(), sound.data(), en.data()) ||
+            lsc_euler_init_problem(slabs[r], LSC_EULER_IC_TABEOS))
+            return die();
     }
     if (!quiet) std::cout << "finished loop!" << std::endl;                                  // T:952
-    if (lsc_euler_run_until(ctx, tStop, log_line, &quiet, nullptr)) {                        // T:959-971
-        std::fprintf(stderr, "%s\n", lsc_last_error());
-        return 1;
+    const auto t0 = std::chrono::steady_clock::now();
+    long steps = 0;
+    if (lsc_euler_group_run_until(slabs.data(), nslabs, tStop, log_line, &quiet, &steps)) return die();  // T:959-971
+    if (timing) {
+        const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        std::fprintf(stderr, "steps=%ld elapsed_s=%.6f cell_updates_per_s=%.6e slabs=%d\n", steps, secs,
+                     (double)cfg.nx * cfg.ny * steps / secs, nslabs);
     }
-    std::vector<double> host((size_t)(cfg.nx + 4) * (cfg.ny + 4) * LSC_EULER_NVAR);
-    if (!nodat && (lsc_euler_download(ctx, host.data()) ||
-                   lsc_euler_tabeos_write_dat(&cfg, host.data(), (outdir + "SLIC2d.dat").c_str(), dens.data(),
-                                              pres.data(), en.data()))) {
-        std::fprintf(stderr, "%s\n", lsc_last_error());
-        return 1;
+    if (!nodat) {
+        std::vector<double> host((size_t)(cfg.nx + 4) * (cfg.ny + 4) * LSC_EULER_NVAR);
+        if (lsc_euler_group_download(slabs.data(), nslabs, host.data()) ||
+            lsc_euler_tabeos_write_dat(&cfg, host.data(), (outdir + "SLIC2d.dat").c_str(), dens.data(), pres.data(),
+                                       en.data()))
+            return die();
     }
-    lsc_euler_destroy(ctx);
+    for (auto c : slabs) lsc_euler_destroy(c);
     return 0;
 }

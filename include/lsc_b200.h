@@ -270,6 +270,12 @@ int lsc_euler_comm_init(lsc_euler_ctx* ctx, const void* id128);
 /* single process: advance the n slabs of one grid (contexts with rank 0..n-1 of n, on any devices of this
  * process) in lock step, halos by peer copies, max on the host -- same kernels and slab-edge path as NCCL. */
 int lsc_euler_group_step(lsc_euler_ctx** slabs, int n, long nsteps);
+/* lsc_euler_run_until / lsc_euler_download for the slabs of one process: the loop S:600-617 / G:627-646 in lock step,
+ * and the WHOLE grid [(nx+4)][(ny+4)][4] assembled with the ghost ring u holds after S:616 (what lsc_euler_write_dat
+ * takes).  This is how drivers/slic_euler_2d and drivers/tab_eos use several GPUs (--gpus N). */
+int lsc_euler_group_run_until(lsc_euler_ctx** slabs, int n, double t_stop, lsc_euler_log_cb log_cb, void* user,
+                              long* steps_out);
+int lsc_euler_group_download(lsc_euler_ctx** slabs, int n, double* aos);
 /* IC loop S:552-594 / G:586-620 followed by the boundary fill S:596, into [(nx+4)][(ny+4)][4] (the slab
  * [(nxl+4)][(ny+4)][4] of cfg->rank when cfg->nranks > 1). Host libm. */
 int lsc_euler_initial_condition(const lsc_euler_config* cfg, int problem, double* aos);

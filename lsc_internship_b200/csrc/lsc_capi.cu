@@ -169,6 +169,15 @@ struct lsc_mhd_ctx {
     bool relaxed = false;  // LSC_ARITH_RELAXED: FMA-contracted sweeps with 1-multiply quotients (not the parity path)
     std::vector<cudaEvent_t> prof_events;  // quadruples: x begin, x end, y begin, y end
     std::vector<cudaEvent_t> halo_events, reduce_events;  // pairs around the NCCL halo exchange / max-allreduce
+    // CUDA graphs of GRAPH_STEPS steps (plain contexts), keyed on what is baked into them
+    struct StepGraph {
+        int key;
+        cudaGraphExec_t exec;
+        unsigned long long launches;
+    };
+    std::vector<StepGraph> graphs;
+    bool graph_disabled = false;
+    bool peers_enabled = false;  // team: peer access from this context's GPU to the other members' GPUs
 };
 
 namespace {
@@ -349,6 +358,7 @@ int lsc_mhd_create(const lsc_mhd_config* cfg, lsc_mhd_ctx** out) {
         return fail(LSC_ENOMEM, "allocation of staging / scalars / stream failed");
     }
     std::memset(c->h, 0, sizeof(HostBlock));
+    if (const char* e = std::getenv("LSC_NO_GRAPH")) c->graph_disabled = (*e && *e != '0');
     build_exp_table(c);
     int rc = reset_ctl(c);
     if (rc) {
@@ -384,6 +394,7 @@ int lsc_mhd_destroy(lsc_mhd_ctx* c) {
     destroy_events(c->prof_events);
     destroy_events(c->halo_events);
     destroy_events(c->reduce_events);
+    for (auto& g : c->graphs) cudaGraphExecDestroy(g.exec);
     if (c->comm_stream) cudaStreamDestroy(c->comm_stream);
     if (c->stream) cudaStreamDestroy(c->stream);
     slot_release(c->cfg.device, c->slot);
@@ -686,7 +697,75 @@ int launch_sweeps(lsc_mhd_ctx* c, int cur, int prev, bool first_step) {
     return LSC_OK;
 }
 
-// Enqueue `count` passes of the loop body MUSCL_NEW.cpp:831-971 on every member.  Nothing is read back.
+// One pass of the loop body MUSCL_NEW.cpp:831-971 on every member, enqueued; cur/prev are rotated for the next one.
+int enqueue_one_step(const Team& T, std::vector<int>& cur, std::vector<int>& prev, bool first_step) {
+    NvtxRange range("lsc step");
+    lsc_mhd_ctx* L = T.lead();
+    int rc = reduce_max_speed(T);  // ComputeTimeStep (:833): the reduction itself ran inside the last y sweep
+    if (rc) return rc;
+    for (int r = 0; r < T.n; ++r) {
+        lsc_mhd_ctx* c = T.m[r];
+        CUDA_TRY(cudaSetDevice(c->cfg.device));
+        lsc::launch_prepare(c->d_ctl, c->d_cmd, c->d_status, c->d_log, c->stream);
+        lsc_count_launches(1);
+        CUDA_TRY(c->relaxed ? lsc::publish_step_scalars_relaxed(c->d_ctl, c->slot, c->stream)
+                            : lsc::publish_step_scalars(c->d_ctl, c->slot, c->stream));
+        rc = launch_sweeps(c, cur[r], prev[r], first_step);
+        if (rc) return rc;
+        std::swap(cur[r], prev[r]);  // u = uPlus1 (:969); the old u^n stays as the limiter's "previous" state
+    }
+    if (T.n > 1) return team_halo(T, cur.data());     // applyBoundaryConditions(u) (:971)
+    if (!overlap_active(L)) return fill_x_ghosts(L, cur[0]);
+    return LSC_OK;  // issued behind the slab-edge columns of the y sweep
+}
+
+// A plain context (one GPU, no communicator) replays GRAPH_STEPS steps as one CUDA graph: the seven small launches
+// of a step then cost ~1 us each instead of ~2.5, which is what a step of a small grid is made of (OT 256^2: the
+// sweeps themselves take ~25 us).  GRAPH_STEPS is even, so a replay leaves the buffer rotation where it was; the
+// graph is captured from the very same enqueue code and keyed on everything that is baked into it.
+constexpr int GRAPH_STEPS = 8;
+
+bool graph_eligible(const Team& T) {
+    const lsc_mhd_ctx* c = T.lead();
+    return T.n == 1 && c->cfg.nranks == 1 && !c->profiling && !c->graph_disabled;
+}
+
+int graph_for(const Team& T, int cur0, cudaGraphExec_t* out) {
+    lsc_mhd_ctx* c = T.lead();
+    const int key = cur0 | (c->relaxed ? 8 : 0) | (c->overlap << 4);
+    for (auto& e : c->graphs)
+        if (e.key == key) {
+            *out = e.exec;
+            return LSC_OK;
+        }
+    *out = nullptr;
+    std::vector<int> cur{cur0}, prev{cur0 == c->cur ? c->prev : c->cur};
+    const unsigned long long before = g_launches.load();
+    if (cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+        cudaGetLastError();
+        c->graph_disabled = true;
+        return LSC_OK;
+    }
+    int rc = LSC_OK;
+    for (int q = 0; q < GRAPH_STEPS && rc == LSC_OK; ++q) rc = enqueue_one_step(T, cur, prev, false);
+    cudaGraph_t graph = nullptr;
+    cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
+    const unsigned long long captured = g_launches.load() - before;
+    g_launches -= captured;  // nothing ran yet: launches are counted per replay
+    cudaGraphExec_t exec = nullptr;
+    if (rc == LSC_OK && e == cudaSuccess && graph) e = cudaGraphInstantiate(&exec, graph, 0);
+    if (graph) cudaGraphDestroy(graph);
+    if (rc != LSC_OK || e != cudaSuccess || !exec) {  // capture not possible here: stay on plain launches
+        cudaGetLastError();
+        c->graph_disabled = true;
+        return LSC_OK;
+    }
+    c->graphs.push_back({key, exec, captured});
+    *out = exec;
+    return LSC_OK;
+}
+
+// Enqueue `count` passes of the loop body on every member.  Nothing is read back.
 int enqueue_steps(const Team& T, long count) {
     lsc_mhd_ctx* L = T.lead();
     std::vector<int> cur(T.n), prev(T.n);
@@ -699,27 +778,23 @@ int enqueue_steps(const Team& T, long count) {
         if (rc) return rc;
         for (int r = 0; r < T.n; ++r) T.m[r]->ghosts_current = true;
     }
-    for (long e = 0; e < count; ++e) {
-        NvtxRange range("lsc step");
-        int rc = reduce_max_speed(T);  // ComputeTimeStep (:833): the reduction itself ran inside the last y sweep
-        if (rc) return rc;
-        for (int r = 0; r < T.n; ++r) {
-            lsc_mhd_ctx* c = T.m[r];
-            CUDA_TRY(cudaSetDevice(c->cfg.device));
-            lsc::launch_prepare(c->d_ctl, c->d_cmd, c->d_status, c->d_log, c->stream);
-            lsc_count_launches(1);
-            CUDA_TRY(c->relaxed ? lsc::publish_step_scalars_relaxed(c->d_ctl, c->slot, c->stream)
-                                : lsc::publish_step_scalars(c->d_ctl, c->slot, c->stream));
-            rc = launch_sweeps(c, cur[r], prev[r], L->step + e == 0);
+    long e = 0;
+    while (e < count) {
+        if (count - e >= GRAPH_STEPS && L->step + e >= 1 && graph_eligible(T)) {
+            cudaGraphExec_t exec = nullptr;
+            int rc = graph_for(T, cur[0], &exec);
             if (rc) return rc;
-            std::swap(cur[r], prev[r]);  // u = uPlus1 (:969); the old u^n stays as the limiter's "previous" state
+            if (exec) {
+                CUDA_TRY(cudaGraphLaunch(exec, L->stream));
+                for (auto& g : L->graphs)
+                    if (g.exec == exec) lsc_count_launches(g.launches);
+                e += GRAPH_STEPS;
+                continue;
+            }
         }
-        if (T.n > 1) {
-            rc = team_halo(T, cur.data());  // applyBoundaryConditions(u) (:971)
-        } else if (!overlap_active(L)) {
-            rc = fill_x_ghosts(L, cur[0]);
-        }  // else: issued behind the slab-edge columns of the y sweep
+        int rc = enqueue_one_step(T, cur, prev, L->step + e == 0);
         if (rc) return rc;
+        e += 1;
     }
     return LSC_OK;
 }
@@ -827,6 +902,24 @@ int team_check(lsc_mhd_ctx** g, int n) {
         if (!g[r]->uploaded) return fail(LSC_ESTATE, "group member %d has no state uploaded", r);
         if (g[r]->comm) return fail(LSC_ESTATE, "group member %d is attached to NCCL", r);
         if (g[r]->step != g[0]->step) return fail(LSC_ESTATE, "group members are at different steps");
+    }
+    // direct NVLink / PCIe peer copies between the members' GPUs (without it cudaMemcpyPeerAsync stages through
+    // the host); enabled once per pair, "already enabled" is not an error
+    for (int r = 0; r < n; ++r) {
+        if (g[r]->peers_enabled) continue;
+        CUDA_TRY(cudaSetDevice(g[r]->cfg.device));
+        for (int q = 0; q < n; ++q) {
+            const int a = g[r]->cfg.device, b = g[q]->cfg.device;
+            if (a == b) continue;
+            int can = 0;
+            if (cudaDeviceCanAccessPeer(&can, a, b) == cudaSuccess && can) {
+                cudaError_t e = cudaDeviceEnablePeerAccess(b, 0);
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
+                    return fail(LSC_ECUDA, "cudaDeviceEnablePeerAccess(%d -> %d): %s", a, b, cudaGetErrorString(e));
+            }
+            cudaGetLastError();
+        }
+        g[r]->peers_enabled = true;
     }
     return LSC_OK;
 }

@@ -272,7 +272,11 @@ int lsc_euler_comm_init(lsc_euler_ctx* c, const void* id128) {
     return LSC_OK;
 }
 
-int lsc_euler_group_step(lsc_euler_ctx** g, int n, long nsteps) {
+}  // extern "C"
+
+namespace {
+
+int eg_check(lsc_euler_ctx** g, int n) {
     if (!g || n < 1) return lsc_fail(LSC_EINVAL, "empty group");
     for (int r = 0; r < n; ++r) {
         if (!g[r]) return lsc_fail(LSC_EINVAL, "null context in group");
@@ -282,19 +286,68 @@ int lsc_euler_group_step(lsc_euler_ctx** g, int n, long nsteps) {
         if (g[r]->comm) return lsc_fail(LSC_ESTATE, "group member %d is attached to NCCL", r);
         if (g[r]->step != g[0]->step) return lsc_fail(LSC_ESTATE, "group members are at different steps");
     }
-    for (int r = 0; r < n; ++r) g[r]->in_group = true;
-    int rc = LSC_OK;
-    for (long s = 0; s < nsteps && rc == LSC_OK; ++s) {
-        rc = eg_resolve(g, n);
-        for (int r = 0; r < n && rc == LSC_OK; ++r) {
-            LSC_CUDA_TRY(cudaSetDevice(g[r]->cfg.device));
-            rc = e_step_launch(g[r]);
+    for (int r = 0; r < n; ++r) {  // direct peer copies between the members' GPUs
+        LSC_CUDA_TRY(cudaSetDevice(g[r]->cfg.device));
+        for (int q = 0; q < n; ++q) {
+            const int a = g[r]->cfg.device, b = g[q]->cfg.device;
+            int can = 0;
+            if (a != b && cudaDeviceCanAccessPeer(&can, a, b) == cudaSuccess && can) cudaDeviceEnablePeerAccess(b, 0);
+            cudaGetLastError();
         }
-        if (rc == LSC_OK) rc = eg_halo(g, n);
     }
-    if (rc == LSC_OK) rc = eg_resolve(g, n);
-    for (int r = 0; r < n; ++r) g[r]->in_group = false;
+    return LSC_OK;
+}
+
+struct EulerGroupScope {  // in_group for the duration of a group call, reset on every exit path
+    lsc_euler_ctx** g;
+    int n;
+    EulerGroupScope(lsc_euler_ctx** g_, int n_) : g(g_), n(n_) {
+        for (int r = 0; r < n; ++r) g[r]->in_group = true;
+    }
+    ~EulerGroupScope() {
+        for (int r = 0; r < n; ++r) g[r]->in_group = false;
+    }
+};
+
+// one pass of the do-body S:600-616 on every slab
+int eg_step_once(lsc_euler_ctx** g, int n) {
+    int rc = eg_resolve(g, n);
+    for (int r = 0; r < n && rc == LSC_OK; ++r) {
+        LSC_CUDA_TRY(cudaSetDevice(g[r]->cfg.device));
+        rc = e_step_launch(g[r]);
+    }
+    if (rc == LSC_OK) rc = eg_halo(g, n);
     return rc;
+}
+
+}  // namespace
+
+extern "C" {
+
+int lsc_euler_group_step(lsc_euler_ctx** g, int n, long nsteps) {
+    int rc = eg_check(g, n);
+    if (rc) return rc;
+    EulerGroupScope scope(g, n);
+    for (long s = 0; s < nsteps && rc == LSC_OK; ++s) rc = eg_step_once(g, n);
+    if (rc == LSC_OK) rc = eg_resolve(g, n);
+    return rc;
+}
+
+int lsc_euler_group_run_until(lsc_euler_ctx** g, int n, double t_stop, lsc_euler_log_cb log_cb, void* user,
+                              long* steps_out) {
+    int rc = eg_check(g, n);
+    if (rc) return rc;
+    EulerGroupScope scope(g, n);
+    long k = 0;
+    do {  // S:600 / G:627
+        rc = eg_step_once(g, n);
+        if (rc) return rc;
+        ++k;
+        if (log_cb && log_cb(g[0]->step, g[0]->t, g[0]->dt, user))  // G:631
+            return lsc_fail(LSC_ECALLBACK, "log callback stopped the loop at step %ld", g[0]->step);
+    } while (g[0]->t < t_stop);  // S:617 / G:646
+    if (steps_out) *steps_out = k;
+    return eg_resolve(g, n);
 }
 
 int lsc_euler_create(const lsc_euler_config* cfg, lsc_euler_ctx** out) {
@@ -628,6 +681,33 @@ int lsc_euler_state_hash(lsc_euler_ctx* c, unsigned long long* hash) {
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
     cudaFree(d);
     LSC_CUDA_TRY(e);
+    return LSC_OK;
+}
+
+int lsc_euler_group_download(lsc_euler_ctx** g, int n, double* aos) {
+    int rc = eg_check(g, n);
+    if (rc) return rc;
+    if (!aos) return lsc_fail(LSC_EINVAL, "null argument");
+    const size_t col = (size_t)(g[0]->cfg.ny + 4) * 4;
+    std::vector<double> slab;
+    for (int r = 0; r < n; ++r) {
+        lsc_euler_ctx* c = g[r];
+        try {
+            slab.resize(col * (size_t)(c->nxl + 4));
+        } catch (...) {
+            return lsc_fail(LSC_ENOMEM, "host allocation failed");
+        }
+        rc = lsc_euler_download(c, slab.data());
+        if (rc) return rc;
+        const int lo = (r == 0) ? 0 : 2, hi = (r == n - 1) ? c->nxl + 4 : c->nxl + 2;
+        std::memcpy(aos + col * (size_t)(c->i0 + lo), slab.data() + col * lo, col * (size_t)(hi - lo) * sizeof(double));
+    }
+    if (g[0]->step > 0) {
+        lsc_euler_config whole = g[0]->cfg;
+        whole.rank = 0;
+        whole.nranks = 1;
+        lsc::euler_fill_ghost_ring(whole, aos);
+    }
     return LSC_OK;
 }
 

@@ -106,6 +106,9 @@ __device__ __forceinline__ void block_max_to_global(double local, unsigned long 
 #ifndef XS_STRIP
 #define XS_STRIP 128
 #endif
+#ifndef XS_MIN_STRIP
+#define XS_MIN_STRIP 2  // shortest strip of an x-sweep thread (small, latency-bound grids; choose_x_strip)
+#endif
 #ifndef XS_PF
 #define XS_PF 2  // the x march prefetches column c + XS_PF into L1 while it works on column c
 #endif
@@ -399,7 +402,7 @@ void launch_x_sweep(const GridDims& g, const SweepArgs& p, const double* u_cur, 
     // chosen so that the blocks fill whole rounds of the 148 SMs x XS_MINB resident blocks (choose_x_strip)
     dim3 block(XS_BLOCK);
     const int row_blocks = (g.ny + block.x - 1) / block.x;
-    const int strip = choose_x_strip(row_blocks, g.nxl, XS_STRIP, 148 * XS_MINB);
+    const int strip = choose_x_strip(row_blocks, g.nxl, XS_STRIP, 148 * XS_MINB, XS_MIN_STRIP);
     dim3 grid(row_blocks, (g.nxl + strip - 1) / strip);
     x_sweep_kernel<MHD_FAST_POLICY><<<grid, block, 0, s>>>(g, p, u_cur, u_prev, u_bar, x_flags, strip);
     const unsigned nblocks = grid.x * grid.y;
@@ -409,14 +412,14 @@ void launch_x_sweep(const GridDims& g, const SweepArgs& p, const double* u_cur, 
 
 long x_sweep_block_count(const GridDims& g) {
     const int row_blocks = (g.ny + XS_BLOCK - 1) / XS_BLOCK;
-    return (long)row_blocks * ((g.nxl + 7) / 8);  // strip is never shorter than 8
+    return (long)row_blocks * ((g.nxl + XS_MIN_STRIP - 1) / XS_MIN_STRIP);  // strips are never shorter
 }
 #else  // LSC_RELAXED_TU
 void launch_x_sweep_relaxed(const GridDims& g, const SweepArgs& p, const double* u_cur, const double* u_prev,
                             double* u_bar, unsigned* x_flags, cudaStream_t s) {
     dim3 block(XS_BLOCK);
     const int row_blocks = (g.ny + block.x - 1) / block.x;
-    const int strip = choose_x_strip(row_blocks, g.nxl, XS_STRIP, 148 * XS_MINB);
+    const int strip = choose_x_strip(row_blocks, g.nxl, XS_STRIP, 148 * XS_MINB, XS_MIN_STRIP);
     dim3 grid(row_blocks, (g.nxl + strip - 1) / strip);
     x_sweep_kernel<RelaxedDiv><<<grid, block, 0, s>>>(g, p, u_cur, u_prev, u_bar, x_flags, strip);
 }

@@ -49,14 +49,17 @@ __host__ __device__ inline size_t mhd_column_doubles(const GridDims& g) { return
 // Columns per thread of an x sweep.  A block runs strip+1 loop iterations after a warm-up worth about half of one;
 // all blocks of a launch cost the same, so the launch takes ceil(blocks / resident) rounds of (strip + 1.5)
 // columns.  Picks the
-// strip in [8, max_strip] that minimises that product: e.g. a 2048-column slab (16384^2 on 8 GPUs) with
+// strip in [min_strip, max_strip] that minimises that product: e.g. a 2048-column slab (16384^2 on 8 GPUs) with
 // 128-column strips is 2048 blocks = 3.46 rounds of the 592 resident blocks (the 4th round 46 % full); 90-column
 // strips make it 2944 blocks = 4.97 rounds of shorter blocks, 12 % less time.  The decomposition does not touch
 // the arithmetic (tests/test_mhd_gpu.py compares different strip lengths bit for bit).
-inline int choose_x_strip(int row_blocks, int nxl, int max_strip, int resident_blocks) {
+// min_strip: small grids are latency-bound (a thread spends ~3.7 us per column when its warp has a scheduler to
+// itself), so while everything still fits one round shorter strips -- more threads, fewer columns each -- win
+// despite the 3 warm-up cells: OT 256^2 x sweep 42 us with 8-column strips.
+inline int choose_x_strip(int row_blocks, int nxl, int max_strip, int resident_blocks, int min_strip = 8) {
     long best_cost = -1;
     int best = max_strip;
-    for (int s = 8; s <= max_strip; ++s) {
+    for (int s = min_strip; s <= max_strip; ++s) {
         const long blocks = (long)row_blocks * ((nxl + s - 1) / s);
         const long rounds = (blocks + resident_blocks - 1) / resident_blocks;
         const long cost = rounds * (2 * s + 3);
