@@ -286,6 +286,8 @@ int lsc_euler_step_timed(lsc_euler_ctx* ctx, long nsteps, float* ms);
 /* do { step } while (t < t_stop)  -- S:600-617 with t_stop = tStop/(21-counter), G:627-646 with tStop. */
 int lsc_euler_run_until(lsc_euler_ctx* ctx, double t_stop, lsc_euler_log_cb log_cb, void* user, long* steps_out);
 int lsc_euler_get_scalars(const lsc_euler_ctx* ctx, double* t, double* dt, long* step);
+/* the Euler loop is device-resident like the MHD one (lsc_mhd_loop_stats): host synchronisations so far */
+int lsc_euler_loop_stats(const lsc_euler_ctx* ctx, long* host_syncs);
 int lsc_euler_download(lsc_euler_ctx* ctx, double* aos);              /* u after S:616, ghost ring included */
 /* S:621-642 (blank_line_per_row = 0, euler_<k>.dat) / G:645-667 (= 1, SLIC2d.dat) */
 int lsc_euler_write_dat(const lsc_euler_config* cfg, const double* aos, const char* path, int blank_line_per_row);

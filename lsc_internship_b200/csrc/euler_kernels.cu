@@ -21,6 +21,82 @@
 
 namespace lsc {
 
+// per-context step scalars (see mhd_kernels.cu: c_step): uniform-indexed, loaded into uniform registers
+static __constant__ EulerStepScalars c_estep[STEP_SLOTS];
+
+__device__ __forceinline__ EulerParams with_step_scalars(const EulerParams& a) {
+    const EulerStepScalars& sc = c_estep[a.slot];
+    EulerParams p = a;
+    p.dtdx = sc.dtdx;
+    p.hdtdx = sc.hdtdx;
+    p.dtdy = sc.dtdy;
+    p.hdtdy = sc.hdtdy;
+    p.hdxdt = sc.hdxdt;
+    p.hdydt = sc.hdydt;
+    return p;
+}
+
+cudaError_t publish_euler_step_scalars(const EulerStepCtl* ctl, int slot, cudaStream_t s) {
+    return cudaMemcpyToSymbolAsync(c_estep, &ctl->sc, sizeof(EulerStepScalars), (size_t)slot * sizeof(EulerStepScalars),
+                                   cudaMemcpyDeviceToDevice, s);
+}
+
+// ComputeTimeStep's scalars and the loop predicate of S:600-617 / G:627-646 by one thread (cf. prepare_kernel in
+// mhd_kernels.cu; the Euler loop has no exp() and no dump cadence).
+__global__ void euler_prepare_kernel(EulerStepCtl* __restrict__ ctl, const StepCmd* __restrict__ cmd,
+                                     unsigned long long* __restrict__ status, double* __restrict__ log_ring) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    EulerStepCtl& c = *ctl;
+    bool fresh = false;
+    if (c.batch_seen != cmd->batch) {
+        c.batch_seen = cmd->batch;
+        c.halt = HALT_NONE;
+        c.log_count = 0;
+        fresh = true;
+    }
+    if (c.halt != HALT_NONE) return;
+    int halt = HALT_NONE;
+    if (!fresh && !(c.t < cmd->t_stop)) halt = HALT_PAUSE;  // S:617 / G:646
+    else if (c.step >= cmd->step_limit) halt = HALT_LIMIT;
+    else if (cmd->keep_log && c.log_count >= STEP_LOG_CAP) halt = HALT_LOG_FULL;
+    if (halt == HALT_NONE) {
+        const double ms = __longlong_as_double((long long)status[0]);
+        if (!(ms > 0.0) || !(ms <= 1.7976931348623157e308)) {
+            c.max_speed = ms;
+            halt = HALT_NAN;
+        } else {
+            const double dt = c.cfl * c.dspace / ms;  // S:192
+            c.max_speed = ms;
+            c.dt = dt;
+            c.t += dt;  // S:602
+            c.step += 1;
+            EulerStepScalars& sc = c.sc;
+            sc.dtdx = dt / c.dx;
+            sc.hdtdx = 0.5 * (dt / c.dx);
+            sc.dtdy = dt / c.dy;
+            sc.hdtdy = 0.5 * (dt / c.dy);
+            sc.hdxdt = 0.5 * c.dx / dt;
+            sc.hdydt = 0.5 * c.dy / dt;
+            c.redo_total += status[1] + status[2] + status[3];
+            status[0] = status[1] = status[2] = status[3] = 0ull;
+            if (cmd->keep_log) {
+                double* rec = log_ring + 3 * c.log_count;
+                rec[0] = c.t;
+                rec[1] = dt;
+                rec[2] = ms;
+                c.log_count += 1;
+            }
+        }
+    }
+    c.halt = halt;
+    c.sc.halt = halt;
+}
+
+void launch_euler_prepare(EulerStepCtl* ctl, const StepCmd* cmd, unsigned long long* status, double* log_ring,
+                          cudaStream_t s) {
+    euler_prepare_kernel<<<1, 32, 0, s>>>(ctl, cmd, status, log_ring);
+}
+
 __host__ __device__ inline size_t euler_index(const GridDims& g, int i, int j) { return blocked_index<NE>(g, i, j); }
 
 __device__ __forceinline__ void eload(const double* __restrict__ base, size_t idx, double (&u)[NE]) {
@@ -132,23 +208,27 @@ __device__ __forceinline__ bool euler_x_sweep_block(const GridDims& g, const Eul
 }
 
 template <class D, class EOS>
-__global__ void __launch_bounds__(128, 4) euler_x_sweep_kernel(const GridDims g, const EulerParams p,
+__global__ void __launch_bounds__(128, 4) euler_x_sweep_kernel(const GridDims g, const EulerParams pin,
                                                                const double* __restrict__ cur,
                                                                double* __restrict__ ubar,
                                                                unsigned long long* __restrict__ status,
                                                                unsigned* __restrict__ fix_list, const int strip) {
+    if (c_estep[pin.slot].halt) return;
+    const EulerParams p = with_step_scalars(pin);
     const bool bad = euler_x_sweep_block<D, EOS>(g, p, cur, ubar, blockIdx.x, blockIdx.y, strip);
     if (__syncthreads_or(bad) && threadIdx.x == 0)
         fix_list[atomicAdd(status + 1, 1ull)] = blockIdx.y * gridDim.x + blockIdx.x;
 }
 
 template <class EOS>
-__global__ void __launch_bounds__(128) euler_x_sweep_fix_kernel(const GridDims g, const EulerParams p,
+__global__ void __launch_bounds__(128) euler_x_sweep_fix_kernel(const GridDims g, const EulerParams pin,
                                                                 const double* __restrict__ cur,
                                                                 double* __restrict__ ubar,
                                                                 const unsigned long long* __restrict__ status,
                                                                 const unsigned* __restrict__ fix_list,
                                                                 const int strip, const unsigned nbx) {
+    if (c_estep[pin.slot].halt) return;
+    const EulerParams p = with_step_scalars(pin);
     const unsigned long long count = status[1];
     for (unsigned long long q = blockIdx.x; q < count; q += gridDim.x) {
         const unsigned bid = fix_list[q];
@@ -336,12 +416,14 @@ __device__ __forceinline__ void euler_block_max(double speed, unsigned long long
 }
 
 template <class D, class EOS>
-__global__ void __launch_bounds__(EBJ, 4) euler_y_sweep_kernel(const GridDims g, const EulerParams p,
+__global__ void __launch_bounds__(EBJ, 4) euler_y_sweep_kernel(const GridDims g, const EulerParams pin,
                                                                const double* __restrict__ ubar,
                                                                const double* __restrict__ cur,
                                                                double* __restrict__ next,
                                                                unsigned long long* __restrict__ status,
                                                                unsigned* __restrict__ fix_list, const YCols yc) {
+    if (c_estep[pin.slot].halt) return;
+    const EulerParams p = with_step_scalars(pin);
     double speed;
     // column of this block row: all columns, the four slab-edge columns or the rest (YCols, mhd_kernels.cuh)
     const int col = yc.c0 + (int)blockIdx.y + ((int)blockIdx.y >= yc.jump_at ? yc.jump : 0);
@@ -356,13 +438,15 @@ __global__ void __launch_bounds__(EBJ, 4) euler_y_sweep_kernel(const GridDims g,
 }
 
 template <class EOS>
-__global__ void __launch_bounds__(EBJ) euler_y_sweep_fix_kernel(const GridDims g, const EulerParams p,
+__global__ void __launch_bounds__(EBJ) euler_y_sweep_fix_kernel(const GridDims g, const EulerParams pin,
                                                                 const double* __restrict__ ubar,
                                                                 const double* __restrict__ cur,
                                                                 double* __restrict__ next,
                                                                 unsigned long long* __restrict__ status,
                                                                 const unsigned* __restrict__ fix_list,
                                                                 const unsigned nbx, const int counter) {
+    if (c_estep[pin.slot].halt) return;
+    const EulerParams p = with_step_scalars(pin);
     const unsigned long long count = status[counter];
     for (unsigned long long q = blockIdx.x; q < count; q += gridDim.x) {
         const unsigned bid = fix_list[q];

@@ -63,24 +63,30 @@ inline int to_kernel_bc(int bc) {
     }
 }
 
-// __constant__ slots of the step scalars: one per context that exists on a device
+// __constant__ slots of the step scalars: one per context that exists on a device (kind 0: MHD, 1: Euler -- the
+// two solver families keep separate __constant__ arrays)
 std::mutex g_slot_mutex;
-bool g_slot_used[MAX_DEVICES][lsc::STEP_SLOTS];
+bool g_slot_used[2][MAX_DEVICES][lsc::STEP_SLOTS];
 
-int slot_acquire(int device) {
+}  // namespace
+
+int lsc_slot_acquire(int device, int kind) {
+    if (device < 0 || device >= MAX_DEVICES) return -1;
     std::lock_guard<std::mutex> lock(g_slot_mutex);
     for (int s = 0; s < lsc::STEP_SLOTS; ++s)
-        if (!g_slot_used[device][s]) {
-            g_slot_used[device][s] = true;
+        if (!g_slot_used[kind][device][s]) {
+            g_slot_used[kind][device][s] = true;
             return s;
         }
     return -1;
 }
-void slot_release(int device, int slot) {
-    if (slot < 0) return;
+void lsc_slot_release(int device, int kind, int slot) {
+    if (slot < 0 || device < 0 || device >= MAX_DEVICES) return;
     std::lock_guard<std::mutex> lock(g_slot_mutex);
-    g_slot_used[device][slot] = false;
+    g_slot_used[kind][device][slot] = false;
 }
+
+namespace {
 
 // NVTX ranges around batches / steps / exchanges when LSC_NVTX=1: off by default
 bool nvtx_on() {
@@ -111,6 +117,7 @@ struct HostBlock {
 }  // namespace
 
 void lsc_count_launches(unsigned long long n) { g_launches += n; }
+void lsc_uncount_launches(unsigned long long n) { g_launches -= n; }  // launches captured into a graph, not run
 
 // error sink shared with the other translation units of the library (lsc_common.h)
 int lsc_fail(int code, const char* fmt, ...) {
@@ -313,7 +320,7 @@ int lsc_mhd_create(const lsc_mhd_config* cfg, lsc_mhd_ctx** out) {
     c->g.ny = cfg->ny;
     c->g.pitch = ((cfg->ny + 4 + lsc::JOFF) + lsc::JBLK - 1) / lsc::JBLK * lsc::JBLK;
     c->g.plane = (size_t)(c->nxl + 4) * (size_t)c->g.pitch;
-    c->slot = slot_acquire(cfg->device);
+    c->slot = lsc_slot_acquire(cfg->device, 0);
     if (c->slot < 0) {
         delete c;
         return fail(LSC_ENOMEM, "more than %d live contexts on device %d", lsc::STEP_SLOTS, cfg->device);
@@ -397,7 +404,7 @@ int lsc_mhd_destroy(lsc_mhd_ctx* c) {
     for (auto& g : c->graphs) cudaGraphExecDestroy(g.exec);
     if (c->comm_stream) cudaStreamDestroy(c->comm_stream);
     if (c->stream) cudaStreamDestroy(c->stream);
-    slot_release(c->cfg.device, c->slot);
+    lsc_slot_release(c->cfg.device, 0, c->slot);
     delete c;
     return LSC_OK;
 }

@@ -5,7 +5,12 @@
 #include "../../include/lsc_b200.h"
 
 void lsc_count_launches(unsigned long long n);
+void lsc_uncount_launches(unsigned long long n);
+extern "C" unsigned long long lsc_kernel_launch_count(void);
 int lsc_fail(int code, const char* fmt, ...);  // records the message lsc_last_error() returns
+// one __constant__ slot of step scalars per live context and device (kind 0: MHD, 1: Euler); -1: none free
+int lsc_slot_acquire(int device, int kind);
+void lsc_slot_release(int device, int kind, int slot);
 
 // stream for the halo exchange that overlaps a sweep: highest priority, so that the few NCCL / ghost-column blocks
 // are scheduled ahead of the queued sweep blocks

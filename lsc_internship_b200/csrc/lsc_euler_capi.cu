@@ -1,8 +1,10 @@
 // lsc_euler_capi.cu -- C ABI of the 2-D Euler SLIC solver (include/lsc_b200.h, lsc_euler_*): the time loop of
 // Euler_codes/SLIC_euler_2d.cpp main() (S:528-643) / generaliseSLIC.cpp main() (G:564-668) driving the
 // sm_100a kernels of euler_kernels.cu.
+#include <climits>
 #include <cmath>
 #include <cstring>
+#include <limits>
 #include <new>
 #include <vector>
 
@@ -12,6 +14,18 @@
 #include "lsc_common.h"
 #include "state_hash.h"
 
+namespace {
+// everything the host reads back after a batch of steps, in one pinned block (cf. lsc_capi.cu)
+struct EulerHostBlock {
+    lsc::StepCmd cmd;
+    lsc::EulerStepCtl ctl;
+    unsigned long long status[4];
+    double log[3 * lsc::STEP_LOG_CAP];
+};
+constexpr long E_BATCH_MAX = 4096;
+constexpr int E_GRAPH_STEPS = 8;
+}  // namespace
+
 struct lsc_euler_ctx {
     lsc_euler_config cfg;
     int nxl = 0, i0 = 0;  // slab: interior columns, first global interior column (0-based)
@@ -20,12 +34,18 @@ struct lsc_euler_ctx {
     // u^n, ubar, u^{n+1}
     double* state[3] = {nullptr, nullptr, nullptr};
     int cur = 0, bar = 1, next = 2;
-    // [0] max signal speed bits of state[cur], [1]/[2] x/y blocks recomputed with IEEE division, [3] unused
+    // [0] max signal speed bits of state[cur], [1]/[2] x/y blocks recomputed with IEEE division, [3] slab-edge y launch
     unsigned long long* d_status = nullptr;
     unsigned* d_fix = nullptr;
-    unsigned long long* h_status = nullptr;
-    bool pending = false, pending_step = false;
-    double max_speed = 0;
+    // device-resident loop state (euler_kernels.cuh: EulerStepCtl; step_ctl.cuh: StepCmd) and its host mirror
+    lsc::EulerStepCtl* d_ctl = nullptr;
+    lsc::StepCmd* d_cmd = nullptr;
+    double* d_log = nullptr;
+    unsigned long long* d_gather = nullptr;  // team leader: members' status[0] words, then their maximum
+    EulerHostBlock* h = nullptr;             // pinned
+    int slot = -1;
+    unsigned long long batch = 0;
+    long batches = 0;
     long ieee_redos = 0;
     double* d_stage = nullptr;
     int stage_cols = 0;
@@ -45,13 +65,22 @@ struct lsc_euler_ctx {
     bool table_monotone = false;       // energy columns ascending with margin: searches may be warm-started
     bool warm_search = true;           // lsc_euler_set_eos_search
     lsc::Comm* comm = nullptr;         // NCCL mode (one process per GPU)
-    bool in_group = false;             // driven by lsc_euler_group_step
-    cudaEvent_t halo_event = nullptr;  // "new u complete" marker for neighbours in a group
+    bool in_group = false;             // driven by the lsc_euler_group_* calls
+    cudaEvent_t halo_event = nullptr;  // team: "new u of this slab complete"
+    cudaEvent_t red_event = nullptr;   // team: "status word of this slab is in the leader's gather buffer"
+    cudaEvent_t max_event = nullptr;   // team leader: "the maximum over the slabs is ready"
+    struct StepGraph {
+        int key;
+        cudaGraphExec_t exec;
+        unsigned long long launches;
+    };
+    std::vector<StepGraph> graphs;  // CUDA graphs of E_GRAPH_STEPS steps (plain contexts)
+    bool graph_disabled = false;
 };
 
 namespace {
 
-int kernel_bc(int bc) { return bc == LSC_BC_PERIODIC ? lsc::BC_PERIODIC : lsc::BC_TRANSMISSIVE_E; }
+int kernel_bc(int bc) { return bc == LSC_BC_PERIODIC ? (int)lsc::BC_PERIODIC : (int)lsc::BC_TRANSMISSIVE_E; }
 
 constexpr size_t TAB_N = 500, TAB_DOUBLES = 2 * TAB_N + 2 * TAB_N * TAB_N;
 
@@ -71,13 +100,13 @@ void fill_eos(const lsc_euler_ctx* c, lsc::EulerParams& p) {
     p.tab_hints = p.tab_warm ? c->d_hints : nullptr;
 }
 
-int e_read_status(lsc_euler_ctx* c) {
-    LSC_CUDA_TRY(cudaMemcpyAsync(c->h_status, c->d_status, 32, cudaMemcpyDeviceToHost, c->stream));
-    LSC_CUDA_TRY(cudaStreamSynchronize(c->stream));
-    return LSC_OK;
-}
+struct ETeam {  // a plain context / NCCL rank (n == 1) or the slabs of one grid owned by this process
+    lsc_euler_ctx** m;
+    int n;
+    lsc_euler_ctx* lead() const { return m[0]; }
+};
 
-// boundary images / neighbour data into the two ghost columns on each side of state b
+// boundary images / neighbour data into the two ghost columns on each side of state b (plain context / NCCL rank)
 int e_fill_x_ghosts(lsc_euler_ctx* c, int b, cudaStream_t s = nullptr) {
     if (!s) s = c->stream;
     if (c->cfg.nranks <= 1) {
@@ -98,8 +127,89 @@ bool e_overlap_active(const lsc_euler_ctx* c) {
     return c->overlap == 2 || (c->overlap == 1 && c->cfg.nranks > 1 && c->comm);
 }
 
-int e_launch(lsc_euler_ctx* c, const lsc::EulerParams& p, int in, int out) {
-    LSC_CUDA_TRY(cudaMemsetAsync(c->d_status, 0, 32, c->stream));
+// team halos of state[buf[r]]: every slab records "complete", then pulls its neighbours' edge columns
+int eg_halo(const ETeam& T, const int* buf) {
+    const bool ring = (T.lead()->cfg.bc == LSC_BC_PERIODIC);
+    for (int r = 0; r < T.n; ++r) {
+        LSC_CUDA_TRY(cudaSetDevice(T.m[r]->cfg.device));
+        LSC_CUDA_TRY(cudaEventRecord(T.m[r]->halo_event, T.m[r]->stream));
+    }
+    for (int r = 0; r < T.n; ++r) {
+        lsc_euler_ctx* c = T.m[r];
+        LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
+        const int left = (r > 0) ? r - 1 : (ring ? T.n - 1 : -1);
+        const int right = (r < T.n - 1) ? r + 1 : (ring ? 0 : -1);
+        const size_t col = lsc::column_doubles(c->g, 4);  // a column of the blocked layout is one contiguous run
+        const size_t bytes = 2 * col * sizeof(double);
+        for (int side = 0; side < 2; ++side) {
+            const int nb = side == 0 ? left : right;
+            if (nb < 0) {
+                lsc::launch_euler_x_ghosts_side(c->g, side, c->state[buf[r]], c->stream);
+                lsc_count_launches(1);
+                continue;
+            }
+            lsc_euler_ctx* o = T.m[nb];
+            LSC_CUDA_TRY(cudaStreamWaitEvent(c->stream, o->halo_event, 0));
+            double* dst = c->state[buf[r]] + (side == 0 ? 0 : (size_t)(c->g.nxl + 2) * col);
+            const double* src = o->state[buf[nb]] + (side == 0 ? (size_t)o->g.nxl * col : 2 * col);
+            LSC_CUDA_TRY(cudaMemcpyPeerAsync(dst, c->cfg.device, src, o->cfg.device, bytes, c->stream));
+        }
+    }
+    LSC_CUDA_TRY(cudaGetLastError());
+    return LSC_OK;
+}
+
+// status[0] of every member <- maximum over the members (S:165-195 is a global reduction); see lsc_capi.cu
+int e_reduce_max_speed(const ETeam& T) {
+    if (T.n == 1) {
+        lsc_euler_ctx* c = T.lead();
+        if (c->cfg.nranks <= 1) return LSC_OK;
+        if (!c->comm) return lsc_fail(LSC_ESTATE, "nranks > 1 but lsc_euler_comm_init was not called");
+        if (lsc::comm_allreduce_max_u64(c->comm, c->d_status, 1, c->stream))
+            return lsc_fail(LSC_ECOMM, "allreduce failed: %s", lsc::comm_error());
+        return LSC_OK;
+    }
+    lsc_euler_ctx* L = T.lead();
+    for (int r = 0; r < T.n; ++r) {
+        lsc_euler_ctx* c = T.m[r];
+        LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
+        LSC_CUDA_TRY(cudaMemcpyPeerAsync(L->d_gather + r, L->cfg.device, c->d_status, c->cfg.device,
+                                         sizeof(unsigned long long), c->stream));
+        LSC_CUDA_TRY(cudaEventRecord(c->red_event, c->stream));
+    }
+    LSC_CUDA_TRY(cudaSetDevice(L->cfg.device));
+    for (int r = 1; r < T.n; ++r) LSC_CUDA_TRY(cudaStreamWaitEvent(L->stream, T.m[r]->red_event, 0));
+    lsc::launch_max_words(L->d_gather, T.n, L->stream);
+    lsc_count_launches(1);
+    LSC_CUDA_TRY(cudaEventRecord(L->max_event, L->stream));
+    for (int r = 0; r < T.n; ++r) {
+        lsc_euler_ctx* c = T.m[r];
+        LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
+        if (r > 0) LSC_CUDA_TRY(cudaStreamWaitEvent(c->stream, L->max_event, 0));
+        LSC_CUDA_TRY(cudaMemcpyPeerAsync(c->d_status, c->cfg.device, L->d_gather + T.n, L->cfg.device,
+                                         sizeof(unsigned long long), c->stream));
+    }
+    return LSC_OK;
+}
+
+// the host-known part of the kernel parameters; the step scalars come from the context's __constant__ slot
+void fill_params(const lsc_euler_ctx* c, lsc::EulerParams& p) {
+    fill_eos(c, p);
+    p.slot = c->slot;
+    p.cm = 0.5 * (1 + c->cfg.omega);
+    p.cp = 0.5 * (1 - c->cfg.omega);
+    p.bcy = kernel_bc(c->cfg.bc);
+    // physical boundary type at each end of this slab; -1 at an inter-rank edge (ghost columns = neighbour data)
+    const bool split = c->cfg.nranks > 1;
+    const bool ring = split && c->cfg.bc == LSC_BC_PERIODIC;
+    p.bcx_lo = (ring || (split && c->cfg.rank > 0)) ? -1 : kernel_bc(c->cfg.bc);
+    p.bcx_hi = (ring || (split && c->cfg.rank < c->cfg.nranks - 1)) ? -1 : kernel_bc(c->cfg.bc);
+}
+
+// the two sweeps of one step for one context: state[in] -> state[out] (S:604-615)
+int e_launch(lsc_euler_ctx* c, int in, int out) {
+    lsc::EulerParams p{};
+    fill_params(c, p);
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     const bool prof = c->profiling;
     if (prof) {
@@ -138,143 +248,233 @@ int e_launch(lsc_euler_ctx* c, const lsc::EulerParams& p, int in, int out) {
         if (rc) return rc;
         LSC_CUDA_TRY(cudaEventRecord(c->halo_done, c->comm_stream));
         LSC_CUDA_TRY(cudaStreamWaitEvent(c->stream, c->halo_done, 0));  // later work on `stream` sees the halos
+    }
+    return LSC_OK;
+}
+
+// one pass of the do-body S:600-616 on every member, enqueued; cur/next are rotated for the following one
+int e_enqueue_one_step(const ETeam& T, std::vector<int>& cur, std::vector<int>& next) {
+    lsc_euler_ctx* L = T.lead();
+    int rc = e_reduce_max_speed(T);  // ComputeTimeStep (S:601): the reduction itself ran inside the last y sweep
+    if (rc) return rc;
+    for (int r = 0; r < T.n; ++r) {
+        lsc_euler_ctx* c = T.m[r];
+        LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
+        lsc::launch_euler_prepare(c->d_ctl, c->d_cmd, c->d_status, c->d_log, c->stream);
+        lsc_count_launches(1);
+        LSC_CUDA_TRY(lsc::publish_euler_step_scalars(c->d_ctl, c->slot, c->stream));
+        rc = e_launch(c, cur[r], next[r]);
+        if (rc) return rc;
+        std::swap(cur[r], next[r]);
+    }
+    if (T.n > 1) return eg_halo(T, cur.data());  // applyBoundaryConditions(u) after the average (S:616)
+    if (!e_overlap_active(L)) return e_fill_x_ghosts(L, cur[0]);
+    return LSC_OK;
+}
+
+bool e_graph_eligible(const ETeam& T) {
+    const lsc_euler_ctx* c = T.lead();
+    return T.n == 1 && c->cfg.nranks <= 1 && !c->profiling && !c->graph_disabled;
+}
+
+// E_GRAPH_STEPS steps of a plain context as one CUDA graph (see lsc_capi.cu: graph_for)
+int e_graph_for(const ETeam& T, int cur0, cudaGraphExec_t* out) {
+    lsc_euler_ctx* c = T.lead();
+    const int key = cur0 | (c->overlap << 4) | (c->d_table ? 256 : 0) | ((c->d_table && c->table_monotone && c->warm_search) ? 512 : 0);
+    for (auto& e : c->graphs)
+        if (e.key == key) {
+            *out = e.exec;
+            return LSC_OK;
+        }
+    *out = nullptr;
+    std::vector<int> cur{cur0}, next{cur0 == c->cur ? c->next : c->cur};
+    const unsigned long long before = lsc_kernel_launch_count();
+    if (cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+        cudaGetLastError();
+        c->graph_disabled = true;
         return LSC_OK;
     }
-    // applyBoundaryConditions(u) after the average (S:616): only x ghost columns are read on the device
-    return c->in_group ? LSC_OK : e_fill_x_ghosts(c, out);
-}
-
-// status of the step launched last: max signal speed of the new state, blocks the IEEE fix kernels recomputed
-int e_resolve(lsc_euler_ctx* c) {
-    if (!c->pending) return LSC_OK;
-    if (c->in_group) return lsc_fail(LSC_ESTATE, "context belongs to a group: use lsc_euler_group_step");
-    if (c->cfg.nranks > 1) {
-        if (!c->comm) return lsc_fail(LSC_ESTATE, "nranks > 1 but lsc_euler_comm_init was not called");
-        if (lsc::comm_allreduce_max_u64(c->comm, c->d_status, 1, c->stream))
-            return lsc_fail(LSC_ECOMM, "allreduce failed: %s", lsc::comm_error());
-    }
-    int rc = e_read_status(c);
-    if (rc) return rc;
-    if (c->pending_step) c->ieee_redos += (long)(c->h_status[1] + c->h_status[2] + c->h_status[3]);
-    std::memcpy(&c->max_speed, &c->h_status[0], sizeof(double));
-    c->pending = false;
-    return LSC_OK;
-}
-
-// body of the do-loop S:600-616
-int e_step_launch(lsc_euler_ctx* c);
-int e_step_once(lsc_euler_ctx* c) {
-    int rc = e_resolve(c);
-    if (rc) return rc;
-    return e_step_launch(c);
-}
-
-// everything of the loop body after ComputeTimeStep's reduction is known (c->max_speed)
-int e_step_launch(lsc_euler_ctx* c) {
     int rc = LSC_OK;
-    if (!(c->max_speed > 0.0) || !std::isfinite(c->max_speed))
-        return lsc_fail(LSC_ENAN, "max signal speed is %g at step %ld", c->max_speed, c->step);
-    double dspace = c->dx;  // S:166-169
-    if (c->dy < c->dx) dspace = c->dy;
-    const double dt = c->cfg.cfl * dspace / c->max_speed;  // S:192
-    c->dt = dt;
-    c->t += dt;  // S:602
-    lsc::EulerParams p{};
-    fill_eos(c, p);
-    p.cm = 0.5 * (1 + c->cfg.omega);
-    p.cp = 0.5 * (1 - c->cfg.omega);
-    p.dtdx = dt / c->dx;
-    p.hdtdx = 0.5 * (dt / c->dx);
-    p.dtdy = dt / c->dy;
-    p.hdtdy = 0.5 * (dt / c->dy);
-    p.hdxdt = 0.5 * c->dx / dt;
-    p.hdydt = 0.5 * c->dy / dt;
-    p.bcy = kernel_bc(c->cfg.bc);
-    // physical boundary type at each end of this slab; -1 at an inter-rank edge (ghost columns = neighbour data)
-    const bool split = c->cfg.nranks > 1;
-    const bool ring = split && c->cfg.bc == LSC_BC_PERIODIC;
-    p.bcx_lo = (ring || (split && c->cfg.rank > 0)) ? -1 : kernel_bc(c->cfg.bc);
-    p.bcx_hi = (ring || (split && c->cfg.rank < c->cfg.nranks - 1)) ? -1 : kernel_bc(c->cfg.bc);
-    rc = e_launch(c, p, c->cur, c->next);
-    if (rc) return rc;
-    const int old = c->cur;
-    c->cur = c->next;
-    c->next = old;
-    c->pending = true;
-    c->pending_step = true;
-    c->step += 1;
+    for (int q = 0; q < E_GRAPH_STEPS && rc == LSC_OK; ++q) rc = e_enqueue_one_step(T, cur, next);
+    cudaGraph_t graph = nullptr;
+    cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
+    const unsigned long long captured = lsc_kernel_launch_count() - before;
+    lsc_uncount_launches(captured);  // nothing ran yet: launches are counted per replay
+    cudaGraphExec_t exec = nullptr;
+    if (rc == LSC_OK && e == cudaSuccess && graph) e = cudaGraphInstantiate(&exec, graph, 0);
+    if (graph) cudaGraphDestroy(graph);
+    if (rc != LSC_OK || e != cudaSuccess || !exec) {
+        cudaGetLastError();
+        c->graph_disabled = true;
+        return LSC_OK;
+    }
+    c->graphs.push_back({key, exec, captured});
+    *out = exec;
     return LSC_OK;
 }
 
-// ---- single-process slab group (same slab-edge code path as NCCL; see lsc_capi.cu) ----------------------
-int eg_halo(lsc_euler_ctx** g, int n) {
-    const bool ring = (g[0]->cfg.bc == LSC_BC_PERIODIC);
-    for (int r = 0; r < n; ++r) {
-        LSC_CUDA_TRY(cudaSetDevice(g[r]->cfg.device));
-        LSC_CUDA_TRY(cudaEventRecord(g[r]->halo_event, g[r]->stream));
+int e_enqueue_steps(const ETeam& T, long count) {
+    lsc_euler_ctx* L = T.lead();
+    std::vector<int> cur(T.n), next(T.n);
+    for (int r = 0; r < T.n; ++r) {
+        cur[r] = T.m[r]->cur;
+        next[r] = T.m[r]->next;
     }
-    for (int r = 0; r < n; ++r) {
-        lsc_euler_ctx* c = g[r];
-        LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
-        const int left = (r > 0) ? r - 1 : (ring ? n - 1 : -1);
-        const int right = (r < n - 1) ? r + 1 : (ring ? 0 : -1);
-        const size_t col = lsc::column_doubles(c->g, 4);  // a column of the blocked layout is one contiguous run
-        const size_t bytes = 2 * col * sizeof(double);
-        for (int side = 0; side < 2; ++side) {
-            const int nb = side == 0 ? left : right;
-            if (nb < 0) {
-                lsc::launch_euler_x_ghosts_side(c->g, side, c->state[c->cur], c->stream);
-                lsc_count_launches(1);
+    long e = 0;
+    while (e < count) {
+        if (count - e >= E_GRAPH_STEPS && e_graph_eligible(T)) {
+            cudaGraphExec_t exec = nullptr;
+            int rc = e_graph_for(T, cur[0], &exec);
+            if (rc) return rc;
+            if (exec) {
+                LSC_CUDA_TRY(cudaGraphLaunch(exec, L->stream));
+                for (auto& g : L->graphs)
+                    if (g.exec == exec) lsc_count_launches(g.launches);
+                e += E_GRAPH_STEPS;
                 continue;
             }
-            lsc_euler_ctx* o = g[nb];
-            LSC_CUDA_TRY(cudaStreamWaitEvent(c->stream, o->halo_event, 0));
-            double* dst = c->state[c->cur] + (side == 0 ? 0 : (size_t)(c->g.nxl + 2) * col);
-            const double* src = o->state[o->cur] + (side == 0 ? (size_t)o->g.nxl * col : 2 * col);
-            LSC_CUDA_TRY(cudaMemcpyPeerAsync(dst, c->cfg.device, src, o->cfg.device, bytes, c->stream));
         }
-    }
-    LSC_CUDA_TRY(cudaGetLastError());
-    return LSC_OK;
-}
-
-int eg_resolve(lsc_euler_ctx** g, int n) {
-    if (!g[0]->pending) return LSC_OK;
-    unsigned long long mx = 0;
-    for (int r = 0; r < n; ++r) {
-        LSC_CUDA_TRY(cudaSetDevice(g[r]->cfg.device));
-        int rc = e_read_status(g[r]);
+        int rc = e_enqueue_one_step(T, cur, next);
         if (rc) return rc;
-        if (g[r]->h_status[0] > mx) mx = g[r]->h_status[0];
-    }
-    for (int r = 0; r < n; ++r) {
-        if (g[r]->pending_step) g[r]->ieee_redos += (long)(g[r]->h_status[1] + g[r]->h_status[2] + g[r]->h_status[3]);
-        std::memcpy(&g[r]->max_speed, &mx, sizeof(double));
-        g[r]->pending = false;
+        e += 1;
     }
     return LSC_OK;
 }
 
-}  // namespace
+struct EBatch {
+    long done = 0;
+    int halt = lsc::HALT_NONE;
+};
 
-extern "C" {
-
-int lsc_euler_local_nx(const lsc_euler_ctx* c) { return c ? c->nxl : -1; }
-int lsc_euler_local_i0(const lsc_euler_ctx* c) { return c ? c->i0 : -1; }
-
-int lsc_euler_comm_init(lsc_euler_ctx* c, const void* id128) {
-    if (!c || !id128) return lsc_fail(LSC_EINVAL, "null argument");
-    if (c->cfg.nranks <= 1) return LSC_OK;
-    if (c->comm) return lsc_fail(LSC_ESTATE, "communicator already initialised");
-    LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
-    c->comm = lsc::comm_create(id128, c->cfg.rank, c->cfg.nranks, c->g, 4);
-    if (!c->comm) return lsc_fail(LSC_ECOMM, "%s", lsc::comm_error());
+// one batch: command block -> device, `count` steps enqueued, ONE synchronisation, host mirrors brought up to date
+int e_run_batch(const ETeam& T, long count, double t_stop, long long step_limit, bool keep_log, EBatch* res) {
+    lsc_euler_ctx* L = T.lead();
+    for (int r = 0; r < T.n; ++r) {
+        lsc_euler_ctx* c = T.m[r];
+        LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
+        c->batch += 1;
+        c->batches += 1;
+        lsc::StepCmd& cmd = c->h->cmd;
+        cmd.batch = c->batch;
+        cmd.step_limit = step_limit;
+        cmd.t_stop = t_stop;
+        cmd.dump_counter = -1;
+        cmd.keep_log = (keep_log && r == 0) ? 1 : 0;
+        LSC_CUDA_TRY(cudaMemcpyAsync(c->d_cmd, &cmd, sizeof cmd, cudaMemcpyHostToDevice, c->stream));
+    }
+    int rc = e_enqueue_steps(T, count);
+    for (int r = 0; r < T.n; ++r) {
+        lsc_euler_ctx* c = T.m[r];
+        cudaSetDevice(c->cfg.device);
+        cudaMemcpyAsync(&c->h->ctl, c->d_ctl, sizeof(lsc::EulerStepCtl), cudaMemcpyDeviceToHost, c->stream);
+        cudaMemcpyAsync(c->h->status, c->d_status, 32, cudaMemcpyDeviceToHost, c->stream);
+    }
+    for (int r = 0; r < T.n; ++r) {
+        cudaSetDevice(T.m[r]->cfg.device);
+        cudaError_t e = cudaStreamSynchronize(T.m[r]->stream);
+        if (e != cudaSuccess && rc == LSC_OK)
+            rc = lsc_fail(LSC_ECUDA, "step batch failed on slab %d: %s", r, cudaGetErrorString(e));
+    }
+    if (rc) return rc;
+    const long before = L->step;
+    for (int r = 0; r < T.n; ++r) {
+        lsc_euler_ctx* c = T.m[r];
+        const lsc::EulerStepCtl& k = c->h->ctl;
+        if (k.step != L->h->ctl.step || k.halt != L->h->ctl.halt)
+            return lsc_fail(LSC_ESTATE, "slab %d is at step %lld (halt %d), the leader at %lld (halt %d)", r, k.step,
+                            k.halt, L->h->ctl.step, L->h->ctl.halt);
+        if (((long)k.step - c->step) & 1) std::swap(c->cur, c->next);
+        c->step = (long)k.step;
+        c->t = k.t;
+        c->dt = k.dt;
+        c->ieee_redos = (long)(k.redo_total + c->h->status[1] + c->h->status[2] + c->h->status[3]);
+    }
+    res->done = L->step - before;
+    res->halt = L->h->ctl.halt;
+    if (res->halt == lsc::HALT_NAN)
+        return lsc_fail(LSC_ENAN, "max signal speed is %g at step %ld", L->h->ctl.max_speed, L->step);
+    if (keep_log && L->h->ctl.log_count > 0) {
+        LSC_CUDA_TRY(cudaSetDevice(L->cfg.device));
+        LSC_CUDA_TRY(cudaMemcpyAsync(L->h->log, L->d_log, sizeof(double) * 3 * (size_t)L->h->ctl.log_count,
+                                     cudaMemcpyDeviceToHost, L->stream));
+        LSC_CUDA_TRY(cudaStreamSynchronize(L->stream));
+    }
     return LSC_OK;
 }
 
-}  // extern "C"
+int e_team_step(const ETeam& T, long nsteps) {
+    lsc_euler_ctx* L = T.lead();
+    const long long target = (long long)L->step + nsteps;
+    while (L->step < target) {
+        EBatch res;
+        const long count = (long)std::min<long long>(target - L->step, E_BATCH_MAX);
+        int rc = e_run_batch(T, count, std::numeric_limits<double>::infinity(), target, false, &res);
+        if (rc) return rc;
+    }
+    return LSC_OK;
+}
 
-namespace {
+// do { step } while (t < t_stop)  -- S:600-617 / G:627-646 (the body runs at least once)
+int e_team_run_until(const ETeam& T, double t_stop, lsc_euler_log_cb log_cb, void* user, long* steps_out) {
+    lsc_euler_ctx* L = T.lead();
+    long n = 0;
+    bool again = true;
+    while (again) {
+        long count = 1;
+        if (L->dt > 0) {
+            const double est = (t_stop - L->t) / L->dt;
+            count = est > (double)E_BATCH_MAX ? E_BATCH_MAX : (est < 1.0 ? 1 : (long)est + 2);
+        }
+        if (log_cb) count = std::min<long>(count, lsc::STEP_LOG_CAP);
+        EBatch res;
+        int rc = e_run_batch(T, count, t_stop, LLONG_MAX, log_cb != nullptr, &res);
+        if (rc) return rc;
+        n += res.done;
+        if (log_cb)
+            for (long q = 0; q < res.done; ++q) {  // G:631
+                const double* rec = L->h->log + 3 * q;
+                if (log_cb(L->step - res.done + q + 1, rec[0], rec[1], user))
+                    return lsc_fail(LSC_ECALLBACK, "log callback stopped the loop at step %ld", L->step - res.done + q + 1);
+            }
+        again = L->t < t_stop;  // S:617 / G:646
+    }
+    if (steps_out) *steps_out = n;
+    return LSC_OK;
+}
+
+int e_team_step_timed(const ETeam& T, long nsteps, float* ms) {
+    lsc_euler_ctx* L = T.lead();
+    LSC_CUDA_TRY(cudaSetDevice(L->cfg.device));
+    cudaEvent_t e0, e1;
+    LSC_CUDA_TRY(cudaEventCreate(&e0));
+    LSC_CUDA_TRY(cudaEventCreate(&e1));
+    for (int r = 0; r < T.n; ++r) {
+        cudaSetDevice(T.m[r]->cfg.device);
+        cudaStreamSynchronize(T.m[r]->stream);
+    }
+    cudaSetDevice(L->cfg.device);
+    cudaEventRecord(e0, L->stream);
+    int rc = e_team_step(T, nsteps);
+    if (rc == LSC_OK) {
+        cudaSetDevice(L->cfg.device);
+        cudaError_t e = cudaEventRecord(e1, L->stream);
+        if (e == cudaSuccess) e = cudaEventSynchronize(e1);
+        if (e == cudaSuccess) e = cudaEventElapsedTime(ms, e0, e1);
+        if (e != cudaSuccess) rc = lsc_fail(LSC_ECUDA, "timing events: %s", cudaGetErrorString(e));
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    return rc;
+}
+
+int e_check_plain(lsc_euler_ctx* c, const char* what) {
+    if (!c) return lsc_fail(LSC_EINVAL, "null argument");
+    if (!c->uploaded) return lsc_fail(LSC_ESTATE, "%s before lsc_euler_upload", what);
+    if (c->cfg.nranks > 1 && !c->comm)
+        return lsc_fail(LSC_ESTATE, "nranks > 1: call lsc_euler_comm_init (one process per GPU) or use the "
+                                    "lsc_euler_group_* calls (slabs owned by one process)");
+    return LSC_OK;
+}
 
 int eg_check(lsc_euler_ctx** g, int n) {
     if (!g || n < 1) return lsc_fail(LSC_EINVAL, "empty group");
@@ -302,35 +502,36 @@ struct EulerGroupScope {  // in_group for the duration of a group call, reset on
     lsc_euler_ctx** g;
     int n;
     EulerGroupScope(lsc_euler_ctx** g_, int n_) : g(g_), n(n_) {
-        for (int r = 0; r < n; ++r) g[r]->in_group = true;
+        for (int r = 0; r < n; ++r) g[r]->in_group = n > 1;
     }
     ~EulerGroupScope() {
         for (int r = 0; r < n; ++r) g[r]->in_group = false;
     }
 };
 
-// one pass of the do-body S:600-616 on every slab
-int eg_step_once(lsc_euler_ctx** g, int n) {
-    int rc = eg_resolve(g, n);
-    for (int r = 0; r < n && rc == LSC_OK; ++r) {
-        LSC_CUDA_TRY(cudaSetDevice(g[r]->cfg.device));
-        rc = e_step_launch(g[r]);
-    }
-    if (rc == LSC_OK) rc = eg_halo(g, n);
-    return rc;
-}
-
 }  // namespace
 
 extern "C" {
+
+int lsc_euler_local_nx(const lsc_euler_ctx* c) { return c ? c->nxl : -1; }
+int lsc_euler_local_i0(const lsc_euler_ctx* c) { return c ? c->i0 : -1; }
+
+int lsc_euler_comm_init(lsc_euler_ctx* c, const void* id128) {
+    if (!c || !id128) return lsc_fail(LSC_EINVAL, "null argument");
+    if (c->cfg.nranks <= 1) return LSC_OK;
+    if (c->comm) return lsc_fail(LSC_ESTATE, "communicator already initialised");
+    LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
+    c->comm = lsc::comm_create(id128, c->cfg.rank, c->cfg.nranks, c->g, 4);
+    if (!c->comm) return lsc_fail(LSC_ECOMM, "%s", lsc::comm_error());
+    return LSC_OK;
+}
 
 int lsc_euler_group_step(lsc_euler_ctx** g, int n, long nsteps) {
     int rc = eg_check(g, n);
     if (rc) return rc;
     EulerGroupScope scope(g, n);
-    for (long s = 0; s < nsteps && rc == LSC_OK; ++s) rc = eg_step_once(g, n);
-    if (rc == LSC_OK) rc = eg_resolve(g, n);
-    return rc;
+    ETeam T{g, n};
+    return e_team_step(T, nsteps);
 }
 
 int lsc_euler_group_run_until(lsc_euler_ctx** g, int n, double t_stop, lsc_euler_log_cb log_cb, void* user,
@@ -338,16 +539,8 @@ int lsc_euler_group_run_until(lsc_euler_ctx** g, int n, double t_stop, lsc_euler
     int rc = eg_check(g, n);
     if (rc) return rc;
     EulerGroupScope scope(g, n);
-    long k = 0;
-    do {  // S:600 / G:627
-        rc = eg_step_once(g, n);
-        if (rc) return rc;
-        ++k;
-        if (log_cb && log_cb(g[0]->step, g[0]->t, g[0]->dt, user))  // G:631
-            return lsc_fail(LSC_ECALLBACK, "log callback stopped the loop at step %ld", g[0]->step);
-    } while (g[0]->t < t_stop);  // S:617 / G:646
-    if (steps_out) *steps_out = k;
-    return eg_resolve(g, n);
+    ETeam T{g, n};
+    return e_team_run_until(T, t_stop, log_cb, user, steps_out);
 }
 
 int lsc_euler_create(const lsc_euler_config* cfg, lsc_euler_ctx** out) {
@@ -398,11 +591,23 @@ int lsc_euler_create(const lsc_euler_config* cfg, lsc_euler_ctx** out) {
         ok = cudaMalloc(&c->state[b], state_bytes) == cudaSuccess;
         if (ok) cudaMemset(c->state[b], 0, state_bytes);
     }
+    c->slot = lsc_slot_acquire(cfg->device, 1);
+    if (c->slot < 0) {
+        lsc_euler_destroy(c);
+        return lsc_fail(LSC_ENOMEM, "more than %d live Euler contexts on device %d", lsc::STEP_SLOTS, cfg->device);
+    }
     ok = ok && cudaMalloc(&c->d_stage, col_bytes * (size_t)cols) == cudaSuccess &&
-         cudaMalloc(&c->d_status, 32) == cudaSuccess &&
+         cudaMalloc(&c->d_status, 32) == cudaSuccess && cudaMemset(c->d_status, 0, 32) == cudaSuccess &&
+         cudaMalloc(&c->d_ctl, sizeof(lsc::EulerStepCtl)) == cudaSuccess &&
+         cudaMalloc(&c->d_cmd, sizeof(lsc::StepCmd)) == cudaSuccess &&
+         cudaMemset(c->d_cmd, 0, sizeof(lsc::StepCmd)) == cudaSuccess &&
+         cudaMalloc(&c->d_log, sizeof(double) * 3 * lsc::STEP_LOG_CAP) == cudaSuccess &&
+         cudaMalloc(&c->d_gather, sizeof(unsigned long long) * (size_t)(c->cfg.nranks + 1)) == cudaSuccess &&
+         cudaHostAlloc(&c->h, sizeof(EulerHostBlock), cudaHostAllocPortable) == cudaSuccess &&
+         cudaEventCreateWithFlags(&c->red_event, cudaEventDisableTiming) == cudaSuccess &&
+         cudaEventCreateWithFlags(&c->max_event, cudaEventDisableTiming) == cudaSuccess &&
          cudaMalloc(&c->d_fix, sizeof(unsigned) * (size_t)(lsc::euler_fix_list_entries(c->g) +
                                                            lsc::euler_edge_list_entries(c->g))) == cudaSuccess &&
-         cudaHostAlloc(&c->h_status, 32, cudaHostAllocDefault) == cudaSuccess &&
          cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess &&
          cudaEventCreateWithFlags(&c->halo_event, cudaEventDisableTiming) == cudaSuccess &&
          cudaEventCreateWithFlags(&c->edges_done, cudaEventDisableTiming) == cudaSuccess &&
@@ -413,6 +618,8 @@ int lsc_euler_create(const lsc_euler_config* cfg, lsc_euler_ctx** out) {
         lsc_euler_destroy(c);
         return lsc_fail(LSC_ENOMEM, "device allocation failed (%zu bytes per state)", state_bytes);
     }
+    std::memset(c->h, 0, sizeof(EulerHostBlock));
+    if (const char* e = std::getenv("LSC_NO_GRAPH")) c->graph_disabled = (*e && *e != '0');
     *out = c;
     return LSC_OK;
 }
@@ -421,12 +628,21 @@ int lsc_euler_destroy(lsc_euler_ctx* c) {
     if (!c) return LSC_OK;
     cudaSetDevice(c->cfg.device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->comm_stream) cudaStreamSynchronize(c->comm_stream);
     for (int b = 0; b < 3; ++b)
         if (c->state[b]) cudaFree(c->state[b]);
     if (c->d_stage) cudaFree(c->d_stage);
     if (c->d_status) cudaFree(c->d_status);
     if (c->d_fix) cudaFree(c->d_fix);
-    if (c->h_status) cudaFreeHost(c->h_status);
+    if (c->d_ctl) cudaFree(c->d_ctl);
+    if (c->d_cmd) cudaFree(c->d_cmd);
+    if (c->d_log) cudaFree(c->d_log);
+    if (c->d_gather) cudaFree(c->d_gather);
+    if (c->h) cudaFreeHost(c->h);
+    if (c->red_event) cudaEventDestroy(c->red_event);
+    if (c->max_event) cudaEventDestroy(c->max_event);
+    for (auto& g : c->graphs) cudaGraphExecDestroy(g.exec);
+    lsc_slot_release(c->cfg.device, 1, c->slot);
     if (c->d_table) cudaFree(c->d_table);
     if (c->d_hints) cudaFree(c->d_hints);
     if (c->comm) lsc::comm_destroy(c->comm);
@@ -462,6 +678,8 @@ int lsc_euler_set_eos_table(lsc_euler_ctx* c, const double* densities, const dou
                             const double* sound_speeds, const double* energies) {
     if (!c) return lsc_fail(LSC_EINVAL, "null argument");
     LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
+    for (auto& g : c->graphs) cudaGraphExecDestroy(g.exec);  // captured steps hold the old table pointers
+    c->graphs.clear();
     if (!densities) {  // back to the ideal gas of S / G
         if (c->d_table) cudaFree(c->d_table);
         c->d_table = nullptr;
@@ -555,12 +773,21 @@ int lsc_euler_upload(lsc_euler_ctx* c, const double* aos) {
         int rc = e_fill_x_ghosts(c, c->cur);
         if (rc) return rc;
     }  // slabs: the uploaded halo columns already hold the neighbours' cells / the caller's boundary images
+    // fresh loop state: t = 0, step = 0, the run's constants (S:537, S:166-169, S:546-547)
+    lsc::EulerStepCtl& k = c->h->ctl;
+    std::memset(&k, 0, sizeof k);
+    k.cfl = c->cfg.cfl;
+    k.dspace = c->dx;  // S:166-169
+    if (c->dy < c->dx) k.dspace = c->dy;
+    k.dx = c->dx;
+    k.dy = c->dy;
+    k.batch_seen = c->batch;
+    LSC_CUDA_TRY(cudaMemcpyAsync(c->d_ctl, &k, sizeof k, cudaMemcpyHostToDevice, c->stream));
     LSC_CUDA_TRY(cudaStreamSynchronize(c->stream));
     c->t = c->dt = 0;
     c->step = 0;
+    c->ieee_redos = 0;
     c->uploaded = true;
-    c->pending = true;
-    c->pending_step = false;
     return LSC_OK;
 }
 
@@ -584,52 +811,31 @@ int lsc_euler_init_problem(lsc_euler_ctx* c, int problem) {
 }
 
 int lsc_euler_step(lsc_euler_ctx* c, long nsteps) {
-    if (!c) return lsc_fail(LSC_EINVAL, "null argument");
-    if (!c->uploaded) return lsc_fail(LSC_ESTATE, "lsc_euler_step before lsc_euler_upload");
-    LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
-    for (long s = 0; s < nsteps; ++s) {
-        int rc = e_step_once(c);
-        if (rc) return rc;
-    }
-    return e_resolve(c);
+    int rc = e_check_plain(c, "lsc_euler_step");
+    if (rc) return rc;
+    ETeam T{&c, 1};
+    return e_team_step(T, nsteps);
 }
 
 int lsc_euler_step_timed(lsc_euler_ctx* c, long nsteps, float* ms) {
-    if (!c || !ms) return lsc_fail(LSC_EINVAL, "null argument");
-    if (!c->uploaded) return lsc_fail(LSC_ESTATE, "lsc_euler_step_timed before lsc_euler_upload");
-    LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
-    cudaEvent_t e0, e1;
-    LSC_CUDA_TRY(cudaEventCreate(&e0));
-    LSC_CUDA_TRY(cudaEventCreate(&e1));
-    LSC_CUDA_TRY(cudaStreamSynchronize(c->stream));
-    LSC_CUDA_TRY(cudaEventRecord(e0, c->stream));
-    int rc = LSC_OK;
-    for (long s = 0; s < nsteps && rc == LSC_OK; ++s) rc = e_step_once(c);
-    if (rc == LSC_OK) rc = e_resolve(c);
-    if (rc == LSC_OK) {
-        LSC_CUDA_TRY(cudaEventRecord(e1, c->stream));
-        LSC_CUDA_TRY(cudaEventSynchronize(e1));
-        LSC_CUDA_TRY(cudaEventElapsedTime(ms, e0, e1));
-    }
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
-    return rc;
+    if (!ms) return lsc_fail(LSC_EINVAL, "null argument");
+    int rc = e_check_plain(c, "lsc_euler_step_timed");
+    if (rc) return rc;
+    ETeam T{&c, 1};
+    return e_team_step_timed(T, nsteps, ms);
 }
 
 int lsc_euler_run_until(lsc_euler_ctx* c, double t_stop, lsc_euler_log_cb log_cb, void* user, long* steps_out) {
+    int rc = e_check_plain(c, "lsc_euler_run_until");
+    if (rc) return rc;
+    ETeam T{&c, 1};
+    return e_team_run_until(T, t_stop, log_cb, user, steps_out);
+}
+
+int lsc_euler_loop_stats(const lsc_euler_ctx* c, long* host_syncs) {
     if (!c) return lsc_fail(LSC_EINVAL, "null argument");
-    if (!c->uploaded) return lsc_fail(LSC_ESTATE, "lsc_euler_run_until before lsc_euler_upload");
-    LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
-    long n = 0;
-    do {  // S:600 / G:627
-        int rc = e_step_once(c);
-        if (rc) return rc;
-        ++n;
-        if (log_cb && log_cb(c->step, c->t, c->dt, user))  // G:631
-            return lsc_fail(LSC_ECALLBACK, "log callback stopped the loop at step %ld", c->step);
-    } while (c->t < t_stop);  // S:617 / G:646
-    if (steps_out) *steps_out = n;
-    return e_resolve(c);
+    if (host_syncs) *host_syncs = c->batches;
+    return LSC_OK;
 }
 
 int lsc_euler_get_scalars(const lsc_euler_ctx* c, double* t, double* dt, long* step) {
@@ -644,10 +850,6 @@ int lsc_euler_download(lsc_euler_ctx* c, double* aos) {
     if (!c || !aos) return lsc_fail(LSC_EINVAL, "null argument");
     if (!c->uploaded) return lsc_fail(LSC_ESTATE, "lsc_euler_download before lsc_euler_upload");
     LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
-    if (c->pending && c->pending_step && !c->in_group) {
-        int rc = e_resolve(c);
-        if (rc) return rc;
-    }
     const size_t col = (size_t)(c->cfg.ny + 4) * 4;
     const int ncol = c->nxl + 4;
     for (int il = 0; il < ncol; il += c->stage_cols) {
@@ -668,10 +870,6 @@ int lsc_euler_state_hash(lsc_euler_ctx* c, unsigned long long* hash) {
     if (!c || !hash) return lsc_fail(LSC_EINVAL, "null argument");
     if (!c->uploaded) return lsc_fail(LSC_ESTATE, "lsc_euler_state_hash before lsc_euler_upload");
     LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
-    if (c->pending && c->pending_step && !c->in_group) {
-        int rc = e_resolve(c);
-        if (rc) return rc;
-    }
     unsigned long long* d = nullptr;
     LSC_CUDA_TRY(cudaMalloc(&d, sizeof *d));
     cudaMemsetAsync(d, 0, sizeof *d, c->stream);

@@ -17,6 +17,7 @@
 // recomputes exactly those blocks.  No host round trip, no branch per quotient, and the result is the
 // correctly rounded one for any input (e.g. the denormal momenta at a numerical front).
 #include <algorithm>
+#include <cstdlib>
 #include <type_traits>
 
 #include "cfl_reduce.cuh"
@@ -396,13 +397,23 @@ __global__ void __launch_bounds__(XS_BLOCK) x_sweep_fix_kernel(const GridDims g,
     }
 }
 
+// development aid: LSC_XS_STRIP=<columns> overrides choose_x_strip (strip-length experiments, scripts/strip_sweep.py)
+static int strip_override() {
+    static const int v = [] {
+        const char* e = getenv("LSC_XS_STRIP");
+        return e ? atoi(e) : 0;
+    }();
+    return v;
+}
+
 void launch_x_sweep(const GridDims& g, const SweepArgs& p, const double* u_cur, const double* u_prev,
                     double* u_bar, unsigned long long* status, unsigned* x_flags, cudaStream_t s) {
     // strip length along i: at most XS_STRIP columns per thread (3 warm-up cells amortised over the strip),
     // chosen so that the blocks fill whole rounds of the 148 SMs x XS_MINB resident blocks (choose_x_strip)
     dim3 block(XS_BLOCK);
     const int row_blocks = (g.ny + block.x - 1) / block.x;
-    const int strip = choose_x_strip(row_blocks, g.nxl, XS_STRIP, 148 * XS_MINB, XS_MIN_STRIP);
+    int strip = choose_x_strip(row_blocks, g.nxl, XS_STRIP, 148 * XS_MINB, XS_MIN_STRIP);
+    if (strip_override() >= XS_MIN_STRIP) strip = strip_override();
     dim3 grid(row_blocks, (g.nxl + strip - 1) / strip);
     x_sweep_kernel<MHD_FAST_POLICY><<<grid, block, 0, s>>>(g, p, u_cur, u_prev, u_bar, x_flags, strip);
     const unsigned nblocks = grid.x * grid.y;

@@ -170,6 +170,12 @@ class SlicEuler2d:
     def ieee_fallback_count(self):
         return lib().lsc_euler_ieee_fallback_count(self._h)
 
+    def loop_stats(self):
+        """(host synchronisations of the time loop so far, 0): the Euler loop has no exp table"""
+        a = ctypes.c_long()
+        check(lib().lsc_euler_loop_stats(self._h, ctypes.byref(a)))
+        return a.value, 0
+
     def run_until(self, t_stop, log=None):
         """do { step } while (t < t_stop) -- S:600-617 / G:627-646.  Returns the number of steps."""
         err = []

@@ -445,3 +445,70 @@ def test_large_grid_conservation():
     for k in (0, 3):
         a, b = u0[..., k].sum(dtype=np.longdouble), u1[..., k].sum(dtype=np.longdouble)
         assert abs(a - b) / abs(a) < 1e-12
+
+
+@gpu
+def test_euler_time_loop_is_device_resident():
+    """dt, t and the sweeps' scalars are formed on the device (euler_prepare_kernel); a call that advances many steps
+    synchronises with the host once, run_until's log shows every step's (t, dt) as the reference prints them."""
+    import lsc_internship_b200 as lsc
+    nx, ny, n = 72, 60, 43
+    cfg = euler_cfg(nx, ny, DOM, bc="transmissive")
+    u0 = euler_ic(cfg, "cylinder")
+    o = OracleEuler(cfg, u0)
+    log = o.step(n)
+    s = lsc.SlicEuler2d(nx, ny, bc="transmissive", problem="cylinder")
+    s.upload(u0)
+    a, _ = s.loop_stats()
+    s.step(n)
+    b, _ = s.loop_stats()
+    assert b - a == 1
+    t, dt, k = s.scalars()
+    assert (t, dt) == tuple(log[-1]) and k == n
+    assert np.array_equal(bits(s.download()), bits(o.state()[0]))
+    s.upload(u0)
+    o2 = OracleEuler(cfg, u0)
+    lines = []
+    nrun = s.run_until(0.05, log=lambda k, t, dt: lines.append((t, dt)))
+    ref = o2.step(nrun)
+    assert np.array_equal(bits(np.array(lines)), bits(ref))
+    assert ref[-1][0] >= 0.05 > ref[-2][0]
+    c, _ = s.loop_stats()
+    assert c - b <= 3
+    assert np.array_equal(bits(s.download()), bits(o2.state()[0]))
+    s.close()
+
+
+@gpu
+def test_cpp_drivers_with_slabs_are_the_same_programs(tmp_path, golden_dir):
+    """drivers/slic_euler_2d and drivers/tab_eos cut into slabs inside ONE process (--gpus N on a multi-GPU box, --slabs
+    3 on one GPU): stdout and files identical to the single-context runs, i.e. to the reference programs'."""
+    import subprocess
+    import lsc_internship_b200 as lsc
+    from oracle_util import write_eos_table
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    ndev = lsc.lib().lsc_device_count()
+    opt = ["--gpus", str(min(ndev, 4))] if ndev >= 2 else ["--slabs", "3"]
+    exe = os.path.join(root, "drivers", "_bin", "slic_euler_2d")
+    sha = json.load(open(os.path.join(golden_dir, "dat_sha256.json")))
+    a = tmp_path / "s"
+    a.mkdir()
+    r = subprocess.run([exe] + opt, cwd=a, check=True, capture_output=True, text=True)
+    assert r.stdout == open(os.path.join(golden_dir, "slic_euler_2d_stdout.txt")).read()
+    for k in (1, 7, 20):
+        assert hashlib.sha256(open(a / f"euler_{k}.dat", "rb").read()).hexdigest() == sha[f"euler_{k}.dat"]
+    b = tmp_path / "g"
+    b.mkdir()
+    r = subprocess.run([exe, "--generalise"] + opt, cwd=b, check=True, capture_output=True, text=True)
+    assert r.stdout == open(os.path.join(golden_dir, "generalise_slic_stdout.txt")).read()
+    assert hashlib.sha256(open(b / "SLIC2d.dat", "rb").read()).hexdigest() == sha["SLIC2d.dat@generaliseSLIC"]
+    # tab_eos: one context against the slabs, byte for byte
+    exe = os.path.join(root, "drivers", "_bin", "tab_eos")
+    outs = []
+    for name, extra in (("t1", []), ("tn", opt)):
+        d = tmp_path / name
+        d.mkdir()
+        write_eos_table(str(d / "Plasma19_EoS.txt"))
+        r = subprocess.run([exe, "--nx", "48", "--ny", "40"] + extra, cwd=d, check=True, capture_output=True, text=True)
+        outs.append((r.stdout, open(d / "SLIC2d.dat", "rb").read()))
+    assert outs[0] == outs[1]
