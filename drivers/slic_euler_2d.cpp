@@ -93,6 +93,7 @@ int main(int argc, char** argv) {
     }
     lsc_euler_ctx** g = slabs.data();
     std::vector<double> host(nodat ? 0 : (size_t)(cfg.nx + 4) * (cfg.ny + 4) * LSC_EULER_NVAR);
+    if (lsc_euler_group_step(slabs.data(), nslabs, 0)) return die();  // one-time team setup (peer access) outside --time
     const auto t0 = std::chrono::steady_clock::now();
     long steps = 0, k = 0;
     if (generalise) {

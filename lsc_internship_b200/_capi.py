@@ -65,7 +65,7 @@ EXPORTS = [
     "lsc_comm_unique_id", "lsc_mhd_comm_init", "lsc_mhd_kat_hllc", "lsc_mhd_kat_fluxdef", "lsc_mhd_kat_cfl_bound", "lsc_mhd_set_arithmetic",
     "lsc_kernel_launch_count", "lsc_mhd_step_timed", "lsc_mhd_set_profiling", "lsc_mhd_kernel_times", "lsc_mhd_comm_times", "lsc_mhd_set_overlap", "lsc_kat_division", "lsc_mhd_ieee_fallback_count", "lsc_mhd_group_step", "lsc_mhd_fill_ghost_ring", "lsc_mhd_state_hash", "lsc_euler_state_hash",
     "lsc_mhd_group_step_timed", "lsc_mhd_group_run_until", "lsc_mhd_loop_stats", "lsc_mhd_group_download",
-    "lsc_euler_group_run_until", "lsc_euler_group_download", "lsc_euler_loop_stats",
+    "lsc_guard_check", "lsc_euler_group_run_until", "lsc_euler_group_download", "lsc_euler_loop_stats",
     "lsc_euler_create", "lsc_euler_destroy", "lsc_euler_initial_condition", "lsc_euler_upload",
     "lsc_euler_init_problem", "lsc_euler_step", "lsc_euler_step_timed", "lsc_euler_run_until",
     "lsc_euler_get_scalars", "lsc_euler_download", "lsc_euler_write_dat", "lsc_euler_ieee_fallback_count",
@@ -142,6 +142,7 @@ def lib():
     L.lsc_euler_group_step.argtypes = [ctypes.POINTER(vp), ctypes.c_int, ctypes.c_long]
     L.lsc_euler_group_run_until.argtypes = [ctypes.POINTER(vp), ctypes.c_int, ctypes.c_double, EULER_LOG_CB, vp,
                                             ctypes.POINTER(ctypes.c_long)]
+    L.lsc_guard_check.argtypes = [ctypes.POINTER(ctypes.c_ulonglong), ctypes.POINTER(ctypes.c_ulonglong)]
     L.lsc_euler_loop_stats.argtypes = [vp, ctypes.POINTER(ctypes.c_long)]
     L.lsc_euler_group_download.argtypes = [ctypes.POINTER(vp), ctypes.c_int, dp]
     L.lsc_euler_initial_condition.argtypes = [ecfg, ctypes.c_int, dp]
@@ -186,6 +187,13 @@ def state_hash_host(u_interior, i0_global=0, ny_total=None):
         z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
         z = z ^ (z >> np.uint64(31))
         return int(z.sum(dtype=np.uint64)) & _M64
+
+
+def guard_check():
+    """(corrupted guard bytes, watched buffers) -- lsc_guard_check; meaningful when LSC_GUARD=1 was set at create"""
+    a, b = ctypes.c_ulonglong(), ctypes.c_ulonglong()
+    check(lib().lsc_guard_check(ctypes.byref(a), ctypes.byref(b)))
+    return a.value, b.value
 
 
 def check(rc):

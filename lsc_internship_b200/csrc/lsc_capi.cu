@@ -327,7 +327,7 @@ int lsc_mhd_create(const lsc_mhd_config* cfg, lsc_mhd_ctx** out) {
     }
     const size_t state_bytes = c->g.plane * lsc::NV * sizeof(double);
     for (int b = 0; b < 3; ++b) {
-        if (cudaMalloc(&c->state[b], state_bytes) != cudaSuccess) {
+        if (lsc_dev_malloc(&c->state[b], state_bytes) != cudaSuccess) {
             cudaGetLastError();
             lsc_mhd_destroy(c);
             return fail(LSC_ENOMEM, "cudaMalloc of %zu bytes failed", state_bytes);
@@ -340,18 +340,18 @@ int lsc_mhd_create(const lsc_mhd_config* cfg, lsc_mhd_ctx** out) {
     if (cols < 1) cols = 1;
     if (cols > c->nxl + 4) cols = c->nxl + 4;
     c->stage_cols = (int)cols;
-    if (cudaMalloc(&c->d_stage, col_bytes * (size_t)cols) != cudaSuccess ||
-        cudaMalloc(&c->d_status, STATUS_BYTES) != cudaSuccess ||
+    if (lsc_dev_malloc(&c->d_stage, col_bytes * (size_t)cols) != cudaSuccess ||
+        lsc_dev_malloc(&c->d_status, STATUS_BYTES) != cudaSuccess ||
         cudaMemset(c->d_status, 0, STATUS_BYTES) != cudaSuccess ||
-        cudaMalloc(&c->d_fix, sizeof(unsigned) * (size_t)(lsc::y_sweep_block_count(c->g) +
+        lsc_dev_malloc(&c->d_fix, sizeof(unsigned) * (size_t)(lsc::y_sweep_block_count(c->g) +
                                                           lsc::y_edge_block_count(c->g))) != cudaSuccess ||
-        cudaMalloc(&c->d_xflags, sizeof(unsigned) * (size_t)lsc::x_sweep_block_count(c->g)) != cudaSuccess ||
+        lsc_dev_malloc(&c->d_xflags, sizeof(unsigned) * (size_t)lsc::x_sweep_block_count(c->g)) != cudaSuccess ||
         cudaMemset(c->d_xflags, 0, sizeof(unsigned) * (size_t)lsc::x_sweep_block_count(c->g)) != cudaSuccess ||
-        cudaMalloc(&c->d_ctl, sizeof(lsc::StepCtl)) != cudaSuccess ||
-        cudaMalloc(&c->d_cmd, sizeof(lsc::StepCmd)) != cudaSuccess ||
+        lsc_dev_malloc(&c->d_ctl, sizeof(lsc::StepCtl)) != cudaSuccess ||
+        lsc_dev_malloc(&c->d_cmd, sizeof(lsc::StepCmd)) != cudaSuccess ||
         cudaMemset(c->d_cmd, 0, sizeof(lsc::StepCmd)) != cudaSuccess ||
-        cudaMalloc(&c->d_log, sizeof(double) * 3 * lsc::STEP_LOG_CAP) != cudaSuccess ||
-        cudaMalloc(&c->d_gather, sizeof(unsigned long long) * (size_t)(cfg->nranks + 1)) != cudaSuccess ||
+        lsc_dev_malloc(&c->d_log, sizeof(double) * 3 * lsc::STEP_LOG_CAP) != cudaSuccess ||
+        lsc_dev_malloc(&c->d_gather, sizeof(unsigned long long) * (size_t)(cfg->nranks + 1)) != cudaSuccess ||
         cudaHostAlloc(&c->h, sizeof(HostBlock), cudaHostAllocPortable) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->halo_event, cudaEventDisableTiming) != cudaSuccess ||
@@ -383,15 +383,15 @@ int lsc_mhd_destroy(lsc_mhd_ctx* c) {
     if (c->comm_stream) cudaStreamSynchronize(c->comm_stream);
     if (c->comm) lsc::comm_destroy(c->comm);
     for (int b = 0; b < 3; ++b)
-        if (c->state[b]) cudaFree(c->state[b]);
-    if (c->d_fix) cudaFree(c->d_fix);
-    if (c->d_xflags) cudaFree(c->d_xflags);
-    if (c->d_stage) cudaFree(c->d_stage);
-    if (c->d_status) cudaFree(c->d_status);
-    if (c->d_ctl) cudaFree(c->d_ctl);
-    if (c->d_cmd) cudaFree(c->d_cmd);
-    if (c->d_log) cudaFree(c->d_log);
-    if (c->d_gather) cudaFree(c->d_gather);
+        if (c->state[b]) lsc_dev_free(c->state[b]);
+    if (c->d_fix) lsc_dev_free(c->d_fix);
+    if (c->d_xflags) lsc_dev_free(c->d_xflags);
+    if (c->d_stage) lsc_dev_free(c->d_stage);
+    if (c->d_status) lsc_dev_free(c->d_status);
+    if (c->d_ctl) lsc_dev_free(c->d_ctl);
+    if (c->d_cmd) lsc_dev_free(c->d_cmd);
+    if (c->d_log) lsc_dev_free(c->d_log);
+    if (c->d_gather) lsc_dev_free(c->d_gather);
     if (c->h) cudaFreeHost(c->h);
     if (c->halo_event) cudaEventDestroy(c->halo_event);
     if (c->red_event) cudaEventDestroy(c->red_event);

@@ -12,6 +12,15 @@ int lsc_fail(int code, const char* fmt, ...);  // records the message lsc_last_e
 int lsc_slot_acquire(int device, int kind);
 void lsc_slot_release(int device, int kind, int slot);
 
+// device buffers of a context: cudaMalloc / cudaFree, or -- with LSC_GUARD=1 -- the same with 64 KiB guard zones on
+// both sides that lsc_guard_check() inspects (dev_guard.cu)
+cudaError_t lsc_dev_malloc(void** p, size_t bytes);
+cudaError_t lsc_dev_free(void* p);
+template <class T>
+static inline cudaError_t lsc_dev_malloc(T** p, size_t bytes) {
+    return lsc_dev_malloc(reinterpret_cast<void**>(p), bytes);
+}
+
 // stream for the halo exchange that overlaps a sweep: highest priority, so that the few NCCL / ghost-column blocks
 // are scheduled ahead of the queued sweep blocks
 static inline cudaError_t lsc_create_comm_stream(cudaStream_t* s) {

@@ -588,7 +588,7 @@ int lsc_euler_create(const lsc_euler_config* cfg, lsc_euler_ctx** out) {
     c->stage_cols = (int)cols;
     bool ok = true;
     for (int b = 0; b < 3 && ok; ++b) {
-        ok = cudaMalloc(&c->state[b], state_bytes) == cudaSuccess;
+        ok = lsc_dev_malloc(&c->state[b], state_bytes) == cudaSuccess;
         if (ok) cudaMemset(c->state[b], 0, state_bytes);
     }
     c->slot = lsc_slot_acquire(cfg->device, 1);
@@ -596,17 +596,17 @@ int lsc_euler_create(const lsc_euler_config* cfg, lsc_euler_ctx** out) {
         lsc_euler_destroy(c);
         return lsc_fail(LSC_ENOMEM, "more than %d live Euler contexts on device %d", lsc::STEP_SLOTS, cfg->device);
     }
-    ok = ok && cudaMalloc(&c->d_stage, col_bytes * (size_t)cols) == cudaSuccess &&
-         cudaMalloc(&c->d_status, 32) == cudaSuccess && cudaMemset(c->d_status, 0, 32) == cudaSuccess &&
-         cudaMalloc(&c->d_ctl, sizeof(lsc::EulerStepCtl)) == cudaSuccess &&
-         cudaMalloc(&c->d_cmd, sizeof(lsc::StepCmd)) == cudaSuccess &&
+    ok = ok && lsc_dev_malloc(&c->d_stage, col_bytes * (size_t)cols) == cudaSuccess &&
+         lsc_dev_malloc(&c->d_status, 32) == cudaSuccess && cudaMemset(c->d_status, 0, 32) == cudaSuccess &&
+         lsc_dev_malloc(&c->d_ctl, sizeof(lsc::EulerStepCtl)) == cudaSuccess &&
+         lsc_dev_malloc(&c->d_cmd, sizeof(lsc::StepCmd)) == cudaSuccess &&
          cudaMemset(c->d_cmd, 0, sizeof(lsc::StepCmd)) == cudaSuccess &&
-         cudaMalloc(&c->d_log, sizeof(double) * 3 * lsc::STEP_LOG_CAP) == cudaSuccess &&
-         cudaMalloc(&c->d_gather, sizeof(unsigned long long) * (size_t)(c->cfg.nranks + 1)) == cudaSuccess &&
+         lsc_dev_malloc(&c->d_log, sizeof(double) * 3 * lsc::STEP_LOG_CAP) == cudaSuccess &&
+         lsc_dev_malloc(&c->d_gather, sizeof(unsigned long long) * (size_t)(c->cfg.nranks + 1)) == cudaSuccess &&
          cudaHostAlloc(&c->h, sizeof(EulerHostBlock), cudaHostAllocPortable) == cudaSuccess &&
          cudaEventCreateWithFlags(&c->red_event, cudaEventDisableTiming) == cudaSuccess &&
          cudaEventCreateWithFlags(&c->max_event, cudaEventDisableTiming) == cudaSuccess &&
-         cudaMalloc(&c->d_fix, sizeof(unsigned) * (size_t)(lsc::euler_fix_list_entries(c->g) +
+         lsc_dev_malloc(&c->d_fix, sizeof(unsigned) * (size_t)(lsc::euler_fix_list_entries(c->g) +
                                                            lsc::euler_edge_list_entries(c->g))) == cudaSuccess &&
          cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess &&
          cudaEventCreateWithFlags(&c->halo_event, cudaEventDisableTiming) == cudaSuccess &&
@@ -630,21 +630,21 @@ int lsc_euler_destroy(lsc_euler_ctx* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->comm_stream) cudaStreamSynchronize(c->comm_stream);
     for (int b = 0; b < 3; ++b)
-        if (c->state[b]) cudaFree(c->state[b]);
-    if (c->d_stage) cudaFree(c->d_stage);
-    if (c->d_status) cudaFree(c->d_status);
-    if (c->d_fix) cudaFree(c->d_fix);
-    if (c->d_ctl) cudaFree(c->d_ctl);
-    if (c->d_cmd) cudaFree(c->d_cmd);
-    if (c->d_log) cudaFree(c->d_log);
-    if (c->d_gather) cudaFree(c->d_gather);
+        if (c->state[b]) lsc_dev_free(c->state[b]);
+    if (c->d_stage) lsc_dev_free(c->d_stage);
+    if (c->d_status) lsc_dev_free(c->d_status);
+    if (c->d_fix) lsc_dev_free(c->d_fix);
+    if (c->d_ctl) lsc_dev_free(c->d_ctl);
+    if (c->d_cmd) lsc_dev_free(c->d_cmd);
+    if (c->d_log) lsc_dev_free(c->d_log);
+    if (c->d_gather) lsc_dev_free(c->d_gather);
     if (c->h) cudaFreeHost(c->h);
     if (c->red_event) cudaEventDestroy(c->red_event);
     if (c->max_event) cudaEventDestroy(c->max_event);
     for (auto& g : c->graphs) cudaGraphExecDestroy(g.exec);
     lsc_slot_release(c->cfg.device, 1, c->slot);
-    if (c->d_table) cudaFree(c->d_table);
-    if (c->d_hints) cudaFree(c->d_hints);
+    if (c->d_table) lsc_dev_free(c->d_table);
+    if (c->d_hints) lsc_dev_free(c->d_hints);
     if (c->comm) lsc::comm_destroy(c->comm);
     if (c->halo_event) cudaEventDestroy(c->halo_event);
     if (c->edges_done) cudaEventDestroy(c->edges_done);
@@ -681,7 +681,7 @@ int lsc_euler_set_eos_table(lsc_euler_ctx* c, const double* densities, const dou
     for (auto& g : c->graphs) cudaGraphExecDestroy(g.exec);  // captured steps hold the old table pointers
     c->graphs.clear();
     if (!densities) {  // back to the ideal gas of S / G
-        if (c->d_table) cudaFree(c->d_table);
+        if (c->d_table) lsc_dev_free(c->d_table);
         c->d_table = nullptr;
         c->h_table.clear();
         return LSC_OK;
@@ -700,7 +700,7 @@ int lsc_euler_set_eos_table(lsc_euler_ctx* c, const double* densities, const dou
     std::memcpy(t + TAB_N, pressures, TAB_N * sizeof(double));
     std::memcpy(t + 2 * TAB_N, sound_speeds, TAB_N * TAB_N * sizeof(double));
     std::memcpy(t + 2 * TAB_N + TAB_N * TAB_N, energies, TAB_N * TAB_N * sizeof(double));
-    if (!c->d_table && cudaMalloc(&c->d_table, TAB_DOUBLES * sizeof(double)) != cudaSuccess) {
+    if (!c->d_table && lsc_dev_malloc(&c->d_table, TAB_DOUBLES * sizeof(double)) != cudaSuccess) {
         cudaGetLastError();
         c->d_table = nullptr;
         return lsc_fail(LSC_ENOMEM, "device allocation of the EoS table failed");
@@ -709,7 +709,7 @@ int lsc_euler_set_eos_table(lsc_euler_ctx* c, const double* densities, const dou
     c->table_monotone = lsc::eos_table_is_monotone(energies);
     if (!c->d_hints) {  // any in-range bracket is a valid starting point: 0 will do
         const size_t bytes = 3 * sizeof(int) * (size_t)lsc::euler_y_block_count(c->g);
-        if (cudaMalloc(&c->d_hints, bytes) != cudaSuccess) {
+        if (lsc_dev_malloc(&c->d_hints, bytes) != cudaSuccess) {
             cudaGetLastError();
             c->d_hints = nullptr;
             return lsc_fail(LSC_ENOMEM, "device allocation of the search hints failed");

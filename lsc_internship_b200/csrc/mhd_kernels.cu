@@ -119,6 +119,9 @@ __device__ __forceinline__ void block_max_to_global(double local, unsigned long 
 #ifndef YS_BJ
 #define YS_BJ 128
 #endif
+#ifndef YS_TMA
+#define YS_TMA 0  // 1: stage the y tile with cp.async.bulk + mbarrier (experiment J1, profiles/r2/experiments)
+#endif
 #ifndef YS_PF_BLOCKS
 #define YS_PF_BLOCKS (148 * YS_MINB)  // y sweep: L2 prefetch distance in blocks = one resident wave (0 = off)
 #endif
@@ -503,9 +506,23 @@ __device__ __forceinline__ bool y_sweep_block(const GridDims& g, const SweepPara
     float inv_run_max = 0.0f;  // 1/R rounded up (R = 0 -> +inf -> every warp evaluates)
     unsigned long long run_bits = 0;
     if (FILTER) run_bits = running_max_bits(status);
+#if YS_TMA
+    // Experiment J1: the tile of BOTH states staged by one bulk copy (TMA, cp.async.bulk + mbarrier) per
+    // state -- in the blocked layout the rows of a tile are one contiguous run of 5-6 row groups -- and kept in the
+    // device layout; threads read their own and their neighbours' uBar from it, only primitives go through sP.
+    constexpr int RAW_GROUPS = (BJ + 2 + 2 * JBLK - 2) / JBLK;  // row groups a tile of BJ+2 rows can touch (6)
+    constexpr int RAW_DOUBLES = RAW_GROUPS * NV * JBLK;
+    __shared__ __align__(128) double rawU[RAW_DOUBLES];  // uBar, device layout
+    __shared__ __align__(128) double rawC[RAW_DOUBLES];  // u^n, device layout; reused for the bottom face states
+    __shared__ double sP[NV][BJ + 2];                    // primitives of u^n; later the interface fluxes
+    __shared__ unsigned long long tile_mbar;
+    double(*sH)[BJ] = reinterpret_cast<double(*)[BJ]>(rawC);  // [NV][BJ]: written after the first barrier
+    static_assert(NV * BJ <= RAW_DOUBLES, "face states must fit the u^n staging buffer");
+#else
     __shared__ double sU[NV][BJ + 2];  // uBar of cells jo-2 .. jo+BJ-1
     __shared__ double sP[NV][BJ + 2];  // primitives of u^n there; later the interface fluxes
     __shared__ double sH[NV][BJ];      // bottom face state of each thread's cell
+#endif
 
     const int tid = threadIdx.x;
     const int i = 2 + by;
@@ -532,6 +549,112 @@ __device__ __forceinline__ bool y_sweep_block(const GridDims& g, const SweepPara
     const int bc = p.bc_lo;      // the reference uses one y boundary type for both ends
     D dv;
 
+#if YS_TMA
+    const int raw_g0 = (JOFF + jo - 2) >> 5;  // first row group of the tile
+    auto ridx = [&](const int t) -> int {      // tile entry t (row jo-2+t) in the staged device layout
+        const int jj = JOFF + jo - 2 + t;
+        return ((jj >> 5) - raw_g0) * (NV * JBLK) + (jj & (JBLK - 1));
+    };
+    const bool whole_tile_interior = (jo - 2 >= 2) && (jo + BJ - 1 <= g.ny + 1);  // block-uniform
+    if (whole_tile_interior) {
+        const unsigned mbar = (unsigned)__cvta_generic_to_shared(&tile_mbar);
+        // thread 0 alone sets the barrier up, issues the two copies and waits for them; the block barrier behind it
+        // hands the staged tile to everyone else (YS_TMA == 2: every thread waits on the mbarrier itself, which
+        // costs one more block barrier to publish its initialisation)
+        if (tid == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+#if YS_TMA == 2
+        __syncthreads();
+#endif
+        if (tid == 0) {
+            const int g1 = (JOFF + jo + BJ - 1) >> 5;
+            const unsigned bytes = (unsigned)(g1 - raw_g0 + 1) * (NV * JBLK * 8);
+            const size_t off = (size_t)i * mhd_column_doubles(g) + (size_t)raw_g0 * (NV * JBLK);
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(2 * bytes) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                             (unsigned)__cvta_generic_to_shared(rawU)),
+                         "l"(ubar + off), "r"(bytes), "r"(mbar)
+                         : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                             (unsigned)__cvta_generic_to_shared(rawC)),
+                         "l"(cur + off), "r"(bytes), "r"(mbar)
+                         : "memory");
+        }
+#if YS_TMA == 2
+        const bool waits = true;
+#else
+        const bool waits = (tid == 0);
+#endif
+        if (waits)
+            asm volatile(
+                "{\n\t.reg .pred p;\n\t"
+                "WAIT_TILE:\n\t"
+                "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n\t"
+                "@!p bra WAIT_TILE;\n\t}" ::"r"(mbar)
+                : "memory");
+#if YS_TMA != 2
+        __syncthreads();
+#endif
+    } else {
+        // a tile that reaches into the ghost rows (first / last blocks of a column): per-thread loads through the
+        // boundary map, stored at the entry's place in the same staged layout
+        auto fill = [&](const int t) {
+            const int jt = jo - 2 + t;
+            if (jt > g.ny + 3) return;
+            bool flip = false;
+            int js = jt;
+            if (jt < 2 || jt > g.ny + 1) {
+                if (NONPER) js = map_row(jt, g.ny, bc, flip);
+                else js = (jt < 2) ? jt + g.ny : jt - g.ny;
+            }
+            const size_t idx = mhd_index(g, i, js);
+            double qu[NV], q[NV];
+            load_cell(ubar, idx, qu);
+            load_cell(cur, idx, q);
+            if (flip) {
+                qu[2] = -qu[2]; qu[6] = -qu[6];
+                q[2] = -q[2];   q[6] = -q[6];
+            }
+            const int r = ridx(t);
+#pragma unroll
+            for (int k = 0; k < NV; ++k) {
+                rawU[r + k * JBLK] = qu[k];
+                rawC[r + k * JBLK] = q[k];
+            }
+        };
+        fill(tid + 1);
+        if (tid < 2) fill(tid == 0 ? 0 : BJ + 1);
+        __syncthreads();
+    }
+    double ub[NV], p0[NV];
+    {
+        const int r = ridx(tid + 1);
+        double q[NV];
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+            ub[k] = rawU[r + k * JBLK];
+            q[k] = rawC[r + k * JBLK];
+        }
+        c2p_full(dv, q, p.gm1, p0);
+#pragma unroll
+        for (int k = 0; k < NV; ++k) sP[k][tid + 1] = p0[k];
+        if (tid < 2) {  // the two end entries' primitives
+            const int te = (tid == 0) ? 0 : BJ + 1;
+            if (jo - 2 + te <= g.ny + 3) {
+                const int re = ridx(te);
+                double qe[NV], ve[NV];
+#pragma unroll
+                for (int k = 0; k < NV; ++k) qe[k] = rawC[re + k * JBLK];
+                c2p_full(dv, qe, p.gm1, ve);
+#pragma unroll
+                for (int k = 0; k < NV; ++k) sP[k][te] = ve[k];
+            }
+        }
+    }
+#define SU_AT(k, t) rawU[ridx(t) + (k) * JBLK]
+#else
     // Tile of BJ+2 cells (rows jo-2 .. jo+BJ-1): uBar and the primitives of u^n go to shared memory for the
     // neighbours.  A thread fills the tile entry of its OWN cell (t = tid+1) and keeps those 18 values in
     // registers; the two end entries are an extra pass of threads 0 and 1.
@@ -586,6 +709,8 @@ __device__ __forceinline__ bool y_sweep_block(const GridDims& g, const SweepPara
         if (have_o) tile_put(tid + 1, flip_o, ub, qo, p0);
         if (have_e) tile_put(te, flip_e, ue, qe, ve);
     }
+#define SU_AT(k, t) sU[k][t]
+#endif
     __syncthreads();
     // loaded first thing, converted behind the tile loads: a warp that converts right behind the load sits out an L2
     // round trip before it has issued its tile loads
@@ -637,7 +762,7 @@ __device__ __forceinline__ bool y_sweep_block(const GridDims& g, const SweepPara
             for (int k = 0; k < NV; ++k) ratio[k] = limiter_ratio_k(dv, k, sP[k][t - 1], p0[k], sP[k][t + 1]);
 #pragma unroll
             for (int k = 0; k < NV; ++k)
-                reconstruct_with_ratio(dv, ratio[k], sU[k][t - 1], ub[k], sU[k][t + 1], hB[k], hT[k]);
+                reconstruct_with_ratio(dv, ratio[k], SU_AT(k, t - 1), ub[k], SU_AT(k, t + 1), hB[k], hT[k]);
             predictor<1>(dv, hB, hT, p.gm1, p.ch2, p.hdtdh);
             if (nonper && c == 3) {
 #pragma unroll

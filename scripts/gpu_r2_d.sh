@@ -6,7 +6,7 @@ TR="python -m torch.distributed.run --nnodes=1 --master-addr 127.0.0.1"
 nvidia-smi --query-gpu=index,name,clocks.sm,power.draw --format=csv,noheader > gpurun_out/d_smi.txt
 run() { name=$1; shift; timeout 600 "$@" > gpurun_out/$name.json 2> gpurun_out/$name.err; echo "$name exit $?"; cut -c1-330 gpurun_out/$name.json; grep -o '"state_hash": "[0-9a-f]*"' gpurun_out/$name.json; }
 run d_bench_n8 $TR --nproc-per-node 8 --master-port 29501 bench.py --gpus 8 --steps 20 --warmup 3
-run d_bench_n8_even $TR --nproc-per-node 8 --master-port 29502 bench.py --gpus 8 --steps 20 --warmup 3 --no-balance
+run d_bench_n8_even $TR --nproc-per-node 8 --master-port 29502 bench.py --gpus 8 --steps 20 --warmup 3 
 ( cd /tmp && timeout 600 $GRAFT_REPO_ROOT/drivers/_bin/muscl_new --problem ot --nx 16384 --ny 16384 --y0 0 --bcy periodic --steps 23 --gpus 8 --no-dat --quiet --time ) > gpurun_out/d_driver_gpus8.log 2>&1; echo "driver exit $?"; cat gpurun_out/d_driver_gpus8.log
 timeout 600 $TR --nproc-per-node 8 --master-port 29503 scripts/check_nccl_invariance.py > gpurun_out/d_nccl_invariance_n8.log 2>&1; tail -2 gpurun_out/d_nccl_invariance_n8.log
 timeout 900 python -m pytest tests/test_mhd_gpu.py -m gpu -q -k "nccl or same_program or group_run or slab" > gpurun_out/d_pytest_multi.log 2>&1; tail -3 gpurun_out/d_pytest_multi.log
