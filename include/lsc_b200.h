@@ -225,7 +225,8 @@ int lsc_mhd_kat_cfl_bound(int device, long n, const double* U, double gamma, dou
  * differ bitwise from the compiler's IEEE `/` (must be 0) and pairs the guard flagged for the slow path.
  * mode 0: solver-range operands, 1: arbitrary bit patterns, 2: half-ulp / all-ones-mantissa adversaries,
  * 3: tiny / denormal / zero dividends.  mode + 10: the same for the branching policy (BranchDiv), which never
- * flags -- all of its quotients must equal IEEE. */
+ * flags -- all of its quotients must equal IEEE.  mode + 20 (modes 0-2): the guarded branch-free square root
+ * FastDiv::sqrt against sqrt() -- solver-range operands, arbitrary bit patterns, perfect squares +- 1 ulp. */
 int lsc_kat_division(int device, unsigned long long seed, int mode, long nblocks, int per_thread,
                      unsigned long long* mismatches, unsigned long long* flagged);
 

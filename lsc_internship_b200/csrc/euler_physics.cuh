@@ -5,6 +5,9 @@
 // so where the reference adds such a product the pair is issued as one explicit FMA (escaled_add; the argument
 // is the one in the header of mhd_physics.cuh).
 #pragma once
+#ifndef EULER_BRANCHFREE_XI
+#define EULER_BRANCHFREE_XI 0
+#endif
 #include <cuda_runtime.h>
 
 #include "fp64_div.cuh"
@@ -263,6 +266,15 @@ __device__ __forceinline__ void euler_reconstruct1(D& dv, double um, double u0, 
     const double r = dv.div(dMinus, dPlus + 1e-8);
     const double Delta = cm * dMinus + cp * dPlus;
     double xi;
+#if EULER_BRANCHFREE_XI
+    {
+        // no branch around the quotient: it is formed for every cell, with r replaced by 1 where the reference does
+        // not look at it (r <= 1; a NaN r lands in the last case either way and yields fmin(1, NaN) = 1 = fmin(1, 2/2))
+        const double rs = (r > 1) ? r : 1.0;
+        const double q = fmin(1.0, dv.div_pos(2.0, 1 + rs));
+        xi = (r <= 0) ? 0.0 : ((r <= 1) ? r : q);
+    }
+#else
     if (r <= 0) {
         xi = 0;
     } else if (r <= 1) {
@@ -270,6 +282,7 @@ __device__ __forceinline__ void euler_reconstruct1(D& dv, double um, double u0, 
     } else {
         xi = fmin(1.0, dv.div_pos(2.0, 1 + r));  // r > 1 (or NaN): dividend 2, divisor > 2
     }
+#endif
     const double T = xi * Delta;  // 0.5*xi*Delta = 0.5*fl(xi*Delta) exactly
     lo = escaled_add(-0.5, T, u0);
     hi = escaled_add(0.5, T, u0);

@@ -113,6 +113,38 @@ __global__ void kat_div_kernel(unsigned long long seed, int mode, int per_thread
     atomicAdd(flagged, flg);
 }
 
+// FastDiv::sqrt against sqrt(): mode 0 solver-range positive operands, 1 arbitrary bit patterns (negative, NaN, inf,
+// subnormal: must be flagged, never wrong), 2 perfect squares and their neighbours (exact / half-ulp cases)
+__global__ void kat_sqrt_kernel(unsigned long long seed, int mode, int per_thread, unsigned long long* mismatches,
+                                unsigned long long* flagged) {
+    const unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long bad = 0, flg = 0;
+    for (int it = 0; it < per_thread; ++it) {
+        const unsigned long long ra = mix64(seed + (t * per_thread + it));
+        double a;
+        if (mode == 1) {
+            a = __longlong_as_double((long long)ra);
+        } else {
+            const unsigned long long ea = 1023 - 60 + (ra >> 52) % 121;
+            a = __longlong_as_double((long long)((ea << 52) | (ra & 0xfffffffffffffull)));
+            if (mode == 2) {
+                const double k = (double)(1 + (ra & 0x3ffffff));  // k*k is exact (52 bits)
+                a = __longlong_as_double(__double_as_longlong(k * k) + (long long)((ra >> 40) % 3) - 1);
+            }
+        }
+        FastDiv dv;
+        const double q = dv.sqrt(a);
+        const double ref = sqrt(a);
+        if (dv.bad()) {
+            ++flg;
+        } else if (__double_as_longlong(q) != __double_as_longlong(ref) && !(q != q && ref != ref)) {
+            ++bad;
+        }
+    }
+    atomicAdd(mismatches, bad);
+    atomicAdd(flagged, flg);
+}
+
 // exact signal speed (IEEE division) and the fp32 upper bound of speed/run_max; out[2t] = exact, out[2t+1] = bound
 __global__ void kat_cfl_bound_kernel(long n, const double* __restrict__ U, double gamma, double run_max,
                                      double* __restrict__ out) {
@@ -171,7 +203,9 @@ extern "C" int lsc_kat_division(int device, unsigned long long seed, int mode, l
     unsigned long long* d = nullptr;
     if (cudaMalloc(&d, 16) != cudaSuccess) return LSC_ENOMEM;
     cudaMemset(d, 0, 16);
-    if (mode >= 10)
+    if (mode >= 20)
+        lsc::kat_sqrt_kernel<<<(unsigned)nblocks, 256>>>(seed, mode - 20, per_thread, d, d + 1);
+    else if (mode >= 10)
         lsc::kat_div_kernel<lsc::BranchDiv><<<(unsigned)nblocks, 256>>>(seed, mode - 10, per_thread, d, d + 1);
     else
         lsc::kat_div_kernel<lsc::FastDiv><<<(unsigned)nblocks, 256>>>(seed, mode, per_thread, d, d + 1);

@@ -253,7 +253,11 @@ __device__ __forceinline__ bool x_sweep_block(const GridDims& g, const SweepPara
 #pragma unroll
             for (int k = 0; k < NV; ++k) ratio[k] = limiter_ratio_k(dv, k, PM[k], P0[k], Pp[k]);
 #pragma unroll
-            for (int k = 0; k < NV; ++k) reconstruct_with_ratio(dv, ratio[k], uM[k], u0[k], uP[k], hL[k], hR[k]);
+            for (int k = 0; k < NV; ++k) {
+                // v_z / B_z keep the branch: identically zero in planar problems, where it skips the quotient for good
+                if (k == 3 || k == 7) reconstruct_with_ratio<D, false>(dv, ratio[k], uM[k], u0[k], uP[k], hL[k], hR[k]);
+                else reconstruct_with_ratio<D, true>(dv, ratio[k], uM[k], u0[k], uP[k], hL[k], hR[k]);
+            }
             predictor<0>(dv, hL, hR, p.gm1, p.ch2, p.hdtdh);
         }
         double F[NV];
@@ -761,8 +765,12 @@ __device__ __forceinline__ bool y_sweep_block(const GridDims& g, const SweepPara
 #pragma unroll
             for (int k = 0; k < NV; ++k) ratio[k] = limiter_ratio_k(dv, k, sP[k][t - 1], p0[k], sP[k][t + 1]);
 #pragma unroll
-            for (int k = 0; k < NV; ++k)
-                reconstruct_with_ratio(dv, ratio[k], SU_AT(k, t - 1), ub[k], SU_AT(k, t + 1), hB[k], hT[k]);
+            for (int k = 0; k < NV; ++k) {
+                if (k == 3 || k == 7)
+                    reconstruct_with_ratio<D, false>(dv, ratio[k], SU_AT(k, t - 1), ub[k], SU_AT(k, t + 1), hB[k], hT[k]);
+                else
+                    reconstruct_with_ratio<D, true>(dv, ratio[k], SU_AT(k, t - 1), ub[k], SU_AT(k, t + 1), hB[k], hT[k]);
+            }
             predictor<1>(dv, hB, hT, p.gm1, p.ch2, p.hdtdh);
             if (nonper && c == 3) {
 #pragma unroll

@@ -26,6 +26,15 @@
 #include "fp64_div.cuh"
 #include "mhd_kernels.cuh"
 
+// Square roots of the HLLC wave speeds: the policy's branch-free guarded sequence (fp64_div.cuh: FastDiv::sqrt) in
+// the x sweep, plain sqrt() in the y sweep.  A/B on one B200, OT 8192^2, same state hash: x 4.35 -> 4.28 ms with
+// it, y 4.61 -> 4.62 ms (the y sweep sits at 127 registers; the extra live accumulator updates cost it what the
+// removed branches gain) -- so each sweep gets what is faster for it.  MHD_GUARDED_SQRT: 0 never, 1 x only, 2 both.
+#ifndef MHD_GUARDED_SQRT
+#define MHD_GUARDED_SQRT 1
+#endif
+#define MHD_SQRT(DIR, dv, x) (((MHD_GUARDED_SQRT == 2) || (MHD_GUARDED_SQRT == 1 && (DIR) == 0)) ? (dv).sqrt(x) : sqrt(x))
+
 namespace lsc {
 
 // fl(c + k*w) for k = +-0.5, +-0.25, +-4: the exact product k*w and the addition's single rounding
@@ -140,12 +149,24 @@ __device__ __forceinline__ double limiter_ratio_k(D& dv, int k, double pm, doubl
     return (k == 3 || k == 7) ? limiter_ratio_zskip(dv, pm, p0, pp) : limiter_ratio(dv, pm, p0, pp);
 }
 
-template <class D>
+#ifndef MHD_BRANCHFREE_XI
+#define MHD_BRANCHFREE_XI 1
+#endif
+template <class D, bool BRANCHFREE = false>
 __device__ __forceinline__ void reconstruct_with_ratio(D& dv, double r, double um, double u0, double up,
                                                        double& lo, double& hi) {
     const double dPlus = up - u0;
     const double dMinus = u0 - um;
     double xi;
+#if MHD_BRANCHFREE_XI
+    if (BRANCHFREE) {
+        // no branch around the second quotient: r <= 0 is replaced by r = +0, for which 2r/(1+r) = 0/1 = +0 = the
+        // reference's xi (NaN r stays NaN: NaN <= 0 is false).  The nine quotients of a cell then are nine
+        // independent Newton chains in one straight-line region instead of nine branch regions.
+        const double rs = (r <= 0) ? 0.0 : r;
+        xi = dv.div_pos0((rs <= 1.0) ? 2.0 * rs : 2.0, 1 + rs);
+    } else
+#endif
     if (r <= 0) {
         xi = 0;
     } else {
@@ -183,12 +204,12 @@ __device__ __forceinline__ void predictor(D& dv, double (&lo)[NV], double (&hi)[
 
 // fast magnetosonic speed squared along DIR.  speedsx/speedsy MUSCL_NEW.cpp:140-165,
 // :197-222 -- evaluated on the ORIGINAL state (the reference ignores its B?Tilde argument).
-template <class D>
+template <int DIR, class D>
 __device__ __forceinline__ double fast_speed_sq(D& dv, const Rcp& irho, double p, double B2, double Bn, double gamma) {
     const double cs2 = dv.div(gamma * p, irho);
     const double t = cs2 + dv.div(B2, irho);
     // 4.0*cs2*Bn*Bn/rho = 4*fl(fl(fl(cs2*Bn)*Bn)/rho) exactly
-    return 0.5 * (t + sqrt(scaled_add(-4.0, dv.div(cs2 * Bn * Bn, irho), t * t)));
+    return 0.5 * (t + MHD_SQRT(DIR, dv, scaled_add(-4.0, dv.div(cs2 * Bn * Bn, irho), t * t)));
 }
 
 // Second half of hllc_flux for the side the HLLC branch selects (LEFT: flux built from the left state, regions
@@ -319,8 +340,8 @@ __device__ __forceinline__ void hllc_flux(D& dv, const double (&L)[NV], const do
     const double B2R = R[5] * R[5] + R[6] * R[6] + R[7] * R[7];
 
     // ---- wave speeds (:178-192 / :235-250)
-    const double cfL = sqrt(fast_speed_sq(dv, qL.irho, qL.p, B2L, L[N], gamma));
-    const double cfR = sqrt(fast_speed_sq(dv, qR.irho, qR.p, B2R, R[N], gamma));
+    const double cfL = MHD_SQRT(DIR, dv, fast_speed_sq<DIR>(dv, qL.irho, qL.p, B2L, L[N], gamma));
+    const double cfR = MHD_SQRT(DIR, dv, fast_speed_sq<DIR>(dv, qR.irho, qR.p, B2R, R[N], gamma));
     const double cmax = std_max(cfL, cfR);
     const double sL = std_min(vnL, vnR) - cmax;
     const double sR = std_max(vnL, vnR) + cmax;

@@ -603,3 +603,19 @@ def test_uneven_slabs_do_not_change_a_bit():
     g.close()
     with pytest.raises(lsc.LscError):
         lsc.MusclNew(nx, ny, 0, 1, 0, 1, bc_x="periodic", bc_y="periodic", problem="ot", rank=0, nranks=3, slab=(5, 10))
+
+
+@pytest.mark.parametrize("mode", [20, 21, 22])
+def test_custom_sqrt_is_ieee(mode):
+    """FastDiv::sqrt (csrc/fp64_div.cuh: nvcc's fast-path sequence without its range-check branch, operands outside
+    the guarded window flagged for the IEEE recompute) against sqrt() on 2^31 operands per mode: solver-range values,
+    arbitrary bit patterns (negative / NaN / inf / subnormal must be flagged, never wrong), perfect squares +- 1 ulp."""
+    import ctypes
+    bad, flagged = ctypes.c_ulonglong(), ctypes.c_ulonglong()
+    rc = lsc.lib().lsc_kat_division(0, 0x5157 + mode, mode, 1 << 15, 256, ctypes.byref(bad), ctypes.byref(flagged))
+    assert rc == 0
+    assert bad.value == 0, f"{bad.value} square roots differ from sqrt()"
+    if mode == 21:
+        assert flagged.value > (1 << 30)      # half the patterns are negative, many more out of the window
+    else:
+        assert flagged.value == 0
