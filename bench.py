@@ -40,7 +40,7 @@ B_ALG = 432.0          # algorithmic bytes per cell-update (BASELINE.md section 
 B_ALG_X = 216.0        # x sweep: read u^n 72 + read u^{n-1} 72 + write uBar 72
 B_ALG_Y = 216.0        # y sweep: read uBar 72 + read u^n 72 + write u^{n+1} 72
 NOMINAL_HBM_GBS = 8000.0
-TRAFFIC_FILE = "r1_v5_traffic.json"  # ncu --set full dram bytes per cell of each sweep (profiles/)
+TRAFFIC_FILE = "r2/traffic.json"  # ncu --set full dram bytes per cell of each sweep (profiles/)
 
 
 def measured_peaks():

@@ -38,13 +38,26 @@ def test_reference_arm_other_ranks_exit_quietly():
 
 
 def test_files_named_by_the_cuda_arm_exist():
-    """The roofline block cites a committed ncu traffic file and a summary: both must be in profiles/."""
+    """The roofline block cites a committed ncu traffic file: it must be in profiles/ and say what bench.py reads."""
     src = open(os.path.join(ROOT, "bench.py")).read()
-    names = set(re.findall(r"r1_v\d+_[a-z_0-9]+\.(?:json|md)", src))
-    assert names, "bench.py no longer names its profile files"
-    for n in names:
-        assert os.path.exists(os.path.join(ROOT, "profiles", n)), n
-    tj = json.load(open(os.path.join(ROOT, "profiles", sorted(n for n in names if n.endswith("traffic.json"))[-1])))
+    m = re.search(r'TRAFFIC_FILE = "([^"]+)"', src)
+    assert m, "bench.py no longer names its traffic file"
+    path = os.path.join(ROOT, "profiles", m.group(1))
+    assert os.path.exists(path), path
+    tj = json.load(open(path))
     for k in ("x_sweep_kernel", "y_sweep_kernel"):
         # DRAM traffic of a sweep stays within a few per cent of its 216 algorithmic bytes per cell
         assert 200.0 < tj[k]["bytes_per_cell"] < 240.0
+    for k, alg in (("euler_x_sweep_kernel", 64.0), ("euler_y_sweep_kernel", 96.0)):
+        assert 0.95 * alg < tj[k]["bytes_per_cell"] < 1.15 * alg
+    assert os.path.exists(os.path.join(ROOT, "profiles", "r2", "ncu_mhd_sweeps_ot4096.txt"))
+
+
+def test_workloads_and_reference_arm_agree_on_names():
+    """every workload of the CUDA arm has a reference program behind --impl reference"""
+    sys.path.insert(0, ROOT)
+    import importlib
+    bench = importlib.import_module("bench")
+    for w, d in bench.WORKLOADS.items():
+        assert d["ref_exe"] in ("muscl_ref", "gslic_ref", "tabeos_ref")
+        assert d["b_alg"] == d["b_x"] + d["b_y"]
