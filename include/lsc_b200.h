@@ -331,6 +331,32 @@ int lsc_euler_set_profiling(lsc_euler_ctx* ctx, int enabled);
 int lsc_euler_set_overlap(lsc_euler_ctx* ctx, int enabled);   /* as lsc_mhd_set_overlap: 0 serial, 1 default, 2 always */
 int lsc_euler_kernel_times(lsc_euler_ctx* ctx, double ms[2], long launches[2]);
 
+/* ------------------------------------------------------------------------------------------------
+ * First-order sibling of the MHD path (H = MHD_codes/HLLC_MHD_2D.cpp): dimensionally split
+ * Godunov update with the HLLC flux and mixed GLM cleaning, ONE ghost cell, periodic in x and y, Orszag-Tang.
+ * Host arrays are H's: [(nx+2)][(ny+2)][9].  One step = ComputeTimeStep (H:71-120, over i in [1,nx-1], j in [1,ny-1])
+ * -> boundary fill -> x update (H:739-755) -> y update (H:757-771) -> psi damping (H:776-780).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct lsc_hllc2d_config {
+    int nx, ny;            /* H:616-617 */
+    double x0, x1, y0, y1; /* H:618-621 */
+    double gamma;          /* H:625 */
+    double cfl;            /* H:624 (C = 0.75 as committed) */
+    int device;
+} lsc_hllc2d_config;
+typedef struct lsc_hllc2d_ctx lsc_hllc2d_ctx;
+int lsc_hllc2d_create(const lsc_hllc2d_config* cfg, lsc_hllc2d_ctx** out);
+int lsc_hllc2d_destroy(lsc_hllc2d_ctx* ctx);
+int lsc_hllc2d_initial_condition(const lsc_hllc2d_config* cfg, double* aos); /* IC loop H:642-721, host libm */
+int lsc_hllc2d_upload(lsc_hllc2d_ctx* ctx, const double* aos);
+int lsc_hllc2d_init_problem(lsc_hllc2d_ctx* ctx);
+int lsc_hllc2d_step(lsc_hllc2d_ctx* ctx, long nsteps);                        /* n passes of H:728-784 */
+/* do { step } while (t < t_stop), H:728-785; log_cb gets the values of the line H:738 ("t= .. dt= .. ch = ..") */
+int lsc_hllc2d_run_until(lsc_hllc2d_ctx* ctx, double t_stop, lsc_mhd_log_cb log_cb, void* user, long* steps_out);
+int lsc_hllc2d_get_scalars(const lsc_hllc2d_ctx* ctx, double* t, double* dt, double* ch, long* step);
+int lsc_hllc2d_download(lsc_hllc2d_ctx* ctx, double* aos);  /* u after the boundary fill behind the loop, H:787 */
+int lsc_hllc2d_write_dat(const lsc_hllc2d_config* cfg, const double* aos, const char* path); /* MHD.dat, H:793-814 */
+
 /* Debug aid (compute-sanitizer substitute): with LSC_GUARD=1 in the environment at create time, every device buffer
  * of a context sits between two 64 KiB guard zones; *corrupted_bytes receives the number of guard bytes a kernel has
  * overwritten so far (0 = no out-of-bounds write), *guarded_buffers (may be NULL) how many buffers are watched. */

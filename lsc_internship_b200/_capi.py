@@ -39,6 +39,14 @@ class MhdConfig(ctypes.Structure):
                 ("slab_i0", ctypes.c_int), ("slab_nx", ctypes.c_int)]
 
 
+class Hllc2dConfig(ctypes.Structure):
+    """struct lsc_hllc2d_config -- the constants of HLLC_MHD_2D.cpp:616-627."""
+    _fields_ = [("nx", ctypes.c_int), ("ny", ctypes.c_int),
+                ("x0", ctypes.c_double), ("x1", ctypes.c_double),
+                ("y0", ctypes.c_double), ("y1", ctypes.c_double),
+                ("gamma", ctypes.c_double), ("cfl", ctypes.c_double), ("device", ctypes.c_int)]
+
+
 class EulerConfig(ctypes.Structure):
     """struct lsc_euler_config -- the constants of SLIC_euler_2d.cpp:529-540."""
     _fields_ = [("nx", ctypes.c_int), ("ny", ctypes.c_int),
@@ -65,7 +73,10 @@ EXPORTS = [
     "lsc_comm_unique_id", "lsc_mhd_comm_init", "lsc_mhd_kat_hllc", "lsc_mhd_kat_fluxdef", "lsc_mhd_kat_cfl_bound", "lsc_mhd_set_arithmetic",
     "lsc_kernel_launch_count", "lsc_mhd_step_timed", "lsc_mhd_set_profiling", "lsc_mhd_kernel_times", "lsc_mhd_comm_times", "lsc_mhd_set_overlap", "lsc_kat_division", "lsc_mhd_ieee_fallback_count", "lsc_mhd_group_step", "lsc_mhd_fill_ghost_ring", "lsc_mhd_state_hash", "lsc_euler_state_hash",
     "lsc_mhd_group_step_timed", "lsc_mhd_group_run_until", "lsc_mhd_loop_stats", "lsc_mhd_group_download",
-    "lsc_guard_check", "lsc_euler_group_run_until", "lsc_euler_group_download", "lsc_euler_loop_stats",
+    "lsc_guard_check", "lsc_euler_group_run_until",
+    "lsc_hllc2d_create", "lsc_hllc2d_destroy", "lsc_hllc2d_initial_condition", "lsc_hllc2d_upload",
+    "lsc_hllc2d_init_problem", "lsc_hllc2d_step", "lsc_hllc2d_run_until", "lsc_hllc2d_get_scalars",
+    "lsc_hllc2d_download", "lsc_hllc2d_write_dat", "lsc_euler_group_download", "lsc_euler_loop_stats",
     "lsc_euler_create", "lsc_euler_destroy", "lsc_euler_initial_condition", "lsc_euler_upload",
     "lsc_euler_init_problem", "lsc_euler_step", "lsc_euler_step_timed", "lsc_euler_run_until",
     "lsc_euler_get_scalars", "lsc_euler_download", "lsc_euler_write_dat", "lsc_euler_ieee_fallback_count",
@@ -142,6 +153,17 @@ def lib():
     L.lsc_euler_group_step.argtypes = [ctypes.POINTER(vp), ctypes.c_int, ctypes.c_long]
     L.lsc_euler_group_run_until.argtypes = [ctypes.POINTER(vp), ctypes.c_int, ctypes.c_double, EULER_LOG_CB, vp,
                                             ctypes.POINTER(ctypes.c_long)]
+    hcfg = ctypes.POINTER(Hllc2dConfig)
+    L.lsc_hllc2d_create.argtypes = [hcfg, ctypes.POINTER(vp)]
+    L.lsc_hllc2d_destroy.argtypes = [vp]
+    L.lsc_hllc2d_initial_condition.argtypes = [hcfg, dp]
+    L.lsc_hllc2d_upload.argtypes = [vp, dp]
+    L.lsc_hllc2d_init_problem.argtypes = [vp]
+    L.lsc_hllc2d_step.argtypes = [vp, ctypes.c_long]
+    L.lsc_hllc2d_run_until.argtypes = [vp, ctypes.c_double, LOG_CB, vp, ctypes.POINTER(ctypes.c_long)]
+    L.lsc_hllc2d_get_scalars.argtypes = [vp, dp, dp, dp, ctypes.POINTER(ctypes.c_long)]
+    L.lsc_hllc2d_download.argtypes = [vp, dp]
+    L.lsc_hllc2d_write_dat.argtypes = [hcfg, dp, ctypes.c_char_p]
     L.lsc_guard_check.argtypes = [ctypes.POINTER(ctypes.c_ulonglong), ctypes.POINTER(ctypes.c_ulonglong)]
     L.lsc_euler_loop_stats.argtypes = [vp, ctypes.POINTER(ctypes.c_long)]
     L.lsc_euler_group_download.argtypes = [ctypes.POINTER(vp), ctypes.c_int, dp]

@@ -209,6 +209,11 @@ def build_all():
         build_tabeos()
     except ImportError:
         pass
+    try:
+        from build_ref_hllc2d import build_hllc2d  # noqa
+        build_hllc2d()
+    except ImportError:
+        pass
     return True
 
 

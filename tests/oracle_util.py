@@ -185,6 +185,9 @@ def run_euler_ref(which, nx, ny, dom, t_stop, cfl, gamma, nsteps, ic=0, cwd=None
 # = density index.  A gas whose adiabatic index drifts from 1.6 (low p) to 1.2 (high p): not an ideal gas (so the
 # lookup is really exercised), e(p) strictly increasing at fixed rho (T's reverse search needs that).
 # ---------------------------------------------------------------------------------------------------------
+import sys  # noqa: E402
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
 from lsc_internship_b200.synthetic_eos import eos_table, write_eos_table  # noqa: E402,F401  (the synthetic table)
 
 
@@ -227,3 +230,19 @@ def parsed_eos_table():
         en = np.array([num(r) for r in rows[514:1014]])
         _TABLE = (dens, pres, sound, en)
     return _TABLE
+
+
+# ---------------------------------------------------------------------------------------------------------
+# First-order HLLC + GLM program (MHD_codes/HLLC_MHD_2D.cpp): the real program built by
+# oracle/build_ref_hllc2d.py.  Arrays carry ONE ghost layer: [(nx+2)][(ny+2)][9].
+# ---------------------------------------------------------------------------------------------------------
+def run_hllc2d_ref(nx, ny, dom, t_stop, cfl, nsteps, cwd=None, writedat=False):
+    """Returns (state after the program's final boundary fill, log[n,3] of (t, dt, ch), stdout, stderr)."""
+    with tempfile.TemporaryDirectory() as td:
+        st, lg = os.path.join(td, "state.bin"), os.path.join(td, "log.bin")
+        cmd = [os.path.join(REF_DIR, "hllc2d_ref"), str(nx), str(ny)] + [repr(float(d)) for d in dom] + \
+              [repr(float(t_stop)), repr(float(cfl)), str(nsteps), "1" if writedat else "0", st, lg]
+        r = subprocess.run(cmd, cwd=cwd or td, check=True, capture_output=True, text=True)
+        u = np.fromfile(st, dtype=np.float64).reshape(nx + 2, ny + 2, 9)
+        log = np.fromfile(lg, dtype=np.float64).reshape(-1, 3)
+    return u, log, r.stdout, r.stderr
