@@ -225,48 +225,77 @@ __device__ __forceinline__ void load9(const Grid& g, const double* __restrict__ 
     for (int k = 0; k < NQ; ++k) q[k] = __ldg(u + at(g, k, i, j));
 }
 
-// one directional update: out = in - dtdh (F_{+1/2} - F_{-1/2}), neighbours by periodic wrap (H:739-771); the y pass
-// also applies the psi damping (H:776-780) and reduces the next step's signal speed over H's range (H:73-74)
-template <int DIR>
-__global__ void __launch_bounds__(128) sweep_kernel(const Grid g, const double* __restrict__ in, double* __restrict__ out,
-                                                    double gamma, double ch, double dtdh, double psi_factor,
-                                                    unsigned long long* __restrict__ status) {
+// x update (H:739-755): uBar = u - (dt/dx)(F_{i+1/2} - F_{i-1/2}).  One thread per row j marches along i over a strip
+// of columns with the previous interface flux and the next cell in registers, so every interface flux is evaluated
+// once (plus one per strip); adjacent threads are adjacent in j, the contiguous axis.  Neighbours by periodic wrap.
+constexpr int H2D_STRIP = 32;
+__global__ void __launch_bounds__(128) x_update_kernel(const Grid g, const double* __restrict__ in,
+                                                       double* __restrict__ out, double gamma, double ch, double dtdh) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    const int i = blockIdx.y;
-    double speed = 0.0;
-    if (j < g.ny) {
-        double um[NQ], u0[NQ], up[NQ], Fm[NQ], Fp[NQ];
-        load9(g, in, i, j, u0);
-        if (DIR == 0) {
-            load9(g, in, i == 0 ? g.nx - 1 : i - 1, j, um);
-            load9(g, in, i == g.nx - 1 ? 0 : i + 1, j, up);
-        } else {
-            load9(g, in, i, j == 0 ? g.ny - 1 : j - 1, um);
-            load9(g, in, i, j == g.ny - 1 ? 0 : j + 1, up);
+    if (j >= g.ny) return;
+    const int ia = blockIdx.y * H2D_STRIP;
+    const int ib = min(ia + H2D_STRIP, g.nx);
+    double um[NQ], u0[NQ], Fm[NQ];
+    load9(g, in, ia == 0 ? g.nx - 1 : ia - 1, j, um);
+    load9(g, in, ia, j, u0);
+    flux_hllc_h<0>(um, u0, gamma, ch, Fm);
+    for (int i = ia; i < ib; ++i) {
+        double up[NQ], Fp[NQ];
+        load9(g, in, i == g.nx - 1 ? 0 : i + 1, j, up);
+        flux_hllc_h<0>(u0, up, gamma, ch, Fp);
+#pragma unroll
+        for (int k = 0; k < NQ; ++k) {
+            out[at(g, k, i, j)] = u0[k] - dtdh * (Fp[k] - Fm[k]);
+            Fm[k] = Fp[k];
+            u0[k] = up[k];
         }
-        flux_hllc_h<DIR>(um, u0, gamma, ch, Fm);
-        flux_hllc_h<DIR>(u0, up, gamma, ch, Fp);
+    }
+}
+
+// y update (H:757-780): u' = uBar - (dt/dy)(F_{j+1/2} - F_{j-1/2}), psi damping, and the next step's signal speed
+// over H's range (H:73-74).  One thread per cell along j; a block of 128 threads evaluates the 128 interface fluxes
+// above its cells (one per thread), passes them down through shared memory and updates 127 cells.
+constexpr int H2D_BJ = 128;
+__global__ void __launch_bounds__(H2D_BJ) y_update_kernel(const Grid g, const double* __restrict__ in,
+                                                          double* __restrict__ out, double gamma, double ch, double dtdh,
+                                                          double psi_factor, unsigned long long* __restrict__ status) {
+    __shared__ double sF[NQ][H2D_BJ];
+    const int i = blockIdx.y;
+    const int t = threadIdx.x;
+    const int c = (int)blockIdx.x * (H2D_BJ - 1) - 1 + t;  // this thread's cell; thread 0 only supplies the flux below cell 1
+    const bool in_range = c < g.ny;                        // (c == -1 is the periodic image ny-1)
+    double u0[NQ], F[NQ];
+    if (in_range) {
+        const int jc = c < 0 ? g.ny - 1 : c;
+        double up[NQ];
+        load9(g, in, i, jc, u0);
+        load9(g, in, i, jc == g.ny - 1 ? 0 : jc + 1, up);
+        flux_hllc_h<1>(u0, up, gamma, ch, F);
+#pragma unroll
+        for (int k = 0; k < NQ; ++k) sF[k][t] = F[k];
+    }
+    __syncthreads();
+    double speed = 0.0;
+    if (in_range && t >= 1) {
         double un[NQ];
 #pragma unroll
         for (int k = 0; k < NQ; ++k) {
-            double v = u0[k] - dtdh * (Fp[k] - Fm[k]);
-            if (DIR == 1 && k == 8) v = v * psi_factor;
+            double v = u0[k] - dtdh * (F[k] - sF[k][t - 1]);
+            if (k == 8) v = v * psi_factor;
             un[k] = v;
-            out[at(g, k, i, j)] = v;
+            out[at(g, k, i, c)] = v;
         }
-        if (DIR == 1 && i < g.nx - 1 && j < g.ny - 1) {  // H:73-74: the last interior row and column are left out
+        if (i < g.nx - 1 && c < g.ny - 1) {  // H:73-74: the last interior row and column are left out
             IeeeDiv dv;
             speed = cfl_speed(dv, un, gamma);  // H:75-109 == M:75-109
         }
     }
-    if (DIR == 1) {
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const double other = __shfl_xor_sync(0xffffffffu, speed, o);
-            speed = (other > speed) ? other : speed;
-        }
-        if ((threadIdx.x & 31) == 0 && speed > 0.0) atomic_max_nonneg(status, speed);
+    for (int o = 16; o > 0; o >>= 1) {
+        const double other = __shfl_xor_sync(0xffffffffu, speed, o);
+        speed = (other > speed) ? other : speed;
     }
+    if ((t & 31) == 0 && speed > 0.0) atomic_max_nonneg(status, speed);
 }
 
 __global__ void max_speed_kernel_h(const Grid g, const double* __restrict__ u, double gamma,
@@ -480,10 +509,11 @@ static int h2d_step_once(lsc_hllc2d_ctx* c) {
     const double psi_factor = std::exp(-1.0 * (0.5 * dt) * ms / 0.18);  // psiUpdate(psi, maxSpeed, 0.5*dt), H:36-39, H:778
     const int bar = (c->cur + 1) % 3, next = (c->cur + 2) % 3;
     LSC_CUDA_TRY(cudaMemsetAsync(c->d_status, 0, sizeof(unsigned long long), c->stream));
-    lsc::h2d::sweep_kernel<0><<<grid_of(c->g), 128, 0, c->stream>>>(c->g, c->u[c->cur], c->u[bar], c->cfg.gamma, ms,
-                                                                     dt / c->dx, 1.0, c->d_status);
-    lsc::h2d::sweep_kernel<1><<<grid_of(c->g), 128, 0, c->stream>>>(c->g, c->u[bar], c->u[next], c->cfg.gamma, ms,
-                                                                     dt / c->dy, psi_factor, c->d_status);
+    const dim3 gx((c->g.ny + 127) / 128, (c->g.nx + lsc::h2d::H2D_STRIP - 1) / lsc::h2d::H2D_STRIP);
+    lsc::h2d::x_update_kernel<<<gx, 128, 0, c->stream>>>(c->g, c->u[c->cur], c->u[bar], c->cfg.gamma, ms, dt / c->dx);
+    const dim3 gy((c->g.ny + lsc::h2d::H2D_BJ - 2) / (lsc::h2d::H2D_BJ - 1), c->g.nx);
+    lsc::h2d::y_update_kernel<<<gy, lsc::h2d::H2D_BJ, 0, c->stream>>>(c->g, c->u[bar], c->u[next], c->cfg.gamma, ms,
+                                                                       dt / c->dy, psi_factor, c->d_status);
     lsc_count_launches(2);
     LSC_CUDA_TRY(cudaGetLastError());
     c->cur = next;

@@ -7,6 +7,6 @@ import time, lsc_internship_b200 as lsc
 for n in (800, 4096):
     s = lsc.HllcMhd2d(n, n); s.init_problem(); s.step(3)
     t0 = time.perf_counter(); s.step(30); dt = time.perf_counter() - t0
-    print(f"hllc2d OT {n}^2: {dt/30*1e3:.3f} ms/step, {n*n*30/dt/1e9:.2f} G cell-updates/s (host-synced loop, 2 flux evaluations per cell and direction)")
+    print(f"hllc2d OT {n}^2: {dt/30*1e3:.3f} ms/step, {n*n*30/dt/1e9:.2f} G cell-updates/s (host-synced loop, one HLLC flux per interface)")
     s.close()
 PY
