@@ -73,11 +73,20 @@ int comm_exchange_halos(Comm* c, const GridDims& g, int bc_x, double* u, cudaStr
     NCCL_TRY(ncclGroupStart(), -1);
     // Posting order matters when left == right (two ranks on a periodic ring): NCCL matches the sends and
     // receives of a pair in order, so "my low columns" must meet the peer's "high ghost" receive.
-    if (left >= 0) NCCL_TRY(ncclSend(u + 2 * col, n, ncclDouble, left, c->nccl, s), -1);
-    if (right >= 0) NCCL_TRY(ncclRecv(u + (size_t)(g.nxl + 2) * col, n, ncclDouble, right, c->nccl, s), -1);
-    if (right >= 0) NCCL_TRY(ncclSend(u + (size_t)g.nxl * col, n, ncclDouble, right, c->nccl, s), -1);
-    if (left >= 0) NCCL_TRY(ncclRecv(u, n, ncclDouble, left, c->nccl, s), -1);
-    NCCL_TRY(ncclGroupEnd(), -1);
+    // A failing call must not leave the group open: remember the first error, close the group, then report.
+    ncclResult_t first = ncclSuccess;
+    auto post = [&](ncclResult_t r) {
+        if (first == ncclSuccess && r != ncclSuccess) first = r;
+    };
+    if (left >= 0) post(ncclSend(u + 2 * col, n, ncclDouble, left, c->nccl, s));
+    if (right >= 0) post(ncclRecv(u + (size_t)(g.nxl + 2) * col, n, ncclDouble, right, c->nccl, s));
+    if (right >= 0) post(ncclSend(u + (size_t)g.nxl * col, n, ncclDouble, right, c->nccl, s));
+    if (left >= 0) post(ncclRecv(u, n, ncclDouble, left, c->nccl, s));
+    post(ncclGroupEnd());
+    if (first != ncclSuccess) {
+        snprintf(g_comm_err, sizeof g_comm_err, "halo exchange: %s", ncclGetErrorString(first));
+        return -1;
+    }
     // end ranks of a non-periodic decomposition: the boundary image of that side (MHD: M:617-622, 4 variables:
     // the Euler map G:203-208)
     for (int side = 0; side < 2; ++side) {

@@ -30,6 +30,9 @@
 // the x sweep, plain sqrt() in the y sweep.  A/B on one B200, OT 8192^2, same state hash: x 4.35 -> 4.28 ms with
 // it, y 4.61 -> 4.62 ms (the y sweep sits at 127 registers; the extra live accumulator updates cost it what the
 // removed branches gain) -- so each sweep gets what is faster for it.  MHD_GUARDED_SQRT: 0 never, 1 x only, 2 both.
+#ifndef MHD_HLL_BRANCHFREE
+#define MHD_HLL_BRANCHFREE 0
+#endif
 #ifndef MHD_GUARDED_SQRT
 #define MHD_GUARDED_SQRT 1
 #endif
@@ -258,6 +261,16 @@ __device__ __forceinline__ void hllc_side(D& dv, const double (&L)[NV], const do
     }
     const Rcp iw = dv.rcp(sR - sL);  // shared by the three quotients over the fan width
     double BtH, BzH;
+#if MHD_HLL_BRANCHFREE
+    {
+        // the two HLL quotients formed unconditionally (subsonic fans take them anyway), the outer cases selected
+        const double qt = dv.div(sR * R[T1] - sL * L[T1] - fT1R + fT1L, iw);
+        const double qz = dv.div(sR * R[7] - sL * L[7] - f7R + f7L, iw);
+        const bool useL = (sL >= 0), useM = !useL && (sL < 0 && sR > 0);
+        BtH = useL ? L[T1] : (useM ? qt : R[T1]);
+        BzH = useL ? L[7] : (useM ? qz : R[7]);
+    }
+#else
     if (sL >= 0) {
         BtH = L[T1]; BzH = L[7];
     } else if (sL < 0 && sR > 0) {
@@ -266,6 +279,7 @@ __device__ __forceinline__ void hllc_side(D& dv, const double (&L)[NV], const do
     } else {
         BtH = R[T1]; BzH = R[7];
     }
+#endif
 
     // ---- star state on the selected side (uStarX / uStarY), normal field = BnT on both sides
     const double BnS = dv.div(sR * BnT - sL * BnT, iw);
