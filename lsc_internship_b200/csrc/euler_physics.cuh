@@ -2,8 +2,9 @@
 // (Euler_codes/SLIC_euler_2d.cpp = S; transmissive variant generaliseSLIC.cpp = G; tabulated-EoS variant
 // MHD_codes/TabEoS.cpp = T).  Bit-faithful: the
 // reference's association, IEEE division (fp64_div.cuh), no FMA contraction.  Multiplications by 0.5 are exact,
-// so where the reference adds such a product the pair is issued as one explicit FMA (escaled_add; the argument
-// is the one in the header of mhd_physics.cuh).
+// so where the reference adds such a product the pair is issued as one explicit FMA (escaled_add; the argument,
+// its guard for tiny operands and the literal forms of the IEEE fix instantiation are those in the header of
+// mhd_physics.cuh).
 #pragma once
 #ifndef EULER_BRANCHFREE_XI
 #define EULER_BRANCHFREE_XI 0
@@ -57,8 +58,13 @@ struct IdealEos {
     }
 
     template <class D>
-    __device__ __forceinline__ double pressure(D&, const double (&x)[NE], const Rcp&, double vx, double vy) const {
+    __device__ __forceinline__ double pressure(D& dv, const double (&x)[NE], const Rcp&, double vx, double vy) const {
         // KE = 0.5*rho*(vx*vx+vy*vy) = 0.5*fl(rho*(...)) exactly; p = (gamma-1)*(E - KE), S:37-38
+        if (literal_scalings<D>::value) {  // S:35-38 as written
+            const double KE = 0.5 * x[0] * (vx * vx + vy * vy);
+            return gm1 * (x[3] - KE);
+        }
+        dv.note_scaled_aux(x[3]);  // exact while the energy the halved term is taken from is not tiny
         return gm1 * escaled_add(-0.5, x[0] * (vx * vx + vy * vy), x[3]);
     }
 
@@ -71,7 +77,10 @@ struct IdealEos {
         const double vy = dv.div(q[2], ir);
         const double speed = sqrt(vx * vx + vy * vy);
         // KE = 0.5*rho*speed*speed = 0.5*fl(fl(rho*speed)*speed) exactly
-        const double p = (gamma - 1.0) * escaled_add(-0.5, rho * speed * speed, q[3]);
+        dv.note_scaled_aux(q[3]);
+        const double p = literal_scalings<D>::value
+                             ? (gamma - 1.0) * (q[3] - 0.5 * rho * speed * speed)  // S:179-180 as written
+                             : (gamma - 1.0) * escaled_add(-0.5, rho * speed * speed, q[3]);
         const double a = sqrt(dv.div(gamma * p, ir));
         return speed + a;
     }
@@ -162,7 +171,10 @@ struct TableEos {
         bracket(dens, rho, 499, hint_d, db, dt, d_bottom, d_top);
         density_ratio = dv.div(rho - d_bottom, d_top - d_bottom);
         if (d_bottom == d_top) density_ratio = 1;
-        const double e = dv.div(escaled_add(-0.5, rho * (vx * vx + vy * vy), x[3]), ir);  // T:288
+        dv.note_scaled_aux(x[3]);
+        const double e = literal_scalings<D>::value
+                             ? dv.div(x[3] - 0.5 * rho * (vx * vx + vy * vy), ir)  // T:288 as written
+                             : dv.div(escaled_add(-0.5, rho * (vx * vx + vy * vy), x[3]), ir);
         // T:291-299: bisection on the density-interpolated energy column (monotone for 0 <= ratio <= 1 when the
         // table passed the host check; outside that range -- extrapolation -- always the reference's bisection).
         // The four entries the warm test reads are the corners of the interpolation cell.
@@ -283,7 +295,13 @@ __device__ __forceinline__ void euler_reconstruct1(D& dv, double um, double u0, 
         xi = fmin(1.0, dv.div_pos(2.0, 1 + r));  // r > 1 (or NaN): dividend 2, divisor > 2
     }
 #endif
+    if (literal_scalings<D>::value) {  // S:281-282 as written
+        lo = u0 - 0.5 * xi * Delta;
+        hi = u0 + 0.5 * xi * Delta;
+        return;
+    }
     const double T = xi * Delta;  // 0.5*xi*Delta = 0.5*fl(xi*Delta) exactly
+    dv.note_scaled(T);
     lo = escaled_add(-0.5, T, u0);
     hi = escaled_add(0.5, T, u0);
 }
@@ -314,11 +332,17 @@ __device__ __forceinline__ void euler_force(D& dv, const double (&a)[NE], const 
     euler_flux<DIR>(dv, a, eos, f1);
     euler_flux<DIR>(dv, b, eos, f2);
 #pragma unroll
-    for (int k = 0; k < NE; ++k) uh[k] = escaled_add(0.5, a[k] + b[k], -(hdtdh * (f2[k] - f1[k])));
+    for (int k = 0; k < NE; ++k) {
+        const double w = a[k] + b[k];
+        dv.note_scaled_aux(w);
+        uh[k] = sadd<D>(0.5, w, -(hdtdh * (f2[k] - f1[k])));
+    }
     euler_flux<DIR>(dv, uh, eos, ri);
 #pragma unroll
     for (int k = 0; k < NE; ++k) {
-        const double lf = escaled_add(0.5, f1[k] + f2[k], hhdt * (a[k] - b[k]));
+        const double w = f1[k] + f2[k];
+        dv.note_scaled_aux(w);
+        const double lf = sadd<D>(0.5, w, hhdt * (a[k] - b[k]));
         F[k] = 0.5 * (lf + ri[k]);
     }
 }

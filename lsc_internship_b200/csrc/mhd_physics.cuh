@@ -16,10 +16,13 @@
 // addition, the pair is issued as ONE explicit __fma_rn with the constant as multiplier (scaled_add below).
 // That is not a contraction of the reference's arithmetic -- the product is exact, the single rounding is the
 // reference's rounding of the sum -- and it removes ~55 of ~815 fp64 instructions per cell and sweep.  The
-// identity needs the scaled intermediate to be normal; a quantity below 2^-1021 that is not an exact zero
-// reaches these expressions only through operands the division guards already flag (fp64_div.cuh: nonzero
-// dividends below 2^-500), and flagged blocks are recomputed by the IeeeDiv instantiation of the same code, in
-// which the identity holds for the same reason.
+// identity needs the scaled intermediate to be normal or an exact zero.  That is guarded, not assumed: the scaled
+// operand of every such fma whose size the state does not bound from below enters the fast division's window
+// accumulator (FastDiv::note_scaled -- a non-zero value below 2^-500 flags the block), and flagged blocks are
+// recomputed by the IeeeDiv instantiation, for which every one of these sites is the reference's LITERAL
+// expression (literal_scalings / sadd in fp64_div.cuh), two roundings and all.
+// tests/test_mhd_gpu.py::test_subnormal_scalings_match_the_reference_literally holds states with u0 == 0 next to
+// subnormal xi*Delta.
 #pragma once
 #include <cuda_runtime.h>
 
@@ -52,6 +55,7 @@ __device__ __forceinline__ double std_max(double a, double b) { return (a < b) ?
 struct Prim {
     double vx, vy, vz, p;
     double kw;  // rho*(vx*vx+vy*vy+vz*vz): twice the kinetic term 0.5*rho*(...) of the pressure expression
+    double vv;  // vx*vx+vy*vy+vz*vz (only the literal IeeeDiv forms read it)
     Rcp irho;  // shared refined reciprocal of the density (fp64_div.cuh)
 };
 
@@ -63,8 +67,14 @@ __device__ __forceinline__ Prim c2p(D& dv, const double (&u)[NV], double gm1) {
     q.vy = dv.div(u[2], q.irho);
     q.vz = dv.div(u[3], q.irho);
     // v4 = (u4 - 0.5*v0*(v.v) - 0.5*(B.B))*(gamma-1), MUSCL_NEW.cpp:29-31: 0.5*v0*(v.v) = 0.5*fl(v0*(v.v)) exactly
-    q.kw = u[0] * (q.vx * q.vx + q.vy * q.vy + q.vz * q.vz);
-    q.p = scaled_add(-0.5, u[5] * u[5] + u[6] * u[6] + u[7] * u[7], scaled_add(-0.5, q.kw, u[4])) * gm1;
+    q.vv = q.vx * q.vx + q.vy * q.vy + q.vz * q.vz;
+    q.kw = u[0] * q.vv;
+    if (literal_scalings<D>::value) {  // the reference's expression as written (MUSCL_NEW.cpp:29-31)
+        q.p = (u[4] - 0.5 * u[0] * q.vv - 0.5 * (u[5] * u[5] + u[6] * u[6] + u[7] * u[7])) * gm1;
+    } else {
+        dv.note_scaled_aux(u[4]);  // the two halved terms are subtracted from the energy: exact while it is not tiny
+        q.p = scaled_add(-0.5, u[5] * u[5] + u[6] * u[6] + u[7] * u[7], scaled_add(-0.5, q.kw, u[4])) * gm1;
+    }
     return q;
 }
 
@@ -78,17 +88,17 @@ __device__ __forceinline__ void c2p_full(D& dv, const double (&u)[NV], double gm
 
 // Physical flux of a conserved state.  DIR 0: FluxDefX MUSCL_NEW.cpp:36-49,
 // DIR 1: FluxDefY MUSCL_NEW.cpp:51-64.  ch2 = ch*ch.
-template <int DIR>
+template <int DIR, class D>
 __device__ __forceinline__ void flux_from_prim(const double (&u)[NV], const Prim& q, double ch2, double (&f)[NV]) {
     const double B2 = u[5] * u[5] + u[6] * u[6] + u[7] * u[7];
     const double vB = q.vx * u[5] + q.vy * u[6] + q.vz * u[7];
     if (DIR == 0) {
         const double rvx = u[0] * q.vx;
         f[0] = u[1];
-        f[1] = scaled_add(0.5, B2, rvx * q.vx + q.p) - u[5] * u[5];
+        f[1] = sadd<D>(0.5, B2, rvx * q.vx + q.p) - u[5] * u[5];
         f[2] = rvx * q.vy - u[5] * u[6];
         f[3] = rvx * q.vz - u[5] * u[7];
-        f[4] = scaled_add(0.5, B2, u[4] + q.p) * q.vx - vB * u[5];
+        f[4] = sadd<D>(0.5, B2, u[4] + q.p) * q.vx - vB * u[5];
         f[5] = u[8];
         f[6] = u[6] * q.vx - u[5] * q.vy;
         f[7] = u[7] * q.vx - u[5] * q.vz;
@@ -98,9 +108,9 @@ __device__ __forceinline__ void flux_from_prim(const double (&u)[NV], const Prim
         const double rvy = u[0] * q.vy;
         f[0] = u[2];
         f[1] = rvx * q.vy - u[5] * u[6];
-        f[2] = scaled_add(0.5, B2, rvy * q.vy + q.p) - u[6] * u[6];
+        f[2] = sadd<D>(0.5, B2, rvy * q.vy + q.p) - u[6] * u[6];
         f[3] = rvy * q.vz - u[6] * u[7];
-        f[4] = scaled_add(0.5, B2, u[4] + q.p) * q.vy - vB * u[6];
+        f[4] = sadd<D>(0.5, B2, u[4] + q.p) * q.vy - vB * u[6];
         f[5] = u[5] * q.vy - u[6] * q.vx;
         f[6] = u[8];
         f[7] = u[7] * q.vy - u[6] * q.vz;
@@ -111,7 +121,7 @@ __device__ __forceinline__ void flux_from_prim(const double (&u)[NV], const Prim
 template <int DIR, class D>
 __device__ __forceinline__ void flux_def(D& dv, const double (&u)[NV], double gm1, double ch2, double (&f)[NV]) {
     const Prim q = c2p(dv, u, gm1);
-    flux_from_prim<DIR>(u, q, ch2, f);
+    flux_from_prim<DIR, D>(u, q, ch2, f);
 }
 
 // Slope-limited linear reconstruction of one component.  MUSCL_NEW.cpp:845-859
@@ -176,8 +186,15 @@ __device__ __forceinline__ void reconstruct_with_ratio(D& dv, double r, double u
         xi = dv.div_pos((r <= 1.0) ? 2.0 * r : 2.0, 1 + r);  // r > 0 (or NaN): 0 < dividend <= 2, divisor >= 1
     }
     // Delta = 0.5*dMinus + 0.5*dPlus = 0.5*S exactly; 0.5*xi*Delta = 0.25*fl(xi*S) exactly (see the header)
+    if (literal_scalings<D>::value) {  // MUSCL_NEW.cpp:856-859 as written
+        const double Delta = 0.5 * dMinus + 0.5 * dPlus;
+        lo = u0 - 0.5 * xi * Delta;
+        hi = u0 + 0.5 * xi * Delta;
+        return;
+    }
     const double S = dMinus + dPlus;
     const double T = xi * S;
+    dv.note_scaled(T);
     lo = scaled_add(-0.25, T, u0);
     hi = scaled_add(0.25, T, u0);
 }
@@ -212,6 +229,8 @@ __device__ __forceinline__ double fast_speed_sq(D& dv, const Rcp& irho, double p
     const double cs2 = dv.div(gamma * p, irho);
     const double t = cs2 + dv.div(B2, irho);
     // 4.0*cs2*Bn*Bn/rho = 4*fl(fl(fl(cs2*Bn)*Bn)/rho) exactly
+    if (literal_scalings<D>::value)  // MUSCL_NEW.cpp:155: t*t - 4.0*cs2*Bn*Bn/rho as written
+        return 0.5 * (t + sqrt(t * t - dv.div(4.0 * cs2 * Bn * Bn, irho)));
     return 0.5 * (t + MHD_SQRT(DIR, dv, scaled_add(-4.0, dv.div(cs2 * Bn * Bn, irho), t * t)));
 }
 
@@ -239,8 +258,11 @@ __device__ __forceinline__ void hllc_side(D& dv, const double (&L)[NV], const do
     double FS[NV];
     {
         Prim q1 = qs;  // S1[0..4] == S[0..4]: same velocities and kinetic term, new magnetic pressure
-        q1.p = scaled_add(-0.5, S1[5] * S1[5] + S1[6] * S1[6] + S1[7] * S1[7], scaled_add(-0.5, qs.kw, S1[4])) * gm1;
-        flux_from_prim<DIR>(S1, q1, ch2, FS);
+        if (literal_scalings<D>::value)
+            q1.p = (S1[4] - 0.5 * S1[0] * qs.vv - 0.5 * (S1[5] * S1[5] + S1[6] * S1[6] + S1[7] * S1[7])) * gm1;
+        else
+            q1.p = scaled_add(-0.5, S1[5] * S1[5] + S1[6] * S1[6] + S1[7] * S1[7], scaled_add(-0.5, qs.kw, S1[4])) * gm1;
+        flux_from_prim<DIR, D>(S1, q1, ch2, FS);
     }
 
     if (!star) {
@@ -288,7 +310,7 @@ __device__ __forceinline__ void hllc_side(D& dv, const double (&L)[NV], const do
     const double vz = qs.vz;
     // B2 with the cleaned normal component, summed in x,y,z order (:335-336 / :420-421)
     const double B2s = (DIR == 0) ? (BnT * BnT + Bt * Bt + Bz * Bz) : (Bt * Bt + BnT * BnT + Bz * Bz);
-    const double pT = scaled_add(0.5, B2s, qs.p);
+    const double pT = sadd<D>(0.5, B2s, qs.p);
     const double pStar = S[0] * (ss - vn) * (qS - vn) + pT - BnT * BnT + BnS * BnS;
     const Rcp is = dv.rcp(ss - qS);  // shared by the four quotients over (s - qStar)
     const double rhoS = dv.div(S[0] * (ss - vn), is);
@@ -343,8 +365,11 @@ __device__ __forceinline__ void hllc_flux(D& dv, const double (&L)[NV], const do
     constexpr int N = (DIR == 0) ? 5 : 6;  // normal field component
     // ---- mixed GLM interface values (:126-127 / :135-136)
     // inv2ch = 1.0/(2.0*ch), halfch = ch/2.0: per-step scalars, divided once on the host
-    const double BnT = scaled_add(0.5, L[N] + R[N], -(inv2ch * (R[8] - L[8])));
-    const double psiT = scaled_add(0.5, L[8] + R[8], -(halfch * (R[N] - L[N])));
+    const double sBn = L[N] + R[N], sPsi = L[8] + R[8];
+    dv.note_scaled_aux(sBn);
+    dv.note_scaled_aux(sPsi);
+    const double BnT = sadd<D>(0.5, sBn, -(inv2ch * (R[8] - L[8])));
+    const double psiT = sadd<D>(0.5, sPsi, -(halfch * (R[N] - L[N])));
 
     // ---- primitives of the ORIGINAL states
     const Prim qL = c2p(dv, L, gm1), qR = c2p(dv, R, gm1);
@@ -359,8 +384,8 @@ __device__ __forceinline__ void hllc_flux(D& dv, const double (&L)[NV], const do
     const double cmax = std_max(cfL, cfR);
     const double sL = std_min(vnL, vnR) - cmax;
     const double sR = std_max(vnL, vnR) + cmax;
-    const double pModL = scaled_add(0.5, B2L, qL.p) - L[N] * L[N];
-    const double pModR = scaled_add(0.5, B2R, qR.p) - R[N] * R[N];
+    const double pModL = sadd<D>(0.5, B2L, qL.p) - L[N] * L[N];
+    const double pModR = sadd<D>(0.5, B2R, qR.p) - R[N] * R[N];
     const double qS = dv.div(R[0] * vnR * (sR - vnR) - L[0] * vnL * (sL - vnL) + pModL - pModR,
                            R[0] * (sR - vnR) - L[0] * (sL - vnL));
 
@@ -386,6 +411,17 @@ __device__ __forceinline__ double cfl_speed(D& dv, const double (&q)[NV], double
     const Rcp irho = dv.rcp(rho);
     const double ux = dv.div(q[1], irho), uy = dv.div(q[2], irho), uz = dv.div(q[3], irho);
     const double B2 = Bx * Bx + By * By + Bz * Bz;
+    dv.note_scaled_aux(q[4]);
+    if (literal_scalings<D>::value) {  // MUSCL_NEW.cpp:85-101 as written
+        const double ke = 0.5 * rho * (ux * ux + uy * uy + uz * uz) + 0.5 * (Bx * Bx + By * By + Bz * Bz);
+        const double pl = (gamma - 1.0) * (q[4] - ke);
+        const double al = sqrt(dv.div(gamma * pl, irho));
+        const double sl = al * al + dv.div(B2, irho);
+        const double cx = sqrt(0.5 * (sl + sqrt(sl * sl - dv.div(4 * al * al * Bx * Bx, irho))));
+        const double cy = sqrt(0.5 * (sl + sqrt(sl * sl - dv.div(4 * al * al * By * By, irho))));
+        const double cz = sqrt(0.5 * (sl + sqrt(sl * sl - dv.div(4 * al * al * Bz * Bz, irho))));
+        return std_max(std_max(fabs(ux) + cx, fabs(uy) + cy), fabs(uz) + cz);
+    }
     // ke = 0.5*rho*(u.u) + 0.5*B2 = 0.5*fl(rho*(u.u) + B2) exactly
     const double p = (gamma - 1.0) * scaled_add(-0.5, rho * (ux * ux + uy * uy + uz * uz) + B2, q[4]);
     const double a = sqrt(dv.div(gamma * p, irho));

@@ -344,6 +344,48 @@ def test_out_of_window_operands_take_the_ieee_path():
 
 
 @gpu
+@pytest.mark.parametrize("scale_exp", [-1074, -575, -568, -560])
+def test_subnormal_scalings_match_the_reference_literally(scale_exp):
+    """0.5*xi*Delta issued as one fma double-rounds once xi*Delta is subnormal.  Momentum patches (both components,
+    so that rho*vx*vy underflows and the tangential momentum keeps its tiny detail through the sweep) of monotone
+    ramps through exact zeros on a gas at rest: at 2^-1074 the momenta themselves are subnormal (and xi*Delta
+    underflows to zero); at 2^-575 .. 2^-560 they are ~1e-160 and xi*Delta ~ dM*Delta*1e8 is a non-zero subnormal
+    (the `+ 1e-8` of S:266 makes the limiter ratio tiny) next to u0 == 0 -- the build before the literal forms
+    fails these three (profiles/r2/subnormal_kat_previous_build.log).  Those blocks are flagged and recomputed with
+    the reference's literal expressions: bit equality with the oracle, which evaluates S:281-282 as written."""
+    import lsc_internship_b200 as lsc
+    nx, ny = 56, 48
+    cfg = euler_cfg(nx, ny, DOM, bc="periodic")
+    u0 = np.zeros((nx + 4, ny + 4, 4))      # gas at rest: the flux differences of rho, E and p vanish exactly, so
+    u0[..., 0] = 1.0                        # the tiny detail of the momenta survives the step
+    u0[..., 3] = 1.0 / 0.4
+    rng = np.random.default_rng(500 - scale_exp)
+
+    def ramps(shape):
+        ri = np.cumsum(rng.integers(1, 1 << 30, shape[0]))
+        rj = np.cumsum(rng.integers(1, 1 << 30, shape[1]))
+        k = ri[:, None] + rj[None, :]
+        k = k - k[shape[0] // 2, shape[1] // 2]
+        k[shape[0] // 2 - 1, :] = 0
+        return np.ldexp(k.astype(np.float64), scale_exp)
+
+    u0[6:26, 5:25, 1] = ramps((20, 20))
+    u0[6:26, 5:25, 2] = -ramps((20, 20))
+    u0[30:50, 20:40, 2] = ramps((20, 20))
+    o = OracleEuler(cfg, u0)
+    s = lsc.SlicEuler2d(nx, ny)
+    s.upload(u0)
+    for n in (1, 1, 2):
+        o.step(n)
+        s.step(n)
+        ref = o.state()[0]
+        assert np.array_equal(bits(s.download()), bits(ref))
+        assert np.count_nonzero((np.abs(ref) < 2.0 ** -500) & (ref != 0)) > 300
+    assert s.ieee_fallback_count() >= 1
+    s.close()
+
+
+@gpu
 @pytest.mark.parametrize("bc,ic,nx,ny", [
     ("periodic", "ot", 96, 64),
     ("transmissive", "cylinder", 70, 130),

@@ -313,6 +313,55 @@ def test_out_of_window_operands_take_the_ieee_path():
     s.close()
 
 
+def tiny_ramps(rng, shape, scale_exp):
+    """30-bit integer ramps times 2^scale_exp (odd mantissas included), monotone along both axes and crossing zero
+    exactly: cells with u0 == 0 between tiny non-zero neighbours, plus a row and a column of exact zeros."""
+    ri = np.cumsum(rng.integers(1, 1 << 30, shape[0]))
+    rj = np.cumsum(rng.integers(1, 1 << 30, shape[1]))
+    k = ri[:, None] + rj[None, :]
+    k = k - k[shape[0] // 2, shape[1] // 2]
+    k[shape[0] // 2 - 1, :] = 0
+    k[:, shape[1] // 2 + 1] = 0
+    return np.ldexp(k.astype(np.float64), scale_exp)
+
+
+@pytest.mark.parametrize("scale_exp", [-1074, -575, -568, -562])
+def test_subnormal_scalings_match_the_reference_literally(scale_exp):
+    """The one-fma exact scalings (0.5*xi*Delta, 0.5*(a+b) ...) double-round once the scaled product is subnormal.
+    A uniform magnetised gas at rest (all flux differences of the normal-sized quantities vanish exactly, so the
+    tiny detail survives the step) carries patches of z momentum, B_z and psi made of tiny ramps through exact
+    zeros.  At 2^-1074 the values themselves are subnormal (and xi*Delta underflows to zero: the `+ 1e-8` of
+    MUSCL_NEW.cpp:847 makes the limiter ratio ~1e8*dMinus); at 2^-575 .. 2^-562 they are ~1e-160 and
+    xi*Delta ~ 2e8*dMinus*Delta is a non-zero subnormal next to u0 == 0.  Those blocks must be flagged and
+    recomputed with the reference's literal expressions: bit equality with the oracle, which evaluates
+    MUSCL_NEW.cpp:856-859 as written, with the tiny values still there to compare.  (The build before the literal
+    forms fails the three non-subnormal-input cases: profiles/r2/subnormal_kat_previous_build.log.)"""
+    nx, ny = 64, 56
+    cfg = mhd_cfg(nx, ny)
+    u0 = np.zeros((nx + 4, ny + 4, 9))
+    u0[..., 0] = 1.0
+    u0[..., 5] = 0.3
+    u0[..., 6] = 0.2
+    u0[..., 4] = 1.0 / (5.0 / 3.0 - 1.0) + 0.5 * (0.3 * 0.3 + 0.2 * 0.2)
+    rng = np.random.default_rng(3000 - scale_exp)
+    u0[6:26, 5:25, 3] = tiny_ramps(rng, (20, 20), scale_exp)
+    u0[30:50, 8:28, 7] = tiny_ramps(rng, (20, 20), scale_exp)
+    u0[10:30, 32:52, 8] = tiny_ramps(rng, (20, 20), scale_exp)
+    u0[40:60, 34:54, 3] = -tiny_ramps(rng, (20, 20), scale_exp)
+    u0[40:60, 34:54, 7] = tiny_ramps(rng, (20, 20), scale_exp)[::-1, :]
+    o = OracleMhd(cfg, u0)
+    s = lsc.MusclNew(nx, ny, 0, 1, 0, 1, bc_x="periodic", bc_y="periodic", problem="ot")
+    s.upload(u0)
+    for n in (1, 1, 2):
+        o.step(n)
+        s.step(n)
+        ref = o.state()[0]
+        assert np.array_equal(bits(s.download()), bits(ref))
+        assert np.count_nonzero((np.abs(ref) < 2.0 ** -500) & (ref != 0)) > 500
+    assert s.ieee_fallback_count() >= 1
+    s.close()
+
+
 @pytest.mark.parametrize("prob,nx,ny,dom,bcx,bcy", [
     ("ot", 96, 64, (0.0, 1.0, 0.0, 1.0), "periodic", "periodic"),
     ("kh", 64, 96, (0.0, 1.0, -1.0, 1.0), "periodic", "reflective"),
