@@ -190,6 +190,17 @@ int lsc_mhd_download(lsc_mhd_ctx* ctx, double* aos);
  * single-context value exactly when every interior bit agrees. */
 int lsc_mhd_state_hash(lsc_mhd_ctx* ctx, unsigned long long* hash);
 
+/* lsc_mhd_state_hash for callers that cannot allocate device memory: same input, same output word, but no
+ * cudaMalloc / cudaFree (nor any other allocating routine) on the call path.  NO COUNTERPART IN THE REFERENCE.
+ * The scratch words (one partial sum per thread block) live in
+ * a file-scope `static __device__` array of 64 KiB + 256 B that every GPU which loads the library holds until exit;
+ * it bounds the slab height: ny <= LSC_STATE_HASH_NOALLOC_MAX_NY, beyond that the call fails with LSC_EINVAL and
+ * says so in lsc_last_error().  All calls on one device share the array: calls that overlap on the GPU (different
+ * contexts on different host threads) race on it and return garbage -- serialise them.  Nothing is carried over
+ * from one call to the next (the result word is cleared at the start of every call). */
+#define LSC_STATE_HASH_NOALLOC_MAX_NY 1048576
+int lsc_mhd_state_hash_noalloc(lsc_mhd_ctx* ctx, unsigned long long* hash);
+
 /* Host helper for callers that assemble a full-grid array from slabs: rebuilds the ghost ring the
  * reference's `u` holds after M:971 (boundary images per cfg->bc_x / bc_y with the reference's loop bounds,
  * the four never-written corner cells zero) from the interior of `aos` [(nx+4)][(ny+4)][9]. */

@@ -71,7 +71,7 @@ EXPORTS = [
     "lsc_mhd_initial_condition", "lsc_mhd_upload", "lsc_mhd_init_problem", "lsc_mhd_step",
     "lsc_mhd_run_until", "lsc_mhd_get_scalars", "lsc_mhd_download", "lsc_mhd_write_dat",
     "lsc_comm_unique_id", "lsc_mhd_comm_init", "lsc_mhd_kat_hllc", "lsc_mhd_kat_fluxdef", "lsc_mhd_kat_cfl_bound", "lsc_mhd_set_arithmetic",
-    "lsc_kernel_launch_count", "lsc_mhd_step_timed", "lsc_mhd_set_profiling", "lsc_mhd_kernel_times", "lsc_mhd_comm_times", "lsc_mhd_set_overlap", "lsc_kat_division", "lsc_mhd_ieee_fallback_count", "lsc_mhd_group_step", "lsc_mhd_fill_ghost_ring", "lsc_mhd_state_hash", "lsc_euler_state_hash",
+    "lsc_kernel_launch_count", "lsc_mhd_step_timed", "lsc_mhd_set_profiling", "lsc_mhd_kernel_times", "lsc_mhd_comm_times", "lsc_mhd_set_overlap", "lsc_kat_division", "lsc_mhd_ieee_fallback_count", "lsc_mhd_group_step", "lsc_mhd_fill_ghost_ring", "lsc_mhd_state_hash", "lsc_mhd_state_hash_noalloc", "lsc_euler_state_hash",
     "lsc_mhd_group_step_timed", "lsc_mhd_group_run_until", "lsc_mhd_loop_stats", "lsc_mhd_group_download",
     "lsc_guard_check", "lsc_euler_group_run_until",
     "lsc_hllc2d_create", "lsc_hllc2d_destroy", "lsc_hllc2d_initial_condition", "lsc_hllc2d_upload",
@@ -183,6 +183,7 @@ def lib():
     L.lsc_euler_kernel_times.argtypes = [vp, dp, ctypes.POINTER(ctypes.c_long)]
     L.lsc_mhd_fill_ghost_ring.argtypes = [ctypes.POINTER(MhdConfig), dp]
     L.lsc_mhd_state_hash.argtypes = [vp, ctypes.POINTER(ctypes.c_ulonglong)]
+    L.lsc_mhd_state_hash_noalloc.argtypes = [vp, ctypes.POINTER(ctypes.c_ulonglong)]
     L.lsc_euler_state_hash.argtypes = [vp, ctypes.POINTER(ctypes.c_ulonglong)]
     L.lsc_mhd_ieee_fallback_count.argtypes = [vp]
     L.lsc_mhd_ieee_fallback_count.restype = ctypes.c_long

@@ -1230,6 +1230,21 @@ int lsc_mhd_state_hash(lsc_mhd_ctx* c, unsigned long long* hash) {
     return LSC_OK;
 }
 
+// No cudaMalloc / cudaFree on this path: the scratch words are a file-scope __device__ array of state_hash.cu.
+int lsc_mhd_state_hash_noalloc(lsc_mhd_ctx* c, unsigned long long* hash) {
+    if (!c || !hash) return fail(LSC_EINVAL, "null argument");
+    static_assert(lsc::STATE_HASH_STATIC_MAX_NY == LSC_STATE_HASH_NOALLOC_MAX_NY, "header and kernel limit differ");
+    if (c->g.ny > lsc::STATE_HASH_STATIC_MAX_NY)
+        return fail(LSC_EINVAL, "lsc_mhd_state_hash_noalloc: ny = %d exceeds the static scratch array's limit of %d rows "
+                                "(LSC_STATE_HASH_NOALLOC_MAX_NY); use lsc_mhd_state_hash", c->g.ny,
+                    lsc::STATE_HASH_STATIC_MAX_NY);
+    if (!c->uploaded) return fail(LSC_ESTATE, "lsc_mhd_state_hash_noalloc before lsc_mhd_upload");
+    CUDA_TRY(cudaSetDevice(c->cfg.device));
+    CUDA_TRY(lsc::state_hash_static(c->cfg.device, c->g, lsc::NV, c->state[c->cur], c->i0, hash, c->stream));
+    lsc_count_launches(2);
+    return LSC_OK;
+}
+
 int lsc_mhd_fill_ghost_ring(const lsc_mhd_config* cfg, double* aos) {
     if (!cfg || !aos) return fail(LSC_EINVAL, "null argument");
     lsc::mhd_fill_ghost_ring(*cfg, aos);

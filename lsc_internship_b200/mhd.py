@@ -106,6 +106,13 @@ class MusclNew:
         check(lib().lsc_mhd_state_hash(self._h, ctypes.byref(h)))
         return h.value
 
+    def state_hash_noalloc(self):
+        """state_hash() without any device allocation on the call path (lsc_mhd_state_hash_noalloc: scratch in a
+        static device array, ny <= 1048576, calls on one device must not overlap)."""
+        h = ctypes.c_ulonglong()
+        check(lib().lsc_mhd_state_hash_noalloc(self._h, ctypes.byref(h)))
+        return h.value
+
     def comm_init(self, unique_id: bytes):
         buf = ctypes.create_string_buffer(unique_id, 128)
         check(lib().lsc_mhd_comm_init(self._h, ctypes.cast(buf, ctypes.c_void_p)))
