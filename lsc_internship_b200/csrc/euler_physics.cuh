@@ -20,6 +20,26 @@ constexpr int NE = 4;  // rho, rho*vx, rho*vy, E  (S:10-17)
 // fl(c + k*w) for k = +-0.5: the exact product and the addition's single rounding
 __device__ __forceinline__ double escaled_add(double k, double w, double c) { return __fma_rn(k, w, c); }
 
+// Guards on the one-fma scalings other than the limiter product xi*Delta (which is always guarded:
+// euler_reconstruct1).  Off by default, because for this scheme they are redundant: a fused form can differ from the
+// reference's two roundings only if the scaled operand w is a non-zero value below 2^-1021 AND the addend is below
+// ~2^-960 as well.  (a) E - 0.5*rho*(v.v): w that small means |rho*v| < 2^-510*sqrt(rho), and every momentum
+// component of every state the pressure is taken of has just been a DIVIDEND of v = m/rho in the same policy object
+// -- a non-zero dividend below 2^-500 flags the block.  (b) 0.5*(a+b) and 0.5*(f1+f2) in the FORCE flux: density and
+// energy sums are of normal size; a momentum (flux) sum or the difference a-b in the addend that small needs both
+// face momenta below 2^-900 and one of them non-zero, and both are dividends in euler_flux(a) / euler_flux(b).
+// What is left are states with rho > 2^20 together with a total energy below 2^-960, which no run reaches.
+// A/B on one B200, cylinder 4096^2: 1.152 ms/step without, 1.181 with (profiles/r2/ab_scaled_guards_level1.log).
+#ifndef EULER_AUX_SCALED_GUARDS
+#define EULER_AUX_SCALED_GUARDS 0
+#endif
+template <class D>
+__device__ __forceinline__ void euler_note_aux(D& dv, double w) {
+#if EULER_AUX_SCALED_GUARDS
+    dv.note_scaled_aux(w);
+#endif
+}
+
 // ---- equation of state policies ---------------------------------------------------------------------------
 // The sweeps are templated on the EoS: IdealEos is S / G (p = (gamma-1)(E - KE)), TableEos is
 // MHD_codes/TabEoS.cpp = T (bilinear lookup in a 500x500 table, T:147-404).  Both take the state, the shared
@@ -64,7 +84,7 @@ struct IdealEos {
             const double KE = 0.5 * x[0] * (vx * vx + vy * vy);
             return gm1 * (x[3] - KE);
         }
-        dv.note_scaled_aux(x[3]);  // exact while the energy the halved term is taken from is not tiny
+        euler_note_aux(dv, x[3]);  // exact while the energy the halved term is taken from is not tiny
         return gm1 * escaled_add(-0.5, x[0] * (vx * vx + vy * vy), x[3]);
     }
 
@@ -77,7 +97,7 @@ struct IdealEos {
         const double vy = dv.div(q[2], ir);
         const double speed = sqrt(vx * vx + vy * vy);
         // KE = 0.5*rho*speed*speed = 0.5*fl(fl(rho*speed)*speed) exactly
-        dv.note_scaled_aux(q[3]);
+        euler_note_aux(dv, q[3]);
         const double p = literal_scalings<D>::value
                              ? (gamma - 1.0) * (q[3] - 0.5 * rho * speed * speed)  // S:179-180 as written
                              : (gamma - 1.0) * escaled_add(-0.5, rho * speed * speed, q[3]);
@@ -171,7 +191,7 @@ struct TableEos {
         bracket(dens, rho, 499, hint_d, db, dt, d_bottom, d_top);
         density_ratio = dv.div(rho - d_bottom, d_top - d_bottom);
         if (d_bottom == d_top) density_ratio = 1;
-        dv.note_scaled_aux(x[3]);
+        euler_note_aux(dv, x[3]);
         const double e = literal_scalings<D>::value
                              ? dv.div(x[3] - 0.5 * rho * (vx * vx + vy * vy), ir)  // T:288 as written
                              : dv.div(escaled_add(-0.5, rho * (vx * vx + vy * vy), x[3]), ir);
@@ -334,14 +354,14 @@ __device__ __forceinline__ void euler_force(D& dv, const double (&a)[NE], const 
 #pragma unroll
     for (int k = 0; k < NE; ++k) {
         const double w = a[k] + b[k];
-        dv.note_scaled_aux(w);
+        euler_note_aux(dv, w);
         uh[k] = sadd<D>(0.5, w, -(hdtdh * (f2[k] - f1[k])));
     }
     euler_flux<DIR>(dv, uh, eos, ri);
 #pragma unroll
     for (int k = 0; k < NE; ++k) {
         const double w = f1[k] + f2[k];
-        dv.note_scaled_aux(w);
+        euler_note_aux(dv, w);
         const double lf = sadd<D>(0.5, w, hhdt * (a[k] - b[k]));
         F[k] = 0.5 * (lf + ri[k]);
     }
