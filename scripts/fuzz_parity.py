@@ -1,0 +1,162 @@
+"""Fuzz of the bit parity CUDA == oracle (TEST INFRASTRUCTURE, run on the GPU box: it imports tests/oracle_util).
+Random states in regimes the fixtures do not visit -- piecewise-constant states with jumps (every HLLC region, every
+limiter branch), states scaled by powers of two towards the edges of the fast division's operand window (the IEEE
+fix path with its literal expressions), fields that vanish in patches, all boundary-condition pairs, ragged sizes.
+usage: fuzz_parity.py [mhd|euler|both] [first_seed] [count]      prints one line per case, exits 1 on a mismatch"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import lsc_internship_b200 as lsc  # noqa: E402
+from oracle_util import OracleEuler, OracleMhd, euler_cfg, mhd_cfg  # noqa: E402
+
+MHD_BCS = [("periodic", "periodic"), ("periodic", "reflective"), ("transmissive", "transmissive"),
+           ("transmissive", "reflective"), ("periodic", "transmissive")]
+
+
+def bits(a):
+    return np.ascontiguousarray(a).view(np.uint64)
+
+
+def blocky(rng, shape, lo, hi, nblocks):
+    """piecewise-constant random field: nblocks x nblocks patches with values in [lo, hi), plus small noise"""
+    bx = np.sort(rng.choice(np.arange(1, shape[0]), size=min(nblocks, shape[0] - 1), replace=False))
+    by = np.sort(rng.choice(np.arange(1, shape[1]), size=min(nblocks, shape[1] - 1), replace=False))
+    ix = np.searchsorted(bx, np.arange(shape[0]), side="right")
+    iy = np.searchsorted(by, np.arange(shape[1]), side="right")
+    vals = rng.uniform(lo, hi, (len(bx) + 1, len(by) + 1))
+    return vals[ix][:, iy]
+
+
+def mhd_case(seed):
+    rng = np.random.default_rng(seed)
+    nx, ny = int(rng.integers(4, 90)), int(rng.integers(4, 90))
+    bcx, bcy = MHD_BCS[seed % len(MHD_BCS)]
+    regime = ["jumps", "smooth", "scaled", "patchy", "tiny"][(seed // len(MHD_BCS)) % 5]
+    shape = (nx + 4, ny + 4)
+    nb = int(rng.integers(1, 6))
+    if regime == "smooth":
+        x = np.linspace(0, 2 * np.pi, shape[0])[:, None]
+        y = np.linspace(0, 2 * np.pi, shape[1])[None, :]
+        rho = 1.5 + 0.5 * np.sin(x + rng.uniform(0, 6)) * np.cos(y)
+        v = [0.7 * np.sin(y + k) * np.cos(x * (k + 1)) for k in range(3)]
+        B = [0.6 * np.cos(x + 2 * k) * np.sin(y * (k + 1)) for k in range(3)]
+        p = 1.0 + 0.3 * np.cos(x) * np.cos(y)
+        psi = 0.05 * np.sin(x) * np.sin(y)
+    else:
+        rho = blocky(rng, shape, 0.3, 3.0, nb)
+        v = [blocky(rng, shape, -1.0, 1.0, nb) for _ in range(3)]
+        B = [blocky(rng, shape, -1.0, 1.0, nb) for _ in range(3)]
+        p = blocky(rng, shape, 0.5, 3.0, nb)
+        psi = blocky(rng, shape, -0.1, 0.1, nb)
+        noise = 1e-3 if regime != "patchy" else 0.0
+        rho = rho * (1 + noise * rng.uniform(-1, 1, shape))
+    if regime == "tiny":         # out-of-plane fields around 1e-160 (limiter products subnormal) with exact zeros
+        k = int(rng.integers(-575, -525))
+        for f in (v[2], B[2], psi):
+            f *= 2.0 ** k
+            f[blocky(rng, shape, 0.0, 1.0, nb) < 0.3] = 0.0
+    if regime == "patchy":       # fields that vanish exactly in patches, signed zeros included
+        for f in (v[2], B[2], psi, v[0]):
+            m = blocky(rng, shape, 0.0, 1.0, nb) < 0.5
+            f[m] = 0.0
+        B[1][blocky(rng, shape, 0.0, 1.0, nb) < 0.3] = -0.0
+    g = 5.0 / 3.0
+    u = np.zeros(shape + (9,))
+    u[..., 0] = rho
+    for k in range(3):
+        u[..., 1 + k] = rho * v[k]
+        u[..., 5 + k] = B[k]
+    u[..., 4] = p / (g - 1) + 0.5 * rho * (v[0] ** 2 + v[1] ** 2 + v[2] ** 2) + 0.5 * (B[0] ** 2 + B[1] ** 2 + B[2] ** 2)
+    u[..., 8] = psi
+    if regime == "scaled":       # exact power-of-two scaling: densities by 4^k, fields by 2^k (velocities unchanged)
+        k = int(rng.choice([-240, -200, -120, 120, 200, 230]))
+        u[..., 0:5] = np.ldexp(u[..., 0:5], 2 * k)
+        u[..., 5:9] = np.ldexp(u[..., 5:9], k)
+    cfg = mhd_cfg(nx, ny, bcx=bcx, bcy=bcy)
+    o = OracleMhd(cfg, u)
+    s = lsc.MusclNew(nx, ny, 0, 1, 0, 1, bc_x=bcx, bc_y=bcy, problem="ot")
+    s.upload(u)
+    ok, steps = True, 0
+    for n in (1, 2, 3):
+        o.step(n)
+        s.step(n)
+        steps += n
+        ur, tr = o.state()[:2]
+        if not (np.array_equal(bits(s.download()), bits(ur)) and s.scalars()[0] == tr):
+            ok = False
+            break
+    finite = bool(np.isfinite(ur[2:-2, 2:-2]).all())
+    redo = s.ieee_fallback_count()
+    s.close()
+    o.close()
+    print(f"mhd   seed {seed:5d} {nx:3d}x{ny:<3d} {bcx[:5]}/{bcy[:5]} {regime:7s} steps {steps} finite {finite} "
+          f"ieee-redo {redo:6d}  {'ok' if ok else 'MISMATCH'}", flush=True)
+    return ok
+
+
+def euler_case(seed):
+    rng = np.random.default_rng(10_000 + seed)
+    nx, ny = int(rng.integers(4, 100)), int(rng.integers(4, 100))
+    bc = ["periodic", "transmissive"][seed % 2]
+    regime = ["jumps", "scaled", "patchy", "front", "tiny"][(seed // 2) % 5]
+    shape = (nx + 4, ny + 4)
+    nb = int(rng.integers(1, 6))
+    rho = blocky(rng, shape, 0.3, 3.0, nb)
+    vx, vy = blocky(rng, shape, -1.0, 1.0, nb), blocky(rng, shape, -1.0, 1.0, nb)
+    p = blocky(rng, shape, 0.5, 3.0, nb)
+    if regime == "patchy":
+        vx[blocky(rng, shape, 0.0, 1.0, nb) < 0.5] = 0.0
+        vy[blocky(rng, shape, 0.0, 1.0, nb) < 0.5] = -0.0
+    if regime == "tiny":         # one or both velocity components around 1e-160, exact zeros in patches
+        k = int(rng.integers(-575, -525))
+        vy = vy * 2.0 ** k
+        if seed % 3 == 0:
+            vx = vx * 2.0 ** k
+        vy[blocky(rng, shape, 0.0, 1.0, nb) < 0.3] = 0.0
+    if regime == "front":        # momenta decaying through 1e-100 ... 1e-320 across the grid, as at an explosion front
+        decay = 10.0 ** (-np.linspace(0, 330, shape[0]))[:, None]
+        vx, vy = vx * decay, vy * decay
+    g = 1.4
+    u = np.stack([rho, rho * vx, rho * vy, p / (g - 1) + 0.5 * rho * (vx * vx + vy * vy)], axis=-1)
+    if regime == "scaled":
+        k = int(rng.choice([-230, -200, -120, 120, 200, 230]))
+        u = np.ldexp(u, 2 * k)
+    cfg = euler_cfg(nx, ny, (0.0, 1.0, 0.0, 1.0), bc=bc)
+    o = OracleEuler(cfg, u)
+    s = lsc.SlicEuler2d(nx, ny, bc=bc)
+    s.upload(u)
+    ok, steps = True, 0
+    for n in (1, 2, 3):
+        o.step(n)
+        s.step(n)
+        steps += n
+        ur, tr = o.state()[:2]
+        if not (np.array_equal(bits(s.download()), bits(ur)) and s.scalars()[0] == tr):
+            ok = False
+            break
+    finite = bool(np.isfinite(ur[2:-2, 2:-2]).all())
+    redo = s.ieee_fallback_count()
+    s.close()
+    o.close()
+    print(f"euler seed {seed:5d} {nx:3d}x{ny:<3d} {bc[:5]:5s}       {regime:7s} steps {steps} finite {finite} "
+          f"ieee-redo {redo:6d}  {'ok' if ok else 'MISMATCH'}", flush=True)
+    return ok
+
+
+if __name__ == "__main__":
+    which = sys.argv[1] if len(sys.argv) > 1 else "both"
+    first = int(sys.argv[2]) if len(sys.argv) > 2 else 0
+    count = int(sys.argv[3]) if len(sys.argv) > 3 else 40
+    bad = 0
+    for seed in range(first, first + count):
+        if which in ("mhd", "both"):
+            bad += not mhd_case(seed)
+        if which in ("euler", "both"):
+            bad += not euler_case(seed)
+    print(f"{bad} mismatches")
+    sys.exit(1 if bad else 0)

@@ -1,0 +1,24 @@
+"""A slice of scripts/fuzz_parity.py in the suite: random states in regimes the fixtures do not visit (jumps, smooth,
+power-of-two scalings towards the edges of the fast division's window, fields vanishing in patches, out-of-plane
+fields around 1e-160, an explosion-front decay), all boundary pairs, ragged sizes 4..100 -- CUDA == oracle in every
+bit after 1, 3 and 6 steps.  The full run of 4000 cases is profiles/r2/fuzz_parity_4000.log."""
+import os
+import sys
+
+import pytest
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "scripts"))
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("first", [5000, 5025, 5050])
+def test_mhd_fuzz(first):
+    import fuzz_parity
+    assert all([fuzz_parity.mhd_case(seed) for seed in range(first, first + 25)])
+
+
+@pytest.mark.parametrize("first", [5000, 5020, 5040])
+def test_euler_fuzz(first):
+    import fuzz_parity
+    assert all([fuzz_parity.euler_case(seed) for seed in range(first, first + 20)])
