@@ -2,7 +2,10 @@
 Random states in regimes the fixtures do not visit -- piecewise-constant states with jumps (every HLLC region, every
 limiter branch), states scaled by powers of two towards the edges of the fast division's operand window (the IEEE
 fix path with its literal expressions), fields that vanish in patches, all boundary-condition pairs, ragged sizes.
-usage: fuzz_parity.py [mhd|euler|both] [first_seed] [count]      prints one line per case, exits 1 on a mismatch"""
+`slabs`: the MHD cases through a single-process group of 2-4 uneven slabs; `params`: other domains, Courant numbers,
+adiabatic indices and limiter weights; `tabeos`: the table equation of state.
+usage: fuzz_parity.py [mhd|euler|both|slabs|params|tabeos] [first_seed] [count]
+prints one line per case, exits 1 on a mismatch"""
 import os
 import sys
 
@@ -32,9 +35,26 @@ def blocky(rng, shape, lo, hi, nblocks):
     return vals[ix][:, iy]
 
 
-def mhd_case(seed):
+def sizes(rng, seed, small):
+    """mostly small ragged grids; every 16th seed one that spans several strips / tiles / blocks"""
+    if seed % 16 == 7:
+        return int(rng.integers(100, 520)), int(rng.integers(100, 520))
+    return int(rng.integers(4, small)), int(rng.integers(4, small))
+
+
+def slab_bounds(rng, nx):
+    """2-4 uneven slabs of at least 4 columns each"""
+    n = int(rng.integers(2, 5))
+    while n > 1 and nx < 4 * n:
+        n -= 1
+    cuts = np.sort(rng.choice(np.arange(1, nx // 4), size=n - 1, replace=False)) * 4 if n > 1 else np.array([], int)
+    edges = [0] + [int(c) for c in cuts] + [nx]
+    return [(edges[k], edges[k + 1] - edges[k]) for k in range(n)]
+
+
+def mhd_case(seed, slabs=False, params=False):
     rng = np.random.default_rng(seed)
-    nx, ny = int(rng.integers(4, 90)), int(rng.integers(4, 90))
+    nx, ny = sizes(rng, seed, 90)
     bcx, bcy = MHD_BCS[seed % len(MHD_BCS)]
     regime = ["jumps", "smooth", "scaled", "patchy", "tiny"][(seed // len(MHD_BCS)) % 5]
     shape = (nx + 4, ny + 4)
@@ -77,9 +97,28 @@ def mhd_case(seed):
         k = int(rng.choice([-240, -200, -120, 120, 200, 230]))
         u[..., 0:5] = np.ldexp(u[..., 0:5], 2 * k)
         u[..., 5:9] = np.ldexp(u[..., 5:9], k)
-    cfg = mhd_cfg(nx, ny, bcx=bcx, bcy=bcy)
+    dom, cfl = (0.0, 1.0, 0.0, 1.0), 0.8
+    if params:                   # other domains (dx != dy), Courant numbers and adiabatic indices than the committed ones
+        prng = np.random.default_rng(777_000 + seed)
+        dom = (float(prng.uniform(-2, 0)), float(prng.uniform(0.5, 3)), float(prng.uniform(-1, 0)), float(prng.uniform(0.2, 5)))
+        cfl = float(prng.choice([0.3, 0.5, 0.8, 0.9]))
+        gnew = float(prng.choice([5.0 / 3.0, 1.4, 2.0]))
+        u[..., 4] = (u[..., 4] - 0.5 * (u[..., 1] ** 2 + u[..., 2] ** 2 + u[..., 3] ** 2) / u[..., 0]
+                     - 0.5 * (u[..., 5] ** 2 + u[..., 6] ** 2 + u[..., 7] ** 2)) * (g - 1) / (gnew - 1) \
+            + 0.5 * (u[..., 1] ** 2 + u[..., 2] ** 2 + u[..., 3] ** 2) / u[..., 0] \
+            + 0.5 * (u[..., 5] ** 2 + u[..., 6] ** 2 + u[..., 7] ** 2)
+        g = gnew
+    cfg = mhd_cfg(nx, ny, dom=dom, gamma=g, cfl=cfl, bcx=bcx, bcy=bcy)
     o = OracleMhd(cfg, u)
-    s = lsc.MusclNew(nx, ny, 0, 1, 0, 1, bc_x=bcx, bc_y=bcy, problem="ot")
+    kw = dict(nxCells=nx, nyCells=ny, x0=dom[0], x1=dom[1], y0=dom[2], y1=dom[3], C=cfl, gamma=g, bc_x=bcx, bc_y=bcy,
+              problem="ot")
+    if slabs and nx >= 8:
+        bounds = slab_bounds(np.random.default_rng(555_000 + seed), nx)
+        s = lsc.MusclNewGroup.from_parts([lsc.MusclNew(rank=r, nranks=len(bounds), slab=b, **kw)
+                                          for r, b in enumerate(bounds)])
+        regime += f"/{len(bounds)}sl"
+    else:
+        s = lsc.MusclNew(**kw)
     s.upload(u)
     ok, steps = True, 0
     for n in (1, 2, 3):
@@ -94,14 +133,14 @@ def mhd_case(seed):
     redo = s.ieee_fallback_count()
     s.close()
     o.close()
-    print(f"mhd   seed {seed:5d} {nx:3d}x{ny:<3d} {bcx[:5]}/{bcy[:5]} {regime:7s} steps {steps} finite {finite} "
+    print(f"mhd   seed {seed:5d} {nx:3d}x{ny:<3d} {bcx[:5]}/{bcy[:5]} {regime:11s} steps {steps} finite {finite} "
           f"ieee-redo {redo:6d}  {'ok' if ok else 'MISMATCH'}", flush=True)
     return ok
 
 
-def euler_case(seed):
+def euler_case(seed, params=False):
     rng = np.random.default_rng(10_000 + seed)
-    nx, ny = int(rng.integers(4, 100)), int(rng.integers(4, 100))
+    nx, ny = sizes(rng, seed, 100)
     bc = ["periodic", "transmissive"][seed % 2]
     regime = ["jumps", "scaled", "patchy", "front", "tiny"][(seed // 2) % 5]
     shape = (nx + 4, ny + 4)
@@ -121,14 +160,20 @@ def euler_case(seed):
     if regime == "front":        # momenta decaying through 1e-100 ... 1e-320 across the grid, as at an explosion front
         decay = 10.0 ** (-np.linspace(0, 330, shape[0]))[:, None]
         vx, vy = vx * decay, vy * decay
-    g = 1.4
+    g, dom, cfl, omega = 1.4, (0.0, 1.0, 0.0, 1.0), 0.8, 0.0
+    if params:                   # the limiter's omega (S:272), other domains, Courant numbers, adiabatic indices
+        prng = np.random.default_rng(888_000 + seed)
+        dom = (float(prng.uniform(-2, 0)), float(prng.uniform(0.5, 3)), float(prng.uniform(-1, 0)), float(prng.uniform(0.2, 5)))
+        cfl = float(prng.choice([0.3, 0.5, 0.8, 0.9]))
+        g = float(prng.choice([1.4, 5.0 / 3.0, 1.1]))
+        omega = float(prng.choice([0.0, 0.5, -0.5, 0.3, 1.0]))
     u = np.stack([rho, rho * vx, rho * vy, p / (g - 1) + 0.5 * rho * (vx * vx + vy * vy)], axis=-1)
     if regime == "scaled":
         k = int(rng.choice([-230, -200, -120, 120, 200, 230]))
         u = np.ldexp(u, 2 * k)
-    cfg = euler_cfg(nx, ny, (0.0, 1.0, 0.0, 1.0), bc=bc)
+    cfg = euler_cfg(nx, ny, dom, gamma=g, cfl=cfl, omega=omega, bc=bc)
     o = OracleEuler(cfg, u)
-    s = lsc.SlicEuler2d(nx, ny, bc=bc)
+    s = lsc.SlicEuler2d(nx, ny, dom[0], dom[1], dom[2], dom[3], C=cfl, gamma=g, omega=omega, bc=bc)
     s.upload(u)
     ok, steps = True, 0
     for n in (1, 2, 3):
@@ -148,6 +193,53 @@ def euler_case(seed):
     return ok
 
 
+def tabeos_case(seed):
+    """TabEoS.cpp's table equation of state (synthetic Plasma19-format table): the program's four-quadrant state with
+    patchwise random density / energy factors and momenta, warm-started and plain searches alike"""
+    from oracle_util import parsed_eos_table, tabeos_ic
+    rng = np.random.default_rng(20_000 + seed)
+    nx, ny = int(rng.integers(4, 70)), int(rng.integers(4, 70))
+    shape = (nx + 4, ny + 4)
+    nb = int(rng.integers(1, 5))
+    table = parsed_eos_table()
+    cfg = euler_cfg(nx, ny, (0.0, 1.0, 0.0, 1.0), bc="transmissive")
+    u = tabeos_ic(cfg, table)
+    u[..., 0] *= blocky(rng, shape, 0.6, 1.6, nb)
+    u[..., 3] *= blocky(rng, shape, 0.7, 1.5, nb)
+    c = np.sqrt(u[..., 3] / u[..., 0])
+    u[..., 1] = u[..., 0] * c * blocky(rng, shape, -0.3, 0.3, nb)
+    u[..., 2] = u[..., 0] * c * blocky(rng, shape, -0.3, 0.3, nb)
+    if seed % 3 == 1:            # operands the fast division has to hand to the IEEE fix kernels
+        u[..., 1][blocky(rng, shape, 0.0, 1.0, nb) < 0.4] = -0.0
+        u[..., 2] = np.where(blocky(rng, shape, 0.0, 1.0, nb) < 0.5, u[..., 2] * 2.0 ** -550, u[..., 2])
+        u[..., 2][blocky(rng, shape, 0.0, 1.0, nb) < 0.2] = 0.0
+    o = OracleEuler(cfg, u)
+    o.set_table(*table)
+    s = lsc.SlicEuler2d(nx, ny, bc="transmissive", problem="tabeos")
+    s.set_eos_table(*table)
+    if seed % 4 == 3:
+        s.set_eos_search(False)
+    s.upload(u)
+    ok, steps = True, 0
+    for n in (1, 2):
+        o.step(n)
+        s.step(n)
+        steps += n
+        ur, tr = o.state()[:2]
+        if not np.isfinite(ur).all():
+            break
+        if not (np.array_equal(bits(s.download()), bits(ur)) and s.scalars()[0] == tr):
+            ok = False
+            break
+    finite = bool(np.isfinite(ur).all())
+    redo = s.ieee_fallback_count()
+    s.close()
+    o.close()
+    print(f"tabeos seed {seed:5d} {nx:3d}x{ny:<3d} trans       {'table':11s} steps {steps} finite {finite} "
+          f"ieee-redo {redo:6d}  {'ok' if ok else 'MISMATCH'}", flush=True)
+    return ok
+
+
 if __name__ == "__main__":
     which = sys.argv[1] if len(sys.argv) > 1 else "both"
     first = int(sys.argv[2]) if len(sys.argv) > 2 else 0
@@ -158,5 +250,12 @@ if __name__ == "__main__":
             bad += not mhd_case(seed)
         if which in ("euler", "both"):
             bad += not euler_case(seed)
+        if which == "slabs":
+            bad += not mhd_case(seed, slabs=True)
+        if which == "params":
+            bad += not mhd_case(seed, params=True)
+            bad += not euler_case(seed, params=True)
+        if which == "tabeos":
+            bad += not tabeos_case(seed)
     print(f"{bad} mismatches")
     sys.exit(1 if bad else 0)

@@ -1,7 +1,8 @@
 """A slice of scripts/fuzz_parity.py in the suite: random states in regimes the fixtures do not visit (jumps, smooth,
 power-of-two scalings towards the edges of the fast division's window, fields vanishing in patches, out-of-plane
 fields around 1e-160, an explosion-front decay), all boundary pairs, ragged sizes 4..100 -- CUDA == oracle in every
-bit after 1, 3 and 6 steps.  The full run of 4000 cases is profiles/r2/fuzz_parity_4000.log."""
+bit after 1, 3 and 6 steps; also through uneven slab groups, with other physical parameters, and with the table EoS.
+The full runs (5600 cases) are summarised in profiles/r2/fuzz_parity_4000.log."""
 import os
 import sys
 
@@ -22,3 +23,19 @@ def test_mhd_fuzz(first):
 def test_euler_fuzz(first):
     import fuzz_parity
     assert all([fuzz_parity.euler_case(seed) for seed in range(first, first + 20)])
+
+
+def test_mhd_fuzz_through_uneven_slab_groups():
+    import fuzz_parity
+    assert all([fuzz_parity.mhd_case(seed, slabs=True) for seed in range(6000, 6030)])
+
+
+def test_fuzz_other_domains_courant_numbers_gammas_and_limiter_weights():
+    import fuzz_parity
+    assert all([fuzz_parity.mhd_case(seed, params=True) for seed in range(6100, 6120)])
+    assert all([fuzz_parity.euler_case(seed, params=True) for seed in range(6100, 6120)])
+
+
+def test_tabeos_fuzz():
+    import fuzz_parity
+    assert all([fuzz_parity.tabeos_case(seed) for seed in range(6200, 6220)])
