@@ -291,6 +291,9 @@ int lsc_euler_group_download(lsc_euler_ctx** slabs, int n, double* aos);
 /* IC loop S:552-594 / G:586-620 followed by the boundary fill S:596, into [(nx+4)][(ny+4)][4] (the slab
  * [(nxl+4)][(ny+4)][4] of cfg->rank when cfg->nranks > 1). Host libm. */
 int lsc_euler_initial_condition(const lsc_euler_config* cfg, int problem, double* aos);
+/* The first ComputeTimeStep sees the array as given (S:173-174); the x ghost columns are then replaced by boundary
+ * images -- for a slab (nranks > 1) by the neighbours' cells / the images, at the head of the first step -- exactly
+ * as S:604 does, so the caller's ghost columns may hold anything (e.g. the initial data's own values). */
 int lsc_euler_upload(lsc_euler_ctx* ctx, const double* aos);
 int lsc_euler_init_problem(lsc_euler_ctx* ctx, int problem);
 int lsc_euler_step(lsc_euler_ctx* ctx, long nsteps);                 /* n passes of the do-body S:600-616 */

@@ -66,6 +66,7 @@ struct lsc_euler_ctx {
     bool warm_search = true;           // lsc_euler_set_eos_search
     lsc::Comm* comm = nullptr;         // NCCL mode (one process per GPU)
     bool in_group = false;             // driven by the lsc_euler_group_* calls
+    bool ghosts_current = false;       // x ghost / halo columns of state[cur] hold boundary images / neighbour cells
     cudaEvent_t halo_event = nullptr;  // team: "new u of this slab complete"
     cudaEvent_t red_event = nullptr;   // team: "status word of this slab is in the leader's gather buffer"
     cudaEvent_t max_event = nullptr;   // team leader: "the maximum over the slabs is ready"
@@ -319,6 +320,16 @@ int e_enqueue_steps(const ETeam& T, long count) {
     for (int r = 0; r < T.n; ++r) {
         cur[r] = T.m[r]->cur;
         next[r] = T.m[r]->next;
+    }
+    if (!L->ghosts_current) {
+        // applyBoundaryConditions(u) at the head of the first pass (S:604) for a decomposed grid: the uploaded array's
+        // ghost columns at the ends of the domain hold whatever the caller had there (the initial data's own values,
+        // for instance), not boundary images.  A plain context did this at the end of the upload.
+        int rc = LSC_OK;
+        if (T.n > 1) rc = eg_halo(T, cur.data());
+        else if (L->cfg.nranks > 1) rc = e_fill_x_ghosts(L, cur[0]);
+        if (rc) return rc;
+        for (int r = 0; r < T.n; ++r) T.m[r]->ghosts_current = true;
     }
     long e = 0;
     while (e < count) {
@@ -769,10 +780,12 @@ int lsc_euler_upload(lsc_euler_ctx* c, const double* aos) {
     lsc::launch_euler_max_speed(c->g, ep, c->state[c->cur], 2, i_hi, 2, c->cfg.ny + 2, c->d_status, c->stream);
     lsc_count_launches(1);
     LSC_CUDA_TRY(cudaGetLastError());
+    c->ghosts_current = false;
     if (c->cfg.nranks <= 1) {
         int rc = e_fill_x_ghosts(c, c->cur);
         if (rc) return rc;
-    }  // slabs: the uploaded halo columns already hold the neighbours' cells / the caller's boundary images
+        c->ghosts_current = true;
+    }  // slabs: the first pass of the loop exchanges the halo columns / forms the images (e_enqueue_steps)
     // fresh loop state: t = 0, step = 0, the run's constants (S:537, S:166-169, S:546-547)
     lsc::EulerStepCtl& k = c->h->ctl;
     std::memset(&k, 0, sizeof k);

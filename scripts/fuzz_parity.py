@@ -138,7 +138,7 @@ def mhd_case(seed, slabs=False, params=False):
     return ok
 
 
-def euler_case(seed, params=False):
+def euler_case(seed, params=False, slabs=False):
     rng = np.random.default_rng(10_000 + seed)
     nx, ny = sizes(rng, seed, 100)
     bc = ["periodic", "transmissive"][seed % 2]
@@ -173,7 +173,14 @@ def euler_case(seed, params=False):
         u = np.ldexp(u, 2 * k)
     cfg = euler_cfg(nx, ny, dom, gamma=g, cfl=cfl, omega=omega, bc=bc)
     o = OracleEuler(cfg, u)
-    s = lsc.SlicEuler2d(nx, ny, dom[0], dom[1], dom[2], dom[3], C=cfl, gamma=g, omega=omega, bc=bc)
+    kw = dict(nxCells=nx, nyCells=ny, x0=dom[0], x1=dom[1], y0=dom[2], y1=dom[3], C=cfl, gamma=g, omega=omega, bc=bc)
+    nsl = int(np.random.default_rng(666_000 + seed).integers(2, 5))
+    if slabs and nx >= 4 * nsl:
+        s = lsc.SlicEuler2dGroup(nsl, **kw)
+        s.ieee_fallback_count = lambda: sum(q.ieee_fallback_count() for q in s.parts)
+        regime += f"/{nsl}sl"
+    else:
+        s = lsc.SlicEuler2d(**kw)
     s.upload(u)
     ok, steps = True, 0
     for n in (1, 2, 3):
@@ -188,7 +195,7 @@ def euler_case(seed, params=False):
     redo = s.ieee_fallback_count()
     s.close()
     o.close()
-    print(f"euler seed {seed:5d} {nx:3d}x{ny:<3d} {bc[:5]:5s}       {regime:7s} steps {steps} finite {finite} "
+    print(f"euler seed {seed:5d} {nx:3d}x{ny:<3d} {bc[:5]:5s}       {regime:11s} steps {steps} finite {finite} "
           f"ieee-redo {redo:6d}  {'ok' if ok else 'MISMATCH'}", flush=True)
     return ok
 
@@ -252,6 +259,7 @@ if __name__ == "__main__":
             bad += not euler_case(seed)
         if which == "slabs":
             bad += not mhd_case(seed, slabs=True)
+            bad += not euler_case(seed, slabs=True)
         if which == "params":
             bad += not mhd_case(seed, params=True)
             bad += not euler_case(seed, params=True)

@@ -25,9 +25,10 @@ def test_euler_fuzz(first):
     assert all([fuzz_parity.euler_case(seed) for seed in range(first, first + 20)])
 
 
-def test_mhd_fuzz_through_uneven_slab_groups():
+def test_fuzz_through_slab_groups():
     import fuzz_parity
     assert all([fuzz_parity.mhd_case(seed, slabs=True) for seed in range(6000, 6030)])
+    assert all([fuzz_parity.euler_case(seed, slabs=True) for seed in range(6000, 6030)])
 
 
 def test_fuzz_other_domains_courant_numbers_gammas_and_limiter_weights():
