@@ -4,7 +4,8 @@ limiter branch), states scaled by powers of two towards the edges of the fast di
 fix path with its literal expressions), fields that vanish in patches, all boundary-condition pairs, ragged sizes.
 `slabs`: the MHD cases through a single-process group of 2-4 uneven slabs; `params`: other domains, Courant numbers,
 adiabatic indices and limiter weights; `tabeos`: the table equation of state.
-usage: fuzz_parity.py [mhd|euler|both|slabs|params|tabeos] [first_seed] [count]
+`reuse`: contexts uploaded again and again; `long`: 19 steps in one call; `ic`: the initial-condition generators.
+usage: fuzz_parity.py [mhd|euler|both|slabs|params|tabeos|reuse|long|ic] [first_seed] [count]
 prints one line per case, exits 1 on a mismatch"""
 import os
 import sys
@@ -21,8 +22,23 @@ MHD_BCS = [("periodic", "periodic"), ("periodic", "reflective"), ("transmissive"
            ("transmissive", "reflective"), ("periodic", "transmissive")]
 
 
+SCHEDULE = (1, 2, 3)   # steps per call; `long` mode: one call of 19 steps (CUDA graphs of 8 + single steps)
+REUSE = None           # `reuse` mode: contexts kept per shape / parameters and uploaded again and again
+
+
 def bits(a):
     return np.ascontiguousarray(a).view(np.uint64)
+
+
+def solver(key, make):
+    """a fresh context, or -- in `reuse` mode -- the one an earlier case with the same key left behind (a new upload
+    must wipe everything: the step count, u^{n-1} of the MHD limiter, the exp table, the fix lists)"""
+    if REUSE is None:
+        return make()
+    if key not in REUSE:
+        REUSE[key] = make()
+        REUSE[key].close = lambda: None
+    return REUSE[key]
 
 
 def blocky(rng, shape, lo, hi, nblocks):
@@ -118,17 +134,20 @@ def mhd_case(seed, slabs=False, params=False):
                                           for r, b in enumerate(bounds)])
         regime += f"/{len(bounds)}sl"
     else:
-        s = lsc.MusclNew(**kw)
+        s = solver(("mhd",) + tuple(sorted(kw.items())), lambda: lsc.MusclNew(**kw))
     s.upload(u)
     ok, steps = True, 0
-    for n in (1, 2, 3):
-        o.step(n)
+    for n in SCHEDULE:
+        lg = o.step(n)
+        if not np.isfinite(lg).all() or not (lg[:, 2] > 0).all():
+            break                # the reference itself has lost the state (NaN speed): nothing to compare
         s.step(n)
         steps += n
         ur, tr = o.state()[:2]
         if not (np.array_equal(bits(s.download()), bits(ur)) and s.scalars()[0] == tr):
             ok = False
             break
+    ur = o.state()[0]
     finite = bool(np.isfinite(ur[2:-2, 2:-2]).all())
     redo = s.ieee_fallback_count()
     s.close()
@@ -180,17 +199,20 @@ def euler_case(seed, params=False, slabs=False):
         s.ieee_fallback_count = lambda: sum(q.ieee_fallback_count() for q in s.parts)
         regime += f"/{nsl}sl"
     else:
-        s = lsc.SlicEuler2d(**kw)
+        s = solver(("euler",) + tuple(sorted(kw.items())), lambda: lsc.SlicEuler2d(**kw))
     s.upload(u)
     ok, steps = True, 0
-    for n in (1, 2, 3):
-        o.step(n)
+    for n in SCHEDULE:
+        lg = o.step(n)
+        if not np.isfinite(lg).all() or not (lg[:, 1] > 0).all():
+            break
         s.step(n)
         steps += n
         ur, tr = o.state()[:2]
         if not (np.array_equal(bits(s.download()), bits(ur)) and s.scalars()[0] == tr):
             ok = False
             break
+    ur = o.state()[0]
     finite = bool(np.isfinite(ur[2:-2, 2:-2]).all())
     redo = s.ieee_fallback_count()
     s.close()
@@ -247,6 +269,30 @@ def tabeos_case(seed):
     return ok
 
 
+def ic_case(seed):
+    """the library's initial-condition generators (host libm, MUSCL_NEW.cpp:719-825, S:552-596) against the oracle's on
+    random grids and domains -- no GPU work"""
+    from oracle_util import euler_ic, mhd_ic
+    rng = np.random.default_rng(30_000 + seed)
+    nx, ny = int(rng.integers(4, 200)), int(rng.integers(4, 200))
+    dom = (float(rng.uniform(-2, 0)), float(rng.uniform(0.5, 3)), float(rng.uniform(-2, 0)), float(rng.uniform(0.2, 5)))
+    if seed % 2:
+        dom = (0.0, 1.0, 0.0, 1.0) if seed % 4 == 1 else (0.0, 1.0, -1.0, 1.0)
+    ok = True
+    for prob in ("ot", "kh"):
+        cfg = mhd_cfg(nx, ny, dom=dom)
+        s = lsc.MusclNew(nx, ny, *dom, problem=prob)
+        ok &= np.array_equal(bits(s.initial_condition()), bits(mhd_ic(cfg, prob)))
+        s.close()
+    for prob in ("ot", "quadrants", "cylinder"):
+        cfg = euler_cfg(nx, ny, dom, bc="transmissive" if prob != "ot" else "periodic")
+        s = lsc.SlicEuler2d(nx, ny, *dom, bc="transmissive" if prob != "ot" else "periodic", problem=prob)
+        ok &= np.array_equal(bits(s.initial_condition()), bits(euler_ic(cfg, prob)))
+        s.close()
+    print(f"ic    seed {seed:5d} {nx:3d}x{ny:<3d} domain {dom}  {'ok' if ok else 'MISMATCH'}", flush=True)
+    return ok
+
+
 if __name__ == "__main__":
     which = sys.argv[1] if len(sys.argv) > 1 else "both"
     first = int(sys.argv[2]) if len(sys.argv) > 2 else 0
@@ -265,5 +311,16 @@ if __name__ == "__main__":
             bad += not euler_case(seed, params=True)
         if which == "tabeos":
             bad += not tabeos_case(seed)
+        if which == "ic":
+            bad += not ic_case(seed)
+        if which == "reuse":      # few distinct shapes, so that contexts really are reused
+            REUSE = {} if REUSE is None else REUSE
+            sizes = lambda rng, sd, small: (12 + 8 * (sd % 3), 20 + 4 * (sd % 2))  # noqa: E731
+            bad += not mhd_case(seed)
+            bad += not euler_case(seed)
+        if which == "long":
+            SCHEDULE = (19,)
+            bad += not mhd_case(seed)
+            bad += not euler_case(seed)
     print(f"{bad} mismatches")
     sys.exit(1 if bad else 0)

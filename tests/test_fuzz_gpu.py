@@ -40,3 +40,30 @@ def test_fuzz_other_domains_courant_numbers_gammas_and_limiter_weights():
 def test_tabeos_fuzz():
     import fuzz_parity
     assert all([fuzz_parity.tabeos_case(seed) for seed in range(6200, 6220)])
+
+
+def test_fuzz_initial_condition_generators():
+    import fuzz_parity
+    assert all([fuzz_parity.ic_case(seed) for seed in range(6300, 6320)])
+
+
+def test_fuzz_long_single_call(monkeypatch):
+    """19 steps in one call: CUDA graphs of 8 steps plus single steps of the device-resident loop"""
+    import fuzz_parity
+    monkeypatch.setattr(fuzz_parity, "SCHEDULE", (19,))
+    assert all([fuzz_parity.mhd_case(seed) for seed in range(6400, 6415)])
+    assert all([fuzz_parity.euler_case(seed) for seed in range(6400, 6415)])
+
+
+def test_fuzz_contexts_uploaded_again_and_again(monkeypatch):
+    import fuzz_parity
+    cache = {}
+    monkeypatch.setattr(fuzz_parity, "REUSE", cache)
+    monkeypatch.setattr(fuzz_parity, "sizes", lambda rng, sd, small: (12 + 8 * (sd % 2), 20))
+    try:
+        assert all([fuzz_parity.mhd_case(seed) for seed in range(6500, 6530)])
+        assert all([fuzz_parity.euler_case(seed) for seed in range(6500, 6530)])
+    finally:
+        for s in cache.values():
+            del s.close          # the instance-level no-op: the class method closes for real
+            s.close()
