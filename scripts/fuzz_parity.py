@@ -5,7 +5,7 @@ fix path with its literal expressions), fields that vanish in patches, all bound
 `slabs`: the MHD cases through a single-process group of 2-4 uneven slabs; `params`: other domains, Courant numbers,
 adiabatic indices and limiter weights; `tabeos`: the table equation of state.
 `reuse`: contexts uploaded again and again; `long`: 19 steps in one call; `ic`: the initial-condition generators.
-usage: fuzz_parity.py [mhd|euler|both|slabs|params|tabeos|reuse|long|ic] [first_seed] [count]
+usage: fuzz_parity.py [mhd|euler|both|slabs|params|tabeos|reuse|long|ic|run] [first_seed] [count]
 prints one line per case, exits 1 on a mismatch"""
 import os
 import sys
@@ -269,6 +269,60 @@ def tabeos_case(seed):
     return ok
 
 
+def run_case(seed):
+    """The whole loop M:831-1003 through run() -- dump cadence (M:975), stop test, pause / resume of the device-resident
+    loop, psi-factor table -- on a smooth random state with a random stop time (5..50 steps, up to three dumps),
+    alternately on one context and on a group of uneven slabs: step count, t and state against the oracle's loop."""
+    rng = np.random.default_rng(40_000 + seed)
+    nx, ny = int(rng.integers(12, 60)), int(rng.integers(12, 60))
+    bcx, bcy = MHD_BCS[seed % len(MHD_BCS)]
+    shape = (nx + 4, ny + 4)
+    x = np.linspace(0, 2 * np.pi, shape[0])[:, None]
+    y = np.linspace(0, 2 * np.pi, shape[1])[None, :]
+    ph = rng.uniform(0, 6, 8)
+    rho = 1.5 + 0.4 * np.sin(x + ph[0]) * np.cos(y + ph[1])
+    v = [0.5 * np.sin(y + ph[2 + k]) * np.cos(x * (k + 1)) for k in range(3)]
+    B = [0.5 * np.cos(x + ph[5 + k]) * np.sin(y * (k + 1)) for k in range(3)]
+    p = 1.0 + 0.3 * np.cos(x) * np.cos(y)
+    g = 5.0 / 3.0
+    u = np.zeros(shape + (9,))
+    u[..., 0] = rho
+    for k in range(3):
+        u[..., 1 + k] = rho * v[k]
+        u[..., 5 + k] = B[k]
+    u[..., 4] = p / (g - 1) + 0.5 * rho * (v[0] ** 2 + v[1] ** 2 + v[2] ** 2) + 0.5 * (B[0] ** 2 + B[1] ** 2 + B[2] ** 2)
+    cfl = float(rng.choice([0.4, 0.8, 0.9]))
+    t_stop = float(rng.uniform(0.04, 0.33))
+    cfg = mhd_cfg(nx, ny, cfl=cfl, bcx=bcx, bcy=bcy)
+    o = OracleMhd(cfg, u)
+    n_ref = o.run_until(t_stop)
+    ur, tr = o.state()[:2]
+    kw = dict(nxCells=nx, nyCells=ny, x0=0.0, x1=1.0, y0=0.0, y1=1.0, C=cfl, bc_x=bcx, bc_y=bcy, problem="ot")
+    if seed % 2 and nx >= 8:
+        bounds = slab_bounds(np.random.default_rng(555_000 + seed), nx)
+        s = lsc.MusclNewGroup.from_parts([lsc.MusclNew(rank=r, nranks=len(bounds), slab=b, **kw)
+                                          for r, b in enumerate(bounds)])
+        how = f"{len(bounds)} slabs"
+    else:
+        s = lsc.MusclNew(**kw)
+        how = "1 ctx  "
+    s.upload(u)
+    dumps = []
+    import tempfile
+    with tempfile.TemporaryDirectory() as td:
+        n = s.run(tStop=t_stop, outdir=td)
+        dumps = sorted(os.listdir(td))
+    ok = bool(n == n_ref and s.scalars()[0] == tr and np.array_equal(bits(s.download()), bits(ur)))
+    # the reference writes MHD<k>.dat when t crosses 0.1 k, plus the final dump
+    want = sum(1 for k in range(0, 5) if 0.1 * k < tr) + 1
+    ok &= len(dumps) == want
+    s.close()
+    o.close()
+    print(f"run   seed {seed:5d} {nx:3d}x{ny:<3d} {bcx[:5]}/{bcy[:5]} {how} t_stop {t_stop:.4f} steps {n} (ref {n_ref}) "
+          f"files {len(dumps)} (want {want})  {'ok' if ok else 'MISMATCH'}", flush=True)
+    return ok
+
+
 def ic_case(seed):
     """the library's initial-condition generators (host libm, MUSCL_NEW.cpp:719-825, S:552-596) against the oracle's on
     random grids and domains -- no GPU work"""
@@ -313,6 +367,8 @@ if __name__ == "__main__":
             bad += not tabeos_case(seed)
         if which == "ic":
             bad += not ic_case(seed)
+        if which == "run":
+            bad += not run_case(seed)
         if which == "reuse":      # few distinct shapes, so that contexts really are reused
             REUSE = {} if REUSE is None else REUSE
             sizes = lambda rng, sd, small: (12 + 8 * (sd % 3), 20 + 4 * (sd % 2))  # noqa: E731

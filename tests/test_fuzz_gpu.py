@@ -67,3 +67,8 @@ def test_fuzz_contexts_uploaded_again_and_again(monkeypatch):
         for s in cache.values():
             del s.close          # the instance-level no-op: the class method closes for real
             s.close()
+
+
+def test_fuzz_whole_loop_with_dumps_and_random_stop_times():
+    import fuzz_parity
+    assert all([fuzz_parity.run_case(seed) for seed in range(6600, 6630)])
