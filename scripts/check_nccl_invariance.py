@@ -70,6 +70,52 @@ for prob, nx, ny, bc in [("ot", 160, 96, "periodic"), ("cylinder", 144, 120, "tr
     ok = ok and same
     s.close()
     one.close()
+# uploaded random states whose ghost columns are NOT boundary images (every rank builds the same array): the first
+# step has to refill / exchange them as the reference's applyBoundaryConditions does (M:838, S:604)
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+rng = np.random.default_rng(4242)
+for scheme, nx, ny, bcs in [("mhd", 96, 40, ("periodic", "periodic")), ("mhd", 72, 33, ("transmissive", "reflective")),
+                            ("euler", 88, 37, ("periodic",)), ("euler", 64, 50, ("transmissive",))]:
+    shape = (nx + 4, ny + 4)
+    rho = rng.uniform(0.5, 2.0, shape)
+    v = rng.uniform(-0.5, 0.5, (3,) + shape)
+    B = rng.uniform(-0.5, 0.5, (3,) + shape)
+    p = rng.uniform(0.8, 2.0, shape)
+    if scheme == "mhd":
+        u = np.zeros(shape + (9,))
+        u[..., 0] = rho
+        for k in range(3):
+            u[..., 1 + k] = rho * v[k]
+            u[..., 5 + k] = B[k]
+        u[..., 4] = p / (5.0 / 3.0 - 1) + 0.5 * rho * (v ** 2).sum(0) + 0.5 * (B ** 2).sum(0)
+        u[..., 8] = rng.uniform(-0.05, 0.05, shape)
+        kw = dict(nxCells=nx, nyCells=ny, x0=0, x1=1, y0=0, y1=1, bc_x=bcs[0], bc_y=bcs[1], problem="ot")
+        cls = lsc.MusclNew
+    else:
+        u = np.stack([rho, rho * v[0], rho * v[1], p / 0.4 + 0.5 * rho * (v[0] ** 2 + v[1] ** 2)], axis=-1)
+        kw = dict(nxCells=nx, nyCells=ny, bc=bcs[0])
+        cls = lsc.SlicEuler2d
+    s = cls(device=local, rank=rank, nranks=world, **kw)
+    idbuf = ctypes.create_string_buffer(128)
+    if rank == 0:
+        lsc._capi.check(L.lsc_comm_unique_id(ctypes.cast(idbuf, ctypes.c_void_p)))
+    t = torch.tensor(list(idbuf.raw), dtype=torch.uint8, device="cuda")
+    dist.broadcast(t, 0)
+    s.comm_init(bytes(t.cpu().tolist()))
+    s.upload(np.ascontiguousarray(u[s.i0:s.i0 + s.nxl + 4]))
+    s.step(4)
+    mine, sc = s.download(), s.scalars()
+    one = cls(device=local, **kw)
+    one.upload(u)
+    one.step(4)
+    full = one.download()
+    same = np.array_equal(mine[2:-2, 2:-2].view(np.uint64), full[s.i0 + 2:s.i0 + 2 + s.nxl, 2:-2].view(np.uint64)) \
+        and sc == one.scalars()
+    if not same:
+        print(f"[rank {rank}] uploaded random state, {scheme} {bcs}: scalars {sc} vs {one.scalars()}", flush=True)
+    ok = ok and same
+    s.close()
+    one.close()
 flag = torch.tensor([1 if ok else 0], device="cuda")
 dist.all_reduce(flag, op=dist.ReduceOp.MIN)
 if rank == 0:
