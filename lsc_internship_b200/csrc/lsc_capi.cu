@@ -161,6 +161,10 @@ struct lsc_mhd_ctx {
     // halo/compute overlap: the exchange runs on its own high-priority stream behind the
     // slab-edge columns of the y sweep while `stream` sweeps the interior
     cudaStream_t comm_stream = nullptr;
+    // host <-> device transfers of whole states: the staging buffer is used as two halves, the copy of one half
+    // (copy_stream) overlaps the layout transposition of the other (stream)
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t stage_filled[2] = {nullptr, nullptr}, stage_free[2] = {nullptr, nullptr};
     cudaEvent_t edges_done = nullptr, halo_done = nullptr;
     int overlap = 1;  // 0 off, 1 when the slab has NCCL neighbours, 2 always (single rank: the ghost kernel overlaps)
     double t = 0, dt = 0, ch = 0;
@@ -337,7 +341,7 @@ int lsc_mhd_create(const lsc_mhd_config* cfg, lsc_mhd_ctx** out) {
     // staging: at most ~256 MB of AoS columns
     const size_t col_bytes = (size_t)(cfg->ny + 4) * lsc::NV * sizeof(double);
     long long cols = (long long)((256ull << 20) / col_bytes);
-    if (cols < 1) cols = 1;
+    if (cols < 2) cols = 2;  // two halves (lsc_mhd_upload / download_columns)
     if (cols > c->nxl + 4) cols = c->nxl + 4;
     c->stage_cols = (int)cols;
     if (lsc_dev_malloc(&c->d_stage, col_bytes * (size_t)cols) != cudaSuccess ||
@@ -359,7 +363,12 @@ int lsc_mhd_create(const lsc_mhd_config* cfg, lsc_mhd_ctx** out) {
         cudaEventCreateWithFlags(&c->max_event, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->edges_done, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->halo_done, cudaEventDisableTiming) != cudaSuccess ||
-        lsc_create_comm_stream(&c->comm_stream) != cudaSuccess) {
+        lsc_create_comm_stream(&c->comm_stream) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->stage_filled[0], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->stage_filled[1], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->stage_free[0], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->stage_free[1], cudaEventDisableTiming) != cudaSuccess) {
         cudaGetLastError();
         lsc_mhd_destroy(c);
         return fail(LSC_ENOMEM, "allocation of staging / scalars / stream failed");
@@ -381,6 +390,7 @@ int lsc_mhd_destroy(lsc_mhd_ctx* c) {
     cudaSetDevice(c->cfg.device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->comm_stream) cudaStreamSynchronize(c->comm_stream);
+    if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
     if (c->comm) lsc::comm_destroy(c->comm);
     for (int b = 0; b < 3; ++b)
         if (c->state[b]) lsc_dev_free(c->state[b]);
@@ -402,7 +412,12 @@ int lsc_mhd_destroy(lsc_mhd_ctx* c) {
     destroy_events(c->halo_events);
     destroy_events(c->reduce_events);
     for (auto& g : c->graphs) cudaGraphExecDestroy(g.exec);
+    for (int b = 0; b < 2; ++b) {
+        if (c->stage_filled[b]) cudaEventDestroy(c->stage_filled[b]);
+        if (c->stage_free[b]) cudaEventDestroy(c->stage_free[b]);
+    }
     if (c->comm_stream) cudaStreamDestroy(c->comm_stream);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->stream) cudaStreamDestroy(c->stream);
     lsc_slot_release(c->cfg.device, 0, c->slot);
     delete c;
@@ -464,11 +479,24 @@ int lsc_mhd_upload(lsc_mhd_ctx* c, const double* aos) {
     if (!c || !aos) return fail(LSC_EINVAL, "null argument");
     CUDA_TRY(cudaSetDevice(c->cfg.device));
     const size_t col = (size_t)(c->cfg.ny + 4) * lsc::NV;
-    for (int il = 0; il < c->nxl + 4; il += c->stage_cols) {
-        const int ni = std::min(c->stage_cols, c->nxl + 4 - il);
-        int rc = upload_columns(c, aos + col * il, il, ni);
-        if (rc) return rc;
+    // two half buffers: the host->device copy of chunk k+1 (copy_stream) runs while chunk k is transposed into the
+    // device layout (stream); a half is refilled only after its transposition has finished
+    const int half = std::max(1, c->stage_cols / 2);
+    int k = 0;
+    for (int il = 0; il < c->nxl + 4; il += half, ++k) {
+        const int ni = std::min(half, c->nxl + 4 - il);
+        const int b = k & 1;
+        double* buf = c->d_stage + (size_t)b * half * col;
+        if (k >= 2) CUDA_TRY(cudaStreamWaitEvent(c->copy_stream, c->stage_free[b], 0));
+        CUDA_TRY(cudaMemcpyAsync(buf, aos + col * il, col * ni * sizeof(double), cudaMemcpyHostToDevice, c->copy_stream));
+        CUDA_TRY(cudaEventRecord(c->stage_filled[b], c->copy_stream));
+        CUDA_TRY(cudaStreamWaitEvent(c->stream, c->stage_filled[b], 0));
+        lsc::launch_aos_to_soa(c->g, buf, il, ni, c->state[c->cur], c->stream);
+        lsc_count_launches(1);
+        CUDA_TRY(cudaGetLastError());
+        CUDA_TRY(cudaEventRecord(c->stage_free[b], c->stream));
     }
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
     return finish_upload(c);
 }
 
@@ -1161,15 +1189,25 @@ namespace {
 int download_columns(lsc_mhd_ctx* c, int il_lo, int il_hi, double* dst) {
     CUDA_TRY(cudaSetDevice(c->cfg.device));
     const size_t col = (size_t)(c->cfg.ny + 4) * lsc::NV;
-    for (int il = il_lo; il < il_hi; il += c->stage_cols) {
-        const int ni = std::min(c->stage_cols, il_hi - il);
-        lsc::launch_soa_to_aos(c->g, c->state[c->cur], il, ni, c->d_stage, c->stream);
+    // as in lsc_mhd_upload: chunk k is copied to the host (copy_stream) while chunk k+1 is transposed (stream)
+    const int half = std::max(1, c->stage_cols / 2);
+    int k = 0;
+    for (int il = il_lo; il < il_hi; il += half, ++k) {
+        const int ni = std::min(half, il_hi - il);
+        const int b = k & 1;
+        double* buf = c->d_stage + (size_t)b * half * col;
+        if (k >= 2) CUDA_TRY(cudaStreamWaitEvent(c->stream, c->stage_free[b], 0));
+        lsc::launch_soa_to_aos(c->g, c->state[c->cur], il, ni, buf, c->stream);
         lsc_count_launches(1);
         CUDA_TRY(cudaGetLastError());
-        CUDA_TRY(cudaMemcpyAsync(dst + col * (il - il_lo), c->d_stage, col * ni * sizeof(double),
-                                 cudaMemcpyDeviceToHost, c->stream));
-        CUDA_TRY(cudaStreamSynchronize(c->stream));
+        CUDA_TRY(cudaEventRecord(c->stage_filled[b], c->stream));
+        CUDA_TRY(cudaStreamWaitEvent(c->copy_stream, c->stage_filled[b], 0));
+        CUDA_TRY(cudaMemcpyAsync(dst + col * (il - il_lo), buf, col * ni * sizeof(double), cudaMemcpyDeviceToHost,
+                                 c->copy_stream));
+        CUDA_TRY(cudaEventRecord(c->stage_free[b], c->copy_stream));
     }
+    CUDA_TRY(cudaStreamSynchronize(c->copy_stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
     return LSC_OK;
 }
 }  // namespace
