@@ -49,6 +49,10 @@ struct lsc_euler_ctx {
     long ieee_redos = 0;
     double* d_stage = nullptr;
     int stage_cols = 0;
+    // whole-state transfers use the staging buffer as two halves: the PCIe copy of one chunk (copy_stream) overlaps
+    // the layout transposition of the other (stream); created at the first transfer
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t stage_filled[2] = {nullptr, nullptr}, stage_free[2] = {nullptr, nullptr};
     cudaStream_t stream = nullptr;
     // halo/compute overlap as in the MHD solver (lsc_capi.cu): exchange on comm_stream behind the slab-edge columns
     cudaStream_t comm_stream = nullptr;
@@ -594,7 +598,7 @@ int lsc_euler_create(const lsc_euler_config* cfg, lsc_euler_ctx** out) {
     const size_t state_bytes = c->g.plane * 4 * sizeof(double);
     const size_t col_bytes = (size_t)(cfg->ny + 4) * 4 * sizeof(double);
     long long cols = (long long)((256ull << 20) / col_bytes);
-    if (cols < 1) cols = 1;
+    if (cols < 2) cols = 2;  // two halves (lsc_euler_upload / lsc_euler_download)
     if (cols > c->nxl + 4) cols = c->nxl + 4;
     c->stage_cols = (int)cols;
     bool ok = true;
@@ -642,6 +646,14 @@ int lsc_euler_destroy(lsc_euler_ctx* c) {
     if (c->comm_stream) cudaStreamSynchronize(c->comm_stream);
     for (int b = 0; b < 3; ++b)
         if (c->state[b]) lsc_dev_free(c->state[b]);
+    if (c->copy_stream) {
+        cudaStreamSynchronize(c->copy_stream);
+        cudaStreamDestroy(c->copy_stream);
+    }
+    for (int b = 0; b < 2; ++b) {
+        if (c->stage_filled[b]) cudaEventDestroy(c->stage_filled[b]);
+        if (c->stage_free[b]) cudaEventDestroy(c->stage_free[b]);
+    }
     if (c->d_stage) lsc_dev_free(c->d_stage);
     if (c->d_status) lsc_dev_free(c->d_status);
     if (c->d_fix) lsc_dev_free(c->d_fix);
@@ -756,20 +768,39 @@ int lsc_euler_tabeos_write_dat(const lsc_euler_config* cfg, const double* aos, c
     return LSC_OK;
 }
 
+static int e_transfer_init(lsc_euler_ctx* c) {
+    if (c->copy_stream) return LSC_OK;
+    LSC_CUDA_TRY(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    for (int b = 0; b < 2; ++b) {
+        LSC_CUDA_TRY(cudaEventCreateWithFlags(&c->stage_filled[b], cudaEventDisableTiming));
+        LSC_CUDA_TRY(cudaEventCreateWithFlags(&c->stage_free[b], cudaEventDisableTiming));
+    }
+    return LSC_OK;
+}
+
 int lsc_euler_upload(lsc_euler_ctx* c, const double* aos) {
     if (!c || !aos) return lsc_fail(LSC_EINVAL, "null argument");
     LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
+    if (int rc = e_transfer_init(c)) return rc;
     const size_t col = (size_t)(c->cfg.ny + 4) * 4;
     const int ncol = c->nxl + 4;
-    for (int il = 0; il < ncol; il += c->stage_cols) {
-        const int ni = std::min(c->stage_cols, ncol - il);
-        LSC_CUDA_TRY(cudaMemcpyAsync(c->d_stage, aos + col * il, col * ni * sizeof(double), cudaMemcpyHostToDevice,
-                                     c->stream));
-        lsc::launch_euler_aos_to_soa(c->g, c->d_stage, il, ni, c->state[c->cur], c->stream);
+    const int half = std::max(1, c->stage_cols / 2);
+    int chunk = 0;
+    for (int il = 0; il < ncol; il += half, ++chunk) {
+        const int ni = std::min(half, ncol - il);
+        const int b = chunk & 1;
+        double* buf = c->d_stage + (size_t)b * half * col;
+        if (chunk >= 2) LSC_CUDA_TRY(cudaStreamWaitEvent(c->copy_stream, c->stage_free[b], 0));
+        LSC_CUDA_TRY(cudaMemcpyAsync(buf, aos + col * il, col * ni * sizeof(double), cudaMemcpyHostToDevice,
+                                     c->copy_stream));
+        LSC_CUDA_TRY(cudaEventRecord(c->stage_filled[b], c->copy_stream));
+        LSC_CUDA_TRY(cudaStreamWaitEvent(c->stream, c->stage_filled[b], 0));
+        lsc::launch_euler_aos_to_soa(c->g, buf, il, ni, c->state[c->cur], c->stream);
         lsc_count_launches(1);
         LSC_CUDA_TRY(cudaGetLastError());
-        LSC_CUDA_TRY(cudaStreamSynchronize(c->stream));
+        LSC_CUDA_TRY(cudaEventRecord(c->stage_free[b], c->stream));
     }
+    LSC_CUDA_TRY(cudaStreamSynchronize(c->stream));
     // ComputeTimeStep of the first step sees the array as given, over i,j in [2, n+2] (S:173-174); then the
     // loop's own boundary fill (S:604) -- on the device only the x ghost columns are ever read
     LSC_CUDA_TRY(cudaMemsetAsync(c->d_status, 0, 32, c->stream));
@@ -863,17 +894,27 @@ int lsc_euler_download(lsc_euler_ctx* c, double* aos) {
     if (!c || !aos) return lsc_fail(LSC_EINVAL, "null argument");
     if (!c->uploaded) return lsc_fail(LSC_ESTATE, "lsc_euler_download before lsc_euler_upload");
     LSC_CUDA_TRY(cudaSetDevice(c->cfg.device));
+    if (int rc = e_transfer_init(c)) return rc;
     const size_t col = (size_t)(c->cfg.ny + 4) * 4;
     const int ncol = c->nxl + 4;
-    for (int il = 0; il < ncol; il += c->stage_cols) {
-        const int ni = std::min(c->stage_cols, ncol - il);
-        lsc::launch_euler_soa_to_aos(c->g, c->state[c->cur], il, ni, c->d_stage, c->stream);
+    const int half = std::max(1, c->stage_cols / 2);
+    int chunk = 0;
+    for (int il = 0; il < ncol; il += half, ++chunk) {
+        const int ni = std::min(half, ncol - il);
+        const int b = chunk & 1;
+        double* buf = c->d_stage + (size_t)b * half * col;
+        if (chunk >= 2) LSC_CUDA_TRY(cudaStreamWaitEvent(c->stream, c->stage_free[b], 0));
+        lsc::launch_euler_soa_to_aos(c->g, c->state[c->cur], il, ni, buf, c->stream);
         lsc_count_launches(1);
         LSC_CUDA_TRY(cudaGetLastError());
-        LSC_CUDA_TRY(cudaMemcpyAsync(aos + col * il, c->d_stage, col * ni * sizeof(double), cudaMemcpyDeviceToHost,
-                                     c->stream));
-        LSC_CUDA_TRY(cudaStreamSynchronize(c->stream));
+        LSC_CUDA_TRY(cudaEventRecord(c->stage_filled[b], c->stream));
+        LSC_CUDA_TRY(cudaStreamWaitEvent(c->copy_stream, c->stage_filled[b], 0));
+        LSC_CUDA_TRY(cudaMemcpyAsync(aos + col * il, buf, col * ni * sizeof(double), cudaMemcpyDeviceToHost,
+                                     c->copy_stream));
+        LSC_CUDA_TRY(cudaEventRecord(c->stage_free[b], c->copy_stream));
     }
+    LSC_CUDA_TRY(cudaStreamSynchronize(c->copy_stream));
+    LSC_CUDA_TRY(cudaStreamSynchronize(c->stream));
     // y ghost rows are never stored on the device: rebuild the reference's ghost ring (S:616) on the host
     if (c->step > 0) lsc::euler_fill_ghost_ring(c->cfg, aos);
     return LSC_OK;
